@@ -1,0 +1,93 @@
+"""ctypes binding of libwfpt_b200.so (C ABI: include/wfpt_b200.h).  Lazy, loud, no fallback."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import threading
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libwfpt_b200.so")
+
+c_double_p = C.POINTER(C.c_double)
+c_int64_p = C.POINTER(C.c_int64)
+c_float_p = C.POINTER(C.c_float)
+c_int32_p = C.POINTER(C.c_int32)
+
+FAST = 0
+FAITHFUL = 1
+
+_lock = threading.Lock()
+_lib = None
+
+
+class WfptError(RuntimeError):
+    pass
+
+
+def _declare(L):
+    d, i, i64, vp = C.c_double, C.c_int, C.c_int64, C.c_void_p
+    L.wfpt_last_error.restype = C.c_char_p
+    L.wfpt_last_error.argtypes = []
+    L.wfpt_version.restype = i
+    L.wfpt_launch_count.restype = i64
+    L.wfpt_device_info.argtypes = [C.c_char_p, i, C.POINTER(i), C.POINTER(i), C.POINTER(i64)]
+    L.wfpt_release_scratch.argtypes = []
+    L.wfpt_fp64_peak.argtypes = [i, c_double_p, c_double_p]
+    opts = [d, i, i, i, d]  # err, n_st, n_sz, use_adaptive, simps_err
+    L.wfpt_like_batch.argtypes = [vp, i64, vp, i64] + opts + [d, i, vp, vp]
+    L.wfpt_like_batch_host.argtypes = [vp, i64, vp, i64] + opts + [d, i, vp]
+    L.wfpt_pdf_array.argtypes = [vp, i64, c_double_p] + opts + [d, i, i, vp, vp]
+    L.wfpt_pdf_array_host.argtypes = [vp, i64, c_double_p] + opts + [d, i, i, vp]
+    L.wfpt_like_multi.argtypes = [vp, i64, C.POINTER(vp), c_double_p] + opts + [d, d, i, vp, vp]
+    L.wfpt_like_multi_host.argtypes = [vp, i64, C.POINTER(vp), c_double_p] + opts + [d, d, i, vp]
+    L.wfpt_like_rlddm_host.argtypes = [vp, vp, vp, vp, vp, i64, i64] + [d] * 10 + opts + [d, d, i, vp]
+    for name in ("wfpt_device_info", "wfpt_release_scratch", "wfpt_fp64_peak", "wfpt_like_batch",
+                 "wfpt_like_batch_host", "wfpt_pdf_array", "wfpt_pdf_array_host", "wfpt_like_multi",
+                 "wfpt_like_multi_host", "wfpt_like_rlddm_host"):
+        getattr(L, name).restype = i
+    if hasattr(L, "wfpt_sim_run"):
+        from . import _sim_decl
+
+        _sim_decl.declare(L)
+
+
+def load():
+    """Returns the loaded library; raises WfptError when it has not been built (python -m hddm_b200.build)."""
+    global _lib
+    if _lib is None:
+        with _lock:
+            if _lib is None:
+                if not os.path.exists(LIB_PATH):
+                    raise WfptError(
+                        f"{LIB_PATH} is missing: build it with `python -m hddm_b200.build` (needs nvcc). "
+                        "hddm_b200 has no CPU fallback."
+                    )
+                L = C.CDLL(LIB_PATH)
+                _declare(L)
+                _lib = L
+    return _lib
+
+
+def check(rc: int):
+    if rc != 0:
+        msg = load().wfpt_last_error()
+        raise WfptError(msg.decode("utf-8", "replace") if msg else f"libwfpt_b200 call failed (rc={rc})")
+
+
+def launch_count() -> int:
+    return int(load().wfpt_launch_count())
+
+
+def device_info() -> dict:
+    L = load()
+    name = C.create_string_buffer(256)
+    sm, khz, mem = C.c_int(0), C.c_int(0), C.c_int64(0)
+    check(L.wfpt_device_info(name, 256, C.byref(sm), C.byref(khz), C.byref(mem)))
+    return {"name": name.value.decode(), "sm_count": sm.value, "clock_khz": khz.value, "mem_bytes": mem.value}
+
+
+def fp64_peak(iters: int = 8192) -> dict:
+    L = load()
+    rate, ms = C.c_double(0), C.c_double(0)
+    check(L.wfpt_fp64_peak(iters, C.byref(rate), C.byref(ms)))
+    return {"dfma_per_s": rate.value, "ms": ms.value}

@@ -1,0 +1,451 @@
+// extern "C" surface of libwfpt_b200.so (declared in include/wfpt_b200.h): argument checks, scratch management,
+// host<->device staging for the `_host` entry points, launch geometry, and the few small kernels that are not
+// density evaluators (second-stage sum, RL Q-recurrence, FP64 issue-rate probe).
+#include <atomic>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+
+#include "../../include/wfpt_b200.h"
+#include "common.cuh"
+
+namespace wfpt {
+
+// ---- error string / counters -------------------------------------------------------------------------------------------
+static thread_local char g_err[512] = "";
+static std::atomic<int64_t> g_launches{0};
+
+static int fail(const char* fmt, ...)
+{
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+    return 1;
+}
+#define CK(call)                                                                                   \
+    do {                                                                                           \
+        cudaError_t e__ = (call);                                                                  \
+        if (e__ != cudaSuccess) return fail("%s failed: %s (%s:%d)", #call, cudaGetErrorString(e__), __FILE__, __LINE__); \
+    } while (0)
+
+void count_launch(int k) { g_launches.fetch_add(k, std::memory_order_relaxed); }
+
+// ---- per-device grow-only scratch ------------------------------------------------------------------------------------
+enum Slot { kPartSum = 0, kPartZero, kStageX, kStageParams, kStageOut, kStageAux0, kStageAux1, kStageAux2, kStageAux3,
+            kStageAux4, kStageAux5, kStageAux6, kStageAux7, kStageAux8, kNumSlots };
+constexpr int kMaxDev = 16;
+struct Buf { void* p = nullptr; size_t cap = 0; };
+static Buf g_buf[kMaxDev][kNumSlots];
+static std::mutex g_mu;
+
+static int scratch(int slot, size_t bytes, void** out)
+{
+    int dev = 0;
+    CK(cudaGetDevice(&dev));
+    if (dev >= kMaxDev) return fail("device index %d beyond the %d this library tracks", dev, kMaxDev);
+    std::lock_guard<std::mutex> lk(g_mu);
+    Buf& b = g_buf[dev][slot];
+    if (b.cap < bytes) {
+        if (b.p) CK(cudaFree(b.p));
+        b.p = nullptr;
+        b.cap = 0;
+        size_t cap = bytes < 4096 ? 4096 : bytes + bytes / 4;
+        CK(cudaMalloc(&b.p, cap));
+        b.cap = cap;
+    }
+    *out = b.p;
+    return 0;
+}
+
+// ---- small kernels ---------------------------------------------------------------------------------------------------------
+__global__ void finalize_kernel(const double* __restrict__ part_sum, const int* __restrict__ part_zero, int64_t P,
+                                int slices, int early_exit, double* __restrict__ out)
+{
+    const int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= P) return;
+    double s = 0.0;
+    int z = 0;
+    for (int k = 0; k < slices; k++) {
+        s += part_sum[p * slices + k];
+        z |= part_zero[p * slices + k];
+    }
+    out[p] = (early_exit && z) ? -CUDART_INF : s;
+}
+
+// Rescorla-Wagner recurrence of wiener_like_rlddm (/root/reference/src/wfpt.pyx:118-152), one thread per split_by
+// group.  Writes, for every trial j, the drift scale (Q_upper - Q_lower) seen BEFORE that trial's update, and marks the
+// first trial of each group as "update only".  Rounded operation by operation (no FMA) like the reference.
+__global__ void rl_q_kernel(const int64_t* __restrict__ response, const double* __restrict__ feedback,
+                            const int64_t* __restrict__ order, const int64_t* __restrict__ starts, int64_t n_groups,
+                            double q, double alpha, double pos_alfa, double* __restrict__ vscale,
+                            uint8_t* __restrict__ skip)
+{
+    const int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= n_groups) return;
+    // alfa = B^alpha / (1 + B^alpha) with the reference's truncated base B = 2.718281828459 (wfpt.pyx:122-124)
+    const double ea = pow(2.718281828459, alpha), ep = pow(2.718281828459, pos_alfa);
+    const double rate_neg = __ddiv_rn(ea, __dadd_rn(1.0, ea));
+    const double rate_pos = __ddiv_rn(ep, __dadd_rn(1.0, ep));
+    double qs0 = q, qs1 = q;
+    for (int64_t i = starts[g]; i < starts[g + 1]; i++) {
+        const int64_t j = order[i];
+        vscale[j] = __dsub_rn(qs1, qs0);
+        skip[j] = (i == starts[g]) ? 1 : 0;
+        const int64_t r = response[j];
+        const double fb = feedback[j];
+        const double cur = r ? qs1 : qs0;
+        const double alfa = (fb > cur) ? rate_pos : rate_neg;
+        const double upd = __dadd_rn(cur, __dmul_rn(alfa, __dsub_rn(fb, cur)));
+        if (r) qs1 = upd; else qs0 = upd;
+    }
+}
+
+// FP64 issue-rate probe: 8 independent DFMA chains per thread, register resident.
+__global__ void __launch_bounds__(256) dfma_probe_kernel(int iters, double seed, double* sink)
+{
+    double a0 = seed + threadIdx.x, a1 = a0 + 1, a2 = a0 + 2, a3 = a0 + 3, a4 = a0 + 4, a5 = a0 + 5, a6 = a0 + 6,
+           a7 = a0 + 7;
+    const double m = 1.0000001, c = 1e-9;
+    for (int i = 0; i < iters; i++) {
+#pragma unroll
+        for (int u = 0; u < 8; u++) {
+            a0 = fma(a0, m, c); a1 = fma(a1, m, c); a2 = fma(a2, m, c); a3 = fma(a3, m, c);
+            a4 = fma(a4, m, c); a5 = fma(a5, m, c); a6 = fma(a6, m, c); a7 = fma(a7, m, c);
+        }
+    }
+    const double r = ((a0 + a1) + (a2 + a3)) + ((a4 + a5) + (a6 + a7));
+    if (r == 123.456) sink[0] = r;  // never true; keeps the chains alive
+}
+
+// ---- helpers -------------------------------------------------------------------------------------------------------------
+static int check_opts(double err, int n_st, int n_sz, int use_adaptive, double simps_err, int variant, Opts* o)
+{
+    if (variant != WFPT_VARIANT_FAST && variant != WFPT_VARIANT_FAITHFUL) return fail("unknown variant %d", variant);
+    if (use_adaptive && (n_st > kMaxDepth || n_sz > kMaxDepth))
+        return fail("adaptive Simpson depth n_st=%d / n_sz=%d exceeds the supported maximum %d", n_st, n_sz, kMaxDepth);
+    if (n_st < 0 || n_sz < 0) return fail("n_st and n_sz must be non-negative (got %d, %d)", n_st, n_sz);
+    o->err = err;
+    o->simps_err = simps_err;
+    o->n_st = n_st;
+    o->n_sz = n_sz;
+    o->use_adaptive = use_adaptive ? 1 : 0;
+    return 0;
+}
+
+static int g_sm_count[kMaxDev] = {0};
+static int sm_count()
+{
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev >= kMaxDev) return 148;
+    if (!g_sm_count[dev]) {
+        int n = 0;
+        if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+        g_sm_count[dev] = n;
+    }
+    return g_sm_count[dev];
+}
+
+// Trial slicing of the batched kernel: enough CTAs to fill the machine a few times over, never fewer than two
+// RTs per thread, even chunk so that 16-byte loads stay aligned across slices.
+static void plan_slices(int64_t n, int64_t P, int* slices, int64_t* chunk)
+{
+    const int64_t target = (int64_t)sm_count() * 8;
+    int64_t s = (P >= target) ? 1 : (target + P - 1) / (P > 0 ? P : 1);
+    const int64_t max_s = (n + 2 * kBlock - 1) / (2 * kBlock);
+    if (s > max_s) s = max_s;
+    if (s < 1) s = 1;
+    int64_t c = (n + s - 1) / s;
+    if (c & 1) c++;
+    if (c < 2) c = 2;
+    s = (n + c - 1) / c;
+    if (s < 1) s = 1;
+    *slices = (int)s;
+    *chunk = c;
+}
+
+}  // namespace wfpt
+
+using namespace wfpt;
+
+// ============================================================================================================================
+extern "C" {
+
+const char* wfpt_last_error(void) { return g_err; }
+int wfpt_version(void) { return 100; }
+int64_t wfpt_launch_count(void) { return g_launches.load(); }
+
+int wfpt_device_info(char* name, int name_len, int* sm, int* clock_khz, int64_t* mem_bytes)
+{
+    int dev = 0;
+    CK(cudaGetDevice(&dev));
+    cudaDeviceProp prop;
+    CK(cudaGetDeviceProperties(&prop, dev));
+    if (name && name_len > 0) {
+        strncpy(name, prop.name, (size_t)name_len - 1);
+        name[name_len - 1] = 0;
+    }
+    if (sm) *sm = prop.multiProcessorCount;
+    int khz = 0;
+    cudaDeviceGetAttribute(&khz, cudaDevAttrClockRate, dev);
+    if (clock_khz) *clock_khz = khz;
+    if (mem_bytes) *mem_bytes = (int64_t)prop.totalGlobalMem;
+    return 0;
+}
+
+int wfpt_release_scratch(void)
+{
+    int dev = 0;
+    CK(cudaGetDevice(&dev));
+    if (dev >= kMaxDev) return 0;
+    std::lock_guard<std::mutex> lk(g_mu);
+    for (int s = 0; s < kNumSlots; s++) {
+        if (g_buf[dev][s].p) cudaFree(g_buf[dev][s].p);
+        g_buf[dev][s] = Buf();
+    }
+    return 0;
+}
+
+int wfpt_fp64_peak(int iters, double* dfma_per_s, double* ms_out)
+{
+    if (iters <= 0) iters = 4096;
+    void* sink;
+    if (scratch(kStageOut, 64, &sink)) return 1;
+    const int blocks = sm_count() * 8, threads = 256;
+    cudaEvent_t e0, e1;
+    CK(cudaEventCreate(&e0));
+    CK(cudaEventCreate(&e1));
+    dfma_probe_kernel<<<blocks, threads>>>(iters / 8 + 1, 1.0, (double*)sink);  // warm-up
+    CK(cudaEventRecord(e0));
+    dfma_probe_kernel<<<blocks, threads>>>(iters, 1.0, (double*)sink);
+    CK(cudaEventRecord(e1));
+    CK(cudaEventSynchronize(e1));
+    count_launch(2);
+    float ms = 0;
+    CK(cudaEventElapsedTime(&ms, e0, e1));
+    CK(cudaEventDestroy(e0));
+    CK(cudaEventDestroy(e1));
+    const double n = (double)blocks * threads * (double)iters * 64.0;
+    if (dfma_per_s) *dfma_per_s = n / (ms * 1e-3);
+    if (ms_out) *ms_out = ms;
+    return 0;
+}
+
+// ---- wiener_like, batched ------------------------------------------------------------------------------------------------
+int wfpt_like_batch(const double* d_x, int64_t n, const double* d_params, int64_t P, double err, int n_st, int n_sz,
+                    int use_adaptive, double simps_err, double w_outlier, int variant, double* d_out, void* stream)
+{
+    Opts o;
+    if (check_opts(err, n_st, n_sz, use_adaptive, simps_err, variant, &o)) return 1;
+    if (n < 0 || P < 0) return fail("negative size (n=%lld, P=%lld)", (long long)n, (long long)P);
+    if (P == 0) return 0;
+    if (!d_params || !d_out || (n > 0 && !d_x)) return fail("null pointer argument");
+    if ((reinterpret_cast<uintptr_t>(d_x) & 7) != 0) return fail("d_x must be 8-byte aligned");
+    BatchArgs a;
+    a.x = d_x; a.n = n; a.params = d_params; a.P = P; a.o = o; a.w_outlier = w_outlier; a.out = d_out;
+    a.stream = (cudaStream_t)stream;
+    plan_slices(n, P, &a.slices, &a.chunk);
+    if ((double)P * a.slices > 2.0e9) return fail("P*slices too large for one launch (P=%lld)", (long long)P);
+    a.part_sum = nullptr;
+    a.part_zero = nullptr;
+    if (a.slices > 1) {
+        void *ps, *pz;
+        if (scratch(kPartSum, sizeof(double) * (size_t)P * a.slices, &ps)) return 1;
+        if (scratch(kPartZero, sizeof(int) * (size_t)P * a.slices, &pz)) return 1;
+        a.part_sum = (double*)ps;
+        a.part_zero = (int*)pz;
+    }
+    CK(variant == WFPT_VARIANT_FAITHFUL ? launch_like_batch_faithful(a) : launch_like_batch_fast(a));
+    count_launch(1);
+    if (a.slices > 1) {
+        finalize_kernel<<<(unsigned)((P + 127) / 128), 128, 0, a.stream>>>(a.part_sum, a.part_zero, P, a.slices, 1, d_out);
+        CK(cudaGetLastError());
+        count_launch(1);
+    }
+    return 0;
+}
+
+int wfpt_like_batch_host(const double* h_x, int64_t n, const double* h_params, int64_t P, double err, int n_st,
+                         int n_sz, int use_adaptive, double simps_err, double w_outlier, int variant, double* h_out)
+{
+    if (n < 0 || P < 0) return fail("negative size");
+    if (P == 0) return 0;
+    if (!h_params || !h_out || (n > 0 && !h_x)) return fail("null pointer argument");
+    void *dx, *dp, *dout;
+    if (scratch(kStageX, sizeof(double) * (size_t)(n > 0 ? n : 1), &dx)) return 1;
+    if (scratch(kStageParams, sizeof(double) * 8 * (size_t)P, &dp)) return 1;
+    if (scratch(kStageOut, sizeof(double) * (size_t)P, &dout)) return 1;
+    if (n > 0) CK(cudaMemcpyAsync(dx, h_x, sizeof(double) * (size_t)n, cudaMemcpyHostToDevice, 0));
+    CK(cudaMemcpyAsync(dp, h_params, sizeof(double) * 8 * (size_t)P, cudaMemcpyHostToDevice, 0));
+    if (wfpt_like_batch((const double*)dx, n, (const double*)dp, P, err, n_st, n_sz, use_adaptive, simps_err, w_outlier,
+                        variant, (double*)dout, nullptr))
+        return 1;
+    CK(cudaMemcpyAsync(h_out, dout, sizeof(double) * (size_t)P, cudaMemcpyDeviceToHost, 0));
+    CK(cudaStreamSynchronize(0));
+    return 0;
+}
+
+// ---- pdf_array -----------------------------------------------------------------------------------------------------------
+int wfpt_pdf_array(const double* d_x, int64_t n, const double* params8, double err, int n_st, int n_sz,
+                   int use_adaptive, double simps_err, double w_outlier, int logp, int variant, double* d_y, void* stream)
+{
+    Opts o;
+    if (check_opts(err, n_st, n_sz, use_adaptive, simps_err, variant, &o)) return 1;
+    if (n < 0) return fail("negative size");
+    if (n == 0) return 0;
+    if (!d_x || !d_y || !params8) return fail("null pointer argument");
+    PdfArrayArgs a;
+    a.x = d_x; a.n = n; a.o = o; a.w_outlier = w_outlier; a.logp = logp; a.y = d_y; a.stream = (cudaStream_t)stream;
+    a.prm = Params{params8[0], params8[1], params8[2], params8[3], params8[4], params8[5], params8[6], params8[7]};
+    CK(variant == WFPT_VARIANT_FAITHFUL ? launch_pdf_array_faithful(a) : launch_pdf_array_fast(a));
+    count_launch(1);
+    return 0;
+}
+
+int wfpt_pdf_array_host(const double* h_x, int64_t n, const double* params8, double err, int n_st, int n_sz,
+                        int use_adaptive, double simps_err, double w_outlier, int logp, int variant, double* h_y)
+{
+    if (n < 0) return fail("negative size");
+    if (n == 0) return 0;
+    if (!h_x || !h_y) return fail("null pointer argument");
+    void *dx, *dy;
+    if (scratch(kStageX, sizeof(double) * (size_t)n, &dx)) return 1;
+    if (scratch(kStageOut, sizeof(double) * (size_t)n, &dy)) return 1;
+    CK(cudaMemcpyAsync(dx, h_x, sizeof(double) * (size_t)n, cudaMemcpyHostToDevice, 0));
+    if (wfpt_pdf_array((const double*)dx, n, params8, err, n_st, n_sz, use_adaptive, simps_err, w_outlier, logp, variant,
+                       (double*)dy, nullptr))
+        return 1;
+    CK(cudaMemcpyAsync(h_y, dy, sizeof(double) * (size_t)n, cudaMemcpyDeviceToHost, 0));
+    CK(cudaStreamSynchronize(0));
+    return 0;
+}
+
+// ---- per-trial parameters ----------------------------------------------------------------------------------------------
+static int run_multi(const double* d_x, int64_t n, const double* const d_per_trial[7], const double scalars[7],
+                     const Opts& o, double p_outlier, double w_outlier, const double* d_vscale, const uint8_t* d_skip,
+                     int early_exit, int code999, int variant, double* d_out, cudaStream_t stream)
+{
+    MultiArgs a;
+    a.x = d_x; a.n = n; a.o = o; a.p_outlier = p_outlier; a.w_outlier = w_outlier; a.vscale = d_vscale; a.skip = d_skip;
+    a.early_exit = early_exit; a.code999 = code999; a.out = d_out; a.stream = stream;
+    for (int k = 0; k < 7; k++) {
+        a.src.ptr[k] = d_per_trial ? d_per_trial[k] : nullptr;
+        a.src.scalar[k] = scalars[k];
+    }
+    int64_t nb = (n + kBlock - 1) / kBlock;
+    const int64_t cap = (int64_t)sm_count() * 16;
+    if (nb > cap) nb = cap;
+    if (nb < 1) nb = 1;
+    a.nblocks = (int)nb;
+    void *ps, *pz;
+    if (scratch(kPartSum, sizeof(double) * (size_t)nb, &ps)) return 1;
+    if (scratch(kPartZero, sizeof(int) * (size_t)nb, &pz)) return 1;
+    a.part_sum = (double*)ps;
+    a.part_zero = (int*)pz;
+    CK(variant == WFPT_VARIANT_FAITHFUL ? launch_like_multi_faithful(a) : launch_like_multi_fast(a));
+    finalize_kernel<<<1, 32, 0, stream>>>(a.part_sum, a.part_zero, 1, a.nblocks, early_exit, d_out);
+    CK(cudaGetLastError());
+    count_launch(2);
+    return 0;
+}
+
+int wfpt_like_multi(const double* d_x, int64_t n, const double* const d_per_trial[7], const double scalars[7],
+                    double err, int n_st, int n_sz, int use_adaptive, double simps_err, double p_outlier,
+                    double w_outlier, int variant, double* d_out, void* stream)
+{
+    Opts o;
+    if (check_opts(err, n_st, n_sz, use_adaptive, simps_err, variant, &o)) return 1;
+    if (n < 0) return fail("negative size");
+    if (!d_out || !scalars || (n > 0 && !d_x)) return fail("null pointer argument");
+    return run_multi(d_x, n, d_per_trial, scalars, o, p_outlier, w_outlier, nullptr, nullptr, 0, 1, variant, d_out,
+                     (cudaStream_t)stream);
+}
+
+int wfpt_like_multi_host(const double* h_x, int64_t n, const double* const h_per_trial[7], const double scalars[7],
+                         double err, int n_st, int n_sz, int use_adaptive, double simps_err, double p_outlier,
+                         double w_outlier, int variant, double* h_out)
+{
+    if (n < 0) return fail("negative size");
+    if (!h_out || !scalars || (n > 0 && !h_x)) return fail("null pointer argument");
+    void *dx, *dout;
+    const size_t bytes = sizeof(double) * (size_t)(n > 0 ? n : 1);
+    if (scratch(kStageX, bytes, &dx)) return 1;
+    if (scratch(kStageOut, sizeof(double), &dout)) return 1;
+    if (n > 0) CK(cudaMemcpyAsync(dx, h_x, sizeof(double) * (size_t)n, cudaMemcpyHostToDevice, 0));
+    const double* dptr[7];
+    for (int k = 0; k < 7; k++) {
+        dptr[k] = nullptr;
+        if (h_per_trial && h_per_trial[k] && n > 0) {
+            void* d;
+            if (scratch(kStageAux0 + k, bytes, &d)) return 1;
+            CK(cudaMemcpyAsync(d, h_per_trial[k], sizeof(double) * (size_t)n, cudaMemcpyHostToDevice, 0));
+            dptr[k] = (const double*)d;
+        }
+    }
+    if (wfpt_like_multi((const double*)dx, n, dptr, scalars, err, n_st, n_sz, use_adaptive, simps_err, p_outlier,
+                        w_outlier, variant, (double*)dout, nullptr))
+        return 1;
+    CK(cudaMemcpyAsync(h_out, dout, sizeof(double), cudaMemcpyDeviceToHost, 0));
+    CK(cudaStreamSynchronize(0));
+    return 0;
+}
+
+// ---- RL-DDM --------------------------------------------------------------------------------------------------------------
+int wfpt_like_rlddm_host(const double* h_x, const int64_t* h_response, const double* h_feedback, const int64_t* h_order,
+                         const int64_t* h_starts, int64_t n_groups, int64_t n, double q, double alpha, double pos_alpha,
+                         double v, double sv, double a, double z, double sz, double t, double st, double err, int n_st,
+                         int n_sz, int use_adaptive, double simps_err, double p_outlier, double w_outlier, int variant,
+                         double* h_out)
+{
+    Opts o;
+    if (check_opts(err, n_st, n_sz, use_adaptive, simps_err, variant, &o)) return 1;
+    if (n < 0 || n_groups < 0) return fail("negative size");
+    if (!h_out) return fail("null pointer argument");
+    // wfpt.pyx:101-102
+    if (!((p_outlier >= 0) & (p_outlier <= 1))) {
+        *h_out = -HUGE_VAL;
+        return 0;
+    }
+    if (n == 0 || n_groups == 0) {
+        *h_out = 0.0;
+        return 0;
+    }
+    if (!h_x || !h_response || !h_feedback || !h_order || !h_starts) return fail("null pointer argument");
+    for (int64_t g = 0; g < n_groups; g++)
+        if (h_starts[g + 1] <= h_starts[g]) return fail("empty split_by group %lld", (long long)g);
+    for (int64_t i = 0; i < n; i++)
+        if (h_response[i] != 0 && h_response[i] != 1)
+            return fail("response[%lld] = %lld is not 0/1", (long long)i, (long long)h_response[i]);
+    const double pos_alfa = (pos_alpha == 100.00) ? alpha : pos_alpha;  // wfpt.pyx:104-107
+
+    void *dx, *dresp, *dfb, *dord, *dst, *dvs, *dskip, *dout;
+    if (scratch(kStageX, sizeof(double) * (size_t)n, &dx)) return 1;
+    if (scratch(kStageAux0, sizeof(int64_t) * (size_t)n, &dresp)) return 1;
+    if (scratch(kStageAux1, sizeof(double) * (size_t)n, &dfb)) return 1;
+    if (scratch(kStageAux2, sizeof(int64_t) * (size_t)n, &dord)) return 1;
+    if (scratch(kStageAux3, sizeof(int64_t) * (size_t)(n_groups + 1), &dst)) return 1;
+    if (scratch(kStageAux4, sizeof(double) * (size_t)n, &dvs)) return 1;
+    if (scratch(kStageAux5, (size_t)n, &dskip)) return 1;
+    if (scratch(kStageOut, sizeof(double), &dout)) return 1;
+    CK(cudaMemcpyAsync(dx, h_x, sizeof(double) * (size_t)n, cudaMemcpyHostToDevice, 0));
+    CK(cudaMemcpyAsync(dresp, h_response, sizeof(int64_t) * (size_t)n, cudaMemcpyHostToDevice, 0));
+    CK(cudaMemcpyAsync(dfb, h_feedback, sizeof(double) * (size_t)n, cudaMemcpyHostToDevice, 0));
+    CK(cudaMemcpyAsync(dord, h_order, sizeof(int64_t) * (size_t)n, cudaMemcpyHostToDevice, 0));
+    CK(cudaMemcpyAsync(dst, h_starts, sizeof(int64_t) * (size_t)(n_groups + 1), cudaMemcpyHostToDevice, 0));
+    CK(cudaMemsetAsync(dskip, 1, (size_t)n, 0));  // trials not named by `order` contribute nothing
+    rl_q_kernel<<<(unsigned)((n_groups + 63) / 64), 64>>>((const int64_t*)dresp, (const double*)dfb, (const int64_t*)dord,
+                                                        (const int64_t*)dst, n_groups, q, alpha, pos_alfa, (double*)dvs,
+                                                        (uint8_t*)dskip);
+    CK(cudaGetLastError());
+    count_launch(1);
+    const double scalars[7] = {v, sv, a, z, sz, t, st};
+    if (run_multi((const double*)dx, n, nullptr, scalars, o, p_outlier, w_outlier, (const double*)dvs,
+                  (const uint8_t*)dskip, 1, 0, variant, (double*)dout, 0))
+        return 1;
+    CK(cudaMemcpyAsync(h_out, dout, sizeof(double), cudaMemcpyDeviceToHost, 0));
+    CK(cudaStreamSynchronize(0));
+    return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,154 @@
+// Kernel skeletons of the likelihood path, generic over the density evaluator `Impl` (faithful or fast).
+//
+//   like_batch_kernel   wiener_like for P parameter sets on one RT array      (/root/reference/src/wfpt.pyx:54-76)
+//   pdf_array_kernel    per-trial densities                                      (wfpt.pyx:32-48)
+//   like_multi_kernel   per-trial parameters, +-999 coding, RL-DDM drift scaling (wfpt.pyx:357-387, :78-153)
+//   finalize_kernel     second stage of the deterministic two-stage trial sum
+//
+// Data layout in HBM: RTs are one contiguous float64[n]; parameter sets are float64[P][8] rows
+// (v, sv, a, z, sz, t, st, p_outlier); outputs float64[P].  One CTA = (one parameter set, one slice of trials);
+// its 128 threads walk the slice with coalesced 16-byte loads (two RTs per thread per step), reduce with warp
+// shuffles, and either write the final sum (slices == 1) or a partial into scratch (slices > 1).
+#pragma once
+#include "common.cuh"
+
+namespace wfpt {
+
+// wfpt.pyx:70-74: p = p*(1-p_outlier) + w_outlier*p_outlier, each operation rounded on its own.
+__device__ __forceinline__ double mix_outlier(double p, double one_minus_po, double wp)
+{
+    return __dadd_rn(__dmul_rn(p, one_minus_po), wp);
+}
+
+template <class Impl>
+__global__ void __launch_bounds__(kBlock) like_batch_kernel(const double* __restrict__ x, int64_t n,
+                                                          const double* __restrict__ params, int64_t P, Opts o,
+                                                          double w_outlier, int slices, int64_t chunk,
+                                                          double* __restrict__ out_sum, int* __restrict__ out_zero)
+{
+    const int64_t bid = blockIdx.x;
+    const int64_t p = bid / slices;
+    const int s = (int)(bid - p * slices);
+    if (p >= P) return;
+
+    const double* row = params + 8 * p;
+    Params prm{row[0], row[1], row[2], row[3], row[4], row[5], row[6], row[7]};
+    const double po = prm.p_outlier;
+
+    // wfpt.pyx:63-64: p_outlier outside [0,1] -> -inf for the whole set
+    if (!((po >= 0) & (po <= 1))) {
+        if (threadIdx.x == 0) {
+            if (out_zero) { out_sum[bid] = 0.0; out_zero[bid] = 1; }
+            else out_sum[bid] = -CUDART_INF;
+        }
+        return;
+    }
+    const double wp = __dmul_rn(w_outlier, po);
+    const double omp = __dsub_rn(1.0, po);
+    typename Impl::Set set;
+    Impl::prepare(set, prm, o);
+
+    const int64_t beg = (int64_t)s * chunk;
+    const int64_t end = (beg + chunk < n) ? beg + chunk : n;
+    double acc = 0.0;
+    int zero = 0;
+
+    // Coalesced 16-byte loads: two RTs per thread per step.  A slice that starts on an odd element (caller passed
+    // an 8-byte-aligned view) peels one head element; an odd remainder leaves one tail element.
+    int64_t b = beg;
+    if ((reinterpret_cast<uintptr_t>(x + b) & 15) && b < end) {
+        if (threadIdx.x == 0) {
+            const double p0 = mix_outlier(Impl::density(x[b], set), omp, wp);
+            zero |= (p0 == 0);
+            acc += log(p0);
+        }
+        b++;
+    }
+    const int64_t npair = (end - b) >> 1;
+    const double2* x2 = reinterpret_cast<const double2*>(x + b);
+    for (int64_t i = threadIdx.x; i < npair; i += kBlock) {
+        const double2 xx = __ldg(x2 + i);
+        const double p0 = mix_outlier(Impl::density(xx.x, set), omp, wp);
+        const double p1 = mix_outlier(Impl::density(xx.y, set), omp, wp);
+        zero |= (p0 == 0) | (p1 == 0);
+        acc += log(p0);
+        acc += log(p1);
+    }
+    if (((end - b) & 1) && threadIdx.x == kBlock - 1) {
+        const double p0 = mix_outlier(Impl::density(x[end - 1], set), omp, wp);
+        zero |= (p0 == 0);
+        acc += log(p0);
+    }
+
+    int any_zero;
+    const double tot = block_sum_or<kBlock>(acc, zero, &any_zero);
+    if (threadIdx.x == 0) {
+        if (out_zero) {
+            out_sum[bid] = tot;
+            out_zero[bid] = any_zero;
+        } else {
+            // wfpt.pyx:71-72: the first p == 0 returns -inf (a NaN elsewhere never gets to overrule it)
+            out_sum[bid] = any_zero ? -CUDART_INF : tot;
+        }
+    }
+}
+
+// Sequential (fixed-order) sum of the per-slice partials: deterministic and independent of launch geometry.
+__global__ void finalize_kernel(const double* __restrict__ part_sum, const int* __restrict__ part_zero, int64_t P,
+                                int slices, int early_exit, double* __restrict__ out);
+
+template <class Impl>
+__global__ void __launch_bounds__(kBlock) pdf_array_kernel(const double* __restrict__ x, int64_t n, Params prm, Opts o,
+                                                         double w_outlier, int logp, double* __restrict__ y)
+{
+    const int64_t i = (int64_t)blockIdx.x * kBlock + threadIdx.x;
+    typename Impl::Set set;
+    Impl::prepare(set, prm, o);
+    if (i >= n) return;
+    // wfpt.pyx:44: y * (1 - p_outlier) + (w_outlier * p_outlier), then optionally np.log
+    const double wp = __dmul_rn(w_outlier, prm.p_outlier);
+    const double omp = __dsub_rn(1.0, prm.p_outlier);
+    const double p = mix_outlier(Impl::density(x[i], set), omp, wp);
+    y[i] = logp ? log(p) : p;
+}
+
+template <class Impl>
+__global__ void __launch_bounds__(kBlock) like_multi_kernel(const double* __restrict__ x, int64_t n, MultiSrc src,
+                                                          Opts o, double p_outlier, double w_outlier,
+                                                          const double* __restrict__ vscale,
+                                                          const uint8_t* __restrict__ skip, int code999,
+                                                          double* __restrict__ out_sum, int* __restrict__ out_zero)
+{
+    const double wp = __dmul_rn(w_outlier, p_outlier);
+    const double omp = __dsub_rn(1.0, p_outlier);
+    double acc = 0.0;
+    int zero = 0;
+    const int64_t stride = (int64_t)gridDim.x * kBlock;
+    for (int64_t i = (int64_t)blockIdx.x * kBlock + threadIdx.x; i < n; i += stride) {
+        if (skip && skip[i]) continue;
+        double q[7];
+#pragma unroll
+        for (int k = 0; k < 7; k++) q[k] = src.ptr[k] ? __ldg(src.ptr[k] + i) : src.scalar[k];
+        if (vscale) q[0] = __dmul_rn(vscale[i], q[0]);  // wfpt.pyx:133: (qs[1]-qs[0]) * v
+        const double xi = x[i];
+        double p;
+        if (!code999 || fabs(xi) != 999.) {
+            Params prm{q[0], q[1], q[2], q[3], q[4], q[5], q[6], p_outlier};
+            p = mix_outlier(Impl::density_once(xi, prm, o), omp, wp);
+        } else if (xi == 999.) {
+            p = Impl::prob_ub(q[0], q[2], q[3]);
+        } else {
+            p = 1 - Impl::prob_ub(q[0], q[2], q[3]);
+        }
+        zero |= (p == 0);
+        acc += log(p);
+    }
+    int any_zero;
+    const double tot = block_sum_or<kBlock>(acc, zero, &any_zero);
+    if (threadIdx.x == 0) {
+        out_sum[blockIdx.x] = tot;
+        out_zero[blockIdx.x] = any_zero;
+    }
+}
+
+}  // namespace wfpt

@@ -1,0 +1,94 @@
+/*
+ * wfpt_b200.h -- C ABI of libwfpt_b200.so: the WFPT log-likelihood and the Euler-Maruyama sequential-sampling
+ * simulators of HDDM as hand-written sm_100a CUDA kernels.
+ *
+ * The reference has no FFI layer for this path: its "operator API" is the set of module-level callables of the
+ * Cython extension `wfpt` and of `hddm.simulators.simulator`.  Each entry point below names the reference
+ * callable it computes (paths relative to /root/reference).  The Python drop-in (hddm_b200/wfpt.py, top-level
+ * wfpt.py, hddm_b200/simulators.py) binds these with ctypes; INTEGRATION.md shows the stub.
+ *
+ * Conventions
+ *   - every function returns 0 on success, non-zero on failure; wfpt_last_error() then describes the failure
+ *     (thread-local string).  Out-of-support MODEL parameters are not failures: they produce -inf / NaN /
+ *     N*log(w_outlier*p_outlier) exactly as the reference does.
+ *   - `d_` pointers are device pointers on the current CUDA device; `h_` pointers are host pointers.  Functions
+ *     without a `_host` suffix take device pointers, enqueue on `stream` (a cudaStream_t passed as void*, NULL =
+ *     default stream) and return without synchronising.  `_host` functions copy in, run, copy out and synchronise.
+ *   - all likelihood arithmetic is IEEE binary64.  RTs are signed: positive = upper boundary, negative = lower
+ *     (hddm/utils.py:489-517 flip_errors).
+ *   - parameter-set rows are double[8] = {v, sv, a, z, sz, t, st, p_outlier}.
+ *   - integration options, as in every reference signature: err, n_st, n_sz, use_adaptive, simps_err
+ *     (src/pdf.pxi:104-108).  With use_adaptive != 0, n_st/n_sz are recursion depths and must be <= 24.
+ *   - `variant`: WFPT_VARIANT_FAST (default product path) or WFPT_VARIANT_FAITHFUL (operation-for-operation
+ *     evaluation without FMA contraction; slower; kept as the on-device cross-check).
+ */
+#ifndef WFPT_B200_H
+#define WFPT_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define WFPT_VARIANT_FAST 0
+#define WFPT_VARIANT_FAITHFUL 1
+
+/* Library / device housekeeping ------------------------------------------------------------------------------ */
+const char* wfpt_last_error(void);
+int wfpt_version(void);
+/* name[<=name_len], SM count, SM clock (kHz), total memory (bytes) of the current device. */
+int wfpt_device_info(char* name, int name_len, int* sm_count, int* clock_khz, int64_t* mem_bytes);
+/* Cumulative count of kernels this library has launched in this process (bench.py reports it as gpu_launches). */
+int64_t wfpt_launch_count(void);
+/* Frees the library's cached device scratch on the current device. */
+int wfpt_release_scratch(void);
+/* Measures the FP64 issue ceiling on the current device: a register-resident DFMA chain kernel.
+ * Returns DFMA instructions per second (lane-level; x2 = FLOP/s) in *dfma_per_s. */
+int wfpt_fp64_peak(int iters, double* dfma_per_s, double* ms);
+
+/* Likelihood ------------------------------------------------------------------------------------------------- */
+
+/* P independent wiener_like() evaluations on one RT array:
+ *   out[j] = wiener_like(x, *params[j][0:7], err, n_st, n_sz, use_adaptive, simps_err, p_outlier=params[j][7], w_outlier)
+ * replaces src/wfpt.pyx:54-76 (one call per row).  No counterpart with P>1 exists in the reference; P=1 is the
+ * reference call.  Trials are summed with a deterministic two-stage tree (partials live in library scratch). */
+int wfpt_like_batch(const double* d_x, int64_t n, const double* d_params, int64_t P, double err, int n_st, int n_sz,
+                    int use_adaptive, double simps_err, double w_outlier, int variant, double* d_out, void* stream);
+int wfpt_like_batch_host(const double* h_x, int64_t n, const double* h_params, int64_t P, double err, int n_st,
+                         int n_sz, int use_adaptive, double simps_err, double w_outlier, int variant, double* h_out);
+
+/* y[i] = full_pdf(x[i], ...)*(1-p_outlier) + w_outlier*p_outlier, optionally log.  Replaces src/wfpt.pyx:32-48
+ * (pdf_array) and, with n == 1, p_outlier == 0, the cpdef full_pdf of src/pdf.pxi:104-146. */
+int wfpt_pdf_array(const double* d_x, int64_t n, const double* params8, double err, int n_st, int n_sz,
+                   int use_adaptive, double simps_err, double w_outlier, int logp, int variant, double* d_y,
+                   void* stream);
+int wfpt_pdf_array_host(const double* h_x, int64_t n, const double* params8, double err, int n_st, int n_sz,
+                        int use_adaptive, double simps_err, double w_outlier, int logp, int variant, double* h_y);
+
+/* Per-trial parameters.  per_trial[k] (k: v, sv, a, z, sz, t, st) is NULL -> scalars[k] is used for every trial,
+ * else an array of n doubles.  RTs of +-999 mean "choice only" and contribute log P(upper) / log(1-P(upper)).
+ * No early exit: log(0) = -inf flows through the IEEE sum.  Replaces src/wfpt.pyx:357-387 (wiener_like_multi). */
+int wfpt_like_multi(const double* d_x, int64_t n, const double* const d_per_trial[7], const double scalars[7],
+                    double err, int n_st, int n_sz, int use_adaptive, double simps_err, double p_outlier,
+                    double w_outlier, int variant, double* d_out, void* stream);
+int wfpt_like_multi_host(const double* h_x, int64_t n, const double* const h_per_trial[7], const double scalars[7],
+                         double err, int n_st, int n_sz, int use_adaptive, double simps_err, double p_outlier,
+                         double w_outlier, int variant, double* h_out);
+
+/* RL-DDM: Rescorla-Wagner Q recurrence per split_by group (one thread per group, sequential in trial order), then
+ * one density per trial with drift (Q_upper - Q_lower) * v; the first trial of each group only updates Q.
+ * `order`[n] lists trial indices grouped by ascending split_by value (stable), `starts`[n_groups+1] delimits the
+ * groups -- the grouping np.unique + boolean masks produce in src/wfpt.pyx:99,113-116.
+ * Replaces src/wfpt.pyx:78-153 (wiener_like_rlddm). */
+int wfpt_like_rlddm_host(const double* h_x, const int64_t* h_response, const double* h_feedback,
+                         const int64_t* h_order, const int64_t* h_starts, int64_t n_groups, int64_t n, double q,
+                         double alpha, double pos_alpha, double v, double sv, double a, double z, double sz, double t,
+                         double st, double err, int n_st, int n_sz, int use_adaptive, double simps_err,
+                         double p_outlier, double w_outlier, int variant, double* h_out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* WFPT_B200_H */

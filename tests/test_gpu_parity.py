@@ -1,0 +1,189 @@
+"""GPU parity tests (run with -m gpu on a B200): the CUDA path, called through the C ABI, against the CPU oracle
+on the same seeded inputs, against the committed fixtures produced by the reference's own Cython, and through
+size-independent properties at full size.  Tolerance for summed log-likelihoods: 1e-10 relative (north_star);
+bit-exact for the outlier mix of masked trials, the -inf masking and the p_outlier range check."""
+import math
+
+import numpy as np
+import pytest
+
+from conftest import rel_err
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-10
+VARIANTS = [0, 1]  # FAST, FAITHFUL
+
+
+@pytest.fixture(params=VARIANTS, ids=["fast", "faithful"])
+def variant(request, wfpt_gpu):
+    old = wfpt_gpu.get_variant()
+    wfpt_gpu.set_variant(request.param)
+    yield request.param
+    wfpt_gpu.set_variant(old)
+
+
+def test_matlab_known_answers(golden, wfpt_gpu, variant):
+    # /root/reference/hddm/tests/test_likelihoods.py:51-58
+    for v, t, a, z, z_nonorm, rt, err, matlab_wfpt in golden["matlab"]:
+        p = wfpt_gpu.full_pdf(-rt, v, 0, a, z, 0, t, 0, err, 0)
+        assert p == pytest.approx(matlab_wfpt, abs=5e-10)
+
+
+def test_full_pdf_cases(golden, wfpt_gpu, variant):
+    """6000 single-trial densities over every dispatch branch (sv/sz/st on/off, fixed/adaptive, err 1e-13..1)."""
+    cases, vals = golden["full_pdf_cases"], golden["full_pdf_vals"]
+    # group by option tuple so that each group is one pdf_array-style launch per case row (n=1 calls are slow)
+    got = np.array([wfpt_gpu.full_pdf(*c[:9], int(c[9]), int(c[10]), int(c[11]), c[12]) for c in cases[:1500]])
+    want = vals[:1500]
+    assert np.array_equal(got == 0, want == 0)                 # validity mask: exact zeros in the same places
+    assert np.array_equal(np.isnan(got), np.isnan(want))
+    ok = np.isfinite(want) & (want != 0)
+    # a K flip (1-ulp libm difference at an integer ks/kl) would show up here as an error of order `err`
+    assert rel_err(got[ok], want[ok]) < 1e-9
+
+
+def test_wiener_like_cases(golden, wfpt_gpu, variant):
+    x = golden["wl_x"]
+    for c, want in zip(golden["wl_cases"], golden["wl_vals"]):
+        got = wfpt_gpu.wiener_like(x, *c[:8], n_st=int(c[8]), n_sz=int(c[9]), use_adaptive=int(c[10]), simps_err=c[11],
+                                   p_outlier=c[12], w_outlier=c[13])
+        if math.isnan(want):
+            assert math.isnan(got), c
+        elif math.isinf(want):
+            assert got == want, c
+        else:
+            assert abs(got - want) <= TOL * abs(want), (c, got, want)
+    # bit-exact pieces: invalid set under the HDDM outlier mix == N*log(w*p) to the last bit
+    c = golden["wl_cases"][4]
+    got = wfpt_gpu.wiener_like(x, *c[:8], n_st=2, n_sz=2, use_adaptive=1, simps_err=1e-3, p_outlier=c[12], w_outlier=c[13])
+    assert abs(got - golden["wl_vals"][4]) <= 4e-15 * abs(got)
+    assert wfpt_gpu.wiener_like(np.array([1.0, 2, 3, 0]), 1, 0, 2, 0.5, 0, 0, 0, 1e-4) == -np.inf
+    assert wfpt_gpu.wiener_like(np.empty(0), 1, 0, 2, 0.5, 0, 0.3, 0, 1e-4) == 0.0
+
+
+def test_benchmark_configs(golden, wfpt_gpu, variant):
+    x1, x2 = golden["x_cfg1"], golden["x_cfg2"]
+    got = wfpt_gpu.wiener_like(x1, 1, 0, 2, 0.5, 0, 0.3, 0, 1e-4)
+    assert abs(got - float(golden["cfg1_logp"])) <= TOL * abs(got)
+    kw = dict(p_outlier=0.05, w_outlier=0.1)
+    for tag, ad, n, se in (("cfg2a_logp", 0, 2, 1e-3), ("cfg2b_logp", 1, 2, 1e-3), ("cfg2c_logp", 1, 10, 1e-8)):
+        got = wfpt_gpu.wiener_like(x2, 1, 1, 2, 0.5, 0.2, 0.3, 0.1, 1e-4, n_st=n, n_sz=n, use_adaptive=ad, simps_err=se, **kw)
+        want = float(golden[tag])
+        assert abs(got - want) <= TOL * abs(want), (tag, got, want)
+    y = wfpt_gpu.pdf_array(x2, 1, 1, 2, 0.5, 0.2, 0.3, 0.1, 1e-4, 0, 2, 2, 1, 1e-3, 0.05, 0.1)
+    assert rel_err(y, golden["cfg2b_pdf"]) < 1e-11
+
+
+def test_cfg4_slices_vs_reference_fixture(golden, wfpt_gpu, variant):
+    x2, P4 = golden["x_cfg2"], golden["cfg4_params"]
+    for tag, ad in (("fixed", 0), ("adaptive", 1)):
+        got = wfpt_gpu.wiener_like_batch(x2, P4, 1e-4, 2, 2, ad, 1e-3, 0.1, variant=variant)
+        want = golden["cfg4_" + tag]
+        assert np.array_equal(np.isinf(got), np.isinf(want)) and np.array_equal(np.isnan(got), np.isnan(want))
+        assert rel_err(got, want) <= TOL
+
+
+def test_batch_vs_oracle_random(oracle, wfpt_gpu, variant):
+    rng = np.random.default_rng(21)
+    n, P = 3001, 257  # odd sizes: head/tail paths of the vectorised loads, partial slices
+    x = np.where(rng.random(n) < 0.7, 1.0, -1.0) * rng.uniform(0.3, 4.0, n)
+    prm = np.stack([rng.uniform(-4, 4, P), rng.choice([0.0, 1.0], P) * rng.uniform(0, 3, P), rng.uniform(0.5, 4, P),
+                    rng.uniform(0.2, 0.8, P), rng.choice([0.0, 1.0], P) * rng.uniform(0, 0.3, P),
+                    rng.uniform(0.05, 0.5, P), rng.choice([0.0, 1.0], P) * rng.uniform(0, 0.3, P),
+                    rng.choice([0.0, 0.05, 1.0, 1.5], P)], axis=1)
+    for ad, nn, se in ((0, 2, 1e-3), (0, 4, 1e-3), (1, 2, 1e-3), (1, 4, 1e-5)):
+        want = oracle.wiener_like_batch(x, prm, 1e-4, nn, nn, ad, se, 0.1)
+        got = wfpt_gpu.wiener_like_batch(x, prm, 1e-4, nn, nn, ad, se, 0.1, variant=variant)
+        assert np.array_equal(np.isneginf(got), np.isneginf(want))
+        assert np.array_equal(np.isnan(got), np.isnan(want))
+        assert rel_err(got, want) <= TOL, (ad, nn, se)
+    # unaligned view of x (8-byte aligned only) and P=1 with many slices
+    want = oracle.wiener_like_batch(x[1:], prm[:3], 1e-4, 2, 2, 0, 1e-3, 0.1)
+    got = wfpt_gpu.wiener_like_batch(x[1:], prm[:3], 1e-4, 2, 2, 0, 1e-3, 0.1, variant=variant)
+    assert rel_err(got, want) <= TOL
+
+
+def test_batch_device_tensors_match_host_buffers(golden, wfpt_gpu, variant):
+    import torch
+
+    x2, P4 = golden["x_cfg2"], golden["cfg4_params"]
+    host = wfpt_gpu.wiener_like_batch(x2, P4, 1e-4, 2, 2, 0, 1e-3, 0.1, variant=variant)
+    dev = wfpt_gpu.wiener_like_batch(torch.from_numpy(x2).cuda(), torch.from_numpy(P4).cuda(), 1e-4, 2, 2, 0, 1e-3, 0.1,
+                                     variant=variant)
+    torch.cuda.synchronize()
+    assert np.array_equal(host, dev.cpu().numpy(), equal_nan=True)
+
+
+def test_multi(golden, wfpt_gpu, variant):
+    g = golden
+    xm, vm, am, tm, zm = g["multi_x"], g["multi_v"], g["multi_a"], g["multi_t"], g["multi_z"]
+    f = wfpt_gpu.wiener_like_multi
+    for got, want in (
+        (f(xm, vm, 0, 2, 0.5, 0, 0.3, 0, 1e-4, ["v"], p_outlier=0.05, w_outlier=0.1), g["multi_v_only"]),
+        (f(xm, vm, 1.0, am, 0.5, 0.1, tm, 0.1, 1e-4, ["v", "a", "t"], p_outlier=0.05, w_outlier=0.1), g["multi_vat"]),
+        (f(xm, vm, 0.5, am, zm, 0.1, tm, 0.05, 1e-4, ["v", "a", "z", "t"], n_st=2, n_sz=2, use_adaptive=0, p_outlier=0.0, w_outlier=0.0), g["multi_vazt_fixed"]),
+        (f(g["wl_x"], np.linspace(0.5, 1.5, 5), 0, 2, 0.5, 0, 0.3, 0, 1e-4, ["v"], p_outlier=0.05, w_outlier=0.1), g["multi_small"]),
+        (f(np.array([0.8, 999.0, -999.0]), np.ones(3), 0, 2, 0.5, 0, 0.3, 0, 1e-4, ["v"]), g["multi_999"]),
+    ):
+        assert abs(got - float(want)) <= TOL * abs(float(want)), (got, want)
+    xm2 = xm.copy()
+    xm2[3] = 0.05
+    assert f(xm2, vm, 0, 2, 0.5, 0, 0.3, 0, 1e-4, ["v"], p_outlier=0.0, w_outlier=0.1) == -np.inf
+
+
+def test_rlddm(golden, wfpt_gpu, variant):
+    g = golden
+    xr, resp, fb, split = g["rl_x"], g["rl_response"], g["rl_feedback"], g["rl_split"]
+    f = wfpt_gpu.wiener_like_rlddm
+    got = f(xr, resp, fb, split, 0.5, -1.0, 100.0, 2.0, 0, 1.8, 0.5, 0, 0.3, 0, 1e-4, p_outlier=0.05, w_outlier=0.1)
+    assert abs(got - float(g["rlddm_a"])) <= TOL * abs(got)
+    got = f(xr, resp, fb, split, 0.5, -0.5, 0.7, 3.0, 0.5, 1.8, 0.5, 0.1, 0.3, 0.1, 1e-4, n_st=2, n_sz=2, use_adaptive=1,
+            simps_err=1e-3, p_outlier=0.05, w_outlier=0.1)
+    assert abs(got - float(g["rlddm_b"])) <= TOL * abs(got)
+    assert f(xr, resp, fb, split, 0.5, -1.0, 100.0, 2.0, 0, 1.8, 0.5, 0, 0.9, 0, 1e-4) == -np.inf
+    assert f(xr, resp, fb, split, 0.5, -1.0, 100.0, 2.0, 0, 1.8, 0.5, 0, 0.3, 0, 1e-4, p_outlier=2.0) == -np.inf
+
+
+def test_pdf_array_and_cdf_helpers(golden, oracle, wfpt_gpu, variant):
+    g = golden
+    got = wfpt_gpu.pdf_array(g["pdf_grid_x"], 0.7, 0.8, 1.6, 0.45, 0.2, 0.25, 0.15, 1e-4, 0, 2, 2, 1, 1e-3, 0.05, 0.1)
+    assert rel_err(got, g["pdf_grid_full"]) < 1e-11
+    # masked trials carry exactly w_outlier*p_outlier (bit-exact outlier mix)
+    masked = np.abs(g["pdf_grid_x"]) < 0.25 - 0.15 / 2
+    assert masked.any() and np.all(got[masked] == 0.1 * 0.05)
+    got = wfpt_gpu.pdf_array(g["pdf_grid_x"], 0.7, 0, 1.6, 0.45, 0, 0.25, 0, 1e-4, 1, 2, 2, 1, 1e-3, 0.05, 0.1)
+    assert rel_err(got, g["pdf_grid_simple_log"]) < 1e-12
+    # gen_rts_from_cdf reproduces the benchmark inputs generated by the reference (same global-RNG call sequence);
+    # a sample sitting exactly on a CDF step may move by one grid cell under a 1e-16 perturbation
+    np.random.seed(1)
+    x1 = wfpt_gpu.gen_rts_from_cdf(1, 0, 2, 0.5, 0, 0.3, 0, 1000, -6, 6, 1e-3)
+    assert np.mean(x1 == g["x_cfg1"]) > 0.995 and np.max(np.abs(x1 - g["x_cfg1"])) <= 1.5e-3
+    xs, cdf = wfpt_gpu.gen_cdf_using_pdf(0.7, 0.8, 1.6, 0.45, 0.2, 0.25, 0.15, 1e-4, N=300, time=5.0)
+    assert cdf[0] == 0 and cdf[-1] == 1 and np.all(np.diff(cdf) >= 0) and len(xs) == 601
+
+
+def test_density_integrates_to_one(wfpt_gpu, variant):
+    # test_likelihoods.py:215-231, at a size the CPU oracle would not want: 400k-point quadrature
+    xs = np.linspace(-8, 8, 400001)
+    y = wfpt_gpu.pdf_array(xs, 0.6, 0.4, 1.7, 0.45, 0.1, 0.2, 0.1, 1e-6, 0, 2, 2, 1, 1e-4, 0, 0)
+    assert np.trapezoid(y, xs) == pytest.approx(1.0, abs=1e-3)
+
+
+def test_full_size_properties(golden, wfpt_gpu):
+    """cfg-4 sized launch (4096 sets x 10,000 trials here; the bench runs 65,536): (i) permutation invariance of
+    the trial sum within rounding, (ii) additivity over a split of the trials, (iii) fast == faithful."""
+    rng = np.random.default_rng(4)
+    x2 = golden["x_cfg2"]
+    P = 4096
+    prm = np.stack([rng.uniform(-5, 5, P), rng.uniform(0, 4, P), rng.uniform(1, 3, P), rng.uniform(0.3, 0.7, P),
+                    rng.uniform(0, 0.25, P), rng.uniform(0.1, 0.3, P), rng.uniform(0, 0.2, P), np.full(P, 0.05)], axis=1)
+    kw = dict(err=1e-4, n_st=2, n_sz=2, use_adaptive=0, simps_err=1e-3, w_outlier=0.1)
+    full = wfpt_gpu.wiener_like_batch(x2, prm, **kw)
+    assert np.all(np.isfinite(full))
+    perm = wfpt_gpu.wiener_like_batch(x2[rng.permutation(len(x2))], prm, **kw)
+    assert rel_err(perm, full) < 1e-12
+    a = wfpt_gpu.wiener_like_batch(x2[:4000], prm, **kw)
+    b = wfpt_gpu.wiener_like_batch(x2[4000:], prm, **kw)
+    assert rel_err(a + b, full) < 1e-12
+    faithful = wfpt_gpu.wiener_like_batch(x2, prm, variant=1, **kw)
+    assert rel_err(full, faithful) <= TOL
