@@ -41,6 +41,10 @@ def _declare(L):
     L.wfpt_like_multi.argtypes = [vp, i64, C.POINTER(vp), c_double_p] + opts + [d, d, i, vp, vp]
     L.wfpt_like_multi_host.argtypes = [vp, i64, C.POINTER(vp), c_double_p] + opts + [d, d, i, vp]
     L.wfpt_like_rlddm_host.argtypes = [vp, vp, vp, vp, vp, i64, i64] + [d] * 10 + opts + [d, d, i, vp]
+    L.wfpt_ktable.argtypes = [d, C.POINTER(i), C.POINTER(i), C.POINTER(i), C.POINTER(i), c_double_p, C.POINTER(i), i]
+    L.wfpt_ktable.restype = i
+    L.wfpt_ktable_decision.argtypes = [d, d]
+    L.wfpt_ktable_decision.restype = i
     for name in ("wfpt_device_info", "wfpt_release_scratch", "wfpt_fp64_peak", "wfpt_like_batch",
                  "wfpt_like_batch_host", "wfpt_pdf_array", "wfpt_pdf_array_host", "wfpt_like_multi",
                  "wfpt_like_multi_host", "wfpt_like_rlddm_host"):
@@ -84,6 +88,22 @@ def device_info() -> dict:
     sm, khz, mem = C.c_int(0), C.c_int(0), C.c_int64(0)
     check(L.wfpt_device_info(name, 256, C.byref(sm), C.byref(khz), C.byref(mem)))
     return {"name": name.value.decode(), "sm_count": sm.value, "clock_khz": khz.value, "mem_bytes": mem.value}
+
+
+def ktable(err: float) -> dict:
+    """The fast variant's series-term table for `err` (host computation; works without a GPU)."""
+    L = load()
+    n, klm, ksm, d0 = C.c_int(0), C.c_int(0), C.c_int(0), C.c_int(0)
+    thr = (C.c_double * 32)()
+    desc = (C.c_int * 32)()
+    check(L.wfpt_ktable(float(err), C.byref(n), C.byref(klm), C.byref(ksm), C.byref(d0), thr, desc, 32))
+    m = max(n.value, 0)
+    return {"n": n.value, "kl_max": klm.value, "ks_max": ksm.value, "desc0": d0.value,
+            "thr": [thr[k] for k in range(m)], "desc": [desc[k] for k in range(m)]}
+
+
+def ktable_decision(tt: float, err: float) -> int:
+    return int(load().wfpt_ktable_decision(float(tt), float(err)))
 
 
 def fp64_peak(iters: int = 8192) -> dict:

@@ -20,7 +20,7 @@ OBJ = os.path.join(CSRC, "_obj")
 LIB = os.path.join(HERE, "libwfpt_b200.so")
 INCLUDE = os.path.join(os.path.dirname(HERE), "include")
 
-SOURCES = ["api.cu", "like_faithful.cu", "like_fast.cu", "sim.cu"]
+SOURCES = ["api.cu", "ktable.cpp", "like_faithful.cu", "like_fast.cu", "sim.cu"]
 NO_FMAD = {"like_faithful.cu"}
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 COMMON = ["-O3", "-lineinfo", "-std=c++17", "-Xcompiler", "-fPIC", "-I", INCLUDE, "-I", CSRC]
@@ -54,7 +54,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
     objs = []
     for s in srcs:
         src = os.path.join(CSRC, s)
-        obj = os.path.join(OBJ, s.replace(".cu", ".o"))
+        obj = os.path.join(OBJ, os.path.splitext(s)[0] + ".o")
         objs.append(obj)
         if force or _stale(obj, _deps(src)):
             cmd = [nvcc] + ARCH + COMMON + (["--fmad=false"] if s in NO_FMAD else []) + ["-c", src, "-o", obj]

@@ -6,20 +6,21 @@
 namespace wfpt {
 
 struct FaithfulImpl {
+    struct Ctx { int unused; };
     struct Set {
         Params prm;
         Opts o;
     };
-    __device__ static __forceinline__ void prepare(Set& s, const Params& prm, const Opts& o)
+    __device__ static __forceinline__ void prepare(Set& s, const Params& prm, const Opts& o, const Ctx&)
     {
         s.prm = prm;
         s.o = o;
     }
-    __device__ static __forceinline__ double density(double x, const Set& s)
+    __device__ static __forceinline__ double density(double x, const Set& s, const Ctx&)
     {
         return faithful::full_pdf(x, s.prm.v, s.prm.sv, s.prm.a, s.prm.z, s.prm.sz, s.prm.t, s.prm.st, s.o);
     }
-    __device__ static __forceinline__ double density_once(double x, const Params& prm, const Opts& o)
+    __device__ static __forceinline__ double density_once(double x, const Params& prm, const Opts& o, const Ctx&)
     {
         return faithful::full_pdf(x, prm.v, prm.sv, prm.a, prm.z, prm.sz, prm.t, prm.st, o);
     }
@@ -32,7 +33,7 @@ cudaError_t launch_like_batch_faithful(const BatchArgs& a)
     if (nblk == 0) return cudaSuccess;
     like_batch_kernel<FaithfulImpl><<<(unsigned)nblk, kBlock, 0, a.stream>>>(
         a.x, a.n, a.params, a.P, a.o, a.w_outlier, a.slices, a.chunk, a.slices > 1 ? a.part_sum : a.out,
-        a.slices > 1 ? a.part_zero : nullptr);
+        a.slices > 1 ? a.part_zero : nullptr, FaithfulImpl::Ctx{0});
     return cudaGetLastError();
 }
 
@@ -40,14 +41,14 @@ cudaError_t launch_pdf_array_faithful(const PdfArrayArgs& a)
 {
     if (a.n == 0) return cudaSuccess;
     const unsigned nblk = (unsigned)((a.n + kBlock - 1) / kBlock);
-    pdf_array_kernel<FaithfulImpl><<<nblk, kBlock, 0, a.stream>>>(a.x, a.n, a.prm, a.o, a.w_outlier, a.logp, a.y);
+    pdf_array_kernel<FaithfulImpl><<<nblk, kBlock, 0, a.stream>>>(a.x, a.n, a.prm, a.o, a.w_outlier, a.logp, a.y, FaithfulImpl::Ctx{0});
     return cudaGetLastError();
 }
 
 cudaError_t launch_like_multi_faithful(const MultiArgs& a)
 {
     like_multi_kernel<FaithfulImpl><<<(unsigned)a.nblocks, kBlock, 0, a.stream>>>(
-        a.x, a.n, a.src, a.o, a.p_outlier, a.w_outlier, a.vscale, a.skip, a.code999, a.part_sum, a.part_zero);
+        a.x, a.n, a.src, a.o, a.p_outlier, a.w_outlier, a.vscale, a.skip, a.code999, a.part_sum, a.part_zero, FaithfulImpl::Ctx{0});
     return cudaGetLastError();
 }
 

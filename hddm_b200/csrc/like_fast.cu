@@ -1,9 +1,52 @@
-// Fast-variant instantiations of the likelihood kernels (placeholder: forwards to the faithful kernels until the
-// restructured evaluator lands).
-#include "common.cuh"
+// Fast-variant instantiations of the likelihood kernels (table-driven evaluator, wfpt_fast.cuh).
+#include "like_kernels.cuh"
+#include "wfpt_fast.cuh"
 
 namespace wfpt {
-cudaError_t launch_like_batch_fast(const BatchArgs& a) { return launch_like_batch_faithful(a); }
-cudaError_t launch_pdf_array_fast(const PdfArrayArgs& a) { return launch_pdf_array_faithful(a); }
-cudaError_t launch_like_multi_fast(const MultiArgs& a) { return launch_like_multi_faithful(a); }
+
+struct FastImpl {
+    using Ctx = KTable;
+    using Set = fast::Set;
+    __device__ static __forceinline__ void prepare(Set& s, const Params& prm, const Opts& o, const Ctx& kt)
+    {
+        fast::prepare(s, prm, o, kt);
+    }
+    __device__ static __forceinline__ double density(double x, const Set& s, const Ctx& kt)
+    {
+        return fast::density(x, s, kt);
+    }
+    __device__ static __forceinline__ double density_once(double x, const Params& prm, const Opts& o, const Ctx& kt)
+    {
+        return fast::density_once(x, prm, o, kt);
+    }
+    __device__ static __forceinline__ double prob_ub(double v, double a, double z) { return faithful::prob_ub(v, a, z); }
+};
+
+cudaError_t launch_like_batch_fast(const BatchArgs& a)
+{
+    const int64_t nblk = a.P * (int64_t)a.slices;
+    if (nblk == 0) return cudaSuccess;
+    like_batch_kernel<FastImpl><<<(unsigned)nblk, kBlock, 0, a.stream>>>(
+        a.x, a.n, a.params, a.P, a.o, a.w_outlier, a.slices, a.chunk, a.slices > 1 ? a.part_sum : a.out,
+        a.slices > 1 ? a.part_zero : nullptr, get_ktable(a.o.err));
+    return cudaGetLastError();
+}
+
+cudaError_t launch_pdf_array_fast(const PdfArrayArgs& a)
+{
+    if (a.n == 0) return cudaSuccess;
+    const unsigned nblk = (unsigned)((a.n + kBlock - 1) / kBlock);
+    pdf_array_kernel<FastImpl><<<nblk, kBlock, 0, a.stream>>>(a.x, a.n, a.prm, a.o, a.w_outlier, a.logp, a.y,
+                                                             get_ktable(a.o.err));
+    return cudaGetLastError();
+}
+
+cudaError_t launch_like_multi_fast(const MultiArgs& a)
+{
+    like_multi_kernel<FastImpl><<<(unsigned)a.nblocks, kBlock, 0, a.stream>>>(
+        a.x, a.n, a.src, a.o, a.p_outlier, a.w_outlier, a.vscale, a.skip, a.code999, a.part_sum, a.part_zero,
+        get_ktable(a.o.err));
+    return cudaGetLastError();
+}
+
 }  // namespace wfpt

@@ -21,10 +21,11 @@ __device__ __forceinline__ double mix_outlier(double p, double one_minus_po, dou
 }
 
 template <class Impl>
-__global__ void __launch_bounds__(kBlock) like_batch_kernel(const double* __restrict__ x, int64_t n,
+__global__ void __launch_bounds__(kBlock, 4) like_batch_kernel(const double* __restrict__ x, int64_t n,
                                                           const double* __restrict__ params, int64_t P, Opts o,
                                                           double w_outlier, int slices, int64_t chunk,
-                                                          double* __restrict__ out_sum, int* __restrict__ out_zero)
+                                                          double* __restrict__ out_sum, int* __restrict__ out_zero,
+                                                          const __grid_constant__ typename Impl::Ctx ctx)
 {
     const int64_t bid = blockIdx.x;
     const int64_t p = bid / slices;
@@ -46,7 +47,7 @@ __global__ void __launch_bounds__(kBlock) like_batch_kernel(const double* __rest
     const double wp = __dmul_rn(w_outlier, po);
     const double omp = __dsub_rn(1.0, po);
     typename Impl::Set set;
-    Impl::prepare(set, prm, o);
+    Impl::prepare(set, prm, o, ctx);
 
     const int64_t beg = (int64_t)s * chunk;
     const int64_t end = (beg + chunk < n) ? beg + chunk : n;
@@ -54,30 +55,39 @@ __global__ void __launch_bounds__(kBlock) like_batch_kernel(const double* __rest
     int zero = 0;
 
     // Coalesced 16-byte loads: two RTs per thread per step.  A slice that starts on an odd element (caller passed
-    // an 8-byte-aligned view) peels one head element; an odd remainder leaves one tail element.
+    // an 8-byte-aligned view) peels one head element and an odd remainder leaves one tail element; both are handed
+    // to single threads in a final pass through the same (single) evaluation site.
     int64_t b = beg;
-    if ((reinterpret_cast<uintptr_t>(x + b) & 15) && b < end) {
-        if (threadIdx.x == 0) {
-            const double p0 = mix_outlier(Impl::density(x[b], set), omp, wp);
+    const bool head = (reinterpret_cast<uintptr_t>(x + b) & 15) && b < end;
+    if (head) b++;
+    const int64_t npair = (end - b) >> 1;
+    const bool tail = (end - b) & 1;
+    const double2* x2 = reinterpret_cast<const double2*>(x + b);
+    int64_t i = threadIdx.x;
+    bool edges_done = false;
+    for (;;) {
+        double v0 = 0.0, v1 = 0.0;
+        int cnt = 0;
+        if (i < npair) {
+            const double2 xx = __ldg(x2 + i);
+            v0 = xx.x;
+            v1 = xx.y;
+            cnt = 2;
+            i += kBlock;
+        } else if (!edges_done) {
+            edges_done = true;
+            if (head && threadIdx.x == 0) { v0 = x[beg]; cnt = 1; }
+            if (tail && threadIdx.x == kBlock - 1) { v0 = x[end - 1]; cnt = 1; }
+            if (cnt == 0) break;
+        } else {
+            break;
+        }
+#pragma unroll 1
+        for (int h = 0; h < cnt; h++) {
+            const double p0 = mix_outlier(Impl::density(h ? v1 : v0, set, ctx), omp, wp);
             zero |= (p0 == 0);
             acc += log(p0);
         }
-        b++;
-    }
-    const int64_t npair = (end - b) >> 1;
-    const double2* x2 = reinterpret_cast<const double2*>(x + b);
-    for (int64_t i = threadIdx.x; i < npair; i += kBlock) {
-        const double2 xx = __ldg(x2 + i);
-        const double p0 = mix_outlier(Impl::density(xx.x, set), omp, wp);
-        const double p1 = mix_outlier(Impl::density(xx.y, set), omp, wp);
-        zero |= (p0 == 0) | (p1 == 0);
-        acc += log(p0);
-        acc += log(p1);
-    }
-    if (((end - b) & 1) && threadIdx.x == kBlock - 1) {
-        const double p0 = mix_outlier(Impl::density(x[end - 1], set), omp, wp);
-        zero |= (p0 == 0);
-        acc += log(p0);
     }
 
     int any_zero;
@@ -99,16 +109,17 @@ __global__ void finalize_kernel(const double* __restrict__ part_sum, const int* 
 
 template <class Impl>
 __global__ void __launch_bounds__(kBlock) pdf_array_kernel(const double* __restrict__ x, int64_t n, Params prm, Opts o,
-                                                         double w_outlier, int logp, double* __restrict__ y)
+                                                         double w_outlier, int logp, double* __restrict__ y,
+                                                         const __grid_constant__ typename Impl::Ctx ctx)
 {
     const int64_t i = (int64_t)blockIdx.x * kBlock + threadIdx.x;
     typename Impl::Set set;
-    Impl::prepare(set, prm, o);
+    Impl::prepare(set, prm, o, ctx);
     if (i >= n) return;
     // wfpt.pyx:44: y * (1 - p_outlier) + (w_outlier * p_outlier), then optionally np.log
     const double wp = __dmul_rn(w_outlier, prm.p_outlier);
     const double omp = __dsub_rn(1.0, prm.p_outlier);
-    const double p = mix_outlier(Impl::density(x[i], set), omp, wp);
+    const double p = mix_outlier(Impl::density(x[i], set, ctx), omp, wp);
     y[i] = logp ? log(p) : p;
 }
 
@@ -117,7 +128,8 @@ __global__ void __launch_bounds__(kBlock) like_multi_kernel(const double* __rest
                                                           Opts o, double p_outlier, double w_outlier,
                                                           const double* __restrict__ vscale,
                                                           const uint8_t* __restrict__ skip, int code999,
-                                                          double* __restrict__ out_sum, int* __restrict__ out_zero)
+                                                          double* __restrict__ out_sum, int* __restrict__ out_zero,
+                                                          const __grid_constant__ typename Impl::Ctx ctx)
 {
     const double wp = __dmul_rn(w_outlier, p_outlier);
     const double omp = __dsub_rn(1.0, p_outlier);
@@ -134,7 +146,7 @@ __global__ void __launch_bounds__(kBlock) like_multi_kernel(const double* __rest
         double p;
         if (!code999 || fabs(xi) != 999.) {
             Params prm{q[0], q[1], q[2], q[3], q[4], q[5], q[6], p_outlier};
-            p = mix_outlier(Impl::density_once(xi, prm, o), omp, wp);
+            p = mix_outlier(Impl::density_once(xi, prm, o, ctx), omp, wp);
         } else if (xi == 999.) {
             p = Impl::prob_ub(q[0], q[2], q[3]);
         } else {

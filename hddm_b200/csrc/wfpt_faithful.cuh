@@ -18,7 +18,7 @@ namespace faithful {
 __device__ __forceinline__ double max_std(double a, double b) { return (a < b) ? b : a; }  // std::max
 
 // f(tt | 0, 1, w).  K and the expansion are fixed by (tt, err) alone.
-__device__ __noinline__ double ftt_01w(double tt, double w, double err)
+static __device__ __noinline__ double ftt_01w(double tt, double w, double err)
 {
     double kl, ks, p = 0.0;
     if (kPi * tt * err < 1) {

@@ -48,6 +48,15 @@ int wfpt_release_scratch(void);
  * Returns DFMA instructions per second (lane-level; x2 = FLOP/s) in *dfma_per_s. */
 int wfpt_fp64_peak(int iters, double* dfma_per_s, double* ms);
 
+/* Series-term table of the fast variant (host side, no GPU needed).  For a given err the reference's choice of
+ * expansion and term count K (src/pdf.pxi:35-60) is piecewise constant in tt; the library finds the piece boundaries
+ * by bisection on the reference's expressions with the host libm.  wfpt_ktable copies up to `cap` thresholds (as
+ * doubles) and descriptors ((small ? 0x100 : 0) | K) of the pieces starting at them; *desc0 describes the piece below
+ * the first threshold; *n == -1 means "not representable" (the kernels then evaluate the formulas directly).
+ * wfpt_ktable_decision evaluates the reference decision for one tt (same descriptor encoding, -1 if out of range). */
+int wfpt_ktable(double err, int* n, int* kl_max, int* ks_max, int* desc0, double* thr, int* desc, int cap);
+int wfpt_ktable_decision(double tt, double err);
+
 /* Likelihood ------------------------------------------------------------------------------------------------- */
 
 /* P independent wiener_like() evaluations on one RT array:
