@@ -11,10 +11,7 @@ struct FastImpl {
     {
         fast::prepare(s, prm, o, kt);
     }
-    __device__ static __forceinline__ double density(double x, const Set& s, const Ctx& kt)
-    {
-        return fast::density(x, s, kt);
-    }
+    __device__ static __forceinline__ double density(double x, Set& s, const Ctx&) { return fast::density(x, s); }
     __device__ static __forceinline__ double density_once(double x, const Params& prm, const Opts& o, const Ctx& kt)
     {
         return fast::density_once(x, prm, o, kt);

@@ -1,16 +1,23 @@
 // Restructured ("fast") device evaluation of the WFPT density: same mathematics and the same series term count K
-// as the reference, far fewer FP64 instructions.  What changes relative to the operation-for-operation variant:
+// as the reference, far fewer FP64 instructions, and independent instruction chains for the FP64 pipe to overlap.
+// What changes relative to the operation-for-operation variant (wfpt_faithful.cuh):
 //
 //  * K and the small/large-time choice come from a table lookup on the bit pattern of tt (ktable.h) instead of
 //    2 log + 6 sqrt + 2 div per node.  The table is built from the reference's own expressions, so K is the
-//    reference's K.
+//    reference's K.  Each thread remembers the piece it was in and walks from there (RTs are |rt|-sorted by the
+//    batching layer, so the walk is usually zero steps).
 //  * Everything that depends only on the parameter set is computed once per CTA and staged in shared memory: the
-//    quadrature nodes z_j (for both response signs) and t_i with the reference's roundings, the drift-variability
-//    exponent coefficients A_j = (a z_j sv)^2 - 2 a v z_j, and the large-time sines k*sin(k*pi*z_j).
-//  * Everything that depends on (trial, t-node) only is shared by the z-nodes of that t-node: tt, 1/tt, K,
-//    q^(k^2) = exp(-k^2 pi^2 tt/2) by repeated multiplication, 1/(2(sv^2 x+1)), the 1/sqrt prefactors.
-//  * exp(log(p) + E) is evaluated as p*exp(E) with E folded into the small-time exponents, so a small-time node costs
-//    three exp() (k = -1, 0, 1; further terms by the Gaussian ratio recurrence) and a large-time node one.
+//    quadrature nodes z_j (for both response signs) and t_i with the reference's roundings, per node the exponent
+//    coefficient A_j = (a z_j sv)^2 - 2 a v z_j, the small-time lattice u = z_j + 2k and -u^2/2, and the large-time
+//    sines k*sin(k*pi*z_j).
+//  * Everything that depends on (trial, t-node) only is shared by the z-nodes of that t-node: tt (correctly rounded
+//    x'/a^2 from a precomputed reciprocal), tt^-1/2 by rsqrt, K, q^(k^2) = exp(-k^2 pi^2 tt/2) by repeated
+//    multiplication, (sv^2 x'+1)^-1/2 by rsqrt.  No division is left in the trial loop.
+//  * exp(log(p) + E) is evaluated as p*exp(E) with E folded into the small-time exponents; a small-time node costs
+//    three or four exp (k = -1..1 or -1..2; further terms by the Gaussian ratio recurrence), a large-time node one.
+//  * exp is a branch-free table-driven kernel (2^(j/64) table in shared memory, degree-5 polynomial, < 1 ulp); the
+//    exps of all z-nodes of a t-node are issued as one straight-line batch.  Arguments outside the normal range
+//    (result subnormal / overflow / NaN) send the batch to the library exp.
 //  * pdf_sv's NaN for a negative truncated series (log of a negative p, /root/reference/src/pdf.pxi:102) is kept.
 //
 // Differences from the reference's result are rounding-level (~1e-15 relative per density); tests hold the summed
@@ -35,27 +42,38 @@ enum Mode : int {
     kModeZero = 4        // parameter set outside the support: density 0 for every trial
 };
 
+// Per (response sign, z-node) constants.
+struct NodeTab {
+    double A;                 // (a z sv)^2 - 2 a v' z
+    double u[4];              // z + 2k,        k = -1, 0, 1, 2
+    double uh[4];             // -(z + 2k)^2/2
+    double S[kMaxKLarge];     // k sin(k pi z), k = 1..kl_max
+};
+
 // Shared-memory tables of one parameter set (one CTA).
 struct Tables {
-    double zw[2][kMaxNodes];                 // z_j for sign 0 (lower-boundary RT, v, z) and sign 1 (upper: -v, 1-z)
-    double zA[2][kMaxNodes];                 // (a z_j sv)^2 - 2 a v' z_j
-    double zS[2][kMaxNodes][kMaxKLarge];     // k * sin(k pi z_j), k = 1..kl_max
-    double tn[kMaxNodes];                    // t_i
-    double wz[2], hz[2];                     // z interval width / step per response sign, as the reference rounds them
-    double wt, ht;                           // same along t
-    Params prm;                              // the raw parameter set and options (generic fallback only)
+    NodeTab z[2][kMaxNodes];  // sign 0: lower-boundary RT (v, z); sign 1: upper (-v, 1-z)
+    double tn[kMaxNodes];     // t_i
+    double wz[2], hz[2];      // z interval width / step per response sign, as the reference rounds them
+    double wt, ht;            // same along t
+    double exptab[64];        // 2^(j/64)
+    long long thr[kMaxPieces];  // series-term table (copy of the launch's KTable)
+    int desc[kMaxPieces + 1];   // desc[0] = piece below thr[0]
+    Params prm;               // raw parameter set and options (generic fallback only)
     Opts o;
 };
 
 // Per-thread (register) view of the parameter set; everything bulky lives in Tables.
 struct Set {
     int mode;
-    int nz, nt;          // intervals along z / t used by the table paths (0: axis not integrated)
+    int nz, nt;            // intervals along z / t used by the table paths (0: axis not integrated)
     int sv_nonzero;
     int depth_z, depth_t;  // adaptive recursion budgets (n_sz, n_st)
+    int npieces;           // thresholds in the series-term table
+    int piece;             // piece of the last lookup (walk start)
     double simps_err;
     double t;
-    double tlo;          // t - st/2 (validity bound on |x|)
+    double tlo;            // t - st/2 (validity bound on |x|)
     double v2, sv2, a2, inv_a2;
     const Tables* tab;
 };
@@ -73,8 +91,39 @@ __device__ __forceinline__ Tables& tables()
     return t;
 }
 
-// (small, K) for this tt: linear scan over the (few) thresholds; the table sits in the constant bank.
-__device__ __forceinline__ int klookup(const KTable& kt, double tt)
+// ---- exp ------------------------------------------------------------------------------------------------------------------
+// exp(x) = 2^e * 2^(j/64) * exp(r),  k = rint(64 x / ln 2) = 64 e + j,  r = x - k ln2/64, |r| <= 0.0055.
+// Branch-free; valid for -708 <= x <= 709 (normal results).  Max error 0.98 ulp (checked against mpmath).
+__device__ __forceinline__ double exp_core(double x, const double* __restrict__ tab)
+{
+    const double t = fma(x, 92.33248261689366, 6755399441055744.0);
+    const int ki = __double2loint(t);
+    const double kd = t - 6755399441055744.0;
+    double r = fma(kd, -0.01083042469326756, x);          // ln2/64 high part (32 bits: kd * hi is exact)
+    r = fma(kd, -2.9815858269852933e-12, r);              // low part
+    double p = fma(r, 1.0 / 120.0, 1.0 / 24.0);
+    p = fma(p, r, 1.0 / 6.0);
+    p = fma(p, r, 0.5);
+    p = fma(p, r, 1.0);
+    p = p * r;                                            // exp(r) - 1
+    const double T = tab[ki & 63];
+    const double res = fma(T, p, T);
+    return __hiloint2double(__double2hiint(res) + ((ki >> 6) << 20), __double2loint(res));
+}
+__device__ __forceinline__ bool exp_arg_ok(double x) { return (x >= -708.0) & (x <= 709.0); }
+
+// ---- series-term lookup -----------------------------------------------------------------------------------------------
+// Walk from the piece of the previous lookup to the piece holding tt.  Returns (small << 8) | K.
+__device__ __forceinline__ int klookup(const Tables& T, int n, double tt, int& p)
+{
+    const long long b = __double_as_longlong(tt);
+    while (p < n && b >= T.thr[p]) p++;
+    while (p > 0 && b < T.thr[p - 1]) p--;
+    return T.desc[p];
+}
+
+// Scan form for callers without shared tables (per-trial parameter sets).
+__device__ __forceinline__ int klookup_scan(const KTable& kt, double tt)
 {
     const long long b = __double_as_longlong(tt);
     int d = kt.desc0;
@@ -83,36 +132,43 @@ __device__ __forceinline__ int klookup(const KTable& kt, double tt)
     return d;
 }
 
-// Per-(trial, t-node) quantities shared by all z-nodes.
+// ---- per-(trial, t-node) quantities shared by all z-nodes ---------------------------------------------------------------
 struct TNode {
     int alive;       // x' > 0
     int small;
     int K;
     double E0;       // -v^2 x' * c      (E_j = A_j * c + E0)
     double c;        // 1 / (2 (sv^2 x' + 1))
-    double nh;       // -1 / (2 tt)      (small-time)
+    double inv_tt;   // small-time
     double pref;     // everything multiplying the series sum
-    double q1, q4, q9, q16; // q^(k^2), k = 1..4 (large-time); higher powers are rebuilt on demand
+    double q1, q4, q9, q16;  // q^(k^2), k = 1..4 (large-time); higher powers are rebuilt on demand
 };
 
-__device__ __forceinline__ void make_tnode(TNode& tn, double xp, const Set& s, const KTable& kt)
+__device__ __forceinline__ void make_tnode(TNode& tn, double xp, Set& s)
 {
     tn.alive = xp > 0;
     if (!tn.alive) return;
-    const double tt = xp / s.a2;  // the reference's tt, bit for bit: K is decided on it
-    const int d = klookup(kt, tt);
+    const Tables& T = *s.tab;
+    // tt = x'/a^2, correctly rounded from the reciprocal (quotient + one residual correction): K is decided on it
+    const double q0 = xp * s.inv_a2;
+    const double tt = fma(fma(-q0, s.a2, xp), s.inv_a2, q0);
+    const int d = klookup(T, s.npieces, tt, s.piece);
     tn.small = d >> 8;
     tn.K = d & 0xff;
-    const double den = fma(s.sv2, xp, 1.0);
-    tn.c = 0.5 / den;
+    double rs = 1.0;
+    tn.c = 0.5;
+    if (s.sv_nonzero) {
+        rs = rsqrt(fma(s.sv2, xp, 1.0));  // 1/sqrt(sv^2 x' + 1)
+        tn.c = 0.5 * rs * rs;
+    }
     tn.E0 = -s.v2 * xp * tn.c;
-    const double rs = sqrt(2.0 * tn.c);  // 1/sqrt(sv^2 x' + 1)
     if (tn.small) {
-        const double inv_tt = 1.0 / tt;
-        tn.nh = -0.5 * inv_tt;
-        tn.pref = inv_tt * sqrt(inv_tt) * (kInvSqrt2Pi * s.inv_a2) * rs;
+        const double r = rsqrt(tt);
+        tn.inv_tt = r * r;
+        tn.pref = tn.inv_tt * r * (kInvSqrt2Pi * s.inv_a2) * rs;  // tt^-3/2 / sqrt(2 pi) / a^2 / sqrt(sv^2 x'+1)
     } else {
-        const double q = exp(-kHalfPiSq * tt);
+        const double qa = -kHalfPiSq * tt;
+        const double q = exp_arg_ok(qa) ? exp_core(qa, T.exptab) : exp(qa);
         const double q2 = q * q, q4 = q2 * q2, q8 = q4 * q4;
         tn.q1 = q;
         tn.q4 = q4;
@@ -122,86 +178,103 @@ __device__ __forceinline__ void make_tnode(TNode& tn, double xp, const Set& s, c
     }
 }
 
-// sum_k (w+2k) exp(-(w+2k)^2/(2tt) + E), k = -floor((K-1)/2) .. ceil((K-1)/2)   (pdf.pxi:51-56 with E folded in)
-__device__ __forceinline__ double series_small(double w, int K, double nh, double E)
+// Small-time series with the library exp and every term the reference sums (any K); used when an exponent leaves
+// exp_core's range and for K >= 5.   sum_k (w+2k) exp(-(w+2k)^2/(2tt) + E), k = -floor((K-1)/2) .. ceil((K-1)/2)
+static __device__ __noinline__ double series_small_slow(double w, int K, double inv_tt, double E)
 {
-    const double u0 = w, u1 = w + 2.0, um = w - 2.0;
-    const double e0 = exp(fma(u0 * u0, nh, E));
-    const double e1 = exp(fma(u1 * u1, nh, E));
-    if (K <= 2) {
-        // K == 2: k = 0, 1;  K == 1: k = 0;  K == 0: no term (cannot occur: ks >= 2)
-        return K == 2 ? fma(u1, e1, u0 * e0) : (K == 1 ? u0 * e0 : 0.0);
-    }
-    const double em = exp(fma(um * um, nh, E));
-    double sum = fma(u1, e1, fma(u0, e0, um * em));
-    if (K > 3 && e0 > 0.0) {
-        // e_{k+1}/e_k = rho * H^k and e_{-(k+1)}/e_{-k} = sig * H^k with H = rho * sig = exp(-4/tt)
-        const double inv_e0 = 1.0 / e0;
-        const double rho = e1 * inv_e0, sig = em * inv_e0, H = rho * sig;
-        const int upper = K >> 1;        // ceil((K-1)/2)
-        const int lower = (K - 1) >> 1;  // floor((K-1)/2)
-        double ek = e1, r = rho;
-        for (int k = 2; k <= upper; k++) {
-            r *= H;
-            ek *= r;
-            sum = fma(w + 2.0 * k, ek, sum);
-        }
-        ek = em;
-        r = sig;
-        for (int k = 2; k <= lower; k++) {
-            r *= H;
-            ek *= r;
-            sum = fma(w - 2.0 * k, ek, sum);
-        }
+    const int upper = K >> 1, lower = (K - 1) >> 1;
+    double sum = 0.0;
+    for (int k = -lower; k <= upper; k++) {
+        const double u = w + 2.0 * k;
+        sum = fma(u, exp(fma(-0.5 * u * u, inv_tt, E)), sum);
     }
     return sum;
 }
 
-// One quadrature node: pdf_sv(x', v', sv, a, z_j, err) from the staged tables.
-__device__ __forceinline__ double node_table(const TNode& tn, const Set& s, int sign, int j)
+// N consecutive z-nodes (j0 .. j0+N-1) of one t-node: pdf_sv(x', v', sv, a, z_j, err) from the staged tables.
+template <int N>
+__device__ __forceinline__ void nodes(const TNode& tn, const Set& s, int sign, int j0, double* __restrict__ y)
 {
-    if (!tn.alive) return 0.0;
+    if (!tn.alive) {
+#pragma unroll
+        for (int n = 0; n < N; n++) y[n] = 0.0;
+        return;
+    }
     const Tables& T = *s.tab;
-    const double E = fma(T.zA[sign][j], tn.c, tn.E0);
-    double series;
+    const NodeTab* Z = &T.z[sign][j0];
+    const double* tab = T.exptab;
+    double E[N];
+#pragma unroll
+    for (int n = 0; n < N; n++) E[n] = fma(Z[n].A, tn.c, tn.E0);
+
     if (tn.small) {
-        series = series_small(T.zw[sign][j], tn.K, tn.nh, E);
-    } else {
-        const double* S = T.zS[sign][j];
-        double acc = tn.q1 * S[0];
-        if (tn.K > 1) acc = fma(tn.q4, S[1], acc);
-        if (tn.K > 2) acc = fma(tn.q9, S[2], acc);
-        if (tn.K > 3) acc = fma(tn.q16, S[3], acc);
-        if (tn.K > 4) {
-            const double q2 = tn.q1 * tn.q1;
-            double odd = tn.q4 * tn.q4 * tn.q1;  // q^9 = q^(25-16)
-            double qk = tn.q16;
-            for (int k = 4; k < tn.K; k++) {      // term k+1: q^((k+1)^2) = q^(k^2) * q^(2k+1)
-                qk *= odd;
-                odd *= q2;
-                acc = fma(qk, S[k], acc);
+        const int K = tn.K;
+        bool ok = (K <= 4);
+        if (K >= 4) {
+            double a[N][4];
+#pragma unroll
+            for (int n = 0; n < N; n++)
+#pragma unroll
+                for (int k = 0; k < 4; k++) {
+                    a[n][k] = fma(Z[n].uh[k], tn.inv_tt, E[n]);
+                    ok &= exp_arg_ok(a[n][k]);
+                }
+#pragma unroll
+            for (int n = 0; n < N; n++) {
+                const double em = exp_core(a[n][0], tab), e0 = exp_core(a[n][1], tab);
+                const double e1 = exp_core(a[n][2], tab), e2 = exp_core(a[n][3], tab);
+                y[n] = fma(Z[n].u[3], e2, fma(Z[n].u[2], e1, fma(Z[n].u[1], e0, Z[n].u[0] * em)));
+            }
+        } else {
+            double a[N][3];
+#pragma unroll
+            for (int n = 0; n < N; n++)
+#pragma unroll
+                for (int k = 0; k < 3; k++) {
+                    a[n][k] = fma(Z[n].uh[k], tn.inv_tt, E[n]);
+                    ok &= exp_arg_ok(a[n][k]);
+                }
+            const double keep_m = (K >= 3) ? 1.0 : 0.0;  // K == 2 sums k = 0, 1 only
+#pragma unroll
+            for (int n = 0; n < N; n++) {
+                const double em = exp_core(a[n][0], tab), e0 = exp_core(a[n][1], tab), e1 = exp_core(a[n][2], tab);
+                y[n] = fma(Z[n].u[2], e1, fma(Z[n].u[1], e0, keep_m * (Z[n].u[0] * em)));
             }
         }
-        if (tn.K < 1) acc = 0.0;
-        series = acc * exp(E);
+        if (!ok) {
+#pragma unroll 1
+            for (int n = 0; n < N; n++) y[n] = series_small_slow(Z[n].u[1], K, tn.inv_tt, E[n]);
+        }
+    } else {
+        bool ok = true;
+#pragma unroll
+        for (int n = 0; n < N; n++) ok &= exp_arg_ok(E[n]);
+#pragma unroll
+        for (int n = 0; n < N; n++) {
+            const double* S = Z[n].S;
+            double acc = tn.q1 * S[0];
+            if (tn.K > 1) acc = fma(tn.q4, S[1], acc);
+            if (tn.K > 2) acc = fma(tn.q9, S[2], acc);
+            if (tn.K > 3) acc = fma(tn.q16, S[3], acc);
+            if (tn.K > 4) {
+                const double q2 = tn.q1 * tn.q1;
+                double odd = tn.q4 * tn.q4 * tn.q1;  // q^9 = q^(25-16)
+                double qk = tn.q16;
+                for (int k = 4; k < tn.K; k++) {      // term k+1: q^((k+1)^2) = q^(k^2) * q^(2k+1)
+                    qk *= odd;
+                    odd *= q2;
+                    acc = fma(qk, S[k], acc);
+                }
+            }
+            if (tn.K < 1) acc = 0.0;
+            y[n] = acc * (ok ? exp_core(E[n], tab) : exp(E[n]));
+        }
     }
-    if (s.sv_nonzero && series < 0.0) return CUDART_NAN;  // log(p) of a negative truncated series (pdf.pxi:102)
-    return series * tn.pref;
-}
-
-// integrate.pxi:30-45 accumulation order, nodes addressed by index.
-template <class F>
-__device__ __forceinline__ double simpson_idx(const F& f, int n, double width, double h)
-{
-    double S = f(0);
-    double y = 0.0;
-    for (int i = 1; i <= n; i++) {
-        y = f(i);
-        S += (i & 1) ? (4 * y) : (2 * y);
+#pragma unroll
+    for (int n = 0; n < N; n++) {
+        // log(p) of a negative truncated series is NaN in pdf_sv (pdf.pxi:102); pdf (sv == 0) lets it through
+        y[n] = (s.sv_nonzero && y[n] < 0.0) ? CUDART_NAN : y[n] * tn.pref;
     }
-    S = S - y;
-    S = S / width;
-    return (h * S / 3);
 }
 
 // First level of integrate.pxi:72-141 on five equally spaced nodes f0..f4 (already divided by ZT):
@@ -234,6 +307,8 @@ __device__ __forceinline__ void prepare(Set& s, const Params& prm, const Opts& o
     s.simps_err = o.simps_err;
     s.depth_z = o.n_sz;
     s.depth_t = o.n_st;
+    s.npieces = kt.n;
+    s.piece = 0;
     s.nz = s.nt = 0;
     // pdf.pxi:111-113, the trial-independent part
     const bool bad = (z < 0) || (z > 1) || (a < 0) || (t < 0) || (st < 0) || (sv < 0) || (sz < 0) || (sz > 1) ||
@@ -258,6 +333,11 @@ __device__ __forceinline__ void prepare(Set& s, const Params& prm, const Opts& o
     if (mode == kModeZero || mode == kModeGeneric) {
         __syncthreads();
         return;
+    }
+    for (int i = threadIdx.x; i < 64; i += blockDim.x) T.exptab[i] = exp2((double)i * (1.0 / 64.0));
+    for (int i = threadIdx.x; i <= kt.n; i += blockDim.x) {
+        T.desc[i] = (i == 0) ? kt.desc0 : kt.desc[i - 1];
+        if (i < kt.n) T.thr[i] = kt.thr[i];
     }
 
     // intervals / nodes per axis
@@ -313,22 +393,26 @@ __device__ __forceinline__ void prepare(Set& s, const Params& prm, const Opts& o
         T.wz[sign] = w;
         T.hz[sign] = (mode == kModeFixed && nz_div > 0) ? __ddiv_rn(w, (double)nz_div) : 0.0;
     }
-    for (int idx = threadIdx.x; idx < 2 * nzn; idx += blockDim.x) {
-        const int sign = idx / nzn, j = idx - sign * nzn;
-        double w;
-        const double zj = znode(sign, j, &w);
-        const double vv = sign ? -prm.v : prm.v;
-        T.zw[sign][j] = zj;
-        const double azsv = a * zj * sv;
-        T.zA[sign][j] = azsv * azsv - 2 * a * vv * zj;
-    }
-    // k sin(k pi z_j): one (sign, node, k) entry per thread
-    for (int idx = threadIdx.x; idx < 2 * nzn * kMaxKLarge; idx += blockDim.x) {
-        const int k = idx % kMaxKLarge, r = idx / kMaxKLarge;
+    // one (sign, node, slot) entry per thread: slots 0..3 = lattice k = -1..2, slot 4 = A, slots 5.. = sines
+    constexpr int kSlots = 5 + kMaxKLarge;
+    for (int idx = threadIdx.x; idx < 2 * nzn * kSlots; idx += blockDim.x) {
+        const int slot = idx % kSlots, r = idx / kSlots;
         const int sign = r / nzn, j = r - sign * nzn;
         double w;
         const double zj = znode(sign, j, &w);
-        T.zS[sign][j][k] = (k < kt.kl_max) ? (double)(k + 1) * sinpi((double)(k + 1) * zj) : 0.0;
+        NodeTab& Z = T.z[sign][j];
+        if (slot < 4) {
+            const double u = zj + 2.0 * (slot - 1);
+            Z.u[slot] = u;
+            Z.uh[slot] = -0.5 * u * u;
+        } else if (slot == 4) {
+            const double vv = sign ? -prm.v : prm.v;
+            const double azsv = a * zj * sv;
+            Z.A = azsv * azsv - 2 * a * vv * zj;
+        } else {
+            const int k = slot - 4;  // 1..kMaxKLarge
+            Z.S[k - 1] = (k <= kt.kl_max) ? (double)k * sinpi((double)k * zj) : 0.0;
+        }
     }
     __syncthreads();
 }
@@ -336,23 +420,47 @@ __device__ __forceinline__ void prepare(Set& s, const Params& prm, const Opts& o
 // Inner z-integral at one t-node: a single node, a fixed grid, or the first adaptive level (ok &= converged).
 __device__ __forceinline__ double inner_z(const TNode& tn, const Set& s, int sign, bool* ok)
 {
-    if (s.nz == 0) return node_table(tn, s, sign, 0);
+    if (s.nz == 0) {
+        double y;
+        nodes<1>(tn, s, sign, 0, &y);
+        return y;
+    }
     const Tables& T = *s.tab;
     const double wz = T.wz[sign];
-    if (s.mode == kModeFixed) {
-        return simpson_idx([&](int j) { return node_table(tn, s, sign, j); }, s.nz, wz, T.hz[sign]);
+    if (s.mode == kModeAdaptive) {
+        double y[5];
+        nodes<5>(tn, s, sign, 0, y);
+        double val;
+        *ok &= adaptive_level1(y[0] / wz, y[1] / wz, y[2] / wz, y[3] / wz, y[4] / wz, wz, s.simps_err, s.depth_z, &val);
+        return val;
     }
-    const double f0 = node_table(tn, s, sign, 0) / wz;
-    const double f1 = node_table(tn, s, sign, 1) / wz;
-    const double f2 = node_table(tn, s, sign, 2) / wz;
-    const double f3 = node_table(tn, s, sign, 3) / wz;
-    const double f4 = node_table(tn, s, sign, 4) / wz;
-    double val;
-    *ok &= adaptive_level1(f0, f1, f2, f3, f4, wz, s.simps_err, s.depth_z, &val);
-    return val;
+    // integrate.pxi:30-45: S = f(0); S += 4 f(odd) | 2 f(even); S -= f(n); S /= width; h*S/3
+    const double hz = T.hz[sign];
+    double S, last;
+    if (s.nz == 2) {
+        double y[3];
+        nodes<3>(tn, s, sign, 0, y);
+        S = y[0];
+        S += (4 * y[1]);
+        S += (2 * y[2]);
+        last = y[2];
+    } else {
+        double y;
+        nodes<1>(tn, s, sign, 0, &y);
+        S = y;
+        last = 0.0;
+        for (int j = 1; j <= s.nz; j++) {
+            nodes<1>(tn, s, sign, j, &y);
+            S += (j & 1) ? (4 * y) : (2 * y);
+            last = y;
+        }
+    }
+    S = S - last;
+    S = S / wz;
+    return (hz * S / 3);
 }
 
-__device__ __forceinline__ double density(double x, const Set& s, const KTable& kt)
+__device__ __forceinline__ double density(double x, Set& s)
 {
     if (s.mode == kModeZero) return 0.0;
     const Tables& T = *s.tab;
@@ -362,26 +470,31 @@ __device__ __forceinline__ double density(double x, const Set& s, const KTable& 
     const int sign = x > 0;
     bool ok = true;
     double result;
+    TNode tn;
     if (s.nt == 0) {
-        TNode tn;
-        make_tnode(tn, ax - s.t, s, kt);
+        make_tnode(tn, ax - s.t, s);
         result = inner_z(tn, s, sign, &ok);
     } else if (s.mode == kModeFixed) {
-        result = simpson_idx(
-            [&](int i) {
-                TNode tn;
-                make_tnode(tn, ax - T.tn[i], s, kt);
-                return inner_z(tn, s, sign, &ok);
-            },
-            s.nt, T.wt, T.ht);
+        const double wt = T.wt, ht = T.ht;
+        make_tnode(tn, ax - T.tn[0], s);
+        double S = inner_z(tn, s, sign, &ok);
+        double y = 0.0;
+#pragma unroll 1
+        for (int i = 1; i <= s.nt; i++) {
+            make_tnode(tn, ax - T.tn[i], s);
+            y = inner_z(tn, s, sign, &ok);
+            S += (i & 1) ? (4 * y) : (2 * y);
+        }
+        S = S - y;
+        S = S / wt;
+        result = (ht * S / 3);
     } else {
         // kModeAdaptive: first level of the reference's recursion on the staged quarter points
         const double wt = T.wt;
         double g[5];
 #pragma unroll 1
         for (int i = 0; i < 5; i++) {
-            TNode tn;
-            make_tnode(tn, ax - T.tn[i], s, kt);
+            make_tnode(tn, ax - T.tn[i], s);
             g[i] = inner_z(tn, s, sign, &ok) / wt;
         }
         ok &= adaptive_level1(g[0], g[1], g[2], g[3], g[4], wt, s.simps_err, s.depth_t, &result);
@@ -407,7 +520,7 @@ __device__ __forceinline__ double density_once(double x, const Params& prm, cons
     if (!(xp > 0)) return 0.0;
     const double a2 = a * a, inv_a2 = 1.0 / a2;
     const double tt = xp / a2;
-    const int d = klookup(kt, tt);
+    const int d = klookup_scan(kt, tt);
     const int K = d & 0xff;
     const double c = 0.5 / fma(sv * sv, xp, 1.0);
     const double azsv = a * w * sv;
@@ -416,7 +529,7 @@ __device__ __forceinline__ double density_once(double x, const Params& prm, cons
     double series, pref;
     if (d >> 8) {
         const double inv_tt = 1.0 / tt;
-        series = series_small(w, K, -0.5 * inv_tt, E);
+        series = series_small_slow(w, K, inv_tt, E);
         pref = inv_tt * sqrt(inv_tt) * (kInvSqrt2Pi * inv_a2) * rs;
     } else {
         const double q = exp(-kHalfPiSq * tt), q2 = q * q;

@@ -107,7 +107,7 @@ def test_batch_device_tensors_match_host_buffers(golden, wfpt_gpu, variant):
     import torch
 
     x2, P4 = golden["x_cfg2"], golden["cfg4_params"]
-    host = wfpt_gpu.wiener_like_batch(x2, P4, 1e-4, 2, 2, 0, 1e-3, 0.1, variant=variant)
+    host = wfpt_gpu.wiener_like_batch(x2, P4, 1e-4, 2, 2, 0, 1e-3, 0.1, variant=variant, presort=False)
     dev = wfpt_gpu.wiener_like_batch(torch.from_numpy(x2).cuda(), torch.from_numpy(P4).cuda(), 1e-4, 2, 2, 0, 1e-3, 0.1,
                                      variant=variant)
     torch.cuda.synchronize()
