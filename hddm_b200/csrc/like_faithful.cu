@@ -16,10 +16,19 @@ struct FaithfulImpl {
         s.prm = prm;
         s.o = o;
     }
-    __device__ static __forceinline__ double density(double x, const Set& s, const Ctx&)
+    __device__ static __forceinline__ double density(double x, const Set& s, const Ctx&, bool* defer)
     {
+        *defer = false;
         return faithful::full_pdf(x, s.prm.v, s.prm.sv, s.prm.a, s.prm.z, s.prm.sz, s.prm.t, s.prm.st, s.o);
     }
+    __device__ static __forceinline__ double density_generic(double x, const Set& s, const Ctx& c)
+    {
+        bool d;
+        return density(x, s, c, &d);
+    }
+    __device__ static __forceinline__ bool park(Set&, double) { return false; }
+    __device__ static __forceinline__ int parked_count(const Set&) { return 0; }
+    __device__ static __forceinline__ double parked(const Set&, int) { return 0.0; }
     __device__ static __forceinline__ double density_once(double x, const Params& prm, const Opts& o, const Ctx&)
     {
         return faithful::full_pdf(x, prm.v, prm.sv, prm.a, prm.z, prm.sz, prm.t, prm.st, o);

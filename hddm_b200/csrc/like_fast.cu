@@ -11,7 +11,30 @@ struct FastImpl {
     {
         fast::prepare(s, prm, o, kt);
     }
-    __device__ static __forceinline__ double density(double x, Set& s, const Ctx&) { return fast::density(x, s); }
+    __device__ static __forceinline__ double density(double x, Set& s, const Ctx&, bool* defer)
+    {
+        return fast::density(x, s, defer);
+    }
+    __device__ static __forceinline__ double density_generic(double x, const Set& s, const Ctx&)
+    {
+        return fast::density_generic(x, s);
+    }
+    // Parking lot in shared memory (fast::Tables): returns false when full.
+    __device__ static __forceinline__ bool park(Set& s, double x)
+    {
+        fast::Tables& T = fast::tables();
+        const int slot = atomicAdd(&T.qcount, 1);
+        if (slot >= fast::kQueue) return false;
+        T.queue[slot] = x;
+        return true;
+    }
+    __device__ static __forceinline__ int parked_count(const Set&)
+    {
+        __syncthreads();
+        const int n = fast::tables().qcount;
+        return n < fast::kQueue ? n : fast::kQueue;
+    }
+    __device__ static __forceinline__ double parked(const Set&, int q) { return fast::tables().queue[q]; }
     __device__ static __forceinline__ double density_once(double x, const Params& prm, const Opts& o, const Ctx& kt)
     {
         return fast::density_once(x, prm, o, kt);

@@ -84,7 +84,25 @@ __global__ void __launch_bounds__(kBlock, 4) like_batch_kernel(const double* __r
         }
 #pragma unroll 1
         for (int h = 0; h < cnt; h++) {
-            const double p0 = mix_outlier(Impl::density(h ? v1 : v0, set, ctx), omp, wp);
+            const double xv = h ? v1 : v0;
+            bool defer;
+            double dens = Impl::density(xv, set, ctx, &defer);
+            if (defer) {
+                // park the trial; evaluated below by the whole CTA.  A full lot means: do it here and now.
+                if (Impl::park(set, xv)) continue;
+                dens = Impl::density_generic(xv, set, ctx);
+            }
+            const double p0 = mix_outlier(dens, omp, wp);
+            zero |= (p0 == 0);
+            acc += log(p0);
+        }
+    }
+    // parked trials: dense pass through the generic evaluator
+    {
+        const int parked = Impl::parked_count(set);  // CTA-uniform, includes a barrier when parking is in use
+#pragma unroll 1
+        for (int q = threadIdx.x; q < parked; q += kBlock) {
+            const double p0 = mix_outlier(Impl::density_generic(Impl::parked(set, q), set, ctx), omp, wp);
             zero |= (p0 == 0);
             acc += log(p0);
         }
@@ -119,7 +137,10 @@ __global__ void __launch_bounds__(kBlock) pdf_array_kernel(const double* __restr
     // wfpt.pyx:44: y * (1 - p_outlier) + (w_outlier * p_outlier), then optionally np.log
     const double wp = __dmul_rn(w_outlier, prm.p_outlier);
     const double omp = __dsub_rn(1.0, prm.p_outlier);
-    const double p = mix_outlier(Impl::density(x[i], set, ctx), omp, wp);
+    bool defer;
+    double dens = Impl::density(x[i], set, ctx, &defer);
+    if (defer) dens = Impl::density_generic(x[i], set, ctx);
+    const double p = mix_outlier(dens, omp, wp);
     y[i] = logp ? log(p) : p;
 }
 

@@ -33,6 +33,7 @@ namespace fast {
 constexpr int kMaxNodes = 33;               // nodes per axis held in shared memory (n_st, n_sz <= 32)
 constexpr double kInvSqrt2Pi = 0.3989422804014327;
 constexpr double kHalfPiSq = 4.934802200544679;  // pi^2 / 2
+constexpr int kQueue = 1024;                // per-CTA parking lot for trials that need the generic evaluator
 
 enum Mode : int {
     kModePoint = 0,      // sz == 0 and st == 0: one node per trial
@@ -56,11 +57,15 @@ struct Tables {
     double tn[kMaxNodes];     // t_i
     double wz[2], hz[2];      // z interval width / step per response sign, as the reference rounds them
     double wt, ht;            // same along t
+    double cz[2], ct;         // hz/(3 wz) per sign and ht/(3 wt): the fixed-grid Simpson scale as one multiplier
+    double inv_wz[2], inv_wt; // reciprocal widths (first adaptive level)
     double exptab[64];        // 2^(j/64)
     long long thr[kMaxPieces];  // series-term table (copy of the launch's KTable)
     int desc[kMaxPieces + 1];   // desc[0] = piece below thr[0]
     Params prm;               // raw parameter set and options (generic fallback only)
     Opts o;
+    int qcount;               // trials parked for the generic evaluator (adaptive refinement needed)
+    double queue[kQueue];
 };
 
 // Per-thread (register) view of the parameter set; everything bulky lives in Tables.
@@ -93,7 +98,7 @@ __device__ __forceinline__ Tables& tables()
 
 // ---- exp ------------------------------------------------------------------------------------------------------------------
 // exp(x) = 2^e * 2^(j/64) * exp(r),  k = rint(64 x / ln 2) = 64 e + j,  r = x - k ln2/64, |r| <= 0.0055.
-// Branch-free; valid for -708 <= x <= 709 (normal results).  Max error 0.98 ulp (checked against mpmath).
+// Branch-free; valid for |x| < 708 (normal results).  Max error 0.98 ulp (checked against mpmath).
 __device__ __forceinline__ double exp_core(double x, const double* __restrict__ tab)
 {
     const double t = fma(x, 92.33248261689366, 6755399441055744.0);
@@ -110,7 +115,8 @@ __device__ __forceinline__ double exp_core(double x, const double* __restrict__ 
     const double res = fma(T, p, T);
     return __hiloint2double(__double2hiint(res) + ((ki >> 6) << 20), __double2loint(res));
 }
-__device__ __forceinline__ bool exp_arg_ok(double x) { return (x >= -708.0) & (x <= 709.0); }
+// |x| < 708 (and not NaN), tested on the high word so that it costs no FP64-pipe slot
+__device__ __forceinline__ bool exp_arg_ok(double x) { return (unsigned)(__double2hiint(x) & 0x7fffffff) < 0x40862000u; }
 
 // ---- series-term lookup -----------------------------------------------------------------------------------------------
 // Walk from the piece of the previous lookup to the piece holding tt.  Returns (small << 8) | K.
@@ -282,11 +288,12 @@ __device__ __forceinline__ void nodes(const TNode& tn, const Set& s, int sign, i
 __device__ __forceinline__ bool adaptive_level1(double f0, double f1, double f2, double f3, double f4, double h,
                                                 double simps_err, int max_depth, double* out)
 {
-    const double S = (h / 6) * (f0 + 4 * f2 + f4);
-    const double Sl = (h / 12) * (f0 + 4 * f1 + f2);
-    const double Sr = (h / 12) * (f2 + 4 * f3 + f4);
+    const double h12 = h * (1.0 / 12.0);
+    const double S = (2.0 * h12) * (f0 + 4 * f2 + f4);
+    const double Sl = h12 * (f0 + 4 * f1 + f2);
+    const double Sr = h12 * (f2 + 4 * f3 + f4);
     const double S2 = Sl + Sr;
-    *out = S2 + (S2 - S) / 15;
+    *out = fma(S2 - S, 1.0 / 15.0, S2);
     return (max_depth <= 0) || (fabs(S2 - S) <= 15 * simps_err);
 }
 
@@ -329,6 +336,7 @@ __device__ __forceinline__ void prepare(Set& s, const Params& prm, const Opts& o
     if (threadIdx.x == 0) {
         T.prm = prm;
         T.o = o;
+        T.qcount = 0;
     }
     if (mode == kModeZero || mode == kModeGeneric) {
         __syncthreads();
@@ -359,6 +367,8 @@ __device__ __forceinline__ void prepare(Set& s, const Params& prm, const Opts& o
         if (threadIdx.x == 0) {
             T.wt = wt;
             T.ht = ht;
+            T.ct = ht / (3.0 * wt);
+            T.inv_wt = 1.0 / wt;
         }
         for (int i = threadIdx.x; i < ntn; i += blockDim.x) {
             double ti;
@@ -391,7 +401,10 @@ __device__ __forceinline__ void prepare(Set& s, const Params& prm, const Opts& o
         double w;
         (void)znode(sign, 0, &w);
         T.wz[sign] = w;
-        T.hz[sign] = (mode == kModeFixed && nz_div > 0) ? __ddiv_rn(w, (double)nz_div) : 0.0;
+        const double hz = (mode == kModeFixed && nz_div > 0) ? __ddiv_rn(w, (double)nz_div) : 0.0;
+        T.hz[sign] = hz;
+        T.cz[sign] = hz / (3.0 * w);
+        T.inv_wz[sign] = 1.0 / w;
     }
     // one (sign, node, slot) entry per thread: slots 0..3 = lattice k = -1..2, slot 4 = A, slots 5.. = sines
     constexpr int kSlots = 5 + kMaxKLarge;
@@ -426,81 +439,71 @@ __device__ __forceinline__ double inner_z(const TNode& tn, const Set& s, int sig
         return y;
     }
     const Tables& T = *s.tab;
-    const double wz = T.wz[sign];
     if (s.mode == kModeAdaptive) {
         double y[5];
         nodes<5>(tn, s, sign, 0, y);
+        const double iw = T.inv_wz[sign];
         double val;
-        *ok &= adaptive_level1(y[0] / wz, y[1] / wz, y[2] / wz, y[3] / wz, y[4] / wz, wz, s.simps_err, s.depth_z, &val);
+        *ok &= adaptive_level1(y[0] * iw, y[1] * iw, y[2] * iw, y[3] * iw, y[4] * iw, T.wz[sign], s.simps_err,
+                               s.depth_z, &val);
         return val;
     }
-    // integrate.pxi:30-45: S = f(0); S += 4 f(odd) | 2 f(even); S -= f(n); S /= width; h*S/3
-    const double hz = T.hz[sign];
-    double S, last;
+    // integrate.pxi:30-45: S = f(0) + 4 f(odd) + 2 f(even) - f(n), then (h/3) * S / width
+    double S;
     if (s.nz == 2) {
         double y[3];
         nodes<3>(tn, s, sign, 0, y);
-        S = y[0];
-        S += (4 * y[1]);
-        S += (2 * y[2]);
-        last = y[2];
+        S = fma(4.0, y[1], y[0]) + y[2];
     } else {
         double y;
-        nodes<1>(tn, s, sign, 0, &y);
-        S = y;
-        last = 0.0;
-        for (int j = 1; j <= s.nz; j++) {
+        S = 0.0;
+#pragma unroll 1
+        for (int j = 0; j <= s.nz; j++) {
             nodes<1>(tn, s, sign, j, &y);
-            S += (j & 1) ? (4 * y) : (2 * y);
-            last = y;
+            S = fma((j == 0 || j == s.nz) ? 1.0 : ((j & 1) ? 4.0 : 2.0), y, S);
         }
     }
-    S = S - last;
-    S = S / wz;
-    return (hz * S / 3);
+    return S * T.cz[sign];
 }
 
-__device__ __forceinline__ double density(double x, Set& s)
+// Density of one trial from the staged tables.  *defer is set (and the return value is meaningless) when the
+// reference's adaptive recursion would go below the first level for this trial: the caller evaluates those trials
+// with density_generic, preferably all together at the end (a CTA-wide pass instead of one diverged lane at a time).
+__device__ __forceinline__ double density(double x, Set& s, bool* defer)
 {
+    *defer = false;
     if (s.mode == kModeZero) return 0.0;
     const Tables& T = *s.tab;
-    if (s.mode == kModeGeneric) return generic_full_pdf(x, T.prm, T.o);
+    if (s.mode == kModeGeneric) {
+        *defer = true;
+        return 0.0;
+    }
     const double ax = fabs(x);
     if ((ax - s.tlo) < 0) return 0.0;  // pdf.pxi:112, the trial-dependent part
     const int sign = x > 0;
     bool ok = true;
-    double result;
     TNode tn;
-    if (s.nt == 0) {
-        make_tnode(tn, ax - s.t, s);
-        result = inner_z(tn, s, sign, &ok);
-    } else if (s.mode == kModeFixed) {
-        const double wt = T.wt, ht = T.ht;
-        make_tnode(tn, ax - T.tn[0], s);
-        double S = inner_z(tn, s, sign, &ok);
-        double y = 0.0;
+    const bool adaptive = (s.mode == kModeAdaptive) && (s.nt > 0);
+    double g[5];
+    double S = 0.0;
 #pragma unroll 1
-        for (int i = 1; i <= s.nt; i++) {
-            make_tnode(tn, ax - T.tn[i], s);
-            y = inner_z(tn, s, sign, &ok);
-            S += (i & 1) ? (4 * y) : (2 * y);
-        }
-        S = S - y;
-        S = S / wt;
-        result = (ht * S / 3);
-    } else {
-        // kModeAdaptive: first level of the reference's recursion on the staged quarter points
-        const double wt = T.wt;
-        double g[5];
-#pragma unroll 1
-        for (int i = 0; i < 5; i++) {
-            make_tnode(tn, ax - T.tn[i], s);
-            g[i] = inner_z(tn, s, sign, &ok) / wt;
-        }
-        ok &= adaptive_level1(g[0], g[1], g[2], g[3], g[4], wt, s.simps_err, s.depth_t, &result);
+    for (int i = 0; i <= s.nt; i++) {
+        make_tnode(tn, ax - T.tn[i], s);  // tn[0] == t when the t axis is not integrated
+        const double y = inner_z(tn, s, sign, &ok);
+        if (adaptive) g[i] = y * T.inv_wt;
+        else S = fma((i == 0 || i == s.nt) ? 1.0 : ((i & 1) ? 4.0 : 2.0), y, S);
     }
-    if (ok) return result;
-    // some interval needs refinement: walk the full recursion for this trial
+    double result;
+    if (adaptive) ok &= adaptive_level1(g[0], g[1], g[2], g[3], g[4], T.wt, s.simps_err, s.depth_t, &result);
+    else result = (s.nt == 0) ? S : S * T.ct;
+    *defer = !ok;
+    return result;
+}
+
+// The full reference recursion for one trial (any mode).
+__device__ __forceinline__ double density_generic(double x, const Set& s)
+{
+    const Tables& T = *s.tab;
     return generic_full_pdf(x, T.prm, T.o);
 }
 
