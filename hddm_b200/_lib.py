@@ -36,6 +36,8 @@ def _declare(L):
     opts = [d, i, i, i, d]  # err, n_st, n_sz, use_adaptive, simps_err
     L.wfpt_like_batch.argtypes = [vp, i64, vp, i64] + opts + [d, i, vp, vp]
     L.wfpt_like_batch_host.argtypes = [vp, i64, vp, i64] + opts + [d, i, vp]
+    L.wfpt_like_batch_noalloc.argtypes = [vp, i64, vp, i64] + opts + [d, i, vp, vp]
+    L.wfpt_like_batch_noalloc.restype = i
     L.wfpt_pdf_array.argtypes = [vp, i64, c_double_p] + opts + [d, i, i, vp, vp]
     L.wfpt_pdf_array_host.argtypes = [vp, i64, c_double_p] + opts + [d, i, i, vp]
     L.wfpt_like_multi.argtypes = [vp, i64, C.POINTER(vp), c_double_p] + opts + [d, d, i, vp, vp]

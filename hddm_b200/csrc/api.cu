@@ -165,6 +165,20 @@ static void plan_slices(int64_t n, int64_t P, int* slices, int64_t* chunk)
     *chunk = c;
 }
 
+// ---- hooks for sibling translation units ---------------------------------------------------------------------------------
+int api_fail(const char* msg) { return fail("%s", msg); }
+int api_check_opts(double err, int n_st, int n_sz, int use_adaptive, double simps_err, int variant, Opts* o)
+{
+    return check_opts(err, n_st, n_sz, use_adaptive, simps_err, variant, o);
+}
+void api_plan_slices(int64_t n, int64_t P, int* slices, int64_t* chunk) { plan_slices(n, P, slices, chunk); }
+cudaError_t api_launch_finalize(const double* part_sum, const int* part_zero, int64_t P, int slices, int early_exit,
+                                double* out, cudaStream_t stream)
+{
+    finalize_kernel<<<(unsigned)((P + 127) / 128), 128, 0, stream>>>(part_sum, part_zero, P, slices, early_exit, out);
+    return cudaGetLastError();
+}
+
 }  // namespace wfpt
 
 using namespace wfpt;

@@ -68,6 +68,21 @@ int wfpt_like_batch(const double* d_x, int64_t n, const double* d_params, int64_
 int wfpt_like_batch_host(const double* h_x, int64_t n, const double* h_params, int64_t P, double err, int n_st,
                          int n_sz, int use_adaptive, double simps_err, double w_outlier, int variant, double* h_out);
 
+/* Same computation and same results as wfpt_like_batch, for callers that cannot allocate device memory (a process
+ * whose GPU memory is already owned by another pool, a latency-bound caller that cannot afford cudaMalloc's device
+ * synchronisation, a context in which allocation calls are not permitted).  It has no counterpart in the reference.
+ * The partial sums of the two-stage trial reduction live in a fixed array inside the library image
+ * (WFPT_NOALLOC_MAX_SLOTS slots, 192 KiB, held by every GPU that loads the library until process exit) and the
+ * function makes no cudaMalloc/cudaFree call.  A call needs P x slices slots (slices = the trial slicing
+ * wfpt_like_batch picks for the same n and P; P slots when one slice covers all trials); more than
+ * WFPT_NOALLOC_MAX_SLOTS is refused with an error.  All calls on a device share the array, so calls whose kernels
+ * overlap on the GPU race; run them one after another.  The first call on each device looks the array's device
+ * address up and should be made before any stream capture. */
+#define WFPT_NOALLOC_MAX_SLOTS 16384
+int wfpt_like_batch_noalloc(const double* d_x, int64_t n, const double* d_params, int64_t P, double err, int n_st,
+                            int n_sz, int use_adaptive, double simps_err, double w_outlier, int variant,
+                            double* d_out, void* stream);
+
 /* y[i] = full_pdf(x[i], ...)*(1-p_outlier) + w_outlier*p_outlier, optionally log.  Replaces src/wfpt.pyx:32-48
  * (pdf_array) and, with n == 1, p_outlier == 0, the cpdef full_pdf of src/pdf.pxi:104-146. */
 int wfpt_pdf_array(const double* d_x, int64_t n, const double* params8, double err, int n_st, int n_sz,
