@@ -1,0 +1,62 @@
+"""Sharding of the batched likelihood and of simulator histograms over the GPUs of one box.
+
+One process per GPU (torchrun); `torch.distributed` (NCCL on GPUs, gloo in the CPU tests) is plumbing only.
+Parameter sets are independent, so the likelihood needs no data-path collective: rank r evaluates rows r, r+W, ...
+(round-robin balances cheap and expensive sets) and the per-set sums are all-gathered -- no cross-rank arithmetic,
+hence results are bit-identical for every world size.  Simulator histograms are integer counts: all-reduce(sum).
+"""
+from __future__ import annotations
+
+import numpy as np
+
+
+def shard_rows(P: int, rank: int, world: int) -> np.ndarray:
+    """Row indices owned by `rank`: rank, rank+world, ...  (requires nothing of P)."""
+    return np.arange(rank, P, world, dtype=np.int64)
+
+
+def unshard_order(P: int, world: int) -> np.ndarray:
+    """Permutation that maps the rank-major concatenation of padded shards back to row order.
+
+    Every rank pads its shard to ceil(P/world) rows (all_gather needs equal sizes); position k of rank r holds row
+    r + k*world.  Returns idx with full[row] = gathered[idx[row]]."""
+    per = -(-P // world)
+    rows = np.arange(P, dtype=np.int64)
+    return (rows % world) * per + rows // world
+
+
+def wiener_like_batch_sharded(x, params, group=None, evaluate=None, **opts):
+    """All ranks call this with the same (x, params); every rank returns the full float64[P] vector.
+
+    x, params: torch tensors on this rank's device (CUDA for the product path).  `evaluate(x, shard_params, **opts)`
+    defaults to hddm_b200.wfpt.wiener_like_batch; the CPU tests inject their own."""
+    import torch
+    import torch.distributed as dist
+
+    if evaluate is None:
+        from . import wfpt
+
+        evaluate = wfpt.wiener_like_batch
+    world = dist.get_world_size(group) if dist.is_initialized() else 1
+    rank = dist.get_rank(group) if dist.is_initialized() else 0
+    P = params.shape[0]
+    if world == 1:
+        return evaluate(x, params, **opts)
+    rows = torch.from_numpy(shard_rows(P, rank, world)).to(params.device)
+    mine = evaluate(x, params.index_select(0, rows).contiguous(), **opts)
+    per = -(-P // world)
+    padded = torch.zeros(per, dtype=torch.float64, device=params.device)
+    padded[: mine.shape[0]] = mine
+    gathered = torch.empty(per * world, dtype=torch.float64, device=params.device)
+    dist.all_gather_into_tensor(gathered, padded, group=group)
+    idx = torch.from_numpy(unshard_order(P, world)).to(params.device)
+    return gathered.index_select(0, idx)
+
+
+def merge_histograms(counts, group=None):
+    """Sum integer histogram counts over ranks in place (particles sharded over ranks) and return them."""
+    import torch.distributed as dist
+
+    if dist.is_initialized() and dist.get_world_size(group) > 1:
+        dist.all_reduce(counts, op=dist.ReduceOp.SUM, group=group)
+    return counts

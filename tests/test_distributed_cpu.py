@@ -1,0 +1,77 @@
+"""world_size-2 and -3 gloo tests (CPU) of the multi-GPU host logic: round-robin sharding of parameter sets,
+padded all-gather, un-permutation, histogram merge.  The evaluator is injected (the C oracle) because there is no
+GPU here; on the box the same function runs with the CUDA evaluator under NCCL (bench.py --gpus N)."""
+import os
+import socket
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _worker(rank, world, port, P, q):
+    sys.path.insert(0, ROOT)
+    import torch
+    import torch.distributed as dist
+
+    from hddm_b200 import distributed as D
+    from oracle import cpu as oracle
+
+    dist.init_process_group("gloo", init_method=f"tcp://127.0.0.1:{port}", rank=rank, world_size=world)
+    rng = np.random.default_rng(7)
+    x = np.where(rng.random(300) < 0.8, 1.0, -1.0) * rng.uniform(0.4, 3.0, 300)
+    prm = np.stack([rng.uniform(-3, 3, P), rng.uniform(0, 2, P), rng.uniform(1, 3, P), rng.uniform(0.3, 0.7, P),
+                    rng.uniform(0, 0.2, P), rng.uniform(0.1, 0.3, P), rng.uniform(0, 0.2, P), np.full(P, 0.05)], axis=1)
+    calls = []
+
+    def evaluate(xt, pt, **opts):
+        calls.append(pt.shape[0])
+        return torch.from_numpy(oracle.wiener_like_batch(xt.numpy(), pt.numpy(), 1e-4, 2, 2, 0, 1e-3, 0.1))
+
+    full = D.wiener_like_batch_sharded(torch.from_numpy(x), torch.from_numpy(prm), evaluate=evaluate)
+    want = oracle.wiener_like_batch(x, prm, 1e-4, 2, 2, 0, 1e-3, 0.1)
+    hist = torch.full((4, 8, 2), rank + 1, dtype=torch.int64)
+    D.merge_histograms(hist)
+    ok = bool(np.array_equal(full.numpy(), want)) and calls == [len(D.shard_rows(P, rank, world))] and \
+        bool((hist == sum(range(1, world + 1))).all())
+    q.put((rank, ok))
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,P", [(2, 64), (2, 37), (3, 10)])
+def test_sharded_batch_matches_single_process(world, P):
+    import torch.multiprocessing as mp
+
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, world, port, P, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=120) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+    assert sorted(res) == [(r, True) for r in range(world)]
+
+
+def test_shard_helpers():
+    from hddm_b200 import distributed as D
+
+    for P, W in [(1, 1), (8, 2), (37, 2), (10, 3), (65536, 8), (5, 8)]:
+        rows = [D.shard_rows(P, r, W) for r in range(W)]
+        assert sorted(np.concatenate(rows).tolist()) == list(range(P))
+        per = -(-P // W)
+        gathered = np.full(per * W, -1, dtype=np.int64)
+        for r in range(W):
+            gathered[r * per: r * per + len(rows[r])] = rows[r]
+        assert np.array_equal(gathered[D.unshard_order(P, W)], np.arange(P))
