@@ -51,10 +51,14 @@ def _declare(L):
                  "wfpt_like_batch_host", "wfpt_pdf_array", "wfpt_pdf_array_host", "wfpt_like_multi",
                  "wfpt_like_multi_host", "wfpt_like_rlddm_host"):
         getattr(L, name).restype = i
-    if hasattr(L, "wfpt_sim_run"):
-        from . import _sim_decl
-
-        _sim_decl.declare(L)
+    f = C.c_float
+    sim_tail = [i, i, i64, i64, f, f, f, C.c_uint64, vp, vp, vp, i, f, vp, vp, i]
+    L.wfpt_sim_run.argtypes = [i, vp] + sim_tail + [vp]
+    L.wfpt_sim_run.restype = i
+    L.wfpt_sim_run_host.argtypes = [i, vp] + sim_tail
+    L.wfpt_sim_run_host.restype = i
+    L.wfpt_sim_n_params.argtypes = [i]
+    L.wfpt_sim_n_params.restype = i
 
 
 def load():

@@ -1,0 +1,441 @@
+// Euler-Maruyama sequential-sampling simulators (one particle = one first-passage walk) for sm_100a.
+//
+// What is simulated (paths relative to /root/reference/src/cddm_data_simulation.pyx; dispatch and theta column
+// order from /root/reference/graveyard/basic_simulator_old.py:168-480 and hddm/model_config.py):
+//   WFPT_SIM_DDM              ddm                 :294-375   bounds [0, a],  start z*a, choice 0/1
+//   WFPT_SIM_FULL_DDM_BASE    full_ddm_hddm_base  :174-284   bounds [0, a],  sv/sz/st draws in absolute units
+//   WFPT_SIM_DDM_FLEXBOUND    ddm_flexbound       :454-553   symmetric +-a (constant bound), choice sign(y)
+//   WFPT_SIM_ANGLE            ddm_flexbound + angle bound  b(t) = a + t * (-sin(th)/cos(th))   (additive)
+//   WFPT_SIM_WEIBULL          ddm_flexbound + Weibull bound b(t) = a * exp(-(t/beta)^alpha)    (multiplicative)
+//   WFPT_SIM_FULL_DDM         full_ddm            :747-869
+//   WFPT_SIM_DDM_SDV          ddm_sdv             :876-994
+//   WFPT_SIM_ORNSTEIN         ornstein_uhlenbeck  :1119-1219
+//   WFPT_SIM_LEVY             levy_flexbound      :642-741   alpha-stable increments (Chambers-Mallows-Stuck, :28-40)
+//
+// Arithmetic follows the reference: particle state, time and bounds are float32; time is accumulated by repeated
+// float32 addition of delta_t (so RTs land on the reference's grid of values); the increment is
+// y += (v*dt) + (sqrt(dt)*s*N) with each product and sum rounded on its own.  The reference's RNG (C rand() + polar
+// method, cyclic buffer) is replaced by counter-based Philox4x32-10: key = seed, counter = (particle, set, block), so
+// particle p of parameter set k sees the same stream whatever the launch geometry or the number of GPUs.  Parity is
+// distributional ("parity unpinned" for simulator numerics).
+//
+// Mapping: one CTA works on one parameter set at a time (its constants in registers, its RT/choice histogram in
+// shared memory, built with shared-memory atomics and flushed once per item); each thread runs one particle after
+// another without waiting for its warp neighbours (refill inside the step loop); bounds are evaluated in registers.
+#include <cstdio>
+
+#include "../../include/wfpt_b200.h"
+#include "common.cuh"
+
+namespace wfpt {
+namespace sim {
+
+constexpr int kSimBlock = 256;
+constexpr int kMaxBins = 4096;
+
+struct Args {
+    const float* theta;  // [n_sets][n_par]
+    int n_par;
+    int n_sets;
+    long long n_samples;       // particles per set in this launch
+    long long sample_offset;   // global index of this launch's first particle (multi-GPU particle sharding)
+    long long out_stride_samples;  // rows of the (n_samples_total, n_sets) output arrays written by this launch start at 0
+    float dt, max_t, s;
+    unsigned long long seed;
+    float* rts;                // [n_samples][n_sets] or nullptr
+    int* choices;              // same
+    unsigned int* hist;        // [n_sets][nbins][2] or nullptr
+    int nbins;
+    double hist_step;          // max_t_hist / (nbins - 1)
+    double hist_max_t;
+    unsigned long long* steps; // optional: total Euler steps
+    float* traj;               // optional: trajectory of (set 0, particle 0): [int(max_t/dt)+1]
+    int traj_len;
+    long long chunk;           // particles per work item
+    long long items_per_set;
+};
+
+// ---- Philox4x32-10 -------------------------------------------------------------------------------------------------------
+struct Philox {
+    unsigned int k0, k1;
+    uint4 ctr;
+    __device__ __forceinline__ uint4 next()
+    {
+        unsigned int c0 = ctr.x, c1 = ctr.y, c2 = ctr.z, c3 = ctr.w, a = k0, b = k1;
+#pragma unroll
+        for (int r = 0; r < 10; r++) {
+            const unsigned int h0 = __umulhi(0xD2511F53u, c0), l0 = 0xD2511F53u * c0;
+            const unsigned int h1 = __umulhi(0xCD9E8D57u, c2), l1 = 0xCD9E8D57u * c2;
+            c0 = h1 ^ c1 ^ a;
+            c1 = l1;
+            c2 = h0 ^ c3 ^ b;
+            c3 = l0;
+            a += 0x9E3779B9u;
+            b += 0xBB67AE85u;
+        }
+        ctr.w++;  // block counter
+        return make_uint4(c0, c1, c2, c3);
+    }
+};
+
+__device__ __forceinline__ float u01(unsigned int x) { return ((float)x + 0.5f) * 2.3283064365386963e-10f; }  // (0, 1)
+
+// Normal / uniform source of one particle: four normals per Philox block (two Box-Muller pairs).
+struct Stream {
+    Philox ph;
+    float buf[4];
+    int have;
+    __device__ __forceinline__ void start(unsigned long long seed, unsigned long long particle, unsigned int set)
+    {
+        ph.k0 = (unsigned int)seed;
+        ph.k1 = (unsigned int)(seed >> 32);
+        ph.ctr = make_uint4((unsigned int)particle, (unsigned int)(particle >> 32), set, 0u);
+        have = 0;
+    }
+    __device__ __forceinline__ void fill()
+    {
+        const uint4 r = ph.next();
+        const float r0 = sqrtf(-2.0f * __logf(u01(r.x))), r1 = sqrtf(-2.0f * __logf(u01(r.z)));
+        float s0, c0, s1, c1;
+        __sincosf(6.283185307179586f * u01(r.y), &s0, &c0);
+        __sincosf(6.283185307179586f * u01(r.w), &s1, &c1);
+        buf[0] = r0 * c0;
+        buf[1] = r0 * s0;
+        buf[2] = r1 * c1;
+        buf[3] = r1 * s1;
+        have = 4;
+    }
+    __device__ __forceinline__ float normal()
+    {
+        if (have == 0) fill();
+        have--;
+        // select without dynamic indexing
+        return have == 3 ? buf[0] : have == 2 ? buf[1] : have == 1 ? buf[2] : buf[3];
+    }
+    // four uniforms in (0,1) straight from a Philox block (does not disturb the normal buffer)
+    __device__ __forceinline__ float4 uniforms()
+    {
+        const uint4 r = ph.next();
+        return make_float4(u01(r.x), u01(r.y), u01(r.z), u01(r.w));
+    }
+};
+
+// Chambers-Mallows-Stuck draw as the reference writes it (cddm_data_simulation.pyx:28-40)
+__device__ __forceinline__ float stable_draw(float alpha, float U, float U2)
+{
+    const float u = 3.14159265358979f * (U - 0.5f);
+    const float w = -__logf(U2);
+    if (alpha == 1.0f) return __tanf(u);
+    return (__sinf(alpha * u) / __powf(__cosf(u), 1.0f / alpha)) * __powf(__cosf(u - alpha * u) / w, (1.0f - alpha) / alpha);
+}
+
+// ---- per-model constants --------------------------------------------------------------------------------------------------
+struct SetConst {
+    float v, a, z, t;
+    float p4, p5, p6;      // model-specific extras (theta columns 4..6)
+    float vdt;             // v * dt
+    float slope;           // angle: -sin(th)/cos(th)
+    float inv_beta, alpha; // weibull
+    float g;               // ornstein
+    float dt_alpha;        // levy: s * dt^(1/alpha)
+};
+
+template <int MODEL>
+__device__ __forceinline__ void load_set(SetConst& c, const float* __restrict__ th, const Args& A)
+{
+    c.v = th[0];
+    c.a = th[1];
+    c.z = th[2];
+    c.t = th[3];
+    c.p4 = A.n_par > 4 ? th[4] : 0.f;
+    c.p5 = A.n_par > 5 ? th[5] : 0.f;
+    c.p6 = A.n_par > 6 ? th[6] : 0.f;
+    c.slope = 0.f; c.inv_beta = 0.f; c.alpha = 0.f; c.g = 0.f; c.dt_alpha = 0.f;
+    if (MODEL == WFPT_SIM_ANGLE) c.slope = -sinf(c.p4) / cosf(c.p4);
+    if (MODEL == WFPT_SIM_WEIBULL) { c.alpha = c.p4; c.inv_beta = 1.0f / c.p5; }
+    if (MODEL == WFPT_SIM_ORNSTEIN) { c.g = th[3]; c.t = th[4]; }             // theta = v, a, z, g, t
+    if (MODEL == WFPT_SIM_LEVY) { c.alpha = th[3]; c.t = th[4]; c.dt_alpha = A.s * powf(A.dt, 1.0f / th[3]); }  // v, a, z, alpha, t
+    c.vdt = __fmul_rn(c.v, A.dt);
+}
+
+// Upper bound at step ix (time ts = ix*dt); lower bound is -b for the flexbound family and 0 for the [0,a] family.
+template <int MODEL>
+__device__ __forceinline__ float bound_at(const SetConst& c, float ts)
+{
+    if (MODEL == WFPT_SIM_ANGLE) return __fadd_rn(c.a, __fmul_rn(ts, c.slope));
+    if (MODEL == WFPT_SIM_WEIBULL) {
+        // a * exp(-(ts/beta)^alpha);  ts == 0 -> a
+        const float r = ts * c.inv_beta;
+        const float pw = (r > 0.f) ? exp2f(c.alpha * __log2f(r)) : 0.f;
+        return c.a * __expf(-pw);
+    }
+    return c.a;
+}
+
+template <int MODEL>
+struct Traits {
+    static constexpr bool zero_a = (MODEL == WFPT_SIM_DDM || MODEL == WFPT_SIM_FULL_DDM_BASE);  // bounds [0, a]
+    static constexpr bool moving = (MODEL == WFPT_SIM_ANGLE || MODEL == WFPT_SIM_WEIBULL);
+    static constexpr bool full = (MODEL == WFPT_SIM_FULL_DDM_BASE || MODEL == WFPT_SIM_FULL_DDM);
+    static constexpr bool sdv = (MODEL == WFPT_SIM_DDM_SDV);
+};
+
+// ---- the kernel ------------------------------------------------------------------------------------------------------------
+template <int MODEL>
+__global__ void __launch_bounds__(kSimBlock) sim_kernel(const Args A)
+{
+    extern __shared__ unsigned int s_hist[];  // [nbins][2] when A.hist
+    const int nh = A.hist ? A.nbins * 2 : 0;
+    const float sqrt_st = __fmul_rn(sqrtf(A.dt), A.s);
+    unsigned long long my_steps = 0;
+    const long long n_items = (long long)A.n_sets * A.items_per_set;
+
+    for (long long item = blockIdx.x; item < n_items; item += gridDim.x) {
+        const int set = (int)(item / A.items_per_set);
+        const long long beg = (item - (long long)set * A.items_per_set) * A.chunk;
+        const long long end = (beg + A.chunk < A.n_samples) ? beg + A.chunk : A.n_samples;
+        for (int i = threadIdx.x; i < nh; i += kSimBlock) s_hist[i] = 0u;
+        __syncthreads();
+
+        SetConst c;
+        load_set<MODEL>(c, A.theta + (size_t)set * A.n_par, A);
+
+        long long p = beg + threadIdx.x;   // particle (local index within this launch)
+        bool active = p < end;
+        Stream st;
+        float y = 0.f, tp = 0.f, fix = 0.f, drift = c.vdt, t_nd = c.t, b = c.a;
+        int ix = 0;
+        bool fresh = true;
+        while (active) {
+            if (fresh) {
+                // ---- start a particle ----
+                st.start(A.seed, (unsigned long long)(p + A.sample_offset), (unsigned int)set);
+                tp = 0.f;
+                fix = 0.f;
+                ix = 0;
+                drift = c.vdt;
+                t_nd = c.t;
+                b = bound_at<MODEL>(c, 0.f);
+                if (Traits<MODEL>::zero_a) y = __fmul_rn(c.z, c.a);
+                else y = __fadd_rn(-b, __fmul_rn(__fmul_rn(c.z, 2.f), b));
+                if (Traits<MODEL>::full) {
+                    // theta = v, a, z, t, sz, sv, st  (:228-235, :812-820)
+                    const float4 u = st.uniforms();
+                    drift = __fmul_rn(__fadd_rn(c.v, __fmul_rn(c.p5, st.normal())), A.dt);
+                    t_nd = __fadd_rn(c.t, __fmul_rn(__fmul_rn(2.f, u.x - 0.5f), c.p6));
+                    y = __fadd_rn(y, __fmul_rn(__fmul_rn(2.f, u.y - 0.5f), c.p4));
+                }
+                if (Traits<MODEL>::sdv) drift = __fmul_rn(__fadd_rn(c.v, __fmul_rn(c.p4, st.normal())), A.dt);
+                if (A.traj && set == 0 && p + A.sample_offset == 0) A.traj[0] = y;
+                fresh = false;
+            }
+            const float lo = Traits<MODEL>::zero_a ? 0.f : -b;
+            if (y >= lo && y <= b && tp <= A.max_t) {
+                // ---- one Euler step ----
+                float inc;
+                if (MODEL == WFPT_SIM_LEVY) {
+                    const float4 u = st.uniforms();
+                    inc = __fmul_rn(c.dt_alpha, stable_draw(c.alpha, u.x, u.y));
+                } else {
+                    inc = __fmul_rn(sqrt_st, st.normal());
+                }
+                float det = drift;
+                if (MODEL == WFPT_SIM_ORNSTEIN) det = __fmul_rn(__fsub_rn(c.v, __fmul_rn(c.g, y)), A.dt);
+                y = __fadd_rn(y, __fadd_rn(det, inc));
+                tp = __fadd_rn(tp, A.dt);
+                ix++;
+                if (Traits<MODEL>::moving) {
+                    fix += 1.0f;
+                    b = bound_at<MODEL>(c, __fmul_rn(fix, A.dt));
+                }
+                if (A.traj && set == 0 && p + A.sample_offset == 0 && ix < A.traj_len) A.traj[ix] = y;
+            } else {
+                // ---- record and move on ----
+                my_steps += (unsigned long long)ix;
+                const float rt = __fadd_rn(tp, t_nd);
+                int choice;
+                if (Traits<MODEL>::zero_a) choice = (y < 0.f) ? 0 : 1;
+                else choice = (y > 0.f) - (y < 0.f);
+                if (A.rts) {
+                    const size_t o = (size_t)p * A.n_sets + set;
+                    A.rts[o] = rt;
+                    A.choices[o] = choice;
+                }
+                if (A.hist) {
+                    const int col = Traits<MODEL>::zero_a ? choice : (choice > 0 ? 1 : (choice < 0 ? 0 : -1));
+                    if (col >= 0) {
+                        // np.histogram on edges linspace(0, max_t, nbins) + [inf] (basic_simulator_old.py:99-114)
+                        const double r = (double)rt;
+                        int bin = (int)(r / A.hist_step);
+                        if (bin > A.nbins - 1) bin = A.nbins - 1;
+                        if (bin < 0) bin = 0;
+                        const double e_lo = (bin == A.nbins - 1) ? A.hist_max_t : bin * A.hist_step;
+                        if (r < e_lo && bin > 0) bin--;
+                        else if (bin < A.nbins - 1) {
+                            const double e_hi = (bin + 1 == A.nbins - 1) ? A.hist_max_t : (bin + 1) * A.hist_step;
+                            if (r >= e_hi) bin++;
+                        }
+                        if (r >= 0.0) atomicAdd(&s_hist[bin * 2 + col], 1u);
+                    }
+                }
+                p += kSimBlock;
+                active = p < end;
+                fresh = true;
+            }
+        }
+        __syncthreads();
+        if (A.hist) {
+            unsigned int* g = A.hist + (size_t)set * nh;
+            for (int i = threadIdx.x; i < nh; i += kSimBlock) {
+                const unsigned int v = s_hist[i];
+                if (v) atomicAdd(&g[i], v);
+            }
+        }
+        __syncthreads();
+    }
+    if (A.steps) {
+        // CTA sum of the step counts, one global atomic per CTA
+        __shared__ unsigned long long s_steps[kSimBlock / 32];
+        for (int off = 16; off > 0; off >>= 1) my_steps += __shfl_down_sync(0xffffffffu, my_steps, off);
+        if ((threadIdx.x & 31) == 0) s_steps[threadIdx.x >> 5] = my_steps;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            unsigned long long tot = 0;
+            for (int i = 0; i < kSimBlock / 32; i++) tot += s_steps[i];
+            atomicAdd(A.steps, tot);
+        }
+    }
+}
+
+template <int MODEL>
+static cudaError_t launch(const Args& A, int blocks, cudaStream_t stream)
+{
+    const size_t smem = A.hist ? sizeof(unsigned int) * 2 * (size_t)A.nbins : 0;
+    sim_kernel<MODEL><<<blocks, kSimBlock, smem, stream>>>(A);
+    return cudaGetLastError();
+}
+
+static int n_params_of(int model)
+{
+    switch (model) {
+        case WFPT_SIM_DDM: case WFPT_SIM_DDM_FLEXBOUND: return 4;
+        case WFPT_SIM_ANGLE: case WFPT_SIM_DDM_SDV: case WFPT_SIM_ORNSTEIN: case WFPT_SIM_LEVY: return 5;
+        case WFPT_SIM_WEIBULL: return 6;
+        case WFPT_SIM_FULL_DDM_BASE: case WFPT_SIM_FULL_DDM: return 7;
+        default: return -1;
+    }
+}
+
+}  // namespace sim
+}  // namespace wfpt
+
+using namespace wfpt;
+
+extern "C" int wfpt_sim_n_params(int model) { return sim::n_params_of(model); }
+
+extern "C" int wfpt_sim_run(int model, const float* d_theta, int n_par, int n_sets, int64_t n_samples, int64_t sample_offset,
+                            float delta_t, float max_t, float s, uint64_t seed, float* d_rts, int32_t* d_choices,
+                            uint32_t* d_hist, int nbins, float hist_max_t, uint64_t* d_steps, float* d_traj, int traj_len,
+                            void* stream)
+{
+    const int want = sim::n_params_of(model);
+    if (want < 0) { char m[96]; snprintf(m, sizeof m, "wfpt_sim_run: unknown model id %d", model); return api_fail(m); }
+    if (n_par != want) { char m[128]; snprintf(m, sizeof m, "wfpt_sim_run: model %d takes %d parameters per set, got %d", model, want, n_par); return api_fail(m); }
+    if (n_sets < 0 || n_samples < 0) return api_fail("wfpt_sim_run: negative size");
+    if (n_sets == 0 || n_samples == 0) return 0;
+    if (!d_theta) return api_fail("wfpt_sim_run: null theta");
+    if ((d_rts == nullptr) != (d_choices == nullptr)) return api_fail("wfpt_sim_run: rts and choices must be given together");
+    if (!d_rts && !d_hist) return api_fail("wfpt_sim_run: nothing to write (no rts/choices and no histogram)");
+    if (!(delta_t > 0.f) || !(max_t > 0.f)) return api_fail("wfpt_sim_run: delta_t and max_t must be positive");
+    if (d_hist && (nbins < 2 || nbins > sim::kMaxBins)) return api_fail("wfpt_sim_run: nbins must be in [2, 4096]");
+    if (d_hist && !(hist_max_t > 0.f)) return api_fail("wfpt_sim_run: hist_max_t must be positive");
+
+    sim::Args A;
+    A.theta = d_theta; A.n_par = n_par; A.n_sets = n_sets; A.n_samples = n_samples; A.sample_offset = sample_offset;
+    A.out_stride_samples = n_samples;
+    A.dt = delta_t; A.max_t = max_t; A.s = s; A.seed = seed; A.rts = d_rts; A.choices = d_choices;
+    A.hist = d_hist; A.nbins = d_hist ? nbins : 0;
+    A.hist_max_t = (double)hist_max_t;
+    A.hist_step = d_hist ? (double)hist_max_t / (double)(nbins - 1) : 1.0;
+    A.steps = (unsigned long long*)d_steps;
+    A.traj = d_traj; A.traj_len = traj_len;
+
+    int dev = 0, sms = 148;
+    if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    // work items: a set is cut into chunks so that the grid fills the machine (>= 4 CTAs per SM) while every thread
+    // still runs many particles back to back (that is what hides the spread of first-passage times)
+    const long long target_items = (long long)sms * 8;
+    long long per_set = (target_items + n_sets - 1) / n_sets;
+    const long long max_per_set = (n_samples + sim::kSimBlock - 1) / sim::kSimBlock;  // >= 1 particle per thread
+    if (per_set > max_per_set) per_set = max_per_set;
+    if (per_set < 1) per_set = 1;
+    long long chunk = (n_samples + per_set - 1) / per_set;
+    const long long cap = (long long)sim::kSimBlock * 64;                             // <= 64 particles per thread per item
+    if (chunk > cap) chunk = cap;
+    A.chunk = chunk;
+    A.items_per_set = (n_samples + chunk - 1) / chunk;
+    const long long n_items = A.items_per_set * n_sets;
+    const int blocks = (int)(n_items < (long long)sms * 16 ? n_items : (long long)sms * 16);
+
+    cudaError_t e;
+    cudaStream_t st = (cudaStream_t)stream;
+    switch (model) {
+        case WFPT_SIM_DDM: e = sim::launch<WFPT_SIM_DDM>(A, blocks, st); break;
+        case WFPT_SIM_FULL_DDM_BASE: e = sim::launch<WFPT_SIM_FULL_DDM_BASE>(A, blocks, st); break;
+        case WFPT_SIM_DDM_FLEXBOUND: e = sim::launch<WFPT_SIM_DDM_FLEXBOUND>(A, blocks, st); break;
+        case WFPT_SIM_ANGLE: e = sim::launch<WFPT_SIM_ANGLE>(A, blocks, st); break;
+        case WFPT_SIM_WEIBULL: e = sim::launch<WFPT_SIM_WEIBULL>(A, blocks, st); break;
+        case WFPT_SIM_FULL_DDM: e = sim::launch<WFPT_SIM_FULL_DDM>(A, blocks, st); break;
+        case WFPT_SIM_DDM_SDV: e = sim::launch<WFPT_SIM_DDM_SDV>(A, blocks, st); break;
+        case WFPT_SIM_ORNSTEIN: e = sim::launch<WFPT_SIM_ORNSTEIN>(A, blocks, st); break;
+        default: e = sim::launch<WFPT_SIM_LEVY>(A, blocks, st); break;
+    }
+    if (e != cudaSuccess) return api_fail(cudaGetErrorString(e));
+    count_launch(1);
+    return 0;
+}
+
+#define SCK(call)                                                      \
+    do {                                                               \
+        cudaError_t e__ = (call);                                      \
+        if (e__ != cudaSuccess) { rc = api_fail(cudaGetErrorString(e__)); goto done; } \
+    } while (0)
+
+extern "C" int wfpt_sim_run_host(int model, const float* h_theta, int n_par, int n_sets, int64_t n_samples, int64_t sample_offset,
+                                 float delta_t, float max_t, float s, uint64_t seed, float* h_rts, int32_t* h_choices,
+                                 uint32_t* h_hist, int nbins, float hist_max_t, uint64_t* h_steps, float* h_traj, int traj_len)
+{
+    if (n_sets <= 0 || n_samples <= 0) return wfpt_sim_run(model, nullptr, n_par, n_sets, n_samples, sample_offset, delta_t, max_t, s, seed,
+                                                           nullptr, nullptr, nullptr, nbins, hist_max_t, nullptr, nullptr, 0, nullptr);
+    int rc = 0;
+    float *d_theta = nullptr, *d_rts = nullptr, *d_traj = nullptr;
+    int32_t* d_ch = nullptr;
+    uint32_t* d_hist = nullptr;
+    uint64_t* d_steps = nullptr;
+    const size_t n_out = (size_t)n_samples * (size_t)n_sets;
+    const size_t hist_n = (size_t)n_sets * (size_t)(nbins > 0 ? nbins : 0) * 2;
+    SCK(cudaMalloc(&d_theta, sizeof(float) * (size_t)n_sets * n_par));
+    SCK(cudaMemcpy(d_theta, h_theta, sizeof(float) * (size_t)n_sets * n_par, cudaMemcpyHostToDevice));
+    if (h_rts) { SCK(cudaMalloc(&d_rts, sizeof(float) * n_out)); SCK(cudaMalloc(&d_ch, sizeof(int32_t) * n_out)); }
+    if (h_hist) { SCK(cudaMalloc(&d_hist, sizeof(uint32_t) * hist_n)); SCK(cudaMemset(d_hist, 0, sizeof(uint32_t) * hist_n)); }
+    if (h_steps) { SCK(cudaMalloc(&d_steps, sizeof(uint64_t))); SCK(cudaMemset(d_steps, 0, sizeof(uint64_t))); }
+    if (h_traj && traj_len > 0) {
+        SCK(cudaMalloc(&d_traj, sizeof(float) * (size_t)traj_len));
+        // the reference pre-fills the trajectory with -999 (cddm_data_simulation.pyx:318-319)
+        SCK(cudaMemcpy(d_traj, h_traj, sizeof(float) * (size_t)traj_len, cudaMemcpyHostToDevice));
+    }
+    rc = wfpt_sim_run(model, d_theta, n_par, n_sets, n_samples, sample_offset, delta_t, max_t, s, seed, d_rts, d_ch, d_hist, nbins,
+                      hist_max_t, d_steps, d_traj, traj_len, nullptr);
+    if (rc) goto done;
+    SCK(cudaDeviceSynchronize());
+    if (h_rts) {
+        SCK(cudaMemcpy(h_rts, d_rts, sizeof(float) * n_out, cudaMemcpyDeviceToHost));
+        SCK(cudaMemcpy(h_choices, d_ch, sizeof(int32_t) * n_out, cudaMemcpyDeviceToHost));
+    }
+    if (h_hist) SCK(cudaMemcpy(h_hist, d_hist, sizeof(uint32_t) * hist_n, cudaMemcpyDeviceToHost));
+    if (h_steps) SCK(cudaMemcpy(h_steps, d_steps, sizeof(uint64_t), cudaMemcpyDeviceToHost));
+    if (d_traj) SCK(cudaMemcpy(h_traj, d_traj, sizeof(float) * (size_t)traj_len, cudaMemcpyDeviceToHost));
+done:
+    cudaFree(d_theta); cudaFree(d_rts); cudaFree(d_ch); cudaFree(d_hist); cudaFree(d_steps); cudaFree(d_traj);
+    return rc;
+}

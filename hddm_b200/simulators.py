@@ -1,0 +1,191 @@
+"""Drop-in for `hddm.simulators.simulator` (/root/reference/hddm/simulators/basic_simulator.py:6-36), which forwards
+to the compiled simulators of un-vendored `ssm-simulators`; here the walks run on the GPU (hddm_b200/csrc/sim.cu).
+
+Behaviour follows the in-tree ancestor of that dispatch (/root/reference/graveyard/basic_simulator_old.py:168-1073):
+theta coercion to float32 and 2-D (:208-224), `s = 0 if no_noise else 1` (:227-230), theta column order per model,
+output squeeze rules (:1041-1045), `metadata["model"]` (:1047), RT x choice binning (:70-119, :1049-1053).
+Metadata carries every name in the model's parameter list plus the keys the reference's simulators return
+(/root/reference/src/cddm_data_simulation.pyx:364-375, :540-553).
+
+There is no CPU path: without the built library / a GPU every call raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from . import _lib
+
+# name -> (model id, theta columns, reference simulator name, boundary function name, multiplicative, choices)
+_M = {
+    "ddm_hddm_base": (0, ["v", "a", "z", "t"], "ddm", "constant", True, [0, 1]),
+    "full_ddm_hddm_base": (1, ["v", "a", "z", "t", "sz", "sv", "st"], "full_ddm_hddm_base", "constant", True, [0, 1]),
+    "ddm": (2, ["v", "a", "z", "t"], "ddm_flexbound", "constant", True, [-1, 1]),
+    "angle": (3, ["v", "a", "z", "t", "theta"], "ddm_flexbound", "angle", False, [-1, 1]),
+    "weibull": (4, ["v", "a", "z", "t", "alpha", "beta"], "ddm_flexbound", "weibull_cdf", True, [-1, 1]),
+    "full_ddm": (5, ["v", "a", "z", "t", "sz", "sv", "st"], "full_ddm", "constant", True, [-1, 1]),
+    "ddm_sdv": (6, ["v", "a", "z", "t", "sv"], "ddm_sdv", "constant", True, [-1, 1]),
+    "ornstein": (7, ["v", "a", "z", "g", "t"], "ornstein_uhlenbeck", "constant", True, [-1, 1]),
+    "levy": (8, ["v", "a", "z", "alpha", "t"], "levy_flexbound", "constant", True, [-1, 1]),
+}
+_ALIAS = {"ddm_legacy": "ddm_hddm_base", "full_ddm_legacy": "full_ddm_hddm_base", "test": "ddm",
+          "weibull_cdf": "weibull"}
+_NEXT = ("gamma_drift", "gamma_drift_angle", "ds_conflict_drift", "ds_conflict_drift_angle", "race_model", "lca",
+         "ddm_seq2", "ddm_par2", "ddm_mic2_adj", "tradeoff")
+
+# minimal stand-in for the part of hddm.model_config the simulator boundary needs (params and choices per model)
+model_config = {name: {"params": list(cols), "choices": list(ch), "boundary_name": bnd, "boundary_multiplicative": mult}
+                for name, (_, cols, _, bnd, mult, ch) in _M.items()}
+
+
+def _resolve(model):
+    name = _ALIAS.get(model, model)
+    if name not in _M:
+        if any(model.startswith(p) for p in _NEXT):
+            raise NotImplementedError(f"simulator model '{model}' is a next-row model (SURVEY 8(f) rank 4), not built yet")
+        raise ValueError(f"unknown simulator model '{model}'")
+    return name
+
+
+def _coerce_theta(theta, name):
+    """basic_simulator_old.py:208-224."""
+    cols = _M[name][1]
+    if isinstance(theta, list):
+        theta = np.asarray(theta).astype(np.float32)
+    elif isinstance(theta, np.ndarray):
+        theta = theta.astype(np.float32)
+    elif hasattr(theta, "columns") and hasattr(theta, "values"):  # pandas DataFrame
+        theta = theta[cols].values.astype(np.float32)
+    elif hasattr(theta, "numpy"):  # torch tensor
+        theta = theta.detach().cpu().numpy().astype(np.float32)
+    else:
+        raise TypeError(f"theta of type {type(theta).__name__} is not supported")
+    if theta.ndim < 2:
+        theta = np.expand_dims(theta, axis=0)
+    if theta.ndim != 2 or theta.shape[1] != len(cols):
+        raise ValueError(f"model '{name}' takes theta with {len(cols)} columns {cols}, got shape {theta.shape}")
+    return np.ascontiguousarray(theta)
+
+
+def _boundary_array(name, theta_row, delta_t, max_t):
+    """The `boundary` metadata entry: the last parameter set's bound on t_s = arange(0, max_t + dt, dt), float32
+    (cddm_data_simulation.pyx:491-509; the reference overwrites one array per trial, so the last one survives)."""
+    t_s = np.arange(0, max_t + delta_t, delta_t).astype(np.float32)
+    a = theta_row[1]
+    bnd = _M[name][3]
+    if bnd == "angle":
+        th = theta_row[4]
+        return np.add(a, np.multiply(t_s, (-np.sin(th) / np.cos(th)))).astype(np.float32)
+    if bnd == "weibull_cdf":
+        alpha, beta = theta_row[4], theta_row[5]
+        return np.multiply(a, np.exp(-np.power(np.divide(t_s, beta), alpha))).astype(np.float32)
+    return np.multiply(a, np.ones_like(t_s)).astype(np.float32)
+
+
+def _seed(random_state):
+    if random_state is None:
+        return int(np.random.randint(0, 2 ** 62))  # np.random.seed(...) upstream makes the run reproducible
+    return int(random_state) & (2 ** 64 - 1)
+
+
+def _run(name, theta, n_samples, delta_t, max_t, s, seed, want_raw, nbins, sample_offset=0, want_traj=False):
+    L = _lib.load()
+    mid = _M[name][0]
+    n_sets, n_par = theta.shape
+    rts = choices = hist = traj = None
+    steps = np.zeros(1, dtype=np.uint64)
+    if want_raw:
+        rts = np.empty((n_samples, n_sets, 1), dtype=np.float32)
+        choices = np.empty((n_samples, n_sets, 1), dtype=np.int32)
+    if nbins:
+        hist = np.zeros((n_sets, nbins, 2), dtype=np.uint32)
+    traj_len = 0
+    if want_traj:
+        traj_len = int(max_t / delta_t) + 1
+        traj = np.full((traj_len, 1), -999, dtype=np.float32)
+
+    def p(a):
+        return a.ctypes.data_as(C.c_void_p) if a is not None else None
+
+    _lib.check(L.wfpt_sim_run_host(mid, p(theta), n_par, n_sets, int(n_samples), int(sample_offset), float(delta_t),
+                                   float(max_t), float(s), seed, p(rts), p(choices), p(hist), int(nbins or 0),
+                                   float(max_t), p(steps), p(traj), traj_len))
+    return rts, choices, hist, traj, int(steps[0])
+
+
+def simulator(theta, model="angle", n_samples=1000, delta_t=0.001, max_t=20, no_noise=False, bin_dim=None,
+              bin_pointwise=False, random_state=None, **ignored):
+    """(rts, choices, metadata), or (histogram, metadata) when bin_dim > 0 -- see the module docstring.
+
+    rts float32 / choices int32 with shape (n_samples, n_trials, 1); n_trials == 1 -> (n_samples, 1);
+    n_trials > 1 and n_samples == 1 -> (n_trials, 1).  `random_state` (an integer) fixes the Philox seed; when it is
+    None the seed is drawn from NumPy's global RNG."""
+    name = _resolve(model)
+    theta = _coerce_theta(theta, name)
+    n_trials = theta.shape[0]
+    n_samples = int(n_samples)
+    s = 0.0 if no_noise else 1.0
+    seed = _seed(random_state)
+    binned = bin_dim is not None and bin_dim != 0
+    if binned and bin_dim < 0:
+        return "invalid bin_dim"
+    if binned and bin_pointwise:
+        raise NotImplementedError("pointwise binning is a next-row item (SURVEY 8(f) rank 4)")
+    if binned and n_trials > 1:
+        return "currently binned outputs not implemented for multi-trial simulators"
+
+    rts, choices, hist, traj, steps = _run(name, theta, n_samples, delta_t, max_t, s, seed, True,
+                                           int(bin_dim) if binned else 0, want_traj=True)
+    _, cols, sim_name, bnd, mult, ch = _M[name]
+    meta = {c: theta[:, i].copy() for i, c in enumerate(cols)}
+    meta.update({"s": s, "delta_t": delta_t, "max_t": max_t, "n_samples": n_samples, "simulator": sim_name,
+                 "boundary_fun_type": bnd, "possible_choices": list(ch), "trajectory": traj, "model": model,
+                 "n_euler_steps": steps, "seed": seed})
+    if sim_name not in ("ddm", "full_ddm_hddm_base"):
+        meta["boundary"] = _boundary_array(name, theta[-1], delta_t, max_t)
+    if binned:
+        return (hist[0].astype(np.float64) / n_samples, meta)
+    if n_trials == 1:
+        rts, choices = np.squeeze(rts, axis=1), np.squeeze(choices, axis=1)
+    elif n_samples == 1:
+        rts, choices = np.squeeze(rts, axis=0), np.squeeze(choices, axis=0)
+    return (rts, choices, meta)
+
+
+def simulate_histograms(theta, model="angle", n_samples=100000, nbins=512, delta_t=0.001, max_t=20, no_noise=False,
+                        random_state=None, sample_offset=0):
+    """RT x choice count histograms for many parameter sets at once: uint32 [n_sets, nbins, 2] and the total number of
+    Euler steps.  The per-set rule is bin_simulator_output's (basic_simulator_old.py:70-119) with freq_cnt=True; the
+    reference only offers it for one parameter set per call.  No per-particle output is materialised.
+    `sample_offset` shifts the particle indices that key the random streams (ranks sharding particles pass theirs and
+    merge with hddm_b200.distributed.merge_histograms)."""
+    name = _resolve(model)
+    theta = _coerce_theta(theta, name)
+    _, _, hist, _, steps = _run(name, theta, int(n_samples), delta_t, max_t, 0.0 if no_noise else 1.0,
+                                _seed(random_state), False, int(nbins), sample_offset=sample_offset)
+    return hist, steps
+
+
+def bin_simulator_output(out, bin_dt=0.04, nbins=0, max_t=-1, freq_cnt=False):
+    """Host restatement of basic_simulator_old.py:70-119 for already-materialised (rts, choices, metadata)."""
+    if max_t == -1:
+        max_t = out[2]["max_t"]
+    if nbins == 0:
+        nbins = int(max_t / bin_dt)
+    bins = np.zeros(nbins + 1)
+    bins[:nbins] = np.linspace(0, max_t, nbins)
+    bins[nbins] = np.inf
+    counts = np.zeros((nbins, len(out[2]["possible_choices"])))
+    for cnt, choice in enumerate(out[2]["possible_choices"]):
+        counts[:, cnt] = np.histogram(out[0][out[1] == choice], bins=bins)[0]
+    if not freq_cnt:
+        counts = counts / out[2]["n_samples"]
+    return counts
+
+
+def _smoke():
+    rts, ch, meta = simulator([1.0, 1.0, 0.5, 0.3, 0.2], model="angle", n_samples=20000, random_state=1)
+    assert rts.shape == (20000, 1) and ch.shape == (20000, 1) and meta["possible_choices"] == [-1, 1]
+    p_up = float(np.mean(ch == 1))
+    assert 0.80 < p_up < 0.90 and 0.8 < float(rts.mean()) < 1.1, (p_up, float(rts.mean()))

@@ -112,6 +112,39 @@ int wfpt_like_rlddm_host(const double* h_x, const int64_t* h_response, const dou
                          double st, double err, int n_st, int n_sz, int use_adaptive, double simps_err,
                          double p_outlier, double w_outlier, int variant, double* h_out);
 
+/* Simulators ------------------------------------------------------------------------------------------------- */
+
+/* Model ids: which Euler-Maruyama simulator of src/cddm_data_simulation.pyx runs, and the theta column order the
+ * reference's dispatch uses for it (graveyard/basic_simulator_old.py:168-480, hddm/model_config.py). */
+#define WFPT_SIM_DDM 0            /* ddm :294-375                 theta = v, a, z, t                bounds [0,a], choices 0/1  */
+#define WFPT_SIM_FULL_DDM_BASE 1  /* full_ddm_hddm_base :174-284  theta = v, a, z, t, sz, sv, st    bounds [0,a], choices 0/1  */
+#define WFPT_SIM_DDM_FLEXBOUND 2  /* ddm_flexbound :454-553, constant bound  theta = v, a, z, t     bounds +-a,  choices -1/1  */
+#define WFPT_SIM_ANGLE 3          /* ddm_flexbound, angle bound   theta = v, a, z, t, theta                                    */
+#define WFPT_SIM_WEIBULL 4        /* ddm_flexbound, Weibull bound theta = v, a, z, t, alpha, beta                              */
+#define WFPT_SIM_FULL_DDM 5       /* full_ddm :747-869            theta = v, a, z, t, sz, sv, st                               */
+#define WFPT_SIM_DDM_SDV 6        /* ddm_sdv :876-994             theta = v, a, z, t, sv                                       */
+#define WFPT_SIM_ORNSTEIN 7       /* ornstein_uhlenbeck :1119-1219  theta = v, a, z, g, t                                      */
+#define WFPT_SIM_LEVY 8           /* levy_flexbound :642-741      theta = v, a, z, alpha, t                                    */
+
+/* Parameters per set of a model id, or -1 for an unknown id. */
+int wfpt_sim_n_params(int model);
+
+/* n_samples particles for each of n_sets parameter sets (the reference's "n_trials" axis).  theta is float32
+ * [n_sets][n_par].  Outputs, each optional (NULL): rts float32 / choices int32, both [n_samples][n_sets] (the
+ * reference's (n_samples, n_trials, 1) arrays); hist uint32 [n_sets][nbins][2] RT x choice counts, ADDED to what the
+ * buffer holds, with the bin edges of bin_simulator_output (graveyard/basic_simulator_old.py:70-119): nbins edges
+ * linspace(0, hist_max_t, nbins) plus +inf, column 0 = lower / first choice, column 1 = upper; steps: total Euler steps
+ * (added); traj: path of particle 0 of set 0 (float32[traj_len], caller pre-fills with -999 like the reference).
+ * Random numbers: Philox4x32-10 keyed by `seed`, counter = (sample_offset + particle index, set): results do not depend
+ * on launch geometry, and ranks that shard particles pass their global offset in `sample_offset`.
+ * Replaces the compiled simulators behind hddm.simulators.simulator (hddm/simulators/basic_simulator.py:6-36). */
+int wfpt_sim_run(int model, const float* d_theta, int n_par, int n_sets, int64_t n_samples, int64_t sample_offset,
+                 float delta_t, float max_t, float s, uint64_t seed, float* d_rts, int32_t* d_choices, uint32_t* d_hist,
+                 int nbins, float hist_max_t, uint64_t* d_steps, float* d_traj, int traj_len, void* stream);
+int wfpt_sim_run_host(int model, const float* h_theta, int n_par, int n_sets, int64_t n_samples, int64_t sample_offset,
+                      float delta_t, float max_t, float s, uint64_t seed, float* h_rts, int32_t* h_choices,
+                      uint32_t* h_hist, int nbins, float hist_max_t, uint64_t* h_steps, float* h_traj, int traj_len);
+
 #ifdef __cplusplus
 }
 #endif

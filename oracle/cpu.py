@@ -242,6 +242,19 @@ def gen_rts_from_cdf(v, sv, a, z, sz, t, st, samples=1000, cdf_lb=-6, cdf_ub=6, 
     return rt + np.sign(rt) * delay
 
 
+def sim_run(model_id, theta, n_samples, delta_t=0.001, max_t=20.0, s=1.0, seed=0):
+    """(rts float32[n_samples, n_sets], choices int32[n_samples, n_sets]) from oracle/sim_oracle.c."""
+    theta = np.ascontiguousarray(np.atleast_2d(np.asarray(theta, dtype=np.float32)))
+    n_sets, n_par = theta.shape
+    rts = np.empty((n_samples, n_sets), dtype=np.float32)
+    ch = np.empty((n_samples, n_sets), dtype=np.int32)
+    rc = lib().orc_sim_run(model_id, theta.ctypes.data_as(C.POINTER(C.c_float)), n_par, n_sets, n_samples, delta_t, max_t,
+                           s, seed, rts.ctypes.data_as(C.POINTER(C.c_float)), ch.ctypes.data_as(C.POINTER(C.c_int32)))
+    if rc:
+        raise ValueError(f"orc_sim_run failed ({rc})")
+    return rts, ch
+
+
 def nodes_reset():
     lib().orc_nodes_reset()
 

@@ -1,0 +1,114 @@
+/*
+ * oracle/sim_oracle.c -- CPU restatement of HDDM's Euler-Maruyama simulators.  TEST INFRASTRUCTURE ONLY
+ * (same rules as wfpt_oracle.c: nothing under hddm_b200/ may load or call it).
+ *
+ * Follows /root/reference/src/cddm_data_simulation.pyx, float32 state and accumulated float32 time included:
+ *   model 0 ddm :294-375            1 full_ddm_hddm_base :174-284     2 ddm_flexbound (constant bound) :454-553
+ *   model 3 ddm_flexbound + angle bound, 4 + Weibull bound (graveyard/boundary_functions.py:18-28, :50-63; the
+ *           boundary table b[ix] = a (+|*) f(t_s[ix]) is built per parameter set as the reference does, :491-509)
+ *   model 5 full_ddm :747-869       6 ddm_sdv :876-994   7 ornstein_uhlenbeck :1119-1219   8 levy_flexbound :642-741
+ * Gaussian draws: Marsaglia polar method as in :48-60; alpha-stable draws: :28-40.  The RNG is xoshiro256** instead
+ * of C rand(), so results agree with the reference in distribution, not draw by draw.
+ *
+ * Parity pinning: the reference's own tests pin only shapes and metadata keys for simulators
+ * (hddm/tests/test_simulators.py:65-87) -> PARITY UNPINNED for simulator numerics.  tests/test_sim_oracle.py checks
+ * this port distributionally (two-sample KS on RTs, choice-probability intervals) against the reference's Cython
+ * compiled unmodified into oracle/_ref, and against the analytic WFPT for the constant-bound DDM.
+ */
+#include <math.h>
+#include <stdint.h>
+#include <stdlib.h>
+
+#ifndef M_PI
+#define M_PI 3.14159265358979323846
+#endif
+#ifndef M_PI_2
+#define M_PI_2 1.57079632679489661923
+#endif
+
+typedef struct { uint64_t s[4]; } rng_t;
+static inline uint64_t rotl(uint64_t x, int k) { return (x << k) | (x >> (64 - k)); }
+static uint64_t splitmix(uint64_t* x) { uint64_t z = (*x += 0x9e3779b97f4a7c15ULL); z = (z ^ (z >> 30)) * 0xbf58476d1ce4e5b9ULL; z = (z ^ (z >> 27)) * 0x94d049bb133111ebULL; return z ^ (z >> 31); }
+static void rng_seed(rng_t* r, uint64_t seed) { for (int i = 0; i < 4; i++) r->s[i] = splitmix(&seed); }
+static inline uint64_t rng_next(rng_t* r)
+{
+    const uint64_t res = rotl(r->s[1] * 5, 7) * 9, t = r->s[1] << 17;
+    r->s[2] ^= r->s[0]; r->s[3] ^= r->s[1]; r->s[1] ^= r->s[2]; r->s[0] ^= r->s[3]; r->s[2] ^= t; r->s[3] = rotl(r->s[3], 45);
+    return res;
+}
+/* :21-23 random_uniform: a float in [0, 1] */
+static inline float random_uniform(rng_t* r) { return (float)((double)(rng_next(r) >> 11) * (1.0 / 9007199254740992.0)); }
+/* :48-60 random_gaussian (polar method), float32 arithmetic */
+static float random_gaussian(rng_t* r)
+{
+    float x1, x2, w = 2.0f;
+    while (w >= 1.0f) {
+        x1 = 2.0f * random_uniform(r) - 1.0f;
+        x2 = 2.0f * random_uniform(r) - 1.0f;
+        w = x1 * x1 + x2 * x2;
+    }
+    w = (float)pow((-2.0 * log(w)) / w, 0.5);
+    return x1 * w;
+}
+/* :28-40 random_stable */
+static float random_stable(rng_t* r, float alpha)
+{
+    float u = (float)(M_PI * (random_uniform(r) - 0.5));
+    float w = (float)(-log(random_uniform(r)));
+    if (alpha == 1.0f) return (float)((1.0 / M_PI_2) * (M_PI_2 * tan(u)));
+    return (float)((sin(alpha * u) / (pow(cos(u), 1 / alpha))) * pow(cos(u - (alpha * u)) / w, (1.0 - alpha) / alpha));
+}
+static inline int sgn(float x) { return (x > 0) - (x < 0); }
+
+int orc_sim_run(int model, const float* theta, int n_par, int n_sets, int64_t n_samples, float dt, float max_t, float s,
+                uint64_t seed, float* rts, int32_t* choices)
+{
+    static const int npar[9] = {4, 7, 4, 5, 6, 7, 5, 5, 5};
+    if (model < 0 || model > 8 || n_par != npar[model]) return 1;
+    rng_t R;
+    rng_seed(&R, seed);
+    const float sqrt_st = (float)sqrt(dt) * s;
+    const int nb = (int)((max_t / dt) + 1) + 2;
+    float* b = (float*)malloc(sizeof(float) * (size_t)(nb + 1));
+    if (!b) return 2;
+    for (int k = 0; k < n_sets; k++) {
+        const float* th = theta + (size_t)k * n_par;
+        const float v = th[0], a = th[1], z = th[2];
+        float t = th[3], g = 0, alpha = 0, dt_alpha = 0;
+        if (model == 7) { g = th[3]; t = th[4]; }
+        if (model == 8) { alpha = th[3]; t = th[4]; dt_alpha = (float)(s * pow(dt, 1.0 / alpha)); }
+        const int zero_a = (model == 0 || model == 1);
+        /* boundary table on t_s = arange(0, max_t + dt, dt).astype(float32)  (:489-509) */
+        for (int ix = 0; ix <= nb; ix++) {
+            const float ts = (float)((double)ix * (double)dt);
+            if (model == 3) b[ix] = a + ts * (-sinf(th[4]) / cosf(th[4]));
+            else if (model == 4) b[ix] = (float)(a * exp(-pow((double)ts / th[5], (double)th[4])));
+            else b[ix] = a;
+        }
+        for (int64_t n = 0; n < n_samples; n++) {
+            float y = zero_a ? z * a : (-1) * b[0] + (z * 2 * b[0]);
+            float drift = v * dt, t_nd = t;
+            if (model == 1 || model == 5) {
+                const float sz = th[4], sv = th[5], st = th[6];
+                drift = (v + sv * random_gaussian(&R)) * dt;
+                t_nd = t + (2 * (random_uniform(&R) - 0.5f) * st);
+                y += 2 * (random_uniform(&R) - 0.5f) * sz;
+            }
+            if (model == 6) drift = (v + th[4] * random_gaussian(&R)) * dt;
+            float tp = 0.0f;
+            int ix = 0;
+            while ((zero_a ? (y >= 0 && y <= a) : (y >= (-1) * b[ix] && y <= b[ix])) && tp <= max_t) {
+                if (model == 8) y += (v * dt) + (dt_alpha * random_stable(&R, alpha));
+                else if (model == 7) y += ((v - (g * y)) * dt) + sqrt_st * random_gaussian(&R);
+                else y += drift + (sqrt_st * random_gaussian(&R));
+                tp += dt;
+                ix++;
+            }
+            const size_t o = (size_t)n * n_sets + k;
+            rts[o] = tp + t_nd;
+            choices[o] = zero_a ? (y < 0 ? 0 : 1) : sgn(y);
+        }
+    }
+    free(b);
+    return 0;
+}

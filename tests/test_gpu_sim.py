@@ -1,0 +1,139 @@
+"""GPU tests of the simulators (run with -m gpu): the CUDA kernels, through the C ABI / the simulator() drop-in,
+against the CPU oracle port (distributional: two-sample KS on RTs, overlapping choice-probability intervals), the
+analytic choice probability, the reference's own shape/metadata test, and exact properties of the counter-based
+streams (geometry / sharding independence) and of the shared-memory histograms (== np.histogram of the raw output)."""
+import numpy as np
+import pytest
+from scipy import stats
+
+pytestmark = pytest.mark.gpu
+
+CASES = {
+    "ddm_hddm_base": (0, [1.0, 2.0, 0.5, 0.3]),
+    "full_ddm_hddm_base": (1, [0.8, 1.8, 0.5, 0.4, 0.1, 0.7, 0.15]),
+    "ddm": (2, [0.6, 1.1, 0.45, 0.3]),
+    "angle": (3, [1.0, 1.0, 0.5, 0.3, 0.2]),
+    "weibull": (4, [-0.5, 1.5, 0.4, 0.2, 2.0, 1.5]),
+    "full_ddm": (5, [0.8, 1.2, 0.5, 0.4, 0.1, 0.7, 0.15]),
+    "ddm_sdv": (6, [0.8, 1.2, 0.5, 0.3, 1.0]),
+    "ornstein": (7, [0.5, 1.2, 0.5, 0.6, 0.3]),
+    "levy": (8, [0.5, 1.2, 0.5, 1.6, 0.3]),
+}
+
+
+def _ci(k, n, zc=4.0):
+    p = k / n
+    h = zc * np.sqrt(max(p * (1 - p), 1e-12) / n)
+    return p - h, p + h
+
+
+@pytest.fixture(scope="module")
+def sims():
+    from hddm_b200 import _lib, simulators
+
+    _lib.load()
+    return simulators
+
+
+@pytest.mark.parametrize("model", list(CASES))
+def test_distribution_matches_oracle(model, sims, oracle):
+    mid, theta = CASES[model]
+    n_gpu, n_cpu = 400000, 100000
+    rts, ch, meta = sims.simulator(theta, model=model, n_samples=n_gpu, random_state=100 + mid)
+    ort, och = oracle.sim_run(mid, theta, n_cpu, seed=200 + mid)
+    assert rts.shape == (n_gpu, 1) and rts.dtype == np.float32 and ch.dtype == np.int32
+    ks = stats.ks_2samp(rts[:, 0], ort[:, 0])
+    assert ks.pvalue > 1e-3, (model, ks)
+    upper = 1
+    la, ha = _ci(int(np.sum(ch == upper)), n_gpu)
+    lb, hb = _ci(int(np.sum(och == upper)), n_cpu)
+    assert la <= hb and lb <= ha, (model, (la, ha), (lb, hb))
+    # conditional RT distributions per boundary as well
+    for c in meta["possible_choices"]:
+        a, b = rts[ch == c], ort[och == c]
+        if min(len(a), len(b)) > 2000:
+            assert stats.ks_2samp(a, b).pvalue > 1e-3, (model, c)
+    assert set(np.unique(ch)) <= set(meta["possible_choices"]) | {0}
+
+
+def test_shapes_and_metadata_like_reference_test(sims):
+    """/root/reference/hddm/tests/test_simulators.py:65-87."""
+    n_samples, n_trials = 100, 7
+    for model, (mid, theta) in CASES.items():
+        out = sims.simulator(theta=np.tile(theta, reps=(n_trials, 1)), model=model, n_samples=n_samples)
+        assert out[0].shape == out[1].shape == (n_samples, n_trials, 1)
+        assert type(out[2]) is dict
+        for param in sims.model_config[model]["params"]:
+            assert param in out[2].keys()
+        for key in ("possible_choices", "max_t", "n_samples", "delta_t", "s", "model", "trajectory"):
+            assert key in out[2]
+    # squeeze rules (graveyard/basic_simulator_old.py:1041-1045)
+    assert sims.simulator([1.0, 1.0, 0.5, 0.3, 0.2], model="angle", n_samples=50)[0].shape == (50, 1)
+    assert sims.simulator(np.tile([1.0, 1.0, 0.5, 0.3, 0.2], (9, 1)), model="angle", n_samples=1)[0].shape == (9, 1)
+    with pytest.raises(ValueError):
+        sims.simulator([1.0, 1.0, 0.5], model="angle")
+    with pytest.raises(NotImplementedError):
+        sims.simulator([0.0] * 8, model="ddm_par2")
+
+
+def test_streams_do_not_depend_on_geometry_or_sharding(sims):
+    """Same seed -> the same particles, whether simulated in one launch, in two shards with global offsets (what two
+    ranks do), next to other parameter sets, or while a histogram is also being built."""
+    theta = np.array([[1.0, 1.0, 0.5, 0.3, 0.2], [-0.7, 1.4, 0.6, 0.2, 0.1]], dtype=np.float32)
+    n = 5000
+    full = sims._run("angle", theta, n, 0.001, 20.0, 1.0, 77, True, 0)
+    a = sims._run("angle", theta, 2000, 0.001, 20.0, 1.0, 77, True, 0, sample_offset=0)
+    b = sims._run("angle", theta, 3000, 0.001, 20.0, 1.0, 77, True, 0, sample_offset=2000)
+    assert np.array_equal(np.concatenate([a[0], b[0]]), full[0])
+    assert np.array_equal(np.concatenate([a[1], b[1]]), full[1])
+    both = sims._run("angle", theta, n, 0.001, 20.0, 1.0, 77, True, 64)
+    assert np.array_equal(both[0], full[0]) and np.array_equal(both[1], full[1])
+    other = sims._run("angle", theta, n, 0.001, 20.0, 1.0, 78, True, 0)
+    assert not np.array_equal(other[0], full[0])
+    # first particle's trajectory ends where its walk ended
+    rts, ch, meta = sims.simulator(theta[0], model="angle", n_samples=10, random_state=5)
+    traj = meta["trajectory"][:, 0]
+    k = int(np.sum(traj > -999)) - 1
+    assert abs((k * 0.001 + 0.3) - rts[0, 0]) < 2e-3
+
+
+@pytest.mark.parametrize("model,nbins", [("angle", 512), ("ddm_hddm_base", 64)])
+def test_histograms_equal_host_binning_of_raw_output(model, nbins, sims):
+    mid, theta = CASES[model]
+    theta = np.tile(np.asarray(theta, dtype=np.float32), (3, 1))
+    theta[1, 0] = -theta[1, 0]
+    n = 50000
+    rts, ch, hist, _, steps = sims._run(model, theta, n, 0.001, 20.0, 1.0, 9, True, nbins)
+    assert int(hist.sum()) + int(np.sum(ch == 0) if model == "angle" else 0) == 3 * n
+    choices = sims.model_config[model]["choices"]
+    for k in range(3):
+        out = (rts[:, k, :], ch[:, k, :], {"max_t": 20.0, "possible_choices": choices, "n_samples": n})
+        want = sims.bin_simulator_output(out, nbins=nbins, freq_cnt=True)
+        assert np.array_equal(hist[k].astype(np.float64), want), (model, k)
+    # the reference-shaped binned call: proportions for one parameter set
+    h, meta = sims.simulator(theta[0], model=model, n_samples=n, bin_dim=nbins, random_state=9)
+    assert h.shape == (nbins, 2) and abs(h.sum() - 1.0) < 1e-3
+    assert steps > n
+
+
+def test_choice_probability_at_1e7_particles(sims):
+    """north_star: exact choice-probability interval at 1e7 particles.  Constant-bound DDM, P(upper) analytic; the
+    Euler scheme (dt = 1e-3) has a known O(sqrt(dt)) bias, so the analytic value is compared at a finer dt as well."""
+    v, a, z, t = 0.7, 1.6, 0.45, 0.25
+    n = 10_000_000
+    hist, steps = sims.simulate_histograms([v, a, z, t], model="ddm_hddm_base", n_samples=n, nbins=512, random_state=3)
+    assert int(hist.sum()) == n
+    p_gpu = hist[0, :, 1].sum() / n
+    p_true = (np.exp(-2 * v * a * z) - 1) / (np.exp(-2 * v * a) - 1)
+    assert abs(p_gpu - p_true) < 0.004
+    hist2, _ = sims.simulate_histograms([v, a, z, t], model="ddm_hddm_base", n_samples=2_000_000, nbins=512, delta_t=1e-4,
+                                        random_state=4)
+    p_fine = hist2[0, :, 1].sum() / 2_000_000
+    assert abs(p_fine - p_true) < abs(p_gpu - p_true) + 4 * np.sqrt(p_true * (1 - p_true) / 2e6)
+    assert abs(p_fine - p_true) < 0.0015
+    # two independent 1e7 runs agree within their binomial interval, bin by bin in aggregate
+    hist3, _ = sims.simulate_histograms([v, a, z, t], model="ddm_hddm_base", n_samples=n, nbins=512, random_state=5)
+    p3 = hist3[0, :, 1].sum() / n
+    assert abs(p3 - p_gpu) < 5 * np.sqrt(2 * p_true * (1 - p_true) / n)
+    ks = np.max(np.abs(np.cumsum(hist[0].sum(1)) - np.cumsum(hist3[0].sum(1)))) / n
+    assert ks < 1.95 * np.sqrt(2 / n)  # two-sample KS at alpha = 0.001 on the binned RTs

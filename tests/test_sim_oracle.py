@@ -1,0 +1,116 @@
+"""CPU tests of the simulator oracle (oracle/sim_oracle.c): distributional agreement with the reference's own
+Cython simulators (compiled unmodified into oracle/_ref, skipped where that build is absent) and with the analytic
+WFPT for the constant-bound DDM.  The reference's tests pin no simulator numerics (parity unpinned), so the bar is the
+one the north_star names: two-sample KS on RTs and overlapping choice-probability intervals."""
+import numpy as np
+import pytest
+from scipy import stats
+
+
+def _ci(k, n, zc=4.0):
+    p = k / n
+    h = zc * np.sqrt(max(p * (1 - p), 1e-12) / n)
+    return p - h, p + h
+
+
+def _agree(rt_a, ch_a, rt_b, ch_b, upper=1):
+    # RT grid values are shared (same float32 time accumulation); KS handles ties conservatively
+    ks = stats.ks_2samp(rt_a, rt_b)
+    assert ks.pvalue > 1e-3, ks
+    la, ha = _ci(int(np.sum(ch_a == upper)), len(ch_a))
+    lb, hb = _ci(int(np.sum(ch_b == upper)), len(ch_b))
+    assert la <= hb and lb <= ha, ((la, ha), (lb, hb))
+
+
+@pytest.fixture(scope="module")
+def ref_sim():
+    from oracle.build_ref import load_ref, ref_built
+
+    if not ref_built():
+        pytest.skip("oracle/_ref not built on this machine")
+    return load_ref()[1]
+
+
+def constant(t=0):
+    return 1
+
+
+def angle(t=1, theta=1):
+    return np.multiply(t, (-np.sin(theta) / np.cos(theta)))
+
+
+def weibull_cdf(t=1, alpha=1, beta=1):
+    return np.exp(-np.power(np.divide(t, beta), alpha))
+
+
+N = 40000
+
+
+def _f32(*xs):
+    return [np.array([x], dtype=np.float32) for x in xs]
+
+
+def test_ddm_vs_reference(oracle, ref_sim):
+    v, a, z, t = _f32(1.0, 2.0, 0.5, 0.3)
+    r = ref_sim.ddm(v, a, z, t, n_samples=N, n_trials=1)
+    rt, ch = oracle.sim_run(0, [1.0, 2.0, 0.5, 0.3], N, seed=11)
+    _agree(rt[:, 0], ch[:, 0], r[0][:, 0, 0], r[1][:, 0, 0])
+
+
+def test_angle_and_weibull_vs_reference(oracle, ref_sim):
+    v, a, z, t = _f32(1.0, 1.0, 0.5, 0.3)
+    r = ref_sim.ddm_flexbound(v, a, z, t, n_samples=N, n_trials=1, boundary_fun=angle, boundary_multiplicative=False,
+                              boundary_params={"theta": np.array([0.2], dtype=np.float32)})
+    rt, ch = oracle.sim_run(3, [1.0, 1.0, 0.5, 0.3, 0.2], N, seed=12)
+    _agree(rt[:, 0], ch[:, 0], r[0][:, 0, 0], r[1][:, 0, 0])
+    v, a, z, t = _f32(-0.5, 1.5, 0.4, 0.2)
+    r = ref_sim.ddm_flexbound(v, a, z, t, n_samples=N, n_trials=1, boundary_fun=weibull_cdf, boundary_multiplicative=True,
+                              boundary_params={"alpha": np.array([2.0], dtype=np.float32), "beta": np.array([1.5], dtype=np.float32)})
+    rt, ch = oracle.sim_run(4, [-0.5, 1.5, 0.4, 0.2, 2.0, 1.5], N, seed=13)
+    _agree(rt[:, 0], ch[:, 0], r[0][:, 0, 0], r[1][:, 0, 0])
+
+
+def test_full_ddm_family_vs_reference(oracle, ref_sim):
+    th = [0.8, 1.8, 0.5, 0.4, 0.1, 0.7, 0.15]  # v, a, z, t, sz, sv, st
+    arrs = _f32(*th)
+    r = ref_sim.full_ddm_hddm_base(*arrs, n_samples=N, n_trials=1)
+    rt, ch = oracle.sim_run(1, th, N, seed=14)
+    _agree(rt[:, 0], ch[:, 0], r[0][:, 0, 0], r[1][:, 0, 0])
+    r = ref_sim.full_ddm(*arrs, n_samples=N, n_trials=1, boundary_fun=constant, boundary_multiplicative=True, boundary_params={})
+    rt, ch = oracle.sim_run(5, th, N, seed=15)
+    _agree(rt[:, 0], ch[:, 0], r[0][:, 0, 0], r[1][:, 0, 0])
+    v, a, z, t, sv = _f32(0.8, 1.2, 0.5, 0.3, 1.0)
+    r = ref_sim.ddm_sdv(v, a, z, t, sv, n_samples=N, n_trials=1, boundary_fun=constant, boundary_multiplicative=True, boundary_params={})
+    rt, ch = oracle.sim_run(6, [0.8, 1.2, 0.5, 0.3, 1.0], N, seed=16)
+    _agree(rt[:, 0], ch[:, 0], r[0][:, 0, 0], r[1][:, 0, 0])
+
+
+def test_ornstein_and_levy_vs_reference(oracle, ref_sim):
+    v, a, z, g, t = _f32(0.5, 1.2, 0.5, 0.6, 0.3)
+    r = ref_sim.ornstein_uhlenbeck(v, a, z, g, t, n_samples=N, n_trials=1, boundary_fun=constant, boundary_multiplicative=True, boundary_params={})
+    rt, ch = oracle.sim_run(7, [0.5, 1.2, 0.5, 0.6, 0.3], N, seed=17)
+    _agree(rt[:, 0], ch[:, 0], r[0][:, 0, 0], r[1][:, 0, 0])
+    v, a, z, al, t = _f32(0.5, 1.2, 0.5, 1.6, 0.3)
+    r = ref_sim.levy_flexbound(v, a, z, al, t, n_samples=N, n_trials=1, boundary_fun=constant, boundary_multiplicative=True, boundary_params={})
+    rt, ch = oracle.sim_run(8, [0.5, 1.2, 0.5, 1.6, 0.3], N, seed=18)
+    _agree(rt[:, 0], ch[:, 0], r[0][:, 0, 0], r[1][:, 0, 0])
+
+
+def test_ddm_vs_analytic_wfpt(oracle):
+    """Constant bounds: P(upper) from prob_ub (pdf.pxi:67-72) and the RT density from full_pdf, as
+    /root/reference/hddm/tests/test_generate.py:33-50 validates its own random walk."""
+    v, a, z, t = 0.7, 1.6, 0.45, 0.25
+    n = 60000
+    rt, ch = oracle.sim_run(0, [v, a, z, t], n, seed=21)
+    p_up = (np.exp(-2 * v * a * z) - 1) / (np.exp(-2 * v * a) - 1) if v != 0 else z
+    lo, hi = _ci(int(np.sum(ch == 1)), n)
+    assert lo - 0.004 <= p_up <= hi + 0.004  # Euler discretisation (dt=1e-3) biases the hit probability slightly
+    # CDF of upper-boundary RTs against the analytic density integrated on a fine grid
+    grid = np.linspace(t + 1e-4, 8.0, 8000)
+    dens = oracle.pdf_array(grid, v, 0, a, z, 0, t, 0, 1e-10)
+    cdf = np.concatenate([[0], np.cumsum((dens[1:] + dens[:-1]) / 2 * np.diff(grid))])
+    cdf /= cdf[-1]
+    up = np.sort(rt[ch[:, 0] == 1, 0].astype(np.float64))
+    emp = np.arange(1, len(up) + 1) / len(up)
+    D = np.max(np.abs(emp - np.interp(up, grid, cdf)))
+    assert D < 0.04, D  # the Euler walk detects crossings late by O(sqrt(dt)): a small, known shift (~0.024 here)
