@@ -21,7 +21,8 @@
 //
 // Mapping: one CTA works on one parameter set at a time (its constants in registers, its RT/choice histogram in
 // shared memory, built with shared-memory atomics and flushed once per item); each thread runs one particle after
-// another without waiting for its warp neighbours (refill inside the step loop); bounds are evaluated in registers.
+// another without waiting for its warp neighbours (a finished lane picks up its next particle at the next Philox
+// block boundary, at most three sub-steps later); bounds are evaluated in registers.
 #include <cstdio>
 
 #include "../../include/wfpt_b200.h"
@@ -56,69 +57,36 @@ struct Args {
 };
 
 // ---- Philox4x32-10 -------------------------------------------------------------------------------------------------------
-struct Philox {
-    unsigned int k0, k1;
-    uint4 ctr;
-    __device__ __forceinline__ uint4 next()
-    {
-        unsigned int c0 = ctr.x, c1 = ctr.y, c2 = ctr.z, c3 = ctr.w, a = k0, b = k1;
+__device__ __forceinline__ uint4 philox4x32(unsigned int c0, unsigned int c1, unsigned int c2, unsigned int c3,
+                                            unsigned int k0, unsigned int k1)
+{
 #pragma unroll
-        for (int r = 0; r < 10; r++) {
-            const unsigned int h0 = __umulhi(0xD2511F53u, c0), l0 = 0xD2511F53u * c0;
-            const unsigned int h1 = __umulhi(0xCD9E8D57u, c2), l1 = 0xCD9E8D57u * c2;
-            c0 = h1 ^ c1 ^ a;
-            c1 = l1;
-            c2 = h0 ^ c3 ^ b;
-            c3 = l0;
-            a += 0x9E3779B9u;
-            b += 0xBB67AE85u;
-        }
-        ctr.w++;  // block counter
-        return make_uint4(c0, c1, c2, c3);
+    for (int r = 0; r < 10; r++) {
+        const unsigned long long p0 = (unsigned long long)0xD2511F53u * c0;
+        const unsigned long long p1 = (unsigned long long)0xCD9E8D57u * c2;
+        const unsigned int n0 = (unsigned int)(p1 >> 32) ^ c1 ^ k0;
+        const unsigned int n2 = (unsigned int)(p0 >> 32) ^ c3 ^ k1;
+        c1 = (unsigned int)p1;
+        c3 = (unsigned int)p0;
+        c0 = n0;
+        c2 = n2;
+        k0 += 0x9E3779B9u;
+        k1 += 0xBB67AE85u;
     }
-};
+    return make_uint4(c0, c1, c2, c3);
+}
 
 __device__ __forceinline__ float u01(unsigned int x) { return ((float)x + 0.5f) * 2.3283064365386963e-10f; }  // (0, 1)
 
-// Normal / uniform source of one particle: four normals per Philox block (two Box-Muller pairs).
-struct Stream {
-    Philox ph;
-    float buf[4];
-    int have;
-    __device__ __forceinline__ void start(unsigned long long seed, unsigned long long particle, unsigned int set)
-    {
-        ph.k0 = (unsigned int)seed;
-        ph.k1 = (unsigned int)(seed >> 32);
-        ph.ctr = make_uint4((unsigned int)particle, (unsigned int)(particle >> 32), set, 0u);
-        have = 0;
-    }
-    __device__ __forceinline__ void fill()
-    {
-        const uint4 r = ph.next();
-        const float r0 = sqrtf(-2.0f * __logf(u01(r.x))), r1 = sqrtf(-2.0f * __logf(u01(r.z)));
-        float s0, c0, s1, c1;
-        __sincosf(6.283185307179586f * u01(r.y), &s0, &c0);
-        __sincosf(6.283185307179586f * u01(r.w), &s1, &c1);
-        buf[0] = r0 * c0;
-        buf[1] = r0 * s0;
-        buf[2] = r1 * c1;
-        buf[3] = r1 * s1;
-        have = 4;
-    }
-    __device__ __forceinline__ float normal()
-    {
-        if (have == 0) fill();
-        have--;
-        // select without dynamic indexing
-        return have == 3 ? buf[0] : have == 2 ? buf[1] : have == 1 ? buf[2] : buf[3];
-    }
-    // four uniforms in (0,1) straight from a Philox block (does not disturb the normal buffer)
-    __device__ __forceinline__ float4 uniforms()
-    {
-        const uint4 r = ph.next();
-        return make_float4(u01(r.x), u01(r.y), u01(r.z), u01(r.w));
-    }
-};
+// Four standard normals from one Philox block (two Box-Muller pairs, fast intrinsics).
+__device__ __forceinline__ float4 normals4(const uint4 r)
+{
+    const float r0 = sqrtf(-2.0f * __logf(u01(r.x))), r1 = sqrtf(-2.0f * __logf(u01(r.z)));
+    float s0, c0, s1, c1;
+    __sincosf(6.283185307179586f * u01(r.y), &s0, &c0);
+    __sincosf(6.283185307179586f * u01(r.w), &s1, &c1);
+    return make_float4(r0 * c0, r0 * s0, r1 * c1, r1 * s1);
+}
 
 // Chambers-Mallows-Stuck draw as the reference writes it (cddm_data_simulation.pyx:28-40)
 __device__ __forceinline__ float stable_draw(float alpha, float U, float U2)
@@ -181,12 +149,18 @@ struct Traits {
 };
 
 // ---- the kernel ------------------------------------------------------------------------------------------------------------
+// Stream layout of particle (set, p): Philox key = seed, counter = (p_lo, p_hi, set, block).  Block 0xFFFFFFFF feeds the
+// start-of-particle draws (drift, non-decision time and starting point variability); block j = 0, 1, ... feeds Euler
+// steps 4j .. 4j+3 (one normal each; Levy: steps 2j, 2j+1, two uniforms each).  All lanes of a warp fetch their blocks
+// at the same loop iteration: a lane whose particle ends mid-block idles for at most three sub-steps and starts its
+// next particle at the next block boundary, so the Philox rounds and the Box-Muller transform never run diverged.
 template <int MODEL>
 __global__ void __launch_bounds__(kSimBlock) sim_kernel(const Args A)
 {
     extern __shared__ unsigned int s_hist[];  // [nbins][2] when A.hist
     const int nh = A.hist ? A.nbins * 2 : 0;
     const float sqrt_st = __fmul_rn(sqrtf(A.dt), A.s);
+    const unsigned int k0 = (unsigned int)A.seed, k1 = (unsigned int)(A.seed >> 32);
     unsigned long long my_steps = 0;
     const long long n_items = (long long)A.n_sets * A.items_per_set;
 
@@ -202,14 +176,18 @@ __global__ void __launch_bounds__(kSimBlock) sim_kernel(const Args A)
 
         long long p = beg + threadIdx.x;   // particle (local index within this launch)
         bool active = p < end;
-        Stream st;
+        bool walking = false;
         float y = 0.f, tp = 0.f, fix = 0.f, drift = c.vdt, t_nd = c.t, b = c.a;
         int ix = 0;
-        bool fresh = true;
+        unsigned int blk = 0, plo = 0, phi = 0;
+        bool tracing = false;
         while (active) {
-            if (fresh) {
+            if (!walking) {
                 // ---- start a particle ----
-                st.start(A.seed, (unsigned long long)(p + A.sample_offset), (unsigned int)set);
+                const unsigned long long gp = (unsigned long long)(p + A.sample_offset);
+                plo = (unsigned int)gp;
+                phi = (unsigned int)(gp >> 32);
+                blk = 0;
                 tp = 0.f;
                 fix = 0.f;
                 ix = 0;
@@ -218,69 +196,84 @@ __global__ void __launch_bounds__(kSimBlock) sim_kernel(const Args A)
                 b = bound_at<MODEL>(c, 0.f);
                 if (Traits<MODEL>::zero_a) y = __fmul_rn(c.z, c.a);
                 else y = __fadd_rn(-b, __fmul_rn(__fmul_rn(c.z, 2.f), b));
-                if (Traits<MODEL>::full) {
-                    // theta = v, a, z, t, sz, sv, st  (:228-235, :812-820)
-                    const float4 u = st.uniforms();
-                    drift = __fmul_rn(__fadd_rn(c.v, __fmul_rn(c.p5, st.normal())), A.dt);
-                    t_nd = __fadd_rn(c.t, __fmul_rn(__fmul_rn(2.f, u.x - 0.5f), c.p6));
-                    y = __fadd_rn(y, __fmul_rn(__fmul_rn(2.f, u.y - 0.5f), c.p4));
-                }
-                if (Traits<MODEL>::sdv) drift = __fmul_rn(__fadd_rn(c.v, __fmul_rn(c.p4, st.normal())), A.dt);
-                if (A.traj && set == 0 && p + A.sample_offset == 0) A.traj[0] = y;
-                fresh = false;
-            }
-            const float lo = Traits<MODEL>::zero_a ? 0.f : -b;
-            if (y >= lo && y <= b && tp <= A.max_t) {
-                // ---- one Euler step ----
-                float inc;
-                if (MODEL == WFPT_SIM_LEVY) {
-                    const float4 u = st.uniforms();
-                    inc = __fmul_rn(c.dt_alpha, stable_draw(c.alpha, u.x, u.y));
-                } else {
-                    inc = __fmul_rn(sqrt_st, st.normal());
-                }
-                float det = drift;
-                if (MODEL == WFPT_SIM_ORNSTEIN) det = __fmul_rn(__fsub_rn(c.v, __fmul_rn(c.g, y)), A.dt);
-                y = __fadd_rn(y, __fadd_rn(det, inc));
-                tp = __fadd_rn(tp, A.dt);
-                ix++;
-                if (Traits<MODEL>::moving) {
-                    fix += 1.0f;
-                    b = bound_at<MODEL>(c, __fmul_rn(fix, A.dt));
-                }
-                if (A.traj && set == 0 && p + A.sample_offset == 0 && ix < A.traj_len) A.traj[ix] = y;
-            } else {
-                // ---- record and move on ----
-                my_steps += (unsigned long long)ix;
-                const float rt = __fadd_rn(tp, t_nd);
-                int choice;
-                if (Traits<MODEL>::zero_a) choice = (y < 0.f) ? 0 : 1;
-                else choice = (y > 0.f) - (y < 0.f);
-                if (A.rts) {
-                    const size_t o = (size_t)p * A.n_sets + set;
-                    A.rts[o] = rt;
-                    A.choices[o] = choice;
-                }
-                if (A.hist) {
-                    const int col = Traits<MODEL>::zero_a ? choice : (choice > 0 ? 1 : (choice < 0 ? 0 : -1));
-                    if (col >= 0) {
-                        // np.histogram on edges linspace(0, max_t, nbins) + [inf] (basic_simulator_old.py:99-114)
-                        const double r = (double)rt;
-                        int bin = (int)(r / A.hist_step);
-                        if (bin > A.nbins - 1) bin = A.nbins - 1;
-                        if (bin < 0) bin = 0;
-                        const double e_lo = (bin == A.nbins - 1) ? A.hist_max_t : bin * A.hist_step;
-                        if (r < e_lo && bin > 0) bin--;
-                        else if (bin < A.nbins - 1) {
-                            const double e_hi = (bin + 1 == A.nbins - 1) ? A.hist_max_t : (bin + 1) * A.hist_step;
-                            if (r >= e_hi) bin++;
-                        }
-                        if (r >= 0.0) atomicAdd(&s_hist[bin * 2 + col], 1u);
+                if (Traits<MODEL>::full || Traits<MODEL>::sdv) {
+                    const uint4 r = philox4x32(plo, phi, (unsigned int)set, 0xFFFFFFFFu, k0, k1);
+                    const float g = sqrtf(-2.0f * __logf(u01(r.x))) * __cosf(6.283185307179586f * u01(r.y));
+                    if (Traits<MODEL>::full) {
+                        // theta = v, a, z, t, sz, sv, st  (:228-235, :812-820)
+                        drift = __fmul_rn(__fadd_rn(c.v, __fmul_rn(c.p5, g)), A.dt);
+                        t_nd = __fadd_rn(c.t, __fmul_rn(__fmul_rn(2.f, u01(r.z) - 0.5f), c.p6));
+                        y = __fadd_rn(y, __fmul_rn(__fmul_rn(2.f, u01(r.w) - 0.5f), c.p4));
+                    } else {
+                        drift = __fmul_rn(__fadd_rn(c.v, __fmul_rn(c.p4, g)), A.dt);  // theta = v, a, z, t, sv
                     }
                 }
-                p += kSimBlock;
-                active = p < end;
-                fresh = true;
+                tracing = A.traj && set == 0 && gp == 0;
+                if (tracing) A.traj[0] = y;
+                walking = true;
+            }
+            // ---- one Philox block for everybody, then up to four sub-steps ----
+            const uint4 r = philox4x32(plo, phi, (unsigned int)set, blk++, k0, k1);
+            float4 nn;
+            if (MODEL == WFPT_SIM_LEVY) {
+                nn.x = stable_draw(c.alpha, u01(r.x), u01(r.y));
+                nn.y = stable_draw(c.alpha, u01(r.z), u01(r.w));
+                nn.z = nn.w = 0.f;
+            } else {
+                nn = normals4(r);
+            }
+            constexpr int kSub = (MODEL == WFPT_SIM_LEVY) ? 2 : 4;
+#pragma unroll
+            for (int j = 0; j < kSub; j++) {
+                if (!walking) continue;
+                const float lo = Traits<MODEL>::zero_a ? 0.f : -b;
+                if (y >= lo && y <= b && tp <= A.max_t) {
+                    // ---- one Euler step ----
+                    const float nj = (j == 0) ? nn.x : (j == 1) ? nn.y : (j == 2) ? nn.z : nn.w;
+                    const float inc = (MODEL == WFPT_SIM_LEVY) ? __fmul_rn(c.dt_alpha, nj) : __fmul_rn(sqrt_st, nj);
+                    float det = drift;
+                    if (MODEL == WFPT_SIM_ORNSTEIN) det = __fmul_rn(__fsub_rn(c.v, __fmul_rn(c.g, y)), A.dt);
+                    y = __fadd_rn(y, __fadd_rn(det, inc));
+                    tp = __fadd_rn(tp, A.dt);
+                    ix++;
+                    if (Traits<MODEL>::moving) {
+                        fix += 1.0f;
+                        b = bound_at<MODEL>(c, __fmul_rn(fix, A.dt));
+                    }
+                    if (tracing && ix < A.traj_len) A.traj[ix] = y;
+                } else {
+                    // ---- record and move on ----
+                    my_steps += (unsigned long long)ix;
+                    const float rt = __fadd_rn(tp, t_nd);
+                    int choice;
+                    if (Traits<MODEL>::zero_a) choice = (y < 0.f) ? 0 : 1;
+                    else choice = (y > 0.f) - (y < 0.f);
+                    if (A.rts) {
+                        const size_t o = (size_t)p * A.n_sets + set;
+                        A.rts[o] = rt;
+                        A.choices[o] = choice;
+                    }
+                    if (A.hist) {
+                        const int col = Traits<MODEL>::zero_a ? choice : (choice > 0 ? 1 : (choice < 0 ? 0 : -1));
+                        if (col >= 0) {
+                            // np.histogram on edges linspace(0, max_t, nbins) + [inf] (basic_simulator_old.py:99-114)
+                            const double rd = (double)rt;
+                            int bin = (int)(rd / A.hist_step);
+                            if (bin > A.nbins - 1) bin = A.nbins - 1;
+                            if (bin < 0) bin = 0;
+                            const double e_lo = (bin == A.nbins - 1) ? A.hist_max_t : bin * A.hist_step;
+                            if (rd < e_lo && bin > 0) bin--;
+                            else if (bin < A.nbins - 1) {
+                                const double e_hi = (bin + 1 == A.nbins - 1) ? A.hist_max_t : (bin + 1) * A.hist_step;
+                                if (rd >= e_hi) bin++;
+                            }
+                            if (rd >= 0.0) atomicAdd(&s_hist[bin * 2 + col], 1u);
+                        }
+                    }
+                    walking = false;
+                    p += kSimBlock;
+                    active = p < end;
+                }
             }
         }
         __syncthreads();
