@@ -51,6 +51,14 @@ def _declare(L):
                  "wfpt_like_batch_host", "wfpt_pdf_array", "wfpt_pdf_array_host", "wfpt_like_multi",
                  "wfpt_like_multi_host", "wfpt_like_rlddm_host"):
         getattr(L, name).restype = i
+    L.wfpt_like_segments.argtypes = [vp, vp, i64, vp, i64] + opts + [d, i, vp, vp]
+    L.wfpt_like_segments_host.argtypes = [vp, vp, vp, i64] + opts + [d, i, vp]
+    L.wfpt_like_contaminant_host.argtypes = [vp, vp, i64] + [d] * 9 + opts + [i, vp]
+    L.wfpt_like_rl_host.argtypes = [vp, vp, vp, vp, i64, i64] + [d] * 7 + [vp]
+    L.wfpt_like_multi_rlddm_host.argtypes = [vp, vp, vp, vp, i64, d, C.POINTER(vp), c_double_p] + opts + [d, d, i, vp]
+    for name in ("wfpt_like_segments", "wfpt_like_segments_host", "wfpt_like_contaminant_host", "wfpt_like_rl_host",
+                 "wfpt_like_multi_rlddm_host"):
+        getattr(L, name).restype = i
     f = C.c_float
     sim_tail = [i, i, i64, i64, f, f, f, C.c_uint64, vp, vp, vp, i, f, vp, vp, i]
     L.wfpt_sim_run.argtypes = [i, vp] + sim_tail + [vp]

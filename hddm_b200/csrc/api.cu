@@ -2,8 +2,10 @@
 // host<->device staging for the `_host` entry points, launch geometry, and the few small kernels that are not
 // density evaluators (second-stage sum, RL Q-recurrence, FP64 issue-rate probe).
 #include <atomic>
+#include <cmath>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 
@@ -34,7 +36,7 @@ void count_launch(int k) { g_launches.fetch_add(k, std::memory_order_relaxed); }
 
 // ---- per-device grow-only scratch ------------------------------------------------------------------------------------
 enum Slot { kPartSum = 0, kPartZero, kStageX, kStageParams, kStageOut, kStageAux0, kStageAux1, kStageAux2, kStageAux3,
-            kStageAux4, kStageAux5, kStageAux6, kStageAux7, kStageAux8, kNumSlots };
+            kStageAux4, kStageAux5, kStageAux6, kStageAux7, kStageAux8, kStageAux9, kStageAux10, kStageAux11, kNumSlots };
 constexpr int kMaxDev = 16;
 struct Buf { void* p = nullptr; size_t cap = 0; };
 static Buf g_buf[kMaxDev][kNumSlots];
@@ -117,6 +119,65 @@ __global__ void __launch_bounds__(256) dfma_probe_kernel(int iters, double seed,
     }
     const double r = ((a0 + a1) + (a2 + a3)) + ((a4 + a5) + (a6 + a7));
     if (r == 123.456) sink[0] = r;  // never true; keeps the chains alive
+}
+
+// Q recurrence of wiener_like_multi_rlddm (/root/reference/src/wfpt.pyx:411-431): trials in array order, Q reset where
+// split_by changes, per-trial learning rate, no first-trial skip.  One thread per run of equal split_by.
+__global__ void rl_q_runs_kernel(const int64_t* __restrict__ response, const double* __restrict__ feedback,
+                                 const int64_t* __restrict__ run_starts, int64_t n_runs, double q,
+                                 const double* __restrict__ alpha_arr, double alpha_scalar, double* __restrict__ vscale)
+{
+    const int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= n_runs) return;
+    double qs0 = q, qs1 = q;
+    for (int64_t i = run_starts[g]; i < run_starts[g + 1]; i++) {
+        vscale[i] = __dsub_rn(qs1, qs0);
+        const double al = alpha_arr ? alpha_arr[i] : alpha_scalar;
+        const double ea = pow(2.718281828459, al);
+        const double alfa = __ddiv_rn(ea, __dadd_rn(1.0, ea));
+        const int64_t r = response[i];
+        const double cur = r ? qs1 : qs0;
+        const double upd = __dadd_rn(cur, __dmul_rn(alfa, __dsub_rn(feedback[i], cur)));
+        if (r) qs1 = upd; else qs0 = upd;
+    }
+}
+
+// Choice-only RL likelihood (/root/reference/src/wfpt.pyx:318-337): per trial, from the drift scale written by
+// rl_q_kernel, p = (B^(-2 z d) - 1)/(B^(-2 d) - 1) for the upper response (1 - that for the lower), 0.5 at zero drift,
+// B = 2.718281828459; outlier mix, log, CTA sum.
+__global__ void __launch_bounds__(kBlock) rl_choice_kernel(const int64_t* __restrict__ response,
+                                                         const double* __restrict__ vscale,
+                                                         const uint8_t* __restrict__ skip, int64_t n, double v, double z,
+                                                         double p_outlier, double w_outlier,
+                                                         double* __restrict__ out_sum, int* __restrict__ out_zero)
+{
+    const double wp = __dmul_rn(w_outlier, p_outlier);
+    const double omp = __dsub_rn(1.0, p_outlier);
+    double acc = 0.0;
+    int zero = 0;
+    const int64_t stride = (int64_t)gridDim.x * kBlock;
+    for (int64_t i = (int64_t)blockIdx.x * kBlock + threadIdx.x; i < n; i += stride) {
+        if (skip[i]) continue;
+        const double drift = __dmul_rn(vscale[i], v);
+        double p;
+        if (drift == 0) {
+            p = 0.5;
+        } else {
+            const double num = __dsub_rn(pow(2.718281828459, __dmul_rn(__dmul_rn(-2, z), drift)), 1.0);
+            const double den = __dsub_rn(pow(2.718281828459, __dmul_rn(-2, drift)), 1.0);
+            p = __ddiv_rn(num, den);
+            if (response[i] != 1) p = __dsub_rn(1.0, p);
+        }
+        p = __dadd_rn(__dmul_rn(p, omp), wp);
+        zero |= (p == 0);
+        acc += log(p);
+    }
+    int any_zero;
+    const double tot = block_sum_or<kBlock>(acc, zero, &any_zero);
+    if (threadIdx.x == 0) {
+        out_sum[blockIdx.x] = tot;
+        out_zero[blockIdx.x] = any_zero;
+    }
 }
 
 // ---- helpers -------------------------------------------------------------------------------------------------------------
@@ -457,6 +518,216 @@ int wfpt_like_rlddm_host(const double* h_x, const int64_t* h_response, const dou
     if (run_multi((const double*)dx, n, nullptr, scalars, o, p_outlier, w_outlier, (const double*)dvs,
                   (const uint8_t*)dskip, 1, 0, variant, (double*)dout, 0))
         return 1;
+    CK(cudaMemcpyAsync(h_out, dout, sizeof(double), cudaMemcpyDeviceToHost, 0));
+    CK(cudaStreamSynchronize(0));
+    return 0;
+}
+
+// ---- one RT array per parameter set (PyMC nodes) -----------------------------------------------------------------------
+int wfpt_like_segments(const double* d_x, const int64_t* d_seg, int64_t mean_len, const double* d_params, int64_t P,
+                       double err, int n_st, int n_sz, int use_adaptive, double simps_err, double w_outlier, int variant,
+                       double* d_out, void* stream)
+{
+    Opts o;
+    if (check_opts(err, n_st, n_sz, use_adaptive, simps_err, variant, &o)) return 1;
+    if (P < 0 || mean_len < 0) return fail("negative size");
+    if (P == 0) return 0;
+    if (!d_params || !d_out || !d_seg || !d_x) return fail("null pointer argument");
+    BatchArgs a;
+    a.x = d_x; a.n = mean_len; a.params = d_params; a.P = P; a.o = o; a.w_outlier = w_outlier; a.out = d_out;
+    a.stream = (cudaStream_t)stream;
+    a.seg = d_seg;
+    plan_slices(mean_len, P, &a.slices, &a.chunk);
+    a.part_sum = nullptr;
+    a.part_zero = nullptr;
+    if (a.slices > 1) {
+        void *ps, *pz;
+        if (scratch(kPartSum, sizeof(double) * (size_t)P * a.slices, &ps)) return 1;
+        if (scratch(kPartZero, sizeof(int) * (size_t)P * a.slices, &pz)) return 1;
+        a.part_sum = (double*)ps;
+        a.part_zero = (int*)pz;
+    }
+    CK(variant == WFPT_VARIANT_FAITHFUL ? launch_like_batch_faithful(a) : launch_like_batch_fast(a));
+    count_launch(1);
+    if (a.slices > 1) {
+        finalize_kernel<<<(unsigned)((P + 127) / 128), 128, 0, a.stream>>>(a.part_sum, a.part_zero, P, a.slices, 1, d_out);
+        CK(cudaGetLastError());
+        count_launch(1);
+    }
+    return 0;
+}
+
+int wfpt_like_segments_host(const double* h_x, const int64_t* h_seg, const double* h_params, int64_t P, double err,
+                            int n_st, int n_sz, int use_adaptive, double simps_err, double w_outlier, int variant,
+                            double* h_out)
+{
+    if (P < 0) return fail("negative size");
+    if (P == 0) return 0;
+    if (!h_seg || !h_params || !h_out) return fail("null pointer argument");
+    int64_t total = 0, hi = 0;
+    for (int64_t p = 0; p < P; p++) {
+        if (h_seg[2 * p] < 0 || h_seg[2 * p + 1] < h_seg[2 * p]) return fail("segment %lld has a negative start or length", (long long)p);
+        total += h_seg[2 * p + 1] - h_seg[2 * p];
+        if (h_seg[2 * p + 1] > hi) hi = h_seg[2 * p + 1];
+    }
+    if (hi > 0 && !h_x) return fail("null pointer argument");
+    void *dx, *dseg, *dp, *dout;
+    if (scratch(kStageX, sizeof(double) * (size_t)(hi > 0 ? hi : 1), &dx)) return 1;
+    if (scratch(kStageAux0, sizeof(int64_t) * 2 * (size_t)P, &dseg)) return 1;
+    if (scratch(kStageParams, sizeof(double) * 8 * (size_t)P, &dp)) return 1;
+    if (scratch(kStageOut, sizeof(double) * (size_t)P, &dout)) return 1;
+    if (hi > 0) CK(cudaMemcpyAsync(dx, h_x, sizeof(double) * (size_t)hi, cudaMemcpyHostToDevice, 0));
+    CK(cudaMemcpyAsync(dseg, h_seg, sizeof(int64_t) * 2 * (size_t)P, cudaMemcpyHostToDevice, 0));
+    CK(cudaMemcpyAsync(dp, h_params, sizeof(double) * 8 * (size_t)P, cudaMemcpyHostToDevice, 0));
+    if (wfpt_like_segments((const double*)dx, (const int64_t*)dseg, (total + P - 1) / P, (const double*)dp, P, err, n_st,
+                           n_sz, use_adaptive, simps_err, w_outlier, variant, (double*)dout, nullptr))
+        return 1;
+    CK(cudaMemcpyAsync(h_out, dout, sizeof(double) * (size_t)P, cudaMemcpyDeviceToHost, 0));
+    CK(cudaStreamSynchronize(0));
+    return 0;
+}
+
+// ---- contaminant mixture (wfpt.pyx:551-580) -----------------------------------------------------------------------------
+int wfpt_like_contaminant_host(const double* h_x, const int32_t* h_cont, int64_t n, double v, double sv, double a, double z,
+                               double sz, double t, double st, double t_min, double t_max, double err, int n_st, int n_sz,
+                               int use_adaptive, double simps_err, int variant, double* h_out)
+{
+    Opts o;
+    if (check_opts(err, n_st, n_sz, use_adaptive, simps_err, variant, &o)) return 1;
+    if (n < 0) return fail("negative size");
+    if (!h_out || (n > 0 && (!h_x || !h_cont))) return fail("null pointer argument");
+    int64_t n_cont = 0;
+    void *dx, *dskip, *dout;
+    if (scratch(kStageX, sizeof(double) * (size_t)(n > 0 ? n : 1), &dx)) return 1;
+    if (scratch(kStageAux5, (size_t)(n > 0 ? n : 1), &dskip)) return 1;
+    if (scratch(kStageOut, sizeof(double), &dout)) return 1;
+    if (n > 0) {
+        uint8_t* hs = (uint8_t*)malloc((size_t)n);
+        if (!hs) return fail("out of host memory");
+        for (int64_t i = 0; i < n; i++) {
+            n_cont += h_cont[i];
+            hs[i] = h_cont[i] == 0 ? 0 : 1;   // only cont_x == 0 trials enter the diffusion likelihood (:569)
+        }
+        cudaError_t e = cudaMemcpy(dskip, hs, (size_t)n, cudaMemcpyHostToDevice);
+        free(hs);
+        CK(e);
+        CK(cudaMemcpyAsync(dx, h_x, sizeof(double) * (size_t)n, cudaMemcpyHostToDevice, 0));
+    }
+    const double scalars[7] = {v, sv, a, z, sz, t, st};
+    if (run_multi((const double*)dx, n, nullptr, scalars, o, 0.0, 0.0, nullptr, (const uint8_t*)dskip, 1, 0, variant,
+                  (double*)dout, 0))
+        return 1;
+    double s = 0;
+    CK(cudaMemcpy(&s, dout, sizeof(double), cudaMemcpyDeviceToHost));
+    // wfpt.pyx:578: sum_logp += n_cont * log(0.5 * 1. / (t_max - t_min)); an early -inf return skips it, -inf stays -inf
+    *h_out = (s == -HUGE_VAL) ? s : s + (double)(int)n_cont * log(0.5 * 1. / (t_max - t_min));
+    return 0;
+}
+
+// ---- choice-only RL (wfpt.pyx:270-354) -------------------------------------------------------------------------------------
+int wfpt_like_rl_host(const int64_t* h_response, const double* h_feedback, const int64_t* h_order, const int64_t* h_starts,
+                      int64_t n_groups, int64_t n, double q, double alpha, double pos_alpha, double v, double z,
+                      double p_outlier, double w_outlier, double* h_out)
+{
+    if (n < 0 || n_groups < 0) return fail("negative size");
+    if (!h_out) return fail("null pointer argument");
+    if (!((p_outlier >= 0) & (p_outlier <= 1))) { *h_out = -HUGE_VAL; return 0; }
+    if (n == 0 || n_groups == 0) { *h_out = 0.0; return 0; }
+    if (!h_response || !h_feedback || !h_order || !h_starts) return fail("null pointer argument");
+    for (int64_t g = 0; g < n_groups; g++)
+        if (h_starts[g + 1] <= h_starts[g]) return fail("empty split_by group %lld", (long long)g);
+    for (int64_t i = 0; i < n; i++)
+        if (h_response[i] != 0 && h_response[i] != 1) return fail("response[%lld] is not 0/1", (long long)i);
+    const double pos_alfa = (pos_alpha == 100.00) ? alpha : pos_alpha;
+    void *dresp, *dfb, *dord, *dst, *dvs, *dskip, *dout, *ps, *pz;
+    if (scratch(kStageAux0, sizeof(int64_t) * (size_t)n, &dresp)) return 1;
+    if (scratch(kStageAux1, sizeof(double) * (size_t)n, &dfb)) return 1;
+    if (scratch(kStageAux2, sizeof(int64_t) * (size_t)n, &dord)) return 1;
+    if (scratch(kStageAux3, sizeof(int64_t) * (size_t)(n_groups + 1), &dst)) return 1;
+    if (scratch(kStageAux4, sizeof(double) * (size_t)n, &dvs)) return 1;
+    if (scratch(kStageAux5, (size_t)n, &dskip)) return 1;
+    if (scratch(kStageOut, sizeof(double), &dout)) return 1;
+    int64_t nb = (n + kBlock - 1) / kBlock;
+    if (nb > (int64_t)sm_count() * 16) nb = (int64_t)sm_count() * 16;
+    if (scratch(kPartSum, sizeof(double) * (size_t)nb, &ps)) return 1;
+    if (scratch(kPartZero, sizeof(int) * (size_t)nb, &pz)) return 1;
+    CK(cudaMemcpyAsync(dresp, h_response, sizeof(int64_t) * (size_t)n, cudaMemcpyHostToDevice, 0));
+    CK(cudaMemcpyAsync(dfb, h_feedback, sizeof(double) * (size_t)n, cudaMemcpyHostToDevice, 0));
+    CK(cudaMemcpyAsync(dord, h_order, sizeof(int64_t) * (size_t)n, cudaMemcpyHostToDevice, 0));
+    CK(cudaMemcpyAsync(dst, h_starts, sizeof(int64_t) * (size_t)(n_groups + 1), cudaMemcpyHostToDevice, 0));
+    CK(cudaMemsetAsync(dskip, 1, (size_t)n, 0));
+    rl_q_kernel<<<(unsigned)((n_groups + 63) / 64), 64>>>((const int64_t*)dresp, (const double*)dfb, (const int64_t*)dord,
+                                                        (const int64_t*)dst, n_groups, q, alpha, pos_alfa, (double*)dvs,
+                                                        (uint8_t*)dskip);
+    CK(cudaGetLastError());
+    rl_choice_kernel<<<(unsigned)nb, kBlock>>>((const int64_t*)dresp, (const double*)dvs, (const uint8_t*)dskip, n, v, z,
+                                               p_outlier, w_outlier, (double*)ps, (int*)pz);
+    CK(cudaGetLastError());
+    finalize_kernel<<<1, 32>>>((const double*)ps, (const int*)pz, 1, (int)nb, 1, (double*)dout);
+    CK(cudaGetLastError());
+    count_launch(3);
+    CK(cudaMemcpyAsync(h_out, dout, sizeof(double), cudaMemcpyDeviceToHost, 0));
+    CK(cudaStreamSynchronize(0));
+    return 0;
+}
+
+// ---- RL-DDM with per-trial parameters (wfpt.pyx:390-433) ------------------------------------------------------------------
+int wfpt_like_multi_rlddm_host(const double* h_x, const int64_t* h_response, const double* h_feedback,
+                               const int64_t* h_split_by, int64_t n, double q, const double* const h_per_trial[8],
+                               const double scalars[8], double err, int n_st, int n_sz, int use_adaptive,
+                               double simps_err, double p_outlier, double w_outlier, int variant, double* h_out)
+{
+    Opts o;
+    if (check_opts(err, n_st, n_sz, use_adaptive, simps_err, variant, &o)) return 1;
+    if (n < 0) return fail("negative size");
+    if (!h_out || !scalars) return fail("null pointer argument");
+    if (n == 0) { *h_out = 0.0; return 0; }
+    if (!h_x || !h_response || !h_feedback || !h_split_by) return fail("null pointer argument");
+    for (int64_t i = 0; i < n; i++)
+        if (h_response[i] != 0 && h_response[i] != 1) return fail("response[%lld] is not 0/1", (long long)i);
+    // runs of equal split_by: Q is reset at every change between consecutive trials (:414-417)
+    int64_t n_runs = 1;
+    for (int64_t i = 1; i < n; i++) n_runs += (h_split_by[i] != h_split_by[i - 1]);
+    int64_t* runs = (int64_t*)malloc(sizeof(int64_t) * (size_t)(n_runs + 1));
+    if (!runs) return fail("out of host memory");
+    {
+        int64_t r = 0;
+        runs[r++] = 0;
+        for (int64_t i = 1; i < n; i++) if (h_split_by[i] != h_split_by[i - 1]) runs[r++] = i;
+        runs[r] = n;
+    }
+    void *dx, *dresp, *dfb, *druns, *dvs, *dalpha = nullptr, *dout;
+    int rc = 0;
+    const size_t bytes = sizeof(double) * (size_t)n;
+    const double* dptr[7];
+    if (scratch(kStageX, bytes, &dx) || scratch(kStageAux7, sizeof(int64_t) * (size_t)n, &dresp) ||
+        scratch(kStageAux8, bytes, &dfb) || scratch(kStageAux9, sizeof(int64_t) * (size_t)(n_runs + 1), &druns) ||
+        scratch(kStageAux10, bytes, &dvs) || scratch(kStageOut, sizeof(double), &dout)) { free(runs); return 1; }
+    cudaMemcpy(dx, h_x, bytes, cudaMemcpyHostToDevice);
+    cudaMemcpy(dresp, h_response, sizeof(int64_t) * (size_t)n, cudaMemcpyHostToDevice);
+    cudaMemcpy(dfb, h_feedback, bytes, cudaMemcpyHostToDevice);
+    cudaMemcpy(druns, runs, sizeof(int64_t) * (size_t)(n_runs + 1), cudaMemcpyHostToDevice);
+    free(runs);
+    for (int k = 0; k < 7; k++) {
+        dptr[k] = nullptr;
+        if (h_per_trial && h_per_trial[k]) {
+            void* d;
+            if (scratch(kStageAux0 + k, bytes, &d)) return 1;
+            CK(cudaMemcpy(d, h_per_trial[k], bytes, cudaMemcpyHostToDevice));
+            dptr[k] = (const double*)d;
+        }
+    }
+    if (h_per_trial && h_per_trial[7]) {
+        if (scratch(kStageAux11, bytes, &dalpha)) return 1;
+        CK(cudaMemcpy(dalpha, h_per_trial[7], bytes, cudaMemcpyHostToDevice));
+    }
+    rl_q_runs_kernel<<<(unsigned)((n_runs + 63) / 64), 64>>>((const int64_t*)dresp, (const double*)dfb, (const int64_t*)druns,
+                                                           n_runs, q, (const double*)dalpha, scalars[7], (double*)dvs);
+    CK(cudaGetLastError());
+    count_launch(1);
+    rc = run_multi((const double*)dx, n, dptr, scalars, o, p_outlier, w_outlier, (const double*)dvs, nullptr, 0, 0, variant,
+                   (double*)dout, 0);
+    if (rc) return rc;
     CK(cudaMemcpyAsync(h_out, dout, sizeof(double), cudaMemcpyDeviceToHost, 0));
     CK(cudaStreamSynchronize(0));
     return 0;

@@ -47,6 +47,7 @@ struct BatchArgs {
     int* part_zero;       // [P*slices] when slices>1, else nullptr
     double* out;          // [P]
     cudaStream_t stream;
+    const int64_t* seg = nullptr;  // optional [P][2] (device): set p is evaluated on x[seg[p][0] .. seg[p][1]) instead of all of x
 };
 
 cudaError_t launch_like_batch_faithful(const BatchArgs& a);

@@ -25,12 +25,21 @@ __global__ void __launch_bounds__(kBlock, 4) like_batch_kernel(const double* __r
                                                           const double* __restrict__ params, int64_t P, Opts o,
                                                           double w_outlier, int slices, int64_t chunk,
                                                           double* __restrict__ out_sum, int* __restrict__ out_zero,
+                                                          const int64_t* __restrict__ seg,
                                                           const __grid_constant__ typename Impl::Ctx ctx)
 {
     const int64_t bid = blockIdx.x;
     const int64_t p = bid / slices;
     const int s = (int)(bid - p * slices);
     if (p >= P) return;
+    if (seg) {
+        // segmented form: every parameter set has its own RT array (one PyMC node each), sliced the same way
+        const int64_t s0 = seg[2 * p];
+        x += s0;
+        n = seg[2 * p + 1] - s0;
+        chunk = (((n + slices - 1) / slices) + 1) & ~(int64_t)1;
+        if (chunk < 2) chunk = 2;
+    }
 
     const double* row = params + 8 * p;
     Params prm{row[0], row[1], row[2], row[3], row[4], row[5], row[6], row[7]};
@@ -61,7 +70,7 @@ __global__ void __launch_bounds__(kBlock, 4) like_batch_kernel(const double* __r
     const bool head = (reinterpret_cast<uintptr_t>(x + b) & 15) && b < end;
     if (head) b++;
     const int64_t npair = (end - b) >> 1;
-    const bool tail = (end - b) & 1;
+    const bool tail = (end > b) && ((end - b) & 1);
     const double2* x2 = reinterpret_cast<const double2*>(x + b);
     int64_t i = threadIdx.x;
     bool edges_done = false;

@@ -22,7 +22,7 @@ from ._lib import FAITHFUL, FAST, WfptError  # noqa: F401
 __all__ = [
     "pdf_array", "wiener_like", "wiener_like_rlddm", "wiener_like_rl", "wiener_like_multi", "wiener_like_multi_rlddm",
     "wiener_like_contaminant", "gen_rts_from_cdf", "gen_cdf_using_pdf", "split_cdf", "full_pdf", "wiener_like_batch", "sort_rts",
-    "set_variant", "get_variant",
+    "set_variant", "get_variant", "ResidentData", "wiener_like_segments",
 ]
 
 _variant = FAST
@@ -234,16 +234,122 @@ def wiener_like_rlddm(x, response, feedback, split_by, q, alpha, pos_alpha, v, s
     return float(res[0])
 
 
-def wiener_like_rl(*args, **kwargs):  # src/wfpt.pyx:270-354 -- next row
-    raise NotImplementedError("wiener_like_rl is not yet provided by hddm_b200")
+# ---- src/wfpt.pyx:270-354 ------------------------------------------------------------------------------------------------
+def wiener_like_rl(response, feedback, split_by, q, alpha, pos_alpha, v, z, err=1e-4, n_st=10, n_sz=10,
+                   use_adaptive=1, simps_err=1e-8, p_outlier=0, w_outlier=0):
+    response = _buffer(response, "response", np.int64)
+    feedback = _buffer(feedback, "feedback")
+    split_by = _buffer(split_by, "split_by", np.int64)
+    order, starts = _group_by_split(split_by)
+    res = np.empty(1, dtype=np.double)
+    L = _lib.load()
+    _lib.check(L.wfpt_like_rl_host(_ptr(response), _ptr(feedback), _ptr(order), _ptr(starts), len(starts) - 1,
+                                   response.shape[0], float(q), float(alpha), float(pos_alpha), float(v), float(z),
+                                   float(p_outlier), float(w_outlier), _ptr(res)))
+    return float(res[0])
 
 
-def wiener_like_multi_rlddm(*args, **kwargs):  # src/wfpt.pyx:390-433 -- next row
-    raise NotImplementedError("wiener_like_multi_rlddm is not yet provided by hddm_b200")
+# ---- src/wfpt.pyx:390-433 ------------------------------------------------------------------------------------------------
+def wiener_like_multi_rlddm(x, response, feedback, split_by, q, v, sv, a, z, sz, t, st, alpha, err, multi=None,
+                            n_st=10, n_sz=10, use_adaptive=1, simps_err=1e-3, p_outlier=0, w_outlier=0):
+    x = _buffer(x, "x")
+    response = _buffer(response, "response", np.int64)
+    feedback = _buffer(feedback, "feedback")
+    split_by = _buffer(split_by, "split_by", np.int64)
+    if multi is None:
+        raise TypeError("only size-1 arrays can be converted to Python scalars")  # wfpt.pyx:403-404, as in wiener_like_multi
+    vals = dict(v=v, sv=sv, a=a, z=z, sz=sz, t=t, st=st, alpha=alpha)
+    for name in multi:
+        if name not in vals:
+            raise KeyError(name)
+    n = x.shape[0]
+    keep, ptrs, scal = _pack_multi(_NAMES + ("alpha",), vals, multi, n)
+    res = np.empty(1, dtype=np.double)
+    L = _lib.load()
+    _lib.check(L.wfpt_like_multi_rlddm_host(_ptr(x), _ptr(response), _ptr(feedback), _ptr(split_by), n, float(q), ptrs,
+                                            scal, *_opts(err, n_st, n_sz, use_adaptive, simps_err), float(p_outlier),
+                                            float(w_outlier), _variant, _ptr(res)))
+    return float(res[0])
 
 
-def wiener_like_contaminant(*args, **kwargs):  # src/wfpt.pyx:551-580 -- next row
-    raise NotImplementedError("wiener_like_contaminant is not yet provided by hddm_b200")
+# ---- src/wfpt.pyx:551-580 ------------------------------------------------------------------------------------------------
+def wiener_like_contaminant(x, cont_x, v, sv, a, z, sz, t, st, t_min, t_max, err, n_st=10, n_sz=10, use_adaptive=1,
+                            simps_err=1e-8):
+    x = _buffer(x, "x")
+    cont_x = _buffer(cont_x, "cont_x", np.int32)
+    res = np.empty(1, dtype=np.double)
+    L = _lib.load()
+    _lib.check(L.wfpt_like_contaminant_host(_ptr(x), _ptr(cont_x), x.shape[0], float(v), float(sv), float(a), float(z),
+                                            float(sz), float(t), float(st), float(t_min), float(t_max),
+                                            *_opts(err, n_st, n_sz, use_adaptive, simps_err), _variant, _ptr(res)))
+    return float(res[0])
+
+
+# ---- one launch for all likelihood nodes of a hierarchical model -----------------------------------
+class ResidentData:
+    """RT arrays of many likelihood nodes (one per subject x condition, /root/reference/hddm/models/base.py:1488-1493)
+    kept resident on the GPU, so that an MCMC sweep sends only parameters.
+
+    The observed RTs never change while sampling; only the 8 parameters of each node do.  `ResidentData(arrays)`
+    uploads the arrays once (each |rt|-sorted, packed back to back on even offsets); `logp(params)` evaluates
+    wiener_like for every node -- params[i] belongs to arrays[i] -- in ONE kernel launch and returns float64[len(arrays)].
+    `logp(params, nodes=idx)` evaluates a subset (params[i] belongs to arrays[idx[i]]; a node may appear many times,
+    e.g. several proposals for the same node).  Needs torch (device memory and streams only)."""
+
+    def __init__(self, arrays, device=None):
+        import torch
+
+        self._torch = torch
+        self.device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+        arrs = [sort_rts(_buffer(np.asarray(a), "x")) for a in arrays]
+        self.lengths = np.array([len(a) for a in arrs], dtype=np.int64)
+        starts = np.zeros(len(arrs) + 1, dtype=np.int64)
+        pos = 0
+        for i, n in enumerate(self.lengths):
+            starts[i] = pos
+            pos += int(n) + (int(n) & 1)
+        starts[-1] = pos
+        packed = np.zeros(max(pos, 1), dtype=np.double)
+        for a, s0 in zip(arrs, starts[:-1]):
+            packed[s0:s0 + len(a)] = a
+        self.starts = starts[:-1].copy()
+        self.x = torch.from_numpy(packed).to(self.device)
+        self._seg_all = self._segments(np.arange(len(arrs)))
+        self.mean_len = int(max(1, self.lengths.mean())) if len(arrs) else 1
+
+    def _segments(self, nodes):
+        st = self.starts[nodes]
+        return np.ascontiguousarray(np.stack([st, st + self.lengths[nodes]], axis=1), dtype=np.int64)
+
+    def logp(self, params, nodes=None, err=1e-4, n_st=2, n_sz=2, use_adaptive=1, simps_err=1e-3, w_outlier=0.1,
+             variant=None):
+        torch = self._torch
+        var = _variant if variant is None else variant
+        seg = self._seg_all if nodes is None else self._segments(np.asarray(nodes, dtype=np.int64))
+        P = seg.shape[0]
+        if isinstance(params, np.ndarray):
+            ps = torch.from_numpy(np.ascontiguousarray(params, dtype=np.double)).to(self.device)
+            as_numpy = True
+        else:
+            ps, as_numpy = params.contiguous(), False
+        if ps.shape != (P, 8):
+            raise ValueError(f"params must have shape ({P}, 8)")
+        out = torch.empty(P, dtype=torch.float64, device=self.device)
+        if P == 0:
+            return out.cpu().numpy() if as_numpy else out
+        dseg = torch.from_numpy(seg.reshape(-1)).to(self.device)
+        L = _lib.load()
+        with torch.cuda.device(self.device):
+            s = torch.cuda.current_stream().cuda_stream
+            _lib.check(L.wfpt_like_segments(self.x.data_ptr(), dseg.data_ptr(), self.mean_len, ps.data_ptr(), P,
+                                            *_opts(err, n_st, n_sz, use_adaptive, simps_err), float(w_outlier), var,
+                                            out.data_ptr(), s))
+        return out.cpu().numpy() if as_numpy else out
+
+
+def wiener_like_segments(arrays, params, **kw):
+    """One-shot form of ResidentData: out[i] = wiener_like(arrays[i], *params[i, :7], ..., p_outlier=params[i, 7])."""
+    return ResidentData(arrays).logp(np.asarray(params, dtype=np.double), **kw)
 
 
 # ---- src/wfpt.pyx:517-548 ------------------------------------------------------------------------------------------------

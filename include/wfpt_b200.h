@@ -112,6 +112,37 @@ int wfpt_like_rlddm_host(const double* h_x, const int64_t* h_response, const dou
                          double st, double err, int n_st, int n_sz, int use_adaptive, double simps_err,
                          double p_outlier, double w_outlier, int variant, double* h_out);
 
+/* One RT array per parameter set: set p is evaluated on x[seg[p][0] .. seg[p][1]) (what a hierarchical model's logp
+ * sweep is: one wiener_like per (subject x condition) node, hddm/models/base.py:1488-1493, all in one launch; a
+ * segment may be named by several sets, e.g. several proposals for one node).  seg is int64[P][2] (start, end);
+ * mean_len (average segment length) only steers the launch geometry.  Each out[p] equals wiener_like on that segment
+ * (src/wfpt.pyx:54-76).  The _host form copies x[0 .. max end) to the device. */
+int wfpt_like_segments(const double* d_x, const int64_t* d_seg, int64_t mean_len, const double* d_params, int64_t P,
+                       double err, int n_st, int n_sz, int use_adaptive, double simps_err, double w_outlier, int variant,
+                       double* d_out, void* stream);
+int wfpt_like_segments_host(const double* h_x, const int64_t* h_seg, const double* h_params, int64_t P, double err,
+                            int n_st, int n_sz, int use_adaptive, double simps_err, double w_outlier, int variant,
+                            double* h_out);
+
+/* Replaces src/wfpt.pyx:551-580 (wiener_like_contaminant): trials with cont_x == 0 enter the diffusion likelihood (no
+ * outlier mix, -inf on the first zero density), the others contribute n_cont * log(0.5 / (t_max - t_min)). */
+int wfpt_like_contaminant_host(const double* h_x, const int32_t* h_cont, int64_t n, double v, double sv, double a, double z,
+                               double sz, double t, double st, double t_min, double t_max, double err, int n_st, int n_sz,
+                               int use_adaptive, double simps_err, int variant, double* h_out);
+
+/* Replaces src/wfpt.pyx:270-354 (wiener_like_rl): choice-only RL likelihood; grouping arguments as in
+ * wfpt_like_rlddm_host. */
+int wfpt_like_rl_host(const int64_t* h_response, const double* h_feedback, const int64_t* h_order, const int64_t* h_starts,
+                      int64_t n_groups, int64_t n, double q, double alpha, double pos_alpha, double v, double z,
+                      double p_outlier, double w_outlier, double* h_out);
+
+/* Replaces src/wfpt.pyx:390-433 (wiener_like_multi_rlddm): trials in array order, Q reset where split_by changes,
+ * per-trial parameters; per_trial[0..6] = v, sv, a, z, sz, t, st and per_trial[7] = alpha (NULL -> scalars[k]). */
+int wfpt_like_multi_rlddm_host(const double* h_x, const int64_t* h_response, const double* h_feedback,
+                               const int64_t* h_split_by, int64_t n, double q, const double* const h_per_trial[8],
+                               const double scalars[8], double err, int n_st, int n_sz, int use_adaptive,
+                               double simps_err, double p_outlier, double w_outlier, int variant, double* h_out);
+
 /* Simulators ------------------------------------------------------------------------------------------------- */
 
 /* Model ids: which Euler-Maruyama simulator of src/cddm_data_simulation.pyx runs, and the theta column order the

@@ -144,6 +144,53 @@ def test_rlddm(golden, wfpt_gpu, variant):
     assert f(xr, resp, fb, split, 0.5, -1.0, 100.0, 2.0, 0, 1.8, 0.5, 0, 0.3, 0, 1e-4, p_outlier=2.0) == -np.inf
 
 
+def test_rl_multi_rlddm_contaminant(golden, wfpt_gpu, variant):
+    g = golden
+    xr, resp, fb, split = g["rl_x"], g["rl_response"], g["rl_feedback"], g["rl_split"]
+    got = wfpt_gpu.wiener_like_rl(resp, fb, split, 0.5, -1.0, 100.0, 2.0, 0.5, p_outlier=0.05, w_outlier=0.1)
+    assert abs(got - float(g["rl_a"])) <= TOL * abs(got)
+    got = wfpt_gpu.wiener_like_rl(resp, fb, split, 0.5, -0.5, 0.7, 3.0, 0.45)
+    assert abs(got - float(g["rl_b"])) <= TOL * abs(got)
+    assert wfpt_gpu.wiener_like_rl(resp, fb, split, 0.5, -0.5, 0.7, 3.0, 0.45, p_outlier=-1) == -np.inf
+    got = wfpt_gpu.wiener_like_multi_rlddm(xr, resp, fb, g["rl_split_sorted"], 0.5, g["rl_v_arr"], 0, 1.8, 0.5, 0, 0.3, 0,
+                                           g["rl_alpha_arr"], 1e-4, ["v", "alpha"], p_outlier=0.05, w_outlier=0.1)
+    assert abs(got - float(g["multi_rlddm"])) <= TOL * abs(got)
+    got = wfpt_gpu.wiener_like_contaminant(xr, g["cont_x"], 1.0, 0.5, 1.8, 0.5, 0.1, 0.3, 0.1, 0.1, 5.0, 1e-4, n_st=2, n_sz=2,
+                                           use_adaptive=1, simps_err=1e-3)
+    assert abs(got - float(g["contaminant"])) <= TOL * abs(got)
+    # a non-contaminant trial with zero density -> -inf, contaminant term or not
+    assert wfpt_gpu.wiener_like_contaminant(xr, g["cont_x"], 1.0, 0.5, 1.8, 0.5, 0.1, 0.9, 0.1, 0.1, 5.0, 1e-4) == -np.inf
+
+
+def test_segments_resident_data(oracle, wfpt_gpu, variant):
+    """60 nodes of ragged length, one parameter set each (config 3's sweep), in one launch; subsets and repeats."""
+    rng = np.random.default_rng(33)
+    arrays = [np.where(rng.random(n) < 0.8, 1.0, -1.0) * rng.uniform(0.35, 3.0, n)
+              for n in rng.integers(1, 700, 60)]
+    arrays[7] = np.empty(0)          # an empty node contributes 0.0
+    P = len(arrays)
+    prm = np.stack([rng.normal(1, 0.5, P), rng.uniform(0, 1, P), rng.uniform(1.5, 2.5, P), rng.uniform(0.4, 0.6, P),
+                    rng.uniform(0, 0.2, P), rng.uniform(0.1, 0.3, P), rng.uniform(0, 0.15, P), np.full(P, 0.05)], axis=1)
+    kw = dict(err=1e-4, n_st=2, n_sz=2, use_adaptive=1, simps_err=1e-3, w_outlier=0.1)
+    want = np.array([oracle.wiener_like(a, *q[:7], 1e-4, n_st=2, n_sz=2, use_adaptive=1, simps_err=1e-3, p_outlier=q[7],
+                                        w_outlier=0.1) for a, q in zip(arrays, prm)])
+    rd = wfpt_gpu.ResidentData(arrays)
+    got = rd.logp(prm, variant=variant, **kw)
+    assert want[7] == 0.0 and got[7] == 0.0
+    assert rel_err(got, want) <= TOL
+    idx = np.array([3, 3, 59, 0, 3])
+    got = rd.logp(prm[idx], nodes=idx, variant=variant, **kw)
+    assert rel_err(got, want[idx]) <= TOL
+    got = wfpt_gpu.wiener_like_segments(arrays[:5], prm[:5], variant=variant, **kw)
+    assert rel_err(got, want[:5]) <= TOL
+    # one long node: the segment is cut into many slices
+    big = [np.where(rng.random(9001) < 0.8, 1.0, -1.0) * rng.uniform(0.35, 3.0, 9001), arrays[1]]
+    got = wfpt_gpu.ResidentData(big).logp(prm[:2], variant=variant, **kw)
+    w2 = [oracle.wiener_like(a, *q[:7], 1e-4, n_st=2, n_sz=2, use_adaptive=1, simps_err=1e-3, p_outlier=q[7], w_outlier=0.1)
+          for a, q in zip(big, prm[:2])]
+    assert rel_err(got, np.array(w2)) <= TOL
+
+
 def test_pdf_array_and_cdf_helpers(golden, oracle, wfpt_gpu, variant):
     g = golden
     got = wfpt_gpu.pdf_array(g["pdf_grid_x"], 0.7, 0.8, 1.6, 0.45, 0.2, 0.25, 0.15, 1e-4, 0, 2, 2, 1, 1e-3, 0.05, 0.1)
