@@ -20,8 +20,8 @@ __device__ __forceinline__ double mix_outlier(double p, double one_minus_po, dou
     return __dadd_rn(__dmul_rn(p, one_minus_po), wp);
 }
 
-template <class Impl>
-__global__ void __launch_bounds__(kBlock, 4) like_batch_kernel(const double* __restrict__ x, int64_t n,
+template <class Impl, int MINB = 4>
+__global__ void __launch_bounds__(kBlock, MINB) like_batch_kernel(const double* __restrict__ x, int64_t n,
                                                           const double* __restrict__ params, int64_t P, Opts o,
                                                           double w_outlier, int slices, int64_t chunk,
                                                           double* __restrict__ out_sum, int* __restrict__ out_zero,

@@ -59,6 +59,9 @@ struct Tables {
     double wt, ht;            // same along t
     double cz[2], ct;         // hz/(3 wz) per sign and ht/(3 wt): the fixed-grid Simpson scale as one multiplier
     double inv_wz[2], inv_wt; // reciprocal widths (first adaptive level)
+    double zstep[2];          // spacing of the staged z nodes per sign (lattice factor exp(-2 step / tt))
+    double wts_t[kMaxNodes];  // Simpson weights 1 4 2 ... 4 1 along t (fixed grid)
+    double wts_z[kMaxNodes];  // same along z
     double exptab[64];        // 2^(j/64)
     long long thr[kMaxPieces];  // series-term table (copy of the launch's KTable)
     int desc[kMaxPieces + 1];   // desc[0] = piece below thr[0]
@@ -99,24 +102,52 @@ __device__ __forceinline__ Tables& tables()
 // ---- exp ------------------------------------------------------------------------------------------------------------------
 // exp(x) = 2^e * 2^(j/64) * exp(r),  k = rint(64 x / ln 2) = 64 e + j,  r = x - k ln2/64, |r| <= 0.0055.
 // Branch-free; valid for |x| < 708 (normal results).  Max error 0.98 ulp (checked against mpmath).
+// The coefficients sit in constant memory: as literals the compiler re-materialises each one with two 32-bit moves
+// every time register pressure evicts it (16 % of the trial loop's instructions in the profile of the literal form).
+__constant__ double kExpC[10] = {
+    92.33248261689366,         // 64 / ln 2
+    6755399441055744.0,        // 1.5 * 2^52: adding it leaves rint(x * 64/ln2) in the low word
+    -0.01083042469326756,      // -(ln2/64) high part (32 bits: kd * hi is exact)
+    -2.9815858269852933e-12,   // -(ln2/64) low part
+    1.0 / 120.0, 1.0 / 24.0, 1.0 / 6.0, 0.5, 1.0, 0.0};
+
 __device__ __forceinline__ double exp_core(double x, const double* __restrict__ tab)
 {
-    const double t = fma(x, 92.33248261689366, 6755399441055744.0);
+    const double t = fma(x, kExpC[0], kExpC[1]);
     const int ki = __double2loint(t);
-    const double kd = t - 6755399441055744.0;
-    double r = fma(kd, -0.01083042469326756, x);          // ln2/64 high part (32 bits: kd * hi is exact)
-    r = fma(kd, -2.9815858269852933e-12, r);              // low part
-    double p = fma(r, 1.0 / 120.0, 1.0 / 24.0);
-    p = fma(p, r, 1.0 / 6.0);
-    p = fma(p, r, 0.5);
-    p = fma(p, r, 1.0);
+    const double kd = t - kExpC[1];
+    double r = fma(kd, kExpC[2], x);
+    r = fma(kd, kExpC[3], r);
+    double p = fma(r, kExpC[4], kExpC[5]);
+    p = fma(p, r, kExpC[6]);
+    p = fma(p, r, kExpC[7]);
+    p = fma(p, r, kExpC[8]);
     p = p * r;                                            // exp(r) - 1
     const double T = tab[ki & 63];
     const double res = fma(T, p, T);
-    return __hiloint2double(__double2hiint(res) + ((ki >> 6) << 20), __double2loint(res));
+    return __hiloint2double(__double2hiint(res) + ((ki << 14) & 0xfff00000), __double2loint(res));
 }
 // |x| < 708 (and not NaN), tested on the high word so that it costs no FP64-pipe slot
 __device__ __forceinline__ bool exp_arg_ok(double x) { return (unsigned)(__double2hiint(x) & 0x7fffffff) < 0x40862000u; }
+// exp of a non-positive argument whose true value may underflow: 0 below the kernel's range
+__device__ __forceinline__ double exp_core_or_zero(double x, const double* __restrict__ tab)
+{
+    const double v = exp_core(x, tab);
+    return exp_arg_ok(x) ? v : 0.0;
+}
+
+// 1/sqrt(x) for normal positive x: hardware seed + two Newton steps (straight-line; <= 2 ulp)
+__device__ __forceinline__ double rsqrt_fast(double x)
+{
+    double y;
+    asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
+    const double hx = 0.5 * x;
+    double e = fma(-hx * y, y, 0.5);
+    y = fma(y, e, y);
+    e = fma(-hx * y, y, 0.5);
+    y = fma(y, e, y);
+    return y;
+}
 
 // ---- series-term lookup -----------------------------------------------------------------------------------------------
 // Walk from the piece of the previous lookup to the piece holding tt.  Returns (small << 8) | K.
@@ -164,12 +195,12 @@ __device__ __forceinline__ void make_tnode(TNode& tn, double xp, Set& s)
     double rs = 1.0;
     tn.c = 0.5;
     if (s.sv_nonzero) {
-        rs = rsqrt(fma(s.sv2, xp, 1.0));  // 1/sqrt(sv^2 x' + 1)
+        rs = rsqrt_fast(fma(s.sv2, xp, 1.0));  // 1/sqrt(sv^2 x' + 1)
         tn.c = 0.5 * rs * rs;
     }
     tn.E0 = -s.v2 * xp * tn.c;
     if (tn.small) {
-        const double r = rsqrt(tt);
+        const double r = rsqrt_fast(tt);
         tn.inv_tt = r * r;
         tn.pref = tn.inv_tt * r * (kInvSqrt2Pi * s.inv_a2) * rs;  // tt^-3/2 / sqrt(2 pi) / a^2 / sqrt(sv^2 x'+1)
     } else {
@@ -197,9 +228,16 @@ static __device__ __noinline__ double series_small_slow(double w, int K, double 
     return sum;
 }
 
-// N consecutive z-nodes (j0 .. j0+N-1) of one t-node: pdf_sv(x', v', sv, a, z_j, err) from the staged tables.
+// N consecutive, equally spaced z-nodes (j0 .. j0+N-1) of one t-node: pdf_sv(x', v', sv, a, z_j, err) from the staged
+// tables.  `neg` collects the sign bits of the series sums (pdf_sv turns a negative truncated series into NaN).
+//
+// Small-time nodes: with e0_n = exp(-z_n^2/(2tt) + E_n) (the k = 0 term, evaluated directly), the neighbouring terms are
+//   e(k=+1)/e0 = R_n = exp(-2(z_n+1)/tt),   e(k=-1)/e0 = Q_n = exp(-2(1-z_n)/tt),   e(k=+2)/e(k=+1) = R_n * H,
+// H = R_n Q_n = exp(-4/tt), and along equally spaced nodes R_n = R_0 rho^n, Q_n = Q_last rho^(last-n) with
+// rho = exp(-2 step/tt).  All factors are <= 1, so nothing overflows, and the dominant term keeps full accuracy:
+// a t-node with N z-nodes costs N + 3 exps whatever K is (K <= 4; larger K takes the term-by-term routine).
 template <int N>
-__device__ __forceinline__ void nodes(const TNode& tn, const Set& s, int sign, int j0, double* __restrict__ y)
+__device__ __forceinline__ void nodes(const TNode& tn, const Set& s, int sign, int j0, double* __restrict__ y, int& neg)
 {
     if (!tn.alive) {
 #pragma unroll
@@ -215,37 +253,35 @@ __device__ __forceinline__ void nodes(const TNode& tn, const Set& s, int sign, i
 
     if (tn.small) {
         const int K = tn.K;
+        const double tau = tn.inv_tt, m2t = -2.0 * tau;
         bool ok = (K <= 4);
-        if (K >= 4) {
-            double a[N][4];
+        double e0[N];
 #pragma unroll
-            for (int n = 0; n < N; n++)
+        for (int n = 0; n < N; n++) {
+            const double a = fma(Z[n].uh[1], tau, E[n]);
+            ok &= exp_arg_ok(a);
+            e0[n] = exp_core(a, tab);
+        }
+        const double z_first = Z[0].u[1], z_last = Z[N - 1].u[1];
+        double R = exp_core_or_zero(fma(m2t, z_first, m2t), tab);            // exp(-2 (z_0 + 1) / tt)
+        double Q = exp_core_or_zero(fma(-m2t, z_last, m2t), tab);            // exp(-2 (1 - z_last) / tt)
+        if (K < 3) Q = 0.0;                                                  // K == 2 sums k = 0, 1 only
+        const double rho = (N > 1) ? exp_core_or_zero(m2t * T.zstep[sign], tab) : 1.0;
+        double Rn[N], Qn[N];
+        Rn[0] = R;
+        Qn[N - 1] = Q;
 #pragma unroll
-                for (int k = 0; k < 4; k++) {
-                    a[n][k] = fma(Z[n].uh[k], tn.inv_tt, E[n]);
-                    ok &= exp_arg_ok(a[n][k]);
-                }
+        for (int n = 1; n < N; n++) {
+            Rn[n] = Rn[n - 1] * rho;
+            Qn[N - 1 - n] = Qn[N - n] * rho;
+        }
+        const double H = Rn[0] * Qn[0];  // exp(-4/tt); only the k = 2 term (K >= 4) needs it
 #pragma unroll
-            for (int n = 0; n < N; n++) {
-                const double em = exp_core(a[n][0], tab), e0 = exp_core(a[n][1], tab);
-                const double e1 = exp_core(a[n][2], tab), e2 = exp_core(a[n][3], tab);
-                y[n] = fma(Z[n].u[3], e2, fma(Z[n].u[2], e1, fma(Z[n].u[1], e0, Z[n].u[0] * em)));
-            }
-        } else {
-            double a[N][3];
-#pragma unroll
-            for (int n = 0; n < N; n++)
-#pragma unroll
-                for (int k = 0; k < 3; k++) {
-                    a[n][k] = fma(Z[n].uh[k], tn.inv_tt, E[n]);
-                    ok &= exp_arg_ok(a[n][k]);
-                }
-            const double keep_m = (K >= 3) ? 1.0 : 0.0;  // K == 2 sums k = 0, 1 only
-#pragma unroll
-            for (int n = 0; n < N; n++) {
-                const double em = exp_core(a[n][0], tab), e0 = exp_core(a[n][1], tab), e1 = exp_core(a[n][2], tab);
-                y[n] = fma(Z[n].u[2], e1, fma(Z[n].u[1], e0, keep_m * (Z[n].u[0] * em)));
-            }
+        for (int n = 0; n < N; n++) {
+            double inner = fma(Z[n].u[2], Rn[n], Z[n].u[1]);
+            inner = fma(Z[n].u[0], Qn[n], inner);
+            if (K >= 4) inner = fma(Z[n].u[3], Rn[n] * Rn[n] * H, inner);
+            y[n] = fma(e0[n], inner, 0.0);  // + 0.0: an underflowed e0 times a negative sum must give +0, not -0
         }
         if (!ok) {
 #pragma unroll 1
@@ -273,13 +309,13 @@ __device__ __forceinline__ void nodes(const TNode& tn, const Set& s, int sign, i
                 }
             }
             if (tn.K < 1) acc = 0.0;
-            y[n] = acc * (ok ? exp_core(E[n], tab) : exp(E[n]));
+            y[n] = fma(acc, ok ? exp_core(E[n], tab) : exp(E[n]), 0.0);
         }
     }
 #pragma unroll
     for (int n = 0; n < N; n++) {
-        // log(p) of a negative truncated series is NaN in pdf_sv (pdf.pxi:102); pdf (sv == 0) lets it through
-        y[n] = (s.sv_nonzero && y[n] < 0.0) ? CUDART_NAN : y[n] * tn.pref;
+        y[n] *= tn.pref;                    // pref > 0: the sign is the series sum's
+        neg |= __double2hiint(y[n]);
     }
 }
 
@@ -367,10 +403,11 @@ __device__ __forceinline__ void prepare(Set& s, const Params& prm, const Opts& o
         if (threadIdx.x == 0) {
             T.wt = wt;
             T.ht = ht;
-            T.ct = ht / (3.0 * wt);
+            T.ct = (nt_div > 0) ? ht / (3.0 * wt) : 1.0;
             T.inv_wt = 1.0 / wt;
         }
         for (int i = threadIdx.x; i < ntn; i += blockDim.x) {
+            T.wts_t[i] = (i == 0 || i == ntn - 1) ? 1.0 : ((i & 1) ? 4.0 : 2.0);
             double ti;
             if (ntn == 1) ti = t;
             else if (mode == kModeFixed) ti = __dadd_rn(lb, __dmul_rn(ht, (double)i));
@@ -403,11 +440,13 @@ __device__ __forceinline__ void prepare(Set& s, const Params& prm, const Opts& o
         T.wz[sign] = w;
         const double hz = (mode == kModeFixed && nz_div > 0) ? __ddiv_rn(w, (double)nz_div) : 0.0;
         T.hz[sign] = hz;
+        T.zstep[sign] = (nzn > 1) ? w / (double)(nzn - 1) : 0.0;
         T.cz[sign] = hz / (3.0 * w);
         T.inv_wz[sign] = 1.0 / w;
     }
     // one (sign, node, slot) entry per thread: slots 0..3 = lattice k = -1..2, slot 4 = A, slots 5.. = sines
     constexpr int kSlots = 5 + kMaxKLarge;
+    for (int j = threadIdx.x; j < nzn; j += blockDim.x) T.wts_z[j] = (j == 0 || j == nzn - 1) ? 1.0 : ((j & 1) ? 4.0 : 2.0);
     for (int idx = threadIdx.x; idx < 2 * nzn * kSlots; idx += blockDim.x) {
         const int slot = idx % kSlots, r = idx / kSlots;
         const int sign = r / nzn, j = r - sign * nzn;
@@ -431,17 +470,17 @@ __device__ __forceinline__ void prepare(Set& s, const Params& prm, const Opts& o
 }
 
 // Inner z-integral at one t-node: a single node, a fixed grid, or the first adaptive level (ok &= converged).
-__device__ __forceinline__ double inner_z(const TNode& tn, const Set& s, int sign, bool* ok)
+__device__ __forceinline__ double inner_z(const TNode& tn, const Set& s, int sign, bool* ok, int& neg)
 {
     if (s.nz == 0) {
         double y;
-        nodes<1>(tn, s, sign, 0, &y);
+        nodes<1>(tn, s, sign, 0, &y, neg);
         return y;
     }
     const Tables& T = *s.tab;
     if (s.mode == kModeAdaptive) {
         double y[5];
-        nodes<5>(tn, s, sign, 0, y);
+        nodes<5>(tn, s, sign, 0, y, neg);
         const double iw = T.inv_wz[sign];
         double val;
         *ok &= adaptive_level1(y[0] * iw, y[1] * iw, y[2] * iw, y[3] * iw, y[4] * iw, T.wz[sign], s.simps_err,
@@ -452,15 +491,15 @@ __device__ __forceinline__ double inner_z(const TNode& tn, const Set& s, int sig
     double S;
     if (s.nz == 2) {
         double y[3];
-        nodes<3>(tn, s, sign, 0, y);
+        nodes<3>(tn, s, sign, 0, y, neg);
         S = fma(4.0, y[1], y[0]) + y[2];
     } else {
         double y;
         S = 0.0;
 #pragma unroll 1
         for (int j = 0; j <= s.nz; j++) {
-            nodes<1>(tn, s, sign, j, &y);
-            S = fma((j == 0 || j == s.nz) ? 1.0 : ((j & 1) ? 4.0 : 2.0), y, S);
+            nodes<1>(tn, s, sign, j, &y, neg);
+            S = fma(T.wts_z[j], y, S);
         }
     }
     return S * T.cz[sign];
@@ -482,6 +521,7 @@ __device__ __forceinline__ double density(double x, Set& s, bool* defer)
     if ((ax - s.tlo) < 0) return 0.0;  // pdf.pxi:112, the trial-dependent part
     const int sign = x > 0;
     bool ok = true;
+    int neg = 0;
     TNode tn;
     const bool adaptive = (s.mode == kModeAdaptive) && (s.nt > 0);
     double g[5];
@@ -489,13 +529,15 @@ __device__ __forceinline__ double density(double x, Set& s, bool* defer)
 #pragma unroll 1
     for (int i = 0; i <= s.nt; i++) {
         make_tnode(tn, ax - T.tn[i], s);  // tn[0] == t when the t axis is not integrated
-        const double y = inner_z(tn, s, sign, &ok);
+        const double y = inner_z(tn, s, sign, &ok, neg);
         if (adaptive) g[i] = y * T.inv_wt;
-        else S = fma((i == 0 || i == s.nt) ? 1.0 : ((i & 1) ? 4.0 : 2.0), y, S);
+        else S = fma(T.wts_t[i], y, S);
     }
     double result;
     if (adaptive) ok &= adaptive_level1(g[0], g[1], g[2], g[3], g[4], T.wt, s.simps_err, s.depth_t, &result);
-    else result = (s.nt == 0) ? S : S * T.ct;
+    else result = S * T.ct;  // ct == 1 when the t axis is not integrated
+    // a negative truncated series anywhere makes pdf_sv's log(p) NaN (pdf.pxi:102); pdf (sv == 0) lets it through
+    if (s.sv_nonzero && neg < 0) result = CUDART_NAN;
     *defer = !ok;
     return result;
 }
