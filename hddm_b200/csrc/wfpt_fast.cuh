@@ -79,6 +79,8 @@ struct Set {
     int depth_z, depth_t;  // adaptive recursion budgets (n_sz, n_st)
     int npieces;           // thresholds in the series-term table
     int piece;             // piece of the last lookup (walk start)
+    int piece_desc;        // its descriptor, and the bit patterns bounding it: lo_b <= bits(tt) < hi_b
+    long long lo_b, hi_b;
     double simps_err;
     double t;
     double tlo;            // t - st/2 (validity bound on |x|)
@@ -150,13 +152,24 @@ __device__ __forceinline__ double rsqrt_fast(double x)
 }
 
 // ---- series-term lookup -----------------------------------------------------------------------------------------------
-// Walk from the piece of the previous lookup to the piece holding tt.  Returns (small << 8) | K.
-__device__ __forceinline__ int klookup(const Tables& T, int n, double tt, int& p)
+// (small << 8) | K for this tt.  The thread keeps the piece of its previous lookup with its bounds in registers: RTs are
+// |rt|-sorted, so the next tt nearly always falls into the same piece and the lookup is two 64-bit compares; otherwise
+// walk to the right piece through the shared-memory copy of the table.
+__device__ __forceinline__ int klookup(Set& s, double tt)
 {
     const long long b = __double_as_longlong(tt);
-    while (p < n && b >= T.thr[p]) p++;
-    while (p > 0 && b < T.thr[p - 1]) p--;
-    return T.desc[p];
+    if (b < s.lo_b || b >= s.hi_b) {
+        const Tables& T = *s.tab;
+        int p = s.piece;
+        const int n = s.npieces;
+        while (p < n && b >= T.thr[p]) p++;
+        while (p > 0 && b < T.thr[p - 1]) p--;
+        s.piece = p;
+        s.piece_desc = T.desc[p];
+        s.lo_b = (p > 0) ? T.thr[p - 1] : (long long)0x8000000000000000ull;
+        s.hi_b = (p < n) ? T.thr[p] : (long long)0x7fffffffffffffffull;
+    }
+    return s.piece_desc;
 }
 
 // Scan form for callers without shared tables (per-trial parameter sets).
@@ -189,7 +202,7 @@ __device__ __forceinline__ void make_tnode(TNode& tn, double xp, Set& s)
     // tt = x'/a^2, correctly rounded from the reciprocal (quotient + one residual correction): K is decided on it
     const double q0 = xp * s.inv_a2;
     const double tt = fma(fma(-q0, s.a2, xp), s.inv_a2, q0);
-    const int d = klookup(T, s.npieces, tt, s.piece);
+    const int d = klookup(s, tt);
     tn.small = d >> 8;
     tn.K = d & 0xff;
     double rs = 1.0;
@@ -284,7 +297,7 @@ __device__ __forceinline__ void nodes(const TNode& tn, const Set& s, int sign, i
             y[n] = fma(e0[n], inner, 0.0);  // + 0.0: an underflowed e0 times a negative sum must give +0, not -0
         }
         if (!ok) {
-#pragma unroll 1
+#pragma unroll  // (a rolled loop would index y[] dynamically and push the whole array into local memory)
             for (int n = 0; n < N; n++) y[n] = series_small_slow(Z[n].u[1], K, tn.inv_tt, E[n]);
         }
     } else {
@@ -352,6 +365,9 @@ __device__ __forceinline__ void prepare(Set& s, const Params& prm, const Opts& o
     s.depth_t = o.n_st;
     s.npieces = kt.n;
     s.piece = 0;
+    s.piece_desc = 0;
+    s.lo_b = 1;   // empty interval: the first lookup walks
+    s.hi_b = 0;
     s.nz = s.nt = 0;
     // pdf.pxi:111-113, the trial-independent part
     const bool bad = (z < 0) || (z > 1) || (a < 0) || (t < 0) || (st < 0) || (sv < 0) || (sz < 0) || (sz > 1) ||
