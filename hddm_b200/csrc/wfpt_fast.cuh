@@ -68,6 +68,9 @@ struct Tables {
     Params prm;               // raw parameter set and options (generic fallback only)
     Opts o;
     int qcount;               // trials parked for the generic evaluator (adaptive refinement needed)
+    int depth_z, depth_t;     // adaptive recursion budgets (n_sz, n_st)
+    int npieces;              // thresholds in the series-term table
+    double simps_err;
     double queue[kQueue];
 };
 
@@ -76,13 +79,11 @@ struct Set {
     int mode;
     int nz, nt;            // intervals along z / t used by the table paths (0: axis not integrated)
     int sv_nonzero;
-    int depth_z, depth_t;  // adaptive recursion budgets (n_sz, n_st)
-    int npieces;           // thresholds in the series-term table
+    int kl_max;            // largest large-time K of the table
+    int kind;              // which specialised trial evaluator applies (see density)
     int piece;             // piece of the last lookup (walk start)
     int piece_desc;        // its descriptor, and the bit patterns bounding it: lo_b <= bits(tt) < hi_b
     long long lo_b, hi_b;
-    double simps_err;
-    double t;
     double tlo;            // t - st/2 (validity bound on |x|)
     double v2, sv2, a2, inv_a2;
     const Tables* tab;
@@ -161,7 +162,7 @@ __device__ __forceinline__ int klookup(Set& s, double tt)
     if (b < s.lo_b || b >= s.hi_b) {
         const Tables& T = *s.tab;
         int p = s.piece;
-        const int n = s.npieces;
+        const int n = T.npieces;
         while (p < n && b >= T.thr[p]) p++;
         while (p > 0 && b < T.thr[p - 1]) p--;
         s.piece = p;
@@ -220,10 +221,11 @@ __device__ __forceinline__ void make_tnode(TNode& tn, double xp, Set& s)
         const double qa = -kHalfPiSq * tt;
         const double q = exp_arg_ok(qa) ? exp_core(qa, T.exptab) : exp(qa);
         const double q2 = q * q, q4 = q2 * q2, q8 = q4 * q4;
-        tn.q1 = q;
-        tn.q4 = q4;
-        tn.q9 = q8 * q;
-        tn.q16 = q8 * q8;
+        // powers beyond this node's K are zeroed here so that the node sum below needs no per-term test
+        tn.q1 = (tn.K > 0) ? q : 0.0;
+        tn.q4 = (tn.K > 1) ? q4 : 0.0;
+        tn.q9 = (tn.K > 2) ? q8 * q : 0.0;
+        tn.q16 = (tn.K > 3) ? q8 * q8 : 0.0;
         tn.pref = kPi * s.inv_a2 * rs;
     }
 }
@@ -302,16 +304,21 @@ __device__ __forceinline__ void nodes(const TNode& tn, const Set& s, int sign, i
         }
     } else {
         bool ok = true;
+        double ex[N];
 #pragma unroll
-        for (int n = 0; n < N; n++) ok &= exp_arg_ok(E[n]);
+        for (int n = 0; n < N; n++) {
+            ok &= exp_arg_ok(E[n]);
+            ex[n] = exp_core(E[n], tab);
+        }
+        if (!ok) {
+#pragma unroll
+            for (int n = 0; n < N; n++) ex[n] = exp(E[n]);
+        }
 #pragma unroll
         for (int n = 0; n < N; n++) {
             const double* S = Z[n].S;
-            double acc = tn.q1 * S[0];
-            if (tn.K > 1) acc = fma(tn.q4, S[1], acc);
-            if (tn.K > 2) acc = fma(tn.q9, S[2], acc);
-            if (tn.K > 3) acc = fma(tn.q16, S[3], acc);
-            if (tn.K > 4) {
+            double acc = fma(tn.q16, S[3], fma(tn.q9, S[2], fma(tn.q4, S[1], tn.q1 * S[0])));
+            if (s.kl_max > 4 && tn.K > 4) {           // first test is uniform over the launch
                 const double q2 = tn.q1 * tn.q1;
                 double odd = tn.q4 * tn.q4 * tn.q1;  // q^9 = q^(25-16)
                 double qk = tn.q16;
@@ -321,8 +328,7 @@ __device__ __forceinline__ void nodes(const TNode& tn, const Set& s, int sign, i
                     acc = fma(qk, S[k], acc);
                 }
             }
-            if (tn.K < 1) acc = 0.0;
-            y[n] = fma(acc, ok ? exp_core(E[n], tab) : exp(E[n]), 0.0);
+            y[n] = fma(acc, ex[n], 0.0);
         }
     }
 #pragma unroll
@@ -353,17 +359,14 @@ __device__ __forceinline__ void prepare(Set& s, const Params& prm, const Opts& o
     s.tab = &T;
     const double z = prm.z, a = prm.a, t = prm.t, sv = prm.sv;
     double sz = prm.sz, st = prm.st;
-    s.t = t;
     s.tlo = t - st / 2.;
     s.v2 = prm.v * prm.v;
     s.sv2 = sv * sv;
     s.a2 = a * a;
     s.inv_a2 = 1.0 / s.a2;
     s.sv_nonzero = (sv != 0);
-    s.simps_err = o.simps_err;
-    s.depth_z = o.n_sz;
-    s.depth_t = o.n_st;
-    s.npieces = kt.n;
+    s.kl_max = kt.kl_max;
+    s.kind = 0;
     s.piece = 0;
     s.piece_desc = 0;
     s.lo_b = 1;   // empty interval: the first lookup walks
@@ -389,6 +392,10 @@ __device__ __forceinline__ void prepare(Set& s, const Params& prm, const Opts& o
         T.prm = prm;
         T.o = o;
         T.qcount = 0;
+        T.simps_err = o.simps_err;
+        T.depth_z = o.n_sz;
+        T.depth_t = o.n_st;
+        T.npieces = kt.n;
     }
     if (mode == kModeZero || mode == kModeGeneric) {
         __syncthreads();
@@ -408,6 +415,9 @@ __device__ __forceinline__ void prepare(Set& s, const Params& prm, const Opts& o
         s.nz = (sz == 0) ? 0 : 4;
         s.nt = (st == 0) ? 0 : 4;
     }
+    if (mode == kModeFixed) s.kind = (s.nz == 0) ? 0 : (s.nz == 2 ? 1 : 2);
+    else if (mode == kModeAdaptive) s.kind = (s.nz > 0) ? (s.nt > 0 ? 3 : 4) : 5;
+    else s.kind = 0;
     const int nzn = s.nz + 1, ntn = s.nt + 1;
     const int nz_div = s.nz, nt_div = s.nt;
 
@@ -485,27 +495,29 @@ __device__ __forceinline__ void prepare(Set& s, const Params& prm, const Opts& o
     __syncthreads();
 }
 
-// Inner z-integral at one t-node: a single node, a fixed grid, or the first adaptive level (ok &= converged).
-__device__ __forceinline__ double inner_z(const TNode& tn, const Set& s, int sign, bool* ok, int& neg)
+// Inner z-integral at one t-node.  NZN: staged z-nodes (1: no z-integration, 3: fixed grid n_sz = 2, 5: first adaptive
+// level, 0: fixed grid of any size, one node at a time).  ok &= "the adaptive recursion would stop here".
+template <int NZN>
+__device__ __forceinline__ double inner_t(const TNode& tn, const Set& s, int sign, bool* ok, int& neg)
 {
-    if (s.nz == 0) {
+    const Tables& T = *s.tab;
+    if (NZN == 1) {
         double y;
         nodes<1>(tn, s, sign, 0, &y, neg);
         return y;
     }
-    const Tables& T = *s.tab;
-    if (s.mode == kModeAdaptive) {
+    if (NZN == 5) {
         double y[5];
         nodes<5>(tn, s, sign, 0, y, neg);
         const double iw = T.inv_wz[sign];
         double val;
-        *ok &= adaptive_level1(y[0] * iw, y[1] * iw, y[2] * iw, y[3] * iw, y[4] * iw, T.wz[sign], s.simps_err,
-                               s.depth_z, &val);
+        *ok &= adaptive_level1(y[0] * iw, y[1] * iw, y[2] * iw, y[3] * iw, y[4] * iw, T.wz[sign], T.simps_err,
+                               T.depth_z, &val);
         return val;
     }
     // integrate.pxi:30-45: S = f(0) + 4 f(odd) + 2 f(even) - f(n), then (h/3) * S / width
     double S;
-    if (s.nz == 2) {
+    if (NZN == 3) {
         double y[3];
         nodes<3>(tn, s, sign, 0, y, neg);
         S = fma(4.0, y[1], y[0]) + y[2];
@@ -521,14 +533,40 @@ __device__ __forceinline__ double inner_z(const TNode& tn, const Set& s, int sig
     return S * T.cz[sign];
 }
 
+template <int NZN, bool ADAPT_T>
+__device__ __forceinline__ double density_t(double ax, int sign, Set& s, bool* ok, int& neg)
+{
+    const Tables& T = *s.tab;
+    TNode tn;
+    if (ADAPT_T) {
+        // first level of the reference's recursion over t on the staged quarter points
+        double g[5];
+#pragma unroll 1
+        for (int i = 0; i < 5; i++) {
+            make_tnode(tn, ax - T.tn[i], s);
+            g[i] = inner_t<NZN>(tn, s, sign, ok, neg) * T.inv_wt;
+        }
+        double result;
+        *ok &= adaptive_level1(g[0], g[1], g[2], g[3], g[4], T.wt, T.simps_err, T.depth_t, &result);
+        return result;
+    }
+    double S = 0.0;
+#pragma unroll 1
+    for (int i = 0; i <= s.nt; i++) {
+        make_tnode(tn, ax - T.tn[i], s);  // tn[0] == t when the t axis is not integrated
+        S = fma(T.wts_t[i], inner_t<NZN>(tn, s, sign, ok, neg), S);
+    }
+    return S * T.ct;  // ct == 1 when the t axis is not integrated
+}
+
 // Density of one trial from the staged tables.  *defer is set (and the return value is meaningless) when the
 // reference's adaptive recursion would go below the first level for this trial: the caller evaluates those trials
 // with density_generic, preferably all together at the end (a CTA-wide pass instead of one diverged lane at a time).
+// s.kind (uniform over the CTA) picks the evaluator specialised for this parameter set's integration layout.
 __device__ __forceinline__ double density(double x, Set& s, bool* defer)
 {
     *defer = false;
     if (s.mode == kModeZero) return 0.0;
-    const Tables& T = *s.tab;
     if (s.mode == kModeGeneric) {
         *defer = true;
         return 0.0;
@@ -538,20 +576,14 @@ __device__ __forceinline__ double density(double x, Set& s, bool* defer)
     const int sign = x > 0;
     bool ok = true;
     int neg = 0;
-    TNode tn;
-    const bool adaptive = (s.mode == kModeAdaptive) && (s.nt > 0);
-    double g[5];
-    double S = 0.0;
-#pragma unroll 1
-    for (int i = 0; i <= s.nt; i++) {
-        make_tnode(tn, ax - T.tn[i], s);  // tn[0] == t when the t axis is not integrated
-        const double y = inner_z(tn, s, sign, &ok, neg);
-        if (adaptive) g[i] = y * T.inv_wt;
-        else S = fma(T.wts_t[i], y, S);
-    }
     double result;
-    if (adaptive) ok &= adaptive_level1(g[0], g[1], g[2], g[3], g[4], T.wt, s.simps_err, s.depth_t, &result);
-    else result = S * T.ct;  // ct == 1 when the t axis is not integrated
+    const int kind = s.kind;
+    if (kind == 0) result = density_t<1, false>(ax, sign, s, &ok, neg);        // no z-integration, fixed or no t-grid
+    else if (kind == 1) result = density_t<3, false>(ax, sign, s, &ok, neg);   // fixed grid, n_sz = 2 (any n_st)
+    else if (kind == 3) result = density_t<5, true>(ax, sign, s, &ok, neg);    // adaptive over z and t
+    else if (kind == 4) result = density_t<5, false>(ax, sign, s, &ok, neg);   // adaptive over z only
+    else if (kind == 5) result = density_t<1, true>(ax, sign, s, &ok, neg);    // adaptive over t only
+    else result = density_t<0, false>(ax, sign, s, &ok, neg);                  // fixed grid, other n_sz
     // a negative truncated series anywhere makes pdf_sv's log(p) NaN (pdf.pxi:102); pdf (sv == 0) lets it through
     if (s.sv_nonzero && neg < 0) result = CUDART_NAN;
     *defer = !ok;
