@@ -16,6 +16,7 @@ struct FaithfulImpl {
         s.prm = prm;
         s.o = o;
     }
+    template <bool ADAPT>
     __device__ static __forceinline__ double density(double x, const Set& s, const Ctx&, bool* defer)
     {
         *defer = false;
@@ -24,8 +25,12 @@ struct FaithfulImpl {
     __device__ static __forceinline__ double density_generic(double x, const Set& s, const Ctx& c)
     {
         bool d;
-        return density(x, s, c, &d);
+        return density<true>(x, s, c, &d);
     }
+    static constexpr bool kParks = false;
+    static constexpr int kParkCapacity = 0;
+    __device__ static __forceinline__ bool may_park(const Set&) { return false; }
+    __device__ static __forceinline__ void parked_reset(const Set&) {}
     __device__ static __forceinline__ bool park(Set&, double) { return false; }
     __device__ static __forceinline__ int parked_count(const Set&) { return 0; }
     __device__ static __forceinline__ double parked(const Set&, int) { return 0.0; }
@@ -40,7 +45,7 @@ cudaError_t launch_like_batch_faithful(const BatchArgs& a)
 {
     const int64_t nblk = a.P * (int64_t)a.slices;
     if (nblk == 0) return cudaSuccess;
-    like_batch_kernel<FaithfulImpl><<<(unsigned)nblk, kBlock, 0, a.stream>>>(
+    like_batch_kernel<FaithfulImpl, false><<<(unsigned)nblk, kBlock, 0, a.stream>>>(
         a.x, a.n, a.params, a.P, a.o, a.w_outlier, a.slices, a.chunk, a.slices > 1 ? a.part_sum : a.out,
         a.slices > 1 ? a.part_zero : nullptr, a.seg, FaithfulImpl::Ctx{0});
     return cudaGetLastError();
@@ -50,7 +55,7 @@ cudaError_t launch_pdf_array_faithful(const PdfArrayArgs& a)
 {
     if (a.n == 0) return cudaSuccess;
     const unsigned nblk = (unsigned)((a.n + kBlock - 1) / kBlock);
-    pdf_array_kernel<FaithfulImpl><<<nblk, kBlock, 0, a.stream>>>(a.x, a.n, a.prm, a.o, a.w_outlier, a.logp, a.y, FaithfulImpl::Ctx{0});
+    pdf_array_kernel<FaithfulImpl, false><<<nblk, kBlock, 0, a.stream>>>(a.x, a.n, a.prm, a.o, a.w_outlier, a.logp, a.y, FaithfulImpl::Ctx{0});
     return cudaGetLastError();
 }
 

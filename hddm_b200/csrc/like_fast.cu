@@ -11,13 +11,24 @@ struct FastImpl {
     {
         fast::prepare(s, prm, o, kt);
     }
+    template <bool ADAPT>
     __device__ static __forceinline__ double density(double x, Set& s, const Ctx&, bool* defer)
     {
-        return fast::density(x, s, defer);
+        return fast::density<ADAPT>(x, s, defer);
     }
     __device__ static __forceinline__ double density_generic(double x, const Set& s, const Ctx&)
     {
         return fast::density_generic(x, s);
+    }
+    static constexpr bool kParks = true;
+    static constexpr int kParkCapacity = fast::kQueue;
+    // only adaptive (refinement) and table-less parameter sets ever defer a trial
+    __device__ static __forceinline__ bool may_park(const Set& s) { return s.mode == fast::kModeAdaptive; }
+    __device__ static __forceinline__ void parked_reset(const Set&)
+    {
+        __syncthreads();
+        if (threadIdx.x == 0) fast::tables().qcount = 0;
+        __syncthreads();
     }
     // Parking lot in shared memory (fast::Tables): returns false when full.
     __device__ static __forceinline__ bool park(Set& s, double x)
@@ -46,9 +57,14 @@ cudaError_t launch_like_batch_fast(const BatchArgs& a)
 {
     const int64_t nblk = a.P * (int64_t)a.slices;
     if (nblk == 0) return cudaSuccess;
-    like_batch_kernel<FastImpl><<<(unsigned)nblk, kBlock, 0, a.stream>>>(
-        a.x, a.n, a.params, a.P, a.o, a.w_outlier, a.slices, a.chunk, a.slices > 1 ? a.part_sum : a.out,
-        a.slices > 1 ? a.part_zero : nullptr, a.seg, get_ktable(a.o.err));
+    if (a.o.use_adaptive)
+        like_batch_kernel<FastImpl, true><<<(unsigned)nblk, kBlock, 0, a.stream>>>(
+            a.x, a.n, a.params, a.P, a.o, a.w_outlier, a.slices, a.chunk, a.slices > 1 ? a.part_sum : a.out,
+            a.slices > 1 ? a.part_zero : nullptr, a.seg, get_ktable(a.o.err));
+    else
+        like_batch_kernel<FastImpl, false><<<(unsigned)nblk, kBlock, 0, a.stream>>>(
+            a.x, a.n, a.params, a.P, a.o, a.w_outlier, a.slices, a.chunk, a.slices > 1 ? a.part_sum : a.out,
+            a.slices > 1 ? a.part_zero : nullptr, a.seg, get_ktable(a.o.err));
     return cudaGetLastError();
 }
 
@@ -56,8 +72,12 @@ cudaError_t launch_pdf_array_fast(const PdfArrayArgs& a)
 {
     if (a.n == 0) return cudaSuccess;
     const unsigned nblk = (unsigned)((a.n + kBlock - 1) / kBlock);
-    pdf_array_kernel<FastImpl><<<nblk, kBlock, 0, a.stream>>>(a.x, a.n, a.prm, a.o, a.w_outlier, a.logp, a.y,
-                                                             get_ktable(a.o.err));
+    if (a.o.use_adaptive)
+        pdf_array_kernel<FastImpl, true><<<nblk, kBlock, 0, a.stream>>>(a.x, a.n, a.prm, a.o, a.w_outlier, a.logp, a.y,
+                                                                       get_ktable(a.o.err));
+    else
+        pdf_array_kernel<FastImpl, false><<<nblk, kBlock, 0, a.stream>>>(a.x, a.n, a.prm, a.o, a.w_outlier, a.logp, a.y,
+                                                                        get_ktable(a.o.err));
     return cudaGetLastError();
 }
 

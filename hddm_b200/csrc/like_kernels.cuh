@@ -44,7 +44,10 @@ struct LogProduct {
     __device__ __forceinline__ double value() const { return slow + fma((double)e, 0.6931471805599453, log(m)); }
 };
 
-template <class Impl, int MINB = 4>
+// ADAPT: the launch uses adaptive Simpson (use_adaptive != 0).  Only then can a trial be deferred (refinement below
+// the first level), so only that instantiation carries the parking lot, the round structure and the adaptive
+// evaluators; the fixed-grid instantiation stays lean.
+template <class Impl, bool ADAPT, int MINB = 4>
 __global__ void __launch_bounds__(kBlock, MINB) like_batch_kernel(const double* __restrict__ x, int64_t n,
                                                           const double* __restrict__ params, int64_t P, Opts o,
                                                           double w_outlier, int slices, int64_t chunk,
@@ -97,49 +100,57 @@ __global__ void __launch_bounds__(kBlock, MINB) like_batch_kernel(const double* 
     const int64_t npair = (end - b) >> 1;
     const bool tail = (end > b) && ((end - b) & 1);
     const double2* x2 = reinterpret_cast<const double2*>(x + b);
-    int64_t i = threadIdx.x;
-    bool edges_done = false;
-    for (;;) {
+    // CTA-uniform trip count (every thread runs the same number of rounds, the last ones possibly empty-handed), so
+    // that the parking lot can be drained by the whole CTA between rounds before it overflows.
+    const int64_t rounds = (npair + kBlock - 1) / kBlock + 1;   // + 1: the head / tail elements
+    double acc_slow = 0.0;
+    auto drain = [&](int parked) {
+#pragma unroll 1
+        for (int q = threadIdx.x; q < parked; q += kBlock) {
+            const double p0 = mix_outlier(Impl::density_generic(Impl::parked(set, q), set, ctx), omp, wp);
+            zero |= (p0 == 0);
+            acc_slow += log(p0);
+        }
+    };
+#pragma unroll 1
+    for (int64_t r = 0; r < rounds; r++) {
         double v0 = 0.0, v1 = 0.0;
         int cnt = 0;
+        const int64_t i = r * kBlock + threadIdx.x;
         if (i < npair) {
             const double2 xx = __ldg(x2 + i);
             v0 = xx.x;
             v1 = xx.y;
             cnt = 2;
-            i += kBlock;
-        } else if (!edges_done) {
-            edges_done = true;
+        } else if (r == rounds - 1) {
             if (head && threadIdx.x == 0) { v0 = x[beg]; cnt = 1; }
             if (tail && threadIdx.x == kBlock - 1) { v0 = x[end - 1]; cnt = 1; }
-            if (cnt == 0) break;
-        } else {
-            break;
         }
 #pragma unroll 1
         for (int h = 0; h < cnt; h++) {
             const double xv = h ? v1 : v0;
             bool defer;
-            double dens = Impl::density(xv, set, ctx, &defer);
+            double dens = Impl::template density<ADAPT>(xv, set, ctx, &defer);
             if (defer) {
-                // park the trial; evaluated below by the whole CTA.  A full lot means: do it here and now.
-                if (Impl::park(set, xv)) continue;
+                // park the trial; evaluated by the whole CTA.  (A full lot cannot happen with the drain below; the
+                // inline evaluation is the safety net.)
+                if (ADAPT && Impl::park(set, xv)) continue;
                 dens = Impl::density_generic(xv, set, ctx);
             }
             lp.add(mix_outlier(dens, omp, wp), zero);
         }
-    }
-    acc = lp.value();
-    // parked trials: dense pass through the generic evaluator
-    {
-        const int parked = Impl::parked_count(set);  // CTA-uniform, includes a barrier when parking is in use
-#pragma unroll 1
-        for (int q = threadIdx.x; q < parked; q += kBlock) {
-            const double p0 = mix_outlier(Impl::density_generic(Impl::parked(set, q), set, ctx), omp, wp);
-            zero |= (p0 == 0);
-            acc += log(p0);
+        if (ADAPT && Impl::kParks && Impl::may_park(set)) {   // uniform over the CTA
+            // room for one more round (two trials per thread)?  If not, everybody evaluates the parked trials now.
+            const int parked = Impl::parked_count(set);   // barrier inside
+            if (parked > Impl::kParkCapacity - 2 * kBlock) {
+                drain(parked);
+                Impl::parked_reset(set);                   // barriers inside
+            }
         }
     }
+    // remaining parked trials: dense pass through the generic evaluator
+    if (ADAPT && Impl::kParks && Impl::may_park(set)) drain(Impl::parked_count(set));
+    acc = lp.value() + acc_slow;
 
     int any_zero;
     const double tot = block_sum_or<kBlock>(acc, zero, &any_zero);
@@ -158,7 +169,7 @@ __global__ void __launch_bounds__(kBlock, MINB) like_batch_kernel(const double* 
 __global__ void finalize_kernel(const double* __restrict__ part_sum, const int* __restrict__ part_zero, int64_t P,
                                 int slices, int early_exit, double* __restrict__ out);
 
-template <class Impl>
+template <class Impl, bool ADAPT>
 __global__ void __launch_bounds__(kBlock) pdf_array_kernel(const double* __restrict__ x, int64_t n, Params prm, Opts o,
                                                          double w_outlier, int logp, double* __restrict__ y,
                                                          const __grid_constant__ typename Impl::Ctx ctx)
@@ -171,7 +182,7 @@ __global__ void __launch_bounds__(kBlock) pdf_array_kernel(const double* __restr
     const double wp = __dmul_rn(w_outlier, prm.p_outlier);
     const double omp = __dsub_rn(1.0, prm.p_outlier);
     bool defer;
-    double dens = Impl::density(x[i], set, ctx, &defer);
+    double dens = Impl::template density<ADAPT>(x[i], set, ctx, &defer);
     if (defer) dens = Impl::density_generic(x[i], set, ctx);
     const double p = mix_outlier(dens, omp, wp);
     y[i] = logp ? log(p) : p;

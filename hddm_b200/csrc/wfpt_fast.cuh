@@ -563,14 +563,12 @@ __device__ __forceinline__ double density_t(double ax, int sign, Set& s, bool* o
 // reference's adaptive recursion would go below the first level for this trial: the caller evaluates those trials
 // with density_generic, preferably all together at the end (a CTA-wide pass instead of one diverged lane at a time).
 // s.kind (uniform over the CTA) picks the evaluator specialised for this parameter set's integration layout.
+template <bool ADAPT>
 __device__ __forceinline__ double density(double x, Set& s, bool* defer)
 {
     *defer = false;
     if (s.mode == kModeZero) return 0.0;
-    if (s.mode == kModeGeneric) {
-        *defer = true;
-        return 0.0;
-    }
+    if (s.mode == kModeGeneric) return generic_full_pdf(x, s.tab->prm, s.tab->o);  // no table for this err / layout
     const double ax = fabs(x);
     if ((ax - s.tlo) < 0) return 0.0;  // pdf.pxi:112, the trial-dependent part
     const int sign = x > 0;
@@ -578,22 +576,146 @@ __device__ __forceinline__ double density(double x, Set& s, bool* defer)
     int neg = 0;
     double result;
     const int kind = s.kind;
-    if (kind == 0) result = density_t<1, false>(ax, sign, s, &ok, neg);        // no z-integration, fixed or no t-grid
-    else if (kind == 1) result = density_t<3, false>(ax, sign, s, &ok, neg);   // fixed grid, n_sz = 2 (any n_st)
-    else if (kind == 3) result = density_t<5, true>(ax, sign, s, &ok, neg);    // adaptive over z and t
-    else if (kind == 4) result = density_t<5, false>(ax, sign, s, &ok, neg);   // adaptive over z only
-    else if (kind == 5) result = density_t<1, true>(ax, sign, s, &ok, neg);    // adaptive over t only
-    else result = density_t<0, false>(ax, sign, s, &ok, neg);                  // fixed grid, other n_sz
+    if (kind == 0) result = density_t<1, false>(ax, sign, s, &ok, neg);            // no z-integration, fixed or no t-grid
+    else if (ADAPT) {
+        if (kind == 3) result = density_t<5, true>(ax, sign, s, &ok, neg);         // adaptive over z and t
+        else if (kind == 4) result = density_t<5, false>(ax, sign, s, &ok, neg);   // adaptive over z only
+        else result = density_t<1, true>(ax, sign, s, &ok, neg);                   // adaptive over t only
+    } else {
+        if (kind == 1) result = density_t<3, false>(ax, sign, s, &ok, neg);        // fixed grid, n_sz = 2 (any n_st)
+        else result = density_t<0, false>(ax, sign, s, &ok, neg);                  // fixed grid, other n_sz
+    }
     // a negative truncated series anywhere makes pdf_sv's log(p) NaN (pdf.pxi:102); pdf (sv == 0) lets it through
     if (s.sv_nonzero && neg < 0) result = CUDART_NAN;
     *defer = !ok;
     return result;
 }
 
-// The full reference recursion for one trial (any mode).
+// ---- adaptive recursion below the first level --------------------------------------------------------------------------
+// One pdf_sv node at an arbitrary (x', z): same table-driven K, same lattice identities and exp kernel as the staged
+// path, with the per-node constants computed on the spot (the refinement nodes are not on the staged grid).
+struct AdhocCtx {
+    double v, v2, sv2, asv2, a, a2, inv_a2;  // v already flipped for upper-boundary RTs; asv2 = (a sv)^2
+    int sv_nonzero;
+    const Tables* T;
+};
+
+__device__ __forceinline__ double pdf_sv_adhoc(const AdhocCtx& c, double xp, double z)
+{
+    if (!(xp > 0)) return 0.0;
+    const Tables& T = *c.T;
+    const double q0 = xp * c.inv_a2;
+    const double tt = fma(fma(-q0, c.a2, xp), c.inv_a2, q0);
+    const long long b = __double_as_longlong(tt);
+    int d = T.desc[0];
+    for (int i = 0; i < T.npieces; i++) d = (b >= T.thr[i]) ? T.desc[i + 1] : d;
+    const int K = d & 0xff;
+    double rs = 1.0, cc = 0.5;
+    if (c.sv_nonzero) {
+        rs = rsqrt_fast(fma(c.sv2, xp, 1.0));
+        cc = 0.5 * rs * rs;
+    }
+    const double E = (fma(c.asv2 * z, z, -2.0 * c.a * c.v * z) - c.v2 * xp) * cc;
+    const double* tab = T.exptab;
+    double series, pref;
+    if (d >> 8) {
+        const double r = rsqrt_fast(tt), tau = r * r, m2t = -2.0 * tau;
+        pref = tau * r * (kInvSqrt2Pi * c.inv_a2) * rs;
+        const double a0 = fma(-0.5 * z * z, tau, E);
+        if (K <= 4 && exp_arg_ok(a0)) {
+            const double e0 = exp_core(a0, tab);
+            const double R = exp_core_or_zero(fma(m2t, z, m2t), tab);
+            const double Q = (K >= 3) ? exp_core_or_zero(fma(-m2t, z, m2t), tab) : 0.0;
+            double inner = fma(z + 2.0, R, z);
+            inner = fma(z - 2.0, Q, inner);
+            if (K >= 4) inner = fma(z + 4.0, R * R * (R * Q), inner);
+            series = fma(e0, inner, 0.0);
+        } else {
+            series = series_small_slow(z, K, tau, E);
+        }
+    } else {
+        const double qa = -kHalfPiSq * tt;
+        const double q = exp_arg_ok(qa) ? exp_core(qa, tab) : exp(qa);
+        const double q2 = q * q;
+        double s1, c1;
+        sincospi(z, &s1, &c1);
+        // k sin(k pi z) by the Chebyshev recurrence, q^(k^2) by running products
+        const double two_c = 2.0 * c1;
+        double sk_prev = 0.0, sk = s1, odd = q, qk = q, acc = 0.0;
+        for (int k = 1; k <= K; k++) {
+            acc = fma(qk * (double)k, sk, acc);
+            const double nxt = fma(two_c, sk, -sk_prev);
+            sk_prev = sk;
+            sk = nxt;
+            odd *= q2;
+            qk *= odd;
+        }
+        series = fma(acc, exp_arg_ok(E) ? exp_core(E, tab) : exp(E), 0.0);
+        pref = kPi * c.inv_a2 * rs;
+    }
+    if (c.sv_nonzero && series < 0.0) return CUDART_NAN;  // pdf.pxi:102
+    return series * pref;
+}
+
+struct AdhocAxis {  // integrand along one axis (cf. faithful::Axis)
+    AdhocCtx c;
+    double x, fixed;
+    bool over_z;
+    __device__ __forceinline__ double operator()(double s) const
+    {
+        return over_z ? pdf_sv_adhoc(c, x - fixed, s) : pdf_sv_adhoc(c, x - s, fixed);
+    }
+};
+struct AdhocInner {  // adaptive z-integral as the integrand of the t-integral (integrate.pxi:143-206)
+    AdhocCtx c;
+    double x, lb_z, ub_z, simps_err;
+    int depth_sz;
+    __device__ __forceinline__ double operator()(double t_node) const
+    {
+        AdhocAxis ax{c, x, t_node, true};
+        return faithful::simpson_adaptive(ax, lb_z, ub_z, ub_z - lb_z, simps_err, depth_sz);
+    }
+};
+
+// full_pdf's adaptive branches (pdf.pxi:127-146) with the table-driven node evaluator; the recursion is the
+// explicit-stack walk of wfpt_faithful.cuh, so interval splitting and summation order are the reference's.
+static __device__ __noinline__ double adaptive_full_pdf(double x, const Tables* Tp)
+{
+    const Tables& T = *Tp;
+    const Params& p = T.prm;
+    double v = p.v, z = p.z, sz = p.sz, st = p.st;
+    const double t = p.t;
+    if ((fabs(x) - (t - st / 2.)) < 0) return 0.0;
+    if (x > 0) {
+        v = -v;
+        z = __dsub_rn(1., z);
+    }
+    x = fabs(x);
+    if (st < 1e-3) st = 0;
+    if (sz < 1e-3) sz = 0;
+    AdhocCtx c;
+    c.v = v; c.v2 = v * v; c.sv2 = p.sv * p.sv; c.a = p.a; c.a2 = p.a * p.a; c.inv_a2 = 1.0 / c.a2;
+    c.asv2 = c.a2 * c.sv2; c.sv_nonzero = (p.sv != 0); c.T = Tp;
+    const double lb_z = __dsub_rn(z, __ddiv_rn(sz, 2.)), ub_z = __dadd_rn(z, __ddiv_rn(sz, 2.));
+    const double lb_t = __dsub_rn(t, __ddiv_rn(st, 2.)), ub_t = __dadd_rn(t, __ddiv_rn(st, 2.));
+    if (sz == 0) {
+        AdhocAxis ax{c, x, z, false};
+        return faithful::simpson_adaptive(ax, lb_t, ub_t, __dsub_rn(ub_t, lb_t), T.o.simps_err, T.o.n_st);
+    }
+    if (st == 0) {
+        AdhocAxis ax{c, x, t, true};
+        return faithful::simpson_adaptive(ax, lb_z, ub_z, __dsub_rn(ub_z, lb_z), T.o.simps_err, T.o.n_sz);
+    }
+    AdhocInner in{c, x, lb_z, ub_z, T.o.simps_err, T.o.n_sz};
+    return faithful::simpson_adaptive(in, lb_t, ub_t, __dsub_rn(ub_t, lb_t), T.o.simps_err, T.o.n_st);
+}
+
+// The full reference recursion for one trial: the table-driven walker for adaptive parameter sets, the
+// operation-for-operation evaluator for everything the tables do not cover.
 __device__ __forceinline__ double density_generic(double x, const Set& s)
 {
     const Tables& T = *s.tab;
+    if (s.mode == kModeAdaptive) return adaptive_full_pdf(x, s.tab);
     return generic_full_pdf(x, T.prm, T.o);
 }
 
