@@ -103,6 +103,7 @@ struct SetConst {
     float p4, p5, p6;      // model-specific extras (theta columns 4..6)
     float vdt;             // v * dt
     float slope;           // angle: -sin(th)/cos(th)
+    float sdt;             // angle: slope * dt (bound decrement per step)
     float inv_beta, alpha; // weibull
     float g;               // ornstein
     float dt_alpha;        // levy: s * dt^(1/alpha)
@@ -118,22 +119,24 @@ __device__ __forceinline__ void load_set(SetConst& c, const float* __restrict__ 
     c.p4 = A.n_par > 4 ? th[4] : 0.f;
     c.p5 = A.n_par > 5 ? th[5] : 0.f;
     c.p6 = A.n_par > 6 ? th[6] : 0.f;
-    c.slope = 0.f; c.inv_beta = 0.f; c.alpha = 0.f; c.g = 0.f; c.dt_alpha = 0.f;
-    if (MODEL == WFPT_SIM_ANGLE) c.slope = -sinf(c.p4) / cosf(c.p4);
+    c.slope = 0.f; c.sdt = 0.f; c.inv_beta = 0.f; c.alpha = 0.f; c.g = 0.f; c.dt_alpha = 0.f;
+    if (MODEL == WFPT_SIM_ANGLE) { c.slope = -sinf(c.p4) / cosf(c.p4); c.sdt = c.slope * A.dt; }
     if (MODEL == WFPT_SIM_WEIBULL) { c.alpha = c.p4; c.inv_beta = 1.0f / c.p5; }
     if (MODEL == WFPT_SIM_ORNSTEIN) { c.g = th[3]; c.t = th[4]; }             // theta = v, a, z, g, t
     if (MODEL == WFPT_SIM_LEVY) { c.alpha = th[3]; c.t = th[4]; c.dt_alpha = A.s * powf(A.dt, 1.0f / th[3]); }  // v, a, z, alpha, t
     c.vdt = __fmul_rn(c.v, A.dt);
 }
 
-// Upper bound at step ix (time ts = ix*dt); lower bound is -b for the flexbound family and 0 for the [0,a] family.
+// Upper bound after `fix` steps (time ts = fix*dt); the lower bound is -b for the flexbound family and 0 for the [0,a]
+// family.  The reference tabulates b on t_s = float32(ix*dt); here it is evaluated in registers, the angle bound as one
+// FMA a + fix*(slope*dt) (differs from the table by at most an ulp of b -- far below the sqrt(dt) step noise).
 template <int MODEL>
-__device__ __forceinline__ float bound_at(const SetConst& c, float ts)
+__device__ __forceinline__ float bound_at(const SetConst& c, float fix, float dt)
 {
-    if (MODEL == WFPT_SIM_ANGLE) return __fadd_rn(c.a, __fmul_rn(ts, c.slope));
+    if (MODEL == WFPT_SIM_ANGLE) return fmaf(fix, c.sdt, c.a);
     if (MODEL == WFPT_SIM_WEIBULL) {
         // a * exp(-(ts/beta)^alpha);  ts == 0 -> a
-        const float r = ts * c.inv_beta;
+        const float r = (fix * dt) * c.inv_beta;
         const float pw = (r > 0.f) ? exp2f(c.alpha * __log2f(r)) : 0.f;
         return c.a * __expf(-pw);
     }
@@ -158,6 +161,7 @@ template <int MODEL>
 __global__ void __launch_bounds__(kSimBlock) sim_kernel(const Args A)
 {
     extern __shared__ unsigned int s_hist[];  // [nbins][2] when A.hist
+    __shared__ int s_next;                    // next undistributed particle of the current item
     const int nh = A.hist ? A.nbins * 2 : 0;
     const float sqrt_st = __fmul_rn(sqrtf(A.dt), A.s);
     const unsigned int k0 = (unsigned int)A.seed, k1 = (unsigned int)(A.seed >> 32);
@@ -174,11 +178,14 @@ __global__ void __launch_bounds__(kSimBlock) sim_kernel(const Args A)
         SetConst c;
         load_set<MODEL>(c, A.theta + (size_t)set * A.n_par, A);
 
+        // particles are handed out one at a time from a shared counter: a lane that finishes takes the next one, so the
+        // lanes of the CTA run dry together (results do not depend on who simulates which particle)
+        if (threadIdx.x == 0) s_next = kSimBlock;
+        __syncthreads();
         long long p = beg + threadIdx.x;   // particle (local index within this launch)
         bool active = p < end;
         bool walking = false;
         float y = 0.f, tp = 0.f, fix = 0.f, drift = c.vdt, t_nd = c.t, b = c.a;
-        int ix = 0;
         unsigned int blk = 0, plo = 0, phi = 0;
         bool tracing = false;
         while (active) {
@@ -190,10 +197,9 @@ __global__ void __launch_bounds__(kSimBlock) sim_kernel(const Args A)
                 blk = 0;
                 tp = 0.f;
                 fix = 0.f;
-                ix = 0;
                 drift = c.vdt;
                 t_nd = c.t;
-                b = bound_at<MODEL>(c, 0.f);
+                b = bound_at<MODEL>(c, 0.f, A.dt);
                 if (Traits<MODEL>::zero_a) y = __fmul_rn(c.z, c.a);
                 else y = __fadd_rn(-b, __fmul_rn(__fmul_rn(c.z, 2.f), b));
                 if (Traits<MODEL>::full || Traits<MODEL>::sdv) {
@@ -223,57 +229,57 @@ __global__ void __launch_bounds__(kSimBlock) sim_kernel(const Args A)
                 nn = normals4(r);
             }
             constexpr int kSub = (MODEL == WFPT_SIM_LEVY) ? 2 : 4;
+            bool done = false;
 #pragma unroll
             for (int j = 0; j < kSub; j++) {
-                if (!walking) continue;
                 const float lo = Traits<MODEL>::zero_a ? 0.f : -b;
-                if (y >= lo && y <= b && tp <= A.max_t) {
-                    // ---- one Euler step ----
-                    const float nj = (j == 0) ? nn.x : (j == 1) ? nn.y : (j == 2) ? nn.z : nn.w;
-                    const float inc = (MODEL == WFPT_SIM_LEVY) ? __fmul_rn(c.dt_alpha, nj) : __fmul_rn(sqrt_st, nj);
-                    float det = drift;
-                    if (MODEL == WFPT_SIM_ORNSTEIN) det = __fmul_rn(__fsub_rn(c.v, __fmul_rn(c.g, y)), A.dt);
+                const bool in = (!done) & (y >= lo) & (y <= b) & (tp <= A.max_t);
+                done |= !in;
+                // ---- one Euler step (predicated: lanes that have left the bounds keep their state) ----
+                const float nj = (j == 0) ? nn.x : (j == 1) ? nn.y : (j == 2) ? nn.z : nn.w;
+                const float inc = (MODEL == WFPT_SIM_LEVY) ? __fmul_rn(c.dt_alpha, nj) : __fmul_rn(sqrt_st, nj);
+                float det = drift;
+                if (MODEL == WFPT_SIM_ORNSTEIN) det = __fmul_rn(__fsub_rn(c.v, __fmul_rn(c.g, y)), A.dt);
+                if (in) {
                     y = __fadd_rn(y, __fadd_rn(det, inc));
                     tp = __fadd_rn(tp, A.dt);
-                    ix++;
-                    if (Traits<MODEL>::moving) {
-                        fix += 1.0f;
-                        b = bound_at<MODEL>(c, __fmul_rn(fix, A.dt));
-                    }
-                    if (tracing && ix < A.traj_len) A.traj[ix] = y;
-                } else {
-                    // ---- record and move on ----
-                    my_steps += (unsigned long long)ix;
-                    const float rt = __fadd_rn(tp, t_nd);
-                    int choice;
-                    if (Traits<MODEL>::zero_a) choice = (y < 0.f) ? 0 : 1;
-                    else choice = (y > 0.f) - (y < 0.f);
-                    if (A.rts) {
-                        const size_t o = (size_t)p * A.n_sets + set;
-                        A.rts[o] = rt;
-                        A.choices[o] = choice;
-                    }
-                    if (A.hist) {
-                        const int col = Traits<MODEL>::zero_a ? choice : (choice > 0 ? 1 : (choice < 0 ? 0 : -1));
-                        if (col >= 0) {
-                            // np.histogram on edges linspace(0, max_t, nbins) + [inf] (basic_simulator_old.py:99-114)
-                            const double rd = (double)rt;
-                            int bin = (int)(rd / A.hist_step);
-                            if (bin > A.nbins - 1) bin = A.nbins - 1;
-                            if (bin < 0) bin = 0;
-                            const double e_lo = (bin == A.nbins - 1) ? A.hist_max_t : bin * A.hist_step;
-                            if (rd < e_lo && bin > 0) bin--;
-                            else if (bin < A.nbins - 1) {
-                                const double e_hi = (bin + 1 == A.nbins - 1) ? A.hist_max_t : (bin + 1) * A.hist_step;
-                                if (rd >= e_hi) bin++;
-                            }
-                            if (rd >= 0.0) atomicAdd(&s_hist[bin * 2 + col], 1u);
-                        }
-                    }
-                    walking = false;
-                    p += kSimBlock;
-                    active = p < end;
+                    fix += 1.0f;
+                    if (Traits<MODEL>::moving) b = bound_at<MODEL>(c, fix, A.dt);
+                    if (tracing && (int)fix < A.traj_len) A.traj[(int)fix] = y;
                 }
+            }
+            if (done) {
+                // ---- record and take the next particle ----
+                my_steps += (unsigned long long)fix;
+                const float rt = __fadd_rn(tp, t_nd);
+                int choice;
+                if (Traits<MODEL>::zero_a) choice = (y < 0.f) ? 0 : 1;
+                else choice = (y > 0.f) - (y < 0.f);
+                if (A.rts) {
+                    const size_t o = (size_t)p * A.n_sets + set;
+                    A.rts[o] = rt;
+                    A.choices[o] = choice;
+                }
+                if (A.hist) {
+                    const int col = Traits<MODEL>::zero_a ? choice : (choice > 0 ? 1 : (choice < 0 ? 0 : -1));
+                    if (col >= 0) {
+                        // np.histogram on edges linspace(0, max_t, nbins) + [inf] (basic_simulator_old.py:99-114)
+                        const double rd = (double)rt;
+                        int bin = (int)(rd / A.hist_step);
+                        if (bin > A.nbins - 1) bin = A.nbins - 1;
+                        if (bin < 0) bin = 0;
+                        const double e_lo = (bin == A.nbins - 1) ? A.hist_max_t : bin * A.hist_step;
+                        if (rd < e_lo && bin > 0) bin--;
+                        else if (bin < A.nbins - 1) {
+                            const double e_hi = (bin + 1 == A.nbins - 1) ? A.hist_max_t : (bin + 1) * A.hist_step;
+                            if (rd >= e_hi) bin++;
+                        }
+                        if (rd >= 0.0) atomicAdd(&s_hist[bin * 2 + col], 1u);
+                    }
+                }
+                walking = false;
+                p = beg + (long long)atomicAdd(&s_next, 1);
+                active = p < end;
             }
         }
         __syncthreads();
@@ -355,20 +361,17 @@ extern "C" int wfpt_sim_run(int model, const float* d_theta, int n_par, int n_se
 
     int dev = 0, sms = 148;
     if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    // work items: a set is cut into chunks so that the grid fills the machine (>= 4 CTAs per SM) while every thread
-    // still runs many particles back to back (that is what hides the spread of first-passage times)
-    const long long target_items = (long long)sms * 8;
-    long long per_set = (target_items + n_sets - 1) / n_sets;
-    const long long max_per_set = (n_samples + sim::kSimBlock - 1) / sim::kSimBlock;  // >= 1 particle per thread
-    if (per_set > max_per_set) per_set = max_per_set;
-    if (per_set < 1) per_set = 1;
-    long long chunk = (n_samples + per_set - 1) / per_set;
-    const long long cap = (long long)sim::kSimBlock * 64;                             // <= 64 particles per thread per item
-    if (chunk > cap) chunk = cap;
+    // work items: (parameter set, chunk of its particles), one CTA each.  Chunks of at most 4,096 particles keep the
+    // hardware block scheduler busy balancing cheap and expensive parameter sets, while inside a CTA the shared
+    // particle counter keeps all lanes busy until the chunk is done.
+    long long chunk = 4096;
+    if (chunk > n_samples) chunk = n_samples;
     A.chunk = chunk;
     A.items_per_set = (n_samples + chunk - 1) / chunk;
     const long long n_items = A.items_per_set * n_sets;
-    const int blocks = (int)(n_items < (long long)sms * 16 ? n_items : (long long)sms * 16);
+    if (n_items > 2147483647LL) return api_fail("wfpt_sim_run: too many work items for one launch; split the call");
+    const int blocks = (int)n_items;
+    (void)sms;
 
     cudaError_t e;
     cudaStream_t st = (cudaStream_t)stream;
