@@ -59,6 +59,8 @@ def _declare(L):
     for name in ("wfpt_like_segments", "wfpt_like_segments_host", "wfpt_like_contaminant_host", "wfpt_like_rl_host",
                  "wfpt_like_multi_rlddm_host"):
         getattr(L, name).restype = i
+    L.wfpt_dmat_cdf_array_host.argtypes = [vp, i64] + [d] * 9 + [vp]
+    L.wfpt_dmat_cdf_array_host.restype = i
     f = C.c_float
     sim_tail = [i, i, i64, i64, f, f, f, C.c_uint64, vp, vp, vp, i, f, vp, vp, i]
     L.wfpt_sim_run.argtypes = [i, vp] + sim_tail + [vp]

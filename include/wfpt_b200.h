@@ -143,6 +143,13 @@ int wfpt_like_multi_rlddm_host(const double* h_x, const int64_t* h_response, con
                                const double scalars[8], double err, int n_st, int n_sz, int use_adaptive,
                                double simps_err, double p_outlier, double w_outlier, int variant, double* h_out);
 
+/* y[i] = CDF of the seven-parameter diffusion model at the signed RT x[i], with the outlier mixture of the wrapper.
+ * Replaces hddm.cdfdif.dmat_cdf_array (src/cdfdif_wrapper.pyx:16-53, src/cdfdif.c:36-221; used by Wfpt.cdf,
+ * hddm/likelihoods.py:232-233).  Argument validation (ValueError on out-of-support parameters) is the caller's, as
+ * in the wrapper. */
+int wfpt_dmat_cdf_array_host(const double* h_x, int64_t n, double v, double sv, double a, double z, double sz,
+                             double t, double st, double p_outlier, double w_outlier, double* h_y);
+
 /* Simulators ------------------------------------------------------------------------------------------------- */
 
 /* Model ids: which Euler-Maruyama simulator of src/cddm_data_simulation.pyx runs, and the theta column order the

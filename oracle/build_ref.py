@@ -24,6 +24,35 @@ REF_SRC = "/root/reference/src"
 OUT = os.path.join(HERE, "_ref")
 
 
+CDF_LIB = os.path.join(OUT, "libcdfdif_ref.so")
+
+
+def build_cdf_ref(force: bool = False) -> bool:
+    """The reference's plain-C CDF (src/cdfdif.c) compiled as it lies into oracle/_ref/libcdfdif_ref.so."""
+    import subprocess
+
+    if os.path.exists(CDF_LIB) and not force:
+        return True
+    src = os.path.join(REF_SRC, "cdfdif.c")
+    if not os.path.exists(src):
+        return False
+    os.makedirs(OUT, exist_ok=True)
+    subprocess.run(["gcc", "-O2", "-fPIC", "-shared", "-o", CDF_LIB, src, "-lm"], check=True)
+    return True
+
+
+def load_cdf_ref():
+    """ctypes handle on the reference cdfdif(double t, int x, double* par, double* prob), or ImportError."""
+    import ctypes as C
+
+    if not os.path.exists(CDF_LIB):
+        raise ImportError("oracle/_ref/libcdfdif_ref.so is not built")
+    L = C.CDLL(CDF_LIB)
+    L.cdfdif.restype = C.c_double
+    L.cdfdif.argtypes = [C.c_double, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double)]
+    return L
+
+
 def ref_built() -> bool:
     return bool(glob.glob(os.path.join(OUT, "wfpt*.so"))) and bool(
         glob.glob(os.path.join(OUT, "cddm_data_simulation*.so"))
@@ -32,6 +61,8 @@ def ref_built() -> bool:
 
 def build_ref(force: bool = False, verbose: bool = False) -> bool:
     """Returns True when oracle/_ref holds both modules (built now or earlier)."""
+    if os.path.isdir(REF_SRC):
+        build_cdf_ref(force)
     if ref_built() and not force:
         return True
     if not os.path.isdir(REF_SRC):

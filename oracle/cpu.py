@@ -255,6 +255,24 @@ def sim_run(model_id, theta, n_samples, delta_t=0.001, max_t=20.0, s=1.0, seed=0
     return rts, ch
 
 
+def dmat_cdf_array_ref(x, v, sv, a, z, sz, t, st, p_outlier, w_outlier):
+    """hddm.cdfdif.dmat_cdf_array with the reference's own C (oracle/_ref/libcdfdif_ref.so, built from
+    /root/reference/src/cdfdif.c as it lies) and the wrapper's arithmetic (src/cdfdif_wrapper.pyx:36-51) restated."""
+    from oracle.build_ref import load_cdf_ref
+
+    L = load_cdf_ref()
+    x = np.asarray(x, dtype=np.float64)
+    epsi = 1e-10
+    params = (C.c_double * 7)(a / 10.0, t, sv / 10.0 + epsi, z * (a / 10.0), sz * (a / 10.0) + epsi, st + epsi, v / 10.0)
+    y = np.empty(len(x))
+    pb = C.c_double(0.0)
+    for i, xi in enumerate(x):
+        yi = L.cdfdif(abs(float(xi)), int(xi > 0), params, C.byref(pb))
+        yi = (1 - pb.value) + float(np.sign(xi)) * yi
+        y[i] = yi * (1 - p_outlier) + (xi + (1.0 / (2 * w_outlier))) * w_outlier * p_outlier
+    return y
+
+
 def nodes_reset():
     lib().orc_nodes_reset()
 

@@ -45,6 +45,7 @@ def test_product_never_imports_the_oracle():
                 assert not re.search(r"^\s*(from|import)\s+oracle\b", txt, flags=re.M), f
                 assert "liboracle" not in txt and "oracle/" not in txt, f
     assert "oracle" not in open(os.path.join(ROOT, "wfpt.py")).read()
+    assert "oracle" not in open(os.path.join(ROOT, "cdfdif_wrapper.py")).read()
 
 
 def test_top_level_module_name_and_callables():

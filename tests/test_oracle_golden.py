@@ -189,3 +189,20 @@ def test_against_live_reference(ref_wfpt, oracle):
         p1 = oracle.full_pdf(x, v, sv, a, z, sz, t, st, err, n, n, ad, se)
         p2 = ref_wfpt.full_pdf(x, v, sv, a, z, sz, t, st, err, n, n, ad, se)
         assert p1 == p2 or (math.isnan(p1) and math.isnan(p2))
+
+
+def test_cdf_fixture_comes_from_the_reference_library():
+    """tests/golden/cdf_golden.npz is what the reference's own cdfdif.c (oracle/_ref) returns, bit for bit."""
+    import os
+
+    from oracle import cpu
+    from oracle.build_ref import CDF_LIB
+
+    if not os.path.exists(CDF_LIB):
+        pytest.skip("oracle/_ref/libcdfdif_ref.so not present")
+    g = dict(np.load(os.path.join(os.path.dirname(__file__), "golden", "cdf_golden.npz")))
+    for row, want in zip(g["cases"], g["vals"]):
+        assert np.array_equal(cpu.dmat_cdf_array_ref(g["x"], *row), want)
+    # sanity of the quantity itself: in signed-RT convention the CDF rises from 0 to 1 (outlier-free row)
+    y = g["vals"][1]
+    assert abs(y[0]) < 1e-6 and abs(y[180] - 1) < 1e-3
