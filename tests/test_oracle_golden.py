@@ -205,4 +205,4 @@ def test_cdf_fixture_comes_from_the_reference_library():
         assert np.array_equal(cpu.dmat_cdf_array_ref(g["x"], *row), want)
     # sanity of the quantity itself: in signed-RT convention the CDF rises from 0 to 1 (outlier-free row)
     y = g["vals"][1]
-    assert abs(y[0]) < 1e-6 and abs(y[180] - 1) < 1e-3
+    assert abs(y[0]) < 5e-3 and abs(y[180] - 1) < 5e-3 and np.all(np.diff(y[:181]) >= -1e-12)
