@@ -306,6 +306,132 @@ __global__ void __launch_bounds__(kSimBlock) sim_kernel(const Args A)
     }
 }
 
+// ---- multi-accumulator models ---------------------------------------------------------------------------------------------
+// race_model (cddm_data_simulation.pyx:1253-1374) and lca (:1380-1518): NP accumulators start at z_j * b(0) and run
+// until one exceeds the (common, possibly collapsing) bound b(t) or time runs out; choice = index of the largest.
+//   race: p_j += v_j dt + s sqrt(dt) N
+//   lca : p_j += (v_j - g p_j - b_inh (sum_old - p_j)) dt + s sqrt(dt) N, then p_j = max(0, p_j)
+// theta (canonical layout built by the host shim): v[NP], a, z[NP], g, b_inh, t, angle  -> 2 NP + 5 floats per set.
+// One Philox block per Euler step (NP <= 4 normals), so the lanes of a warp are always in phase.
+template <int NP, bool LCA, bool ANGLE>
+__global__ void __launch_bounds__(kSimBlock) race_kernel(const Args A)
+{
+    extern __shared__ unsigned int s_hist[];  // [nbins][NP] when A.hist
+    __shared__ int s_next;
+    const int nh = A.hist ? A.nbins * NP : 0;
+    const float sqrt_st = __fmul_rn(sqrtf(A.dt), A.s);
+    const unsigned int k0 = (unsigned int)A.seed, k1 = (unsigned int)(A.seed >> 32);
+    unsigned long long my_steps = 0;
+    const long long item = blockIdx.x;
+    const int set = (int)(item / A.items_per_set);
+    const long long beg = (item - (long long)set * A.items_per_set) * A.chunk;
+    const long long end = (beg + A.chunk < A.n_samples) ? beg + A.chunk : A.n_samples;
+    for (int i = threadIdx.x; i < nh; i += kSimBlock) s_hist[i] = 0u;
+    if (threadIdx.x == 0) s_next = kSimBlock;
+    __syncthreads();
+
+    const float* th = A.theta + (size_t)set * A.n_par;
+    float v[NP], z[NP], vdt[NP];
+#pragma unroll
+    for (int j = 0; j < NP; j++) {
+        v[j] = th[j];
+        z[j] = th[NP + 1 + j];
+        vdt[j] = __fmul_rn(v[j], A.dt);
+    }
+    const float a = th[NP], g = th[2 * NP + 1], binh = th[2 * NP + 2], t_nd = th[2 * NP + 3];
+    const float sdt = ANGLE ? (-sinf(th[2 * NP + 4]) / cosf(th[2 * NP + 4])) * A.dt : 0.f;
+
+    long long p = beg + threadIdx.x;
+    while (p < end) {
+        const unsigned long long gp = (unsigned long long)(p + A.sample_offset);
+        float y[NP];
+        float b = a, tp = 0.f, fix = 0.f;
+#pragma unroll
+        for (int j = 0; j < NP; j++) y[j] = __fmul_rn(z[j], b);
+        unsigned int blk = 0;
+        for (;;) {
+            bool hit = false;
+#pragma unroll
+            for (int j = 0; j < NP; j++) hit |= (y[j] > b);
+            if (hit || !(tp <= A.max_t)) break;
+            const float4 nn = normals4(philox4x32((unsigned int)gp, (unsigned int)(gp >> 32), (unsigned int)set, blk++, k0, k1));
+            float sum = 0.f;
+            if (LCA) {
+#pragma unroll
+                for (int j = 0; j < NP; j++) sum = __fadd_rn(sum, y[j]);   // csum(), :62-70
+            }
+#pragma unroll
+            for (int j = 0; j < NP; j++) {
+                const float nj = (j == 0) ? nn.x : (j == 1) ? nn.y : (j == 2) ? nn.z : nn.w;
+                if (LCA) {
+                    const float red = __fadd_rn(-y[j], sum);
+                    const float drift = __fmul_rn(__fsub_rn(__fsub_rn(v[j], __fmul_rn(g, y[j])), __fmul_rn(binh, red)), A.dt);
+                    y[j] = fmaxf(0.0f, __fadd_rn(y[j], __fadd_rn(drift, __fmul_rn(sqrt_st, nj))));
+                } else {
+                    y[j] = __fadd_rn(y[j], __fadd_rn(vdt[j], __fmul_rn(sqrt_st, nj)));
+                }
+            }
+            tp = __fadd_rn(tp, A.dt);
+            fix += 1.0f;
+            if (ANGLE) b = fmaf(fix, sdt, a);
+        }
+        my_steps += (unsigned long long)fix;
+        int choice = 0;                       // np.argmax: first index of the maximum
+        float best = y[0];
+#pragma unroll
+        for (int j = 1; j < NP; j++)
+            if (y[j] > best) { best = y[j]; choice = j; }
+        const float rt = __fadd_rn(tp, t_nd);
+        if (A.rts) {
+            const size_t o = (size_t)p * A.n_sets + set;
+            A.rts[o] = rt;
+            A.choices[o] = choice;
+        }
+        if (A.hist) {
+            const double rd = (double)rt;
+            int bin = (int)(rd / A.hist_step);
+            if (bin > A.nbins - 1) bin = A.nbins - 1;
+            if (bin < 0) bin = 0;
+            const double e_lo = (bin == A.nbins - 1) ? A.hist_max_t : bin * A.hist_step;
+            if (rd < e_lo && bin > 0) bin--;
+            else if (bin < A.nbins - 1) {
+                const double e_hi = (bin + 1 == A.nbins - 1) ? A.hist_max_t : (bin + 1) * A.hist_step;
+                if (rd >= e_hi) bin++;
+            }
+            if (rd >= 0.0) atomicAdd(&s_hist[bin * NP + choice], 1u);
+        }
+        p = beg + (long long)atomicAdd(&s_next, 1);
+    }
+    __syncthreads();
+    if (A.hist) {
+        unsigned int* gh = A.hist + (size_t)set * nh;
+        for (int i = threadIdx.x; i < nh; i += kSimBlock) {
+            const unsigned int c = s_hist[i];
+            if (c) atomicAdd(&gh[i], c);
+        }
+    }
+    if (A.steps) {
+        __shared__ unsigned long long s_steps[kSimBlock / 32];
+        for (int off = 16; off > 0; off >>= 1) my_steps += __shfl_down_sync(0xffffffffu, my_steps, off);
+        if ((threadIdx.x & 31) == 0) s_steps[threadIdx.x >> 5] = my_steps;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            unsigned long long tot = 0;
+            for (int i = 0; i < kSimBlock / 32; i++) tot += s_steps[i];
+            atomicAdd(A.steps, tot);
+        }
+    }
+}
+
+template <int NP, bool LCA>
+static cudaError_t launch_race(const Args& A, int angle, int blocks, cudaStream_t stream)
+{
+    const size_t smem = A.hist ? sizeof(unsigned int) * NP * (size_t)A.nbins : 0;
+    if (angle) race_kernel<NP, LCA, true><<<blocks, kSimBlock, smem, stream>>>(A);
+    else race_kernel<NP, LCA, false><<<blocks, kSimBlock, smem, stream>>>(A);
+    return cudaGetLastError();
+}
+
 template <int MODEL>
 static cudaError_t launch(const Args& A, int blocks, cudaStream_t stream)
 {
@@ -433,5 +559,62 @@ extern "C" int wfpt_sim_run_host(int model, const float* h_theta, int n_par, int
     if (d_traj) SCK(cudaMemcpy(h_traj, d_traj, sizeof(float) * (size_t)traj_len, cudaMemcpyDeviceToHost));
 done:
     cudaFree(d_theta); cudaFree(d_rts); cudaFree(d_ch); cudaFree(d_hist); cudaFree(d_steps); cudaFree(d_traj);
+    return rc;
+}
+
+
+extern "C" int wfpt_sim_race_run_host(int lca, int n_particles, int angle, const float* h_theta, int n_sets, int64_t n_samples,
+                                      int64_t sample_offset, float delta_t, float max_t, float s, uint64_t seed, float* h_rts,
+                                      int32_t* h_choices, uint32_t* h_hist, int nbins, float hist_max_t, uint64_t* h_steps)
+{
+    if (n_particles < 2 || n_particles > 4) return api_fail("wfpt_sim_race_run_host: n_particles must be 2, 3 or 4");
+    if (n_sets < 0 || n_samples < 0) return api_fail("wfpt_sim_race_run_host: negative size");
+    if (n_sets == 0 || n_samples == 0) return 0;
+    if (!h_theta) return api_fail("wfpt_sim_race_run_host: null theta");
+    if ((h_rts == nullptr) != (h_choices == nullptr)) return api_fail("wfpt_sim_race_run_host: rts and choices must be given together");
+    if (!h_rts && !h_hist) return api_fail("wfpt_sim_race_run_host: nothing to write");
+    if (!(delta_t > 0.f) || !(max_t > 0.f)) return api_fail("wfpt_sim_race_run_host: delta_t and max_t must be positive");
+    if (h_hist && (nbins < 2 || nbins * n_particles > 2 * sim::kMaxBins)) return api_fail("wfpt_sim_race_run_host: nbins out of range");
+    const int n_par = 2 * n_particles + 5;
+    int rc = 0;
+    float *d_theta = nullptr, *d_rts = nullptr;
+    int32_t* d_ch = nullptr;
+    uint32_t* d_hist = nullptr;
+    uint64_t* d_steps = nullptr;
+    const size_t n_out = (size_t)n_samples * (size_t)n_sets;
+    const size_t hist_n = (size_t)n_sets * (size_t)(nbins > 0 ? nbins : 0) * n_particles;
+    sim::Args A;
+    cudaError_t e = cudaSuccess;
+    SCK(cudaMalloc(&d_theta, sizeof(float) * (size_t)n_sets * n_par));
+    SCK(cudaMemcpy(d_theta, h_theta, sizeof(float) * (size_t)n_sets * n_par, cudaMemcpyHostToDevice));
+    if (h_rts) { SCK(cudaMalloc(&d_rts, sizeof(float) * n_out)); SCK(cudaMalloc(&d_ch, sizeof(int32_t) * n_out)); }
+    if (h_hist) { SCK(cudaMalloc(&d_hist, sizeof(uint32_t) * hist_n)); SCK(cudaMemset(d_hist, 0, sizeof(uint32_t) * hist_n)); }
+    if (h_steps) { SCK(cudaMalloc(&d_steps, sizeof(uint64_t))); SCK(cudaMemset(d_steps, 0, sizeof(uint64_t))); }
+    A.theta = d_theta; A.n_par = n_par; A.n_sets = n_sets; A.n_samples = n_samples; A.sample_offset = sample_offset;
+    A.out_stride_samples = n_samples; A.dt = delta_t; A.max_t = max_t; A.s = s; A.seed = seed; A.rts = d_rts; A.choices = d_ch;
+    A.hist = d_hist; A.nbins = d_hist ? nbins : 0; A.hist_max_t = (double)hist_max_t;
+    A.hist_step = d_hist ? (double)hist_max_t / (double)(nbins - 1) : 1.0;
+    A.steps = (unsigned long long*)d_steps; A.traj = nullptr; A.traj_len = 0;
+    A.chunk = n_samples < 4096 ? n_samples : 4096;
+    A.items_per_set = (n_samples + A.chunk - 1) / A.chunk;
+    {
+        const long long n_items = A.items_per_set * n_sets;
+        if (n_items > 2147483647LL) { rc = api_fail("wfpt_sim_race_run_host: too many work items; split the call"); goto done; }
+        const int blocks = (int)n_items;
+        if (n_particles == 2) e = lca ? sim::launch_race<2, true>(A, angle, blocks, 0) : sim::launch_race<2, false>(A, angle, blocks, 0);
+        else if (n_particles == 3) e = lca ? sim::launch_race<3, true>(A, angle, blocks, 0) : sim::launch_race<3, false>(A, angle, blocks, 0);
+        else e = lca ? sim::launch_race<4, true>(A, angle, blocks, 0) : sim::launch_race<4, false>(A, angle, blocks, 0);
+        SCK(e);
+        count_launch(1);
+    }
+    SCK(cudaDeviceSynchronize());
+    if (h_rts) {
+        SCK(cudaMemcpy(h_rts, d_rts, sizeof(float) * n_out, cudaMemcpyDeviceToHost));
+        SCK(cudaMemcpy(h_choices, d_ch, sizeof(int32_t) * n_out, cudaMemcpyDeviceToHost));
+    }
+    if (h_hist) SCK(cudaMemcpy(h_hist, d_hist, sizeof(uint32_t) * hist_n, cudaMemcpyDeviceToHost));
+    if (h_steps) SCK(cudaMemcpy(h_steps, d_steps, sizeof(uint64_t), cudaMemcpyDeviceToHost));
+done:
+    cudaFree(d_theta); cudaFree(d_rts); cudaFree(d_ch); cudaFree(d_hist); cudaFree(d_steps);
     return rc;
 }

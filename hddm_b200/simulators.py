@@ -29,18 +29,41 @@ _M = {
     "ornstein": (7, ["v", "a", "z", "g", "t"], "ornstein_uhlenbeck", "constant", True, [-1, 1]),
     "levy": (8, ["v", "a", "z", "alpha", "t"], "levy_flexbound", "constant", True, [-1, 1]),
 }
+# multi-accumulator models: name -> (lca, n_particles, angle, theta columns) -- column orders of the reference's dispatch
+# (/root/reference/graveyard/basic_simulator_old.py:476-760) and hddm/model_config.py:939-1200
+def _race_entries():
+    out = {}
+    for npar in (3, 4):
+        vs = [f"v{i}" for i in range(npar)]
+        zs = [f"z{i}" for i in range(npar)]
+        out[f"race_{npar}"] = (0, npar, 0, vs + ["a"] + zs + ["t"])
+        out[f"race_no_bias_{npar}"] = (0, npar, 0, vs + ["a", "z", "t"])
+        out[f"race_no_bias_angle_{npar}"] = (0, npar, 1, vs + ["a", "z", "t", "theta"])
+        out[f"lca_{npar}"] = (1, npar, 0, vs + ["a"] + zs + ["g", "b", "t"])
+        out[f"lca_no_bias_{npar}"] = (1, npar, 0, vs + ["a", "z", "g", "b", "t"])
+        out[f"lca_no_bias_angle_{npar}"] = (1, npar, 1, vs + ["a", "z", "g", "b", "t", "theta"])
+    return out
+
+
+_RACE = _race_entries()
+
 _ALIAS = {"ddm_legacy": "ddm_hddm_base", "full_ddm_legacy": "full_ddm_hddm_base", "test": "ddm",
           "weibull_cdf": "weibull"}
-_NEXT = ("gamma_drift", "gamma_drift_angle", "ds_conflict_drift", "ds_conflict_drift_angle", "race_model", "lca",
+_NEXT = ("gamma_drift", "gamma_drift_angle", "ds_conflict_drift", "ds_conflict_drift_angle",
          "ddm_seq2", "ddm_par2", "ddm_mic2_adj", "tradeoff")
 
 # minimal stand-in for the part of hddm.model_config the simulator boundary needs (params and choices per model)
 model_config = {name: {"params": list(cols), "choices": list(ch), "boundary_name": bnd, "boundary_multiplicative": mult}
                 for name, (_, cols, _, bnd, mult, ch) in _M.items()}
+model_config.update({name: {"params": list(cols), "choices": list(range(npar)), "boundary_name": "angle" if ang else "constant",
+                            "boundary_multiplicative": not ang}
+                     for name, (_, npar, ang, cols) in _RACE.items()})
 
 
 def _resolve(model):
     name = _ALIAS.get(model, model)
+    if name in _RACE:
+        return name
     if name not in _M:
         if any(model.startswith(p) for p in _NEXT):
             raise NotImplementedError(f"simulator model '{model}' is a next-row model (SURVEY 8(f) rank 4), not built yet")
@@ -50,7 +73,7 @@ def _resolve(model):
 
 def _coerce_theta(theta, name):
     """basic_simulator_old.py:208-224."""
-    cols = _M[name][1]
+    cols = _RACE[name][3] if name in _RACE else _M[name][1]
     if isinstance(theta, list):
         theta = np.asarray(theta).astype(np.float32)
     elif isinstance(theta, np.ndarray):
@@ -114,6 +137,64 @@ def _run(name, theta, n_samples, delta_t, max_t, s, seed, want_raw, nbins, sampl
     return rts, choices, hist, traj, int(steps[0])
 
 
+def _race_canonical(name, theta):
+    """Per-model theta columns -> the kernel's layout v[np], a, z[np], g, b, t, angle (a shared z is replicated)."""
+    lca, npar, ang, cols = _RACE[name]
+    col = {c: theta[:, i] for i, c in enumerate(cols)}
+    zero = np.zeros(theta.shape[0], dtype=np.float32)
+    out = [col[f"v{i}"] for i in range(npar)] + [col["a"]]
+    out += [col.get(f"z{i}", col.get("z")) for i in range(npar)]
+    out += [col.get("g", zero), col.get("b", zero), col["t"], col.get("theta", zero)]
+    return np.ascontiguousarray(np.stack(out, axis=1), dtype=np.float32)
+
+
+def _run_race(name, theta, n_samples, delta_t, max_t, s, seed, want_raw, nbins, sample_offset=0):
+    L = _lib.load()
+    lca, npar, ang, cols = _RACE[name]
+    canon = _race_canonical(name, theta)
+    n_sets = canon.shape[0]
+    rts = choices = hist = None
+    steps = np.zeros(1, dtype=np.uint64)
+    if want_raw:
+        rts = np.empty((n_samples, n_sets, 1), dtype=np.float32)
+        choices = np.empty((n_samples, n_sets, 1), dtype=np.int32)
+    if nbins:
+        hist = np.zeros((n_sets, nbins, npar), dtype=np.uint32)
+
+    def p(a):
+        return a.ctypes.data_as(C.c_void_p) if a is not None else None
+
+    _lib.check(L.wfpt_sim_race_run_host(lca, npar, ang, p(canon), n_sets, int(n_samples), int(sample_offset), float(delta_t),
+                                        float(max_t), float(s), seed, p(rts), p(choices), p(hist), int(nbins or 0),
+                                        float(max_t), p(steps)))
+    return rts, choices, hist, int(steps[0])
+
+
+def _simulator_race(name, model, theta, n_samples, delta_t, max_t, s, seed, bin_dim, binned):
+    lca, npar, ang, cols = _RACE[name]
+    n_trials = theta.shape[0]
+    rts, choices, hist, steps = _run_race(name, theta, n_samples, delta_t, max_t, s, seed, True, int(bin_dim) if binned else 0)
+    meta = {c: theta[:, i].copy() for i, c in enumerate(cols)}
+    if "z" in meta:  # the reference also reports per-accumulator starting points (cddm_data_simulation.pyx:1350-1358)
+        for i in range(npar):
+            meta.setdefault(f"z{i}", meta["z"])
+    t_s = np.arange(0, max_t + delta_t, delta_t).astype(np.float32)
+    a_last = theta[-1, cols.index("a")]
+    bnd = np.add(a_last, np.multiply(t_s, -np.sin(theta[-1, cols.index("theta")]) / np.cos(theta[-1, cols.index("theta")]))) \
+        if ang else np.multiply(a_last, np.ones_like(t_s))
+    meta.update({"s": s, "delta_t": delta_t, "max_t": max_t, "n_samples": n_samples,
+                 "simulator": "lca" if lca else "race_model", "boundary_fun_type": "angle" if ang else "constant",
+                 "possible_choices": list(range(npar)), "trajectory": None, "boundary": bnd.astype(np.float32),
+                 "model": model, "n_euler_steps": steps, "seed": seed})
+    if binned:
+        return (hist[0].astype(np.float64) / n_samples, meta)
+    if n_trials == 1:
+        rts, choices = np.squeeze(rts, axis=1), np.squeeze(choices, axis=1)
+    elif n_samples == 1:
+        rts, choices = np.squeeze(rts, axis=0), np.squeeze(choices, axis=0)
+    return (rts, choices, meta)
+
+
 def simulator(theta, model="angle", n_samples=1000, delta_t=0.001, max_t=20, no_noise=False, bin_dim=None,
               bin_pointwise=False, random_state=None, **ignored):
     """(rts, choices, metadata), or (histogram, metadata) when bin_dim > 0 -- see the module docstring.
@@ -135,6 +216,8 @@ def simulator(theta, model="angle", n_samples=1000, delta_t=0.001, max_t=20, no_
     if binned and n_trials > 1:
         return "currently binned outputs not implemented for multi-trial simulators"
 
+    if name in _RACE:
+        return _simulator_race(name, model, theta, n_samples, delta_t, max_t, s, seed, bin_dim, binned)
     rts, choices, hist, traj, steps = _run(name, theta, n_samples, delta_t, max_t, s, seed, True,
                                            int(bin_dim) if binned else 0, want_traj=True)
     _, cols, sim_name, bnd, mult, ch = _M[name]
@@ -162,6 +245,10 @@ def simulate_histograms(theta, model="angle", n_samples=100000, nbins=512, delta
     merge with hddm_b200.distributed.merge_histograms)."""
     name = _resolve(model)
     theta = _coerce_theta(theta, name)
+    if name in _RACE:
+        _, _, hist, steps = _run_race(name, theta, int(n_samples), delta_t, max_t, 0.0 if no_noise else 1.0,
+                                      _seed(random_state), False, int(nbins), sample_offset=sample_offset)
+        return hist, steps
     _, _, hist, _, steps = _run(name, theta, int(n_samples), delta_t, max_t, 0.0 if no_noise else 1.0,
                                 _seed(random_state), False, int(nbins), sample_offset=sample_offset)
     return hist, steps

@@ -183,6 +183,15 @@ int wfpt_sim_run_host(int model, const float* h_theta, int n_par, int n_sets, in
                       float delta_t, float max_t, float s, uint64_t seed, float* h_rts, int32_t* h_choices,
                       uint32_t* h_hist, int nbins, float hist_max_t, uint64_t* h_steps, float* h_traj, int traj_len);
 
+/* Multi-accumulator simulators: race_model (src/cddm_data_simulation.pyx:1253-1374, lca == 0) and lca (:1380-1518,
+ * lca != 0) with n_particles = 2..4 accumulators and a constant (angle == 0) or linearly collapsing (angle != 0) bound.
+ * theta is float32 [n_sets][2*n_particles + 5] in the canonical layout v[np], a, z[np], g, b, t, angle (the Python shim
+ * builds it from the reference's per-model column orders, graveyard/basic_simulator_old.py:476-760).  choices are
+ * accumulator indices (np.argmax); hist is uint32 [n_sets][nbins][n_particles].  Other arguments as in wfpt_sim_run. */
+int wfpt_sim_race_run_host(int lca, int n_particles, int angle, const float* h_theta, int n_sets, int64_t n_samples,
+                           int64_t sample_offset, float delta_t, float max_t, float s, uint64_t seed, float* h_rts,
+                           int32_t* h_choices, uint32_t* h_hist, int nbins, float hist_max_t, uint64_t* h_steps);
+
 #ifdef __cplusplus
 }
 #endif

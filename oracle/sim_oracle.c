@@ -112,3 +112,60 @@ int orc_sim_run(int model, const float* theta, int n_par, int n_sets, int64_t n_
     free(b);
     return 0;
 }
+
+/* race_model (:1253-1374) and lca (:1380-1518).  theta canonical layout per set (2*np + 5 floats):
+ * v[np], a, z[np], g, b_inh, t, angle.  Bound: a (constant) or a + t_s * (-sin/cos(angle)) on the float32 time grid. */
+int orc_sim_race_run(int lca, int np, int angle, const float* theta, int n_sets, int64_t n_samples, float dt, float max_t,
+                     float s, uint64_t seed, float* rts, int32_t* choices)
+{
+    if (np < 2 || np > 4) return 1;
+    rng_t R;
+    rng_seed(&R, seed);
+    const int n_par = 2 * np + 5;
+    const float sqrt_st = (float)sqrt(dt) * s;
+    const int nb = (int)((max_t / dt) + 1) + 2;
+    float* b = (float*)malloc(sizeof(float) * (size_t)(nb + 1));
+    if (!b) return 2;
+    for (int k = 0; k < n_sets; k++) {
+        const float* th = theta + (size_t)k * n_par;
+        const float* v = th;
+        const float a = th[np];
+        const float* z = th + np + 1;
+        const float g = th[2 * np + 1], binh = th[2 * np + 2], t = th[2 * np + 3], ang = th[2 * np + 4];
+        for (int ix = 0; ix <= nb; ix++) {
+            const float ts = (float)((double)ix * (double)dt);
+            b[ix] = angle ? a + ts * (-sinf(ang) / cosf(ang)) : a;
+        }
+        for (int64_t n = 0; n < n_samples; n++) {
+            float p[4], red[4];
+            for (int j = 0; j < np; j++) p[j] = z[j] * b[0];
+            float tp = 0.0f;
+            int ix = 0;
+            for (;;) {
+                int fin = 0;
+                for (int j = 0; j < np; j++) if (p[j] > b[ix]) fin = 1;
+                if (fin || !(tp <= max_t)) break;
+                if (lca) {
+                    float sum = 0;
+                    for (int j = 0; j < np; j++) sum += p[j];
+                    for (int j = 0; j < np; j++) {
+                        red[j] = (-1) * p[j] + sum;
+                        p[j] += ((v[j] - (g * p[j]) - (binh * red[j])) * dt) + (sqrt_st * random_gaussian(&R));
+                        p[j] = fmaxf(0.0f, p[j]);
+                    }
+                } else {
+                    for (int j = 0; j < np; j++) p[j] += (v[j] * dt) + sqrt_st * random_gaussian(&R);
+                }
+                tp += dt;
+                ix++;
+            }
+            int arg = 0;
+            for (int j = 1; j < np; j++) if (p[j] > p[arg]) arg = j;
+            const size_t o = (size_t)n * n_sets + k;
+            rts[o] = tp + t;
+            choices[o] = arg;
+        }
+    }
+    free(b);
+    return 0;
+}

@@ -56,6 +56,38 @@ def test_distribution_matches_oracle(model, sims, oracle):
     assert set(np.unique(ch)) <= set(meta["possible_choices"]) | {0}
 
 
+RACE_CASES = {
+    "race_no_bias_3": [1.0, 0.5, 0.2, 2.0, 0.3, 0.3],
+    "race_no_bias_angle_4": [1.0, 0.8, 0.5, 0.2, 2.0, 0.3, 0.3, 0.2],
+    "race_3": [1.0, 0.5, 0.2, 2.0, 0.2, 0.3, 0.4, 0.3],
+    "lca_no_bias_3": [1.0, 0.5, 0.2, 2.0, 0.3, 0.5, 0.3, 0.3],
+    "lca_no_bias_angle_4": [1.0, 0.8, 0.5, 0.2, 2.0, 0.3, 0.5, 0.3, 0.3, 0.2],
+    "lca_4": [1.0, 0.8, 0.5, 0.2, 2.0, 0.2, 0.3, 0.3, 0.4, 0.5, 0.3, 0.3],
+}
+
+
+@pytest.mark.parametrize("model", list(RACE_CASES))
+def test_race_and_lca_match_oracle(model, sims, oracle):
+    theta = np.asarray(RACE_CASES[model], dtype=np.float32)
+    lca, npar, ang, cols = sims._RACE[model]
+    n_gpu, n_cpu = 300000, 60000
+    rts, ch, meta = sims.simulator(theta, model=model, n_samples=n_gpu, random_state=41)
+    canon = sims._race_canonical(model, theta[None, :])
+    ort, och = oracle.sim_race_run(lca, npar, ang, canon, n_cpu, seed=42)
+    assert rts.shape == (n_gpu, 1) and meta["possible_choices"] == list(range(npar))
+    assert stats.ks_2samp(rts[:, 0], ort[:, 0]).pvalue > 1e-3
+    for c in range(npar):
+        la, ha = _ci(int(np.sum(ch == c)), n_gpu)
+        lb, hb = _ci(int(np.sum(och == c)), n_cpu)
+        assert la <= hb and lb <= ha, (model, c)
+    for p_name in cols:
+        assert p_name in meta
+    # histogram mode == np.histogram of the raw output, per accumulator
+    r2, c2, hist, steps = sims._run_race(model, theta[None, :], 20000, 0.001, 20.0, 1.0, 7, True, 128)
+    out = (r2[:, 0, :], c2[:, 0, :], {"max_t": 20.0, "possible_choices": list(range(npar)), "n_samples": 20000})
+    assert np.array_equal(hist[0].astype(np.float64), sims.bin_simulator_output(out, nbins=128, freq_cnt=True))
+
+
 def test_shapes_and_metadata_like_reference_test(sims):
     """/root/reference/hddm/tests/test_simulators.py:65-87."""
     n_samples, n_trials = 100, 7
