@@ -11,6 +11,9 @@
 //   WFPT_SIM_DDM_SDV          ddm_sdv             :876-994
 //   WFPT_SIM_ORNSTEIN         ornstein_uhlenbeck  :1119-1219
 //   WFPT_SIM_LEVY             levy_flexbound      :642-741   alpha-stable increments (Chambers-Mallows-Stuck, :28-40)
+//   WFPT_SIM_GAMMA_DRIFT(_ANGLE), WFPT_SIM_DS_CONFLICT(_ANGLE)   ddm_flex :1001-1113 with the time-varying drifts of
+//                             graveyard/drift_functions.py:11-103 added to v, evaluated in registers at every step
+//   WFPT_SIM_DDM_COV          ddm_cov             :384-449   ddm with choice = -sign(y)
 //
 // Arithmetic follows the reference: particle state, time and bounds are float32; time is accumulated by repeated
 // float32 addition of delta_t (so RTs land on the reference's grid of values); the increment is
@@ -107,6 +110,20 @@ struct SetConst {
     float inv_beta, alpha; // weibull
     float g;               // ornstein
     float dt_alpha;        // levy: s * dt^(1/alpha)
+    // time-varying drift (ddm_flex): gamma: c/div, shape-1, -1/scale ; conflict: (init_t - fix_t)*coh_t, fix_t*coh_t, init_d*coh_d, slopes
+    float d0, d1, d2, d3, d4;
+};
+
+template <int MODEL>
+struct Traits {
+    static constexpr bool zero_a = (MODEL == WFPT_SIM_DDM || MODEL == WFPT_SIM_FULL_DDM_BASE || MODEL == WFPT_SIM_DDM_COV);  // bounds [0, a]
+    static constexpr bool angle = (MODEL == WFPT_SIM_ANGLE || MODEL == WFPT_SIM_GAMMA_DRIFT_ANGLE || MODEL == WFPT_SIM_DS_CONFLICT_ANGLE);
+    static constexpr bool moving = angle || (MODEL == WFPT_SIM_WEIBULL);
+    static constexpr bool full = (MODEL == WFPT_SIM_FULL_DDM_BASE || MODEL == WFPT_SIM_FULL_DDM);
+    static constexpr bool sdv = (MODEL == WFPT_SIM_DDM_SDV);
+    static constexpr bool gamma = (MODEL == WFPT_SIM_GAMMA_DRIFT || MODEL == WFPT_SIM_GAMMA_DRIFT_ANGLE);
+    static constexpr bool conflict = (MODEL == WFPT_SIM_DS_CONFLICT || MODEL == WFPT_SIM_DS_CONFLICT_ANGLE);
+    static constexpr bool tdrift = gamma || conflict;   // drift is a function of time
 };
 
 template <int MODEL>
@@ -120,11 +137,47 @@ __device__ __forceinline__ void load_set(SetConst& c, const float* __restrict__ 
     c.p5 = A.n_par > 5 ? th[5] : 0.f;
     c.p6 = A.n_par > 6 ? th[6] : 0.f;
     c.slope = 0.f; c.sdt = 0.f; c.inv_beta = 0.f; c.alpha = 0.f; c.g = 0.f; c.dt_alpha = 0.f;
-    if (MODEL == WFPT_SIM_ANGLE) { c.slope = -sinf(c.p4) / cosf(c.p4); c.sdt = c.slope * A.dt; }
+    c.d0 = c.d1 = c.d2 = c.d3 = c.d4 = 0.f;
+    float ang = c.p4;                                                               // angle model: v, a, z, t, theta
     if (MODEL == WFPT_SIM_WEIBULL) { c.alpha = c.p4; c.inv_beta = 1.0f / c.p5; }
     if (MODEL == WFPT_SIM_ORNSTEIN) { c.g = th[3]; c.t = th[4]; }             // theta = v, a, z, g, t
     if (MODEL == WFPT_SIM_LEVY) { c.alpha = th[3]; c.t = th[4]; c.dt_alpha = A.s * powf(A.dt, 1.0f / th[3]); }  // v, a, z, alpha, t
+    if (Traits<MODEL>::gamma) {
+        // theta = v, a, z, t, [theta,] shape, scale, c   (basic_simulator_old.py:343-377)
+        const int o = (MODEL == WFPT_SIM_GAMMA_DRIFT_ANGLE) ? 5 : 4;
+        const float shape = th[o], scale = th[o + 1], cc = th[o + 2];
+        // c * t^(shape-1) exp(-t/scale) / ((shape-1)^(shape-1) scale^(shape-1) exp(-(shape-1)))   (drift_functions.py:30-36)
+        const float div = powf(shape - 1.f, shape - 1.f) * powf(scale, shape - 1.f) * expf(-(shape - 1.f));
+        c.d0 = cc / div;
+        c.d1 = shape - 1.f;
+        c.d2 = -1.0f / scale;
+    }
+    if (Traits<MODEL>::conflict) {
+        // theta = a, z, t, tinit, dinit, tslope, dslope, tfixedp, tcoh, dcoh [, angle]; v = 0   (:379-425)
+        c.v = 0.f; c.a = th[0]; c.z = th[1]; c.t = th[2];
+        const float tinit = th[3], dinit = th[4], tslope = th[5], dslope = th[6], tfix = th[7], tcoh = th[8], dcoh = th[9];
+        // v(t) = ((tinit - tfix) e^{-tslope t} + tfix) tcoh + (dinit e^{-dslope t}) dcoh   (drift_functions.py:39-103)
+        c.d0 = (tinit - tfix) * tcoh;
+        c.d1 = -tslope;
+        c.d2 = tfix * tcoh;
+        c.d3 = dinit * dcoh;
+        c.d4 = -dslope;
+        ang = A.n_par > 10 ? th[10] : 0.f;
+    }
+    if (Traits<MODEL>::angle) { c.slope = -sinf(ang) / cosf(ang); c.sdt = c.slope * A.dt; }
     c.vdt = __fmul_rn(c.v, A.dt);
+}
+
+// Time-varying part of the drift at time ts (ddm_flex: drift[ix] = v + f(t_s[ix]))
+template <int MODEL>
+__device__ __forceinline__ float drift_at(const SetConst& c, float ts)
+{
+    if (Traits<MODEL>::gamma) {
+        const float pw = (ts > 0.f) ? exp2f(c.d1 * __log2f(ts)) : (c.d1 == 0.f ? 1.f : 0.f);
+        return c.v + c.d0 * pw * __expf(c.d2 * ts);
+    }
+    if (Traits<MODEL>::conflict) return c.d0 * __expf(c.d1 * ts) + c.d2 + c.d3 * __expf(c.d4 * ts);
+    return c.v;
 }
 
 // Upper bound after `fix` steps (time ts = fix*dt); the lower bound is -b for the flexbound family and 0 for the [0,a]
@@ -133,7 +186,7 @@ __device__ __forceinline__ void load_set(SetConst& c, const float* __restrict__ 
 template <int MODEL>
 __device__ __forceinline__ float bound_at(const SetConst& c, float fix, float dt)
 {
-    if (MODEL == WFPT_SIM_ANGLE) return fmaf(fix, c.sdt, c.a);
+    if (Traits<MODEL>::angle) return fmaf(fix, c.sdt, c.a);
     if (MODEL == WFPT_SIM_WEIBULL) {
         // a * exp(-(ts/beta)^alpha);  ts == 0 -> a
         const float r = (fix * dt) * c.inv_beta;
@@ -142,14 +195,6 @@ __device__ __forceinline__ float bound_at(const SetConst& c, float fix, float dt
     }
     return c.a;
 }
-
-template <int MODEL>
-struct Traits {
-    static constexpr bool zero_a = (MODEL == WFPT_SIM_DDM || MODEL == WFPT_SIM_FULL_DDM_BASE);  // bounds [0, a]
-    static constexpr bool moving = (MODEL == WFPT_SIM_ANGLE || MODEL == WFPT_SIM_WEIBULL);
-    static constexpr bool full = (MODEL == WFPT_SIM_FULL_DDM_BASE || MODEL == WFPT_SIM_FULL_DDM);
-    static constexpr bool sdv = (MODEL == WFPT_SIM_DDM_SDV);
-};
 
 // ---- the kernel ------------------------------------------------------------------------------------------------------------
 // Stream layout of particle (set, p): Philox key = seed, counter = (p_lo, p_hi, set, block).  Block 0xFFFFFFFF feeds the
@@ -240,6 +285,7 @@ __global__ void __launch_bounds__(kSimBlock) sim_kernel(const Args A)
                 const float inc = (MODEL == WFPT_SIM_LEVY) ? __fmul_rn(c.dt_alpha, nj) : __fmul_rn(sqrt_st, nj);
                 float det = drift;
                 if (MODEL == WFPT_SIM_ORNSTEIN) det = __fmul_rn(__fsub_rn(c.v, __fmul_rn(c.g, y)), A.dt);
+                if (Traits<MODEL>::tdrift) det = __fmul_rn(drift_at<MODEL>(c, __fmul_rn(fix, A.dt)), A.dt);  // drift[ix] * dt
                 if (in) {
                     y = __fadd_rn(y, __fadd_rn(det, inc));
                     tp = __fadd_rn(tp, A.dt);
@@ -253,7 +299,8 @@ __global__ void __launch_bounds__(kSimBlock) sim_kernel(const Args A)
                 my_steps += (unsigned long long)fix;
                 const float rt = __fadd_rn(tp, t_nd);
                 int choice;
-                if (Traits<MODEL>::zero_a) choice = (y < 0.f) ? 0 : 1;
+                if (MODEL == WFPT_SIM_DDM_COV) choice = (y < 0.f) - (y > 0.f);   // -sign(y)
+                else if (Traits<MODEL>::zero_a) choice = (y < 0.f) ? 0 : 1;
                 else choice = (y > 0.f) - (y < 0.f);
                 if (A.rts) {
                     const size_t o = (size_t)p * A.n_sets + set;
@@ -261,7 +308,7 @@ __global__ void __launch_bounds__(kSimBlock) sim_kernel(const Args A)
                     A.choices[o] = choice;
                 }
                 if (A.hist) {
-                    const int col = Traits<MODEL>::zero_a ? choice : (choice > 0 ? 1 : (choice < 0 ? 0 : -1));
+                    const int col = (Traits<MODEL>::zero_a && MODEL != WFPT_SIM_DDM_COV) ? choice : (choice > 0 ? 1 : (choice < 0 ? 0 : -1));
                     if (col >= 0) {
                         // np.histogram on edges linspace(0, max_t, nbins) + [inf] (basic_simulator_old.py:99-114)
                         const double rd = (double)rt;
@@ -443,7 +490,11 @@ static cudaError_t launch(const Args& A, int blocks, cudaStream_t stream)
 static int n_params_of(int model)
 {
     switch (model) {
-        case WFPT_SIM_DDM: case WFPT_SIM_DDM_FLEXBOUND: return 4;
+        case WFPT_SIM_DDM: case WFPT_SIM_DDM_FLEXBOUND: case WFPT_SIM_DDM_COV: return 4;
+        case WFPT_SIM_GAMMA_DRIFT: return 7;
+        case WFPT_SIM_GAMMA_DRIFT_ANGLE: return 8;
+        case WFPT_SIM_DS_CONFLICT: return 10;
+        case WFPT_SIM_DS_CONFLICT_ANGLE: return 11;
         case WFPT_SIM_ANGLE: case WFPT_SIM_DDM_SDV: case WFPT_SIM_ORNSTEIN: case WFPT_SIM_LEVY: return 5;
         case WFPT_SIM_WEIBULL: return 6;
         case WFPT_SIM_FULL_DDM_BASE: case WFPT_SIM_FULL_DDM: return 7;
@@ -510,6 +561,11 @@ extern "C" int wfpt_sim_run(int model, const float* d_theta, int n_par, int n_se
         case WFPT_SIM_FULL_DDM: e = sim::launch<WFPT_SIM_FULL_DDM>(A, blocks, st); break;
         case WFPT_SIM_DDM_SDV: e = sim::launch<WFPT_SIM_DDM_SDV>(A, blocks, st); break;
         case WFPT_SIM_ORNSTEIN: e = sim::launch<WFPT_SIM_ORNSTEIN>(A, blocks, st); break;
+        case WFPT_SIM_GAMMA_DRIFT: e = sim::launch<WFPT_SIM_GAMMA_DRIFT>(A, blocks, st); break;
+        case WFPT_SIM_GAMMA_DRIFT_ANGLE: e = sim::launch<WFPT_SIM_GAMMA_DRIFT_ANGLE>(A, blocks, st); break;
+        case WFPT_SIM_DS_CONFLICT: e = sim::launch<WFPT_SIM_DS_CONFLICT>(A, blocks, st); break;
+        case WFPT_SIM_DS_CONFLICT_ANGLE: e = sim::launch<WFPT_SIM_DS_CONFLICT_ANGLE>(A, blocks, st); break;
+        case WFPT_SIM_DDM_COV: e = sim::launch<WFPT_SIM_DDM_COV>(A, blocks, st); break;
         default: e = sim::launch<WFPT_SIM_LEVY>(A, blocks, st); break;
     }
     if (e != cudaSuccess) return api_fail(cudaGetErrorString(e));

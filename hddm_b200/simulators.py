@@ -28,6 +28,13 @@ _M = {
     "ddm_sdv": (6, ["v", "a", "z", "t", "sv"], "ddm_sdv", "constant", True, [-1, 1]),
     "ornstein": (7, ["v", "a", "z", "g", "t"], "ornstein_uhlenbeck", "constant", True, [-1, 1]),
     "levy": (8, ["v", "a", "z", "alpha", "t"], "levy_flexbound", "constant", True, [-1, 1]),
+    "gamma_drift": (9, ["v", "a", "z", "t", "shape", "scale", "c"], "ddm_flex", "constant", True, [-1, 1]),
+    "gamma_drift_angle": (10, ["v", "a", "z", "t", "theta", "shape", "scale", "c"], "ddm_flex", "angle", False, [-1, 1]),
+    "ds_conflict_drift": (11, ["a", "z", "t", "tinit", "dinit", "tslope", "dslope", "tfixedp", "tcoh", "dcoh"],
+                          "ddm_flex", "constant", True, [-1, 1]),
+    "ds_conflict_drift_angle": (12, ["a", "z", "t", "tinit", "dinit", "tslope", "dslope", "tfixedp", "tcoh", "dcoh", "angle"],
+                                "ddm_flex", "angle", False, [-1, 1]),
+    "ddm_cov": (13, ["v", "a", "z", "t"], "ddm", "constant", True, [-1, 1]),
 }
 # multi-accumulator models: name -> (lca, n_particles, angle, theta columns) -- column orders of the reference's dispatch
 # (/root/reference/graveyard/basic_simulator_old.py:476-760) and hddm/model_config.py:939-1200
@@ -49,8 +56,7 @@ _RACE = _race_entries()
 
 _ALIAS = {"ddm_legacy": "ddm_hddm_base", "full_ddm_legacy": "full_ddm_hddm_base", "test": "ddm",
           "weibull_cdf": "weibull"}
-_NEXT = ("gamma_drift", "gamma_drift_angle", "ds_conflict_drift", "ds_conflict_drift_angle",
-         "ddm_seq2", "ddm_par2", "ddm_mic2_adj", "tradeoff")
+_NEXT = ("ddm_seq2", "ddm_par2", "ddm_mic2_adj", "tradeoff")
 
 # minimal stand-in for the part of hddm.model_config the simulator boundary needs (params and choices per model)
 model_config = {name: {"params": list(cols), "choices": list(ch), "boundary_name": bnd, "boundary_multiplicative": mult}
@@ -95,10 +101,11 @@ def _boundary_array(name, theta_row, delta_t, max_t):
     """The `boundary` metadata entry: the last parameter set's bound on t_s = arange(0, max_t + dt, dt), float32
     (cddm_data_simulation.pyx:491-509; the reference overwrites one array per trial, so the last one survives)."""
     t_s = np.arange(0, max_t + delta_t, delta_t).astype(np.float32)
-    a = theta_row[1]
+    cols = _M[name][1]
+    a = theta_row[cols.index("a")]
     bnd = _M[name][3]
     if bnd == "angle":
-        th = theta_row[4]
+        th = theta_row[cols.index("theta") if "theta" in cols else cols.index("angle")]
         return np.add(a, np.multiply(t_s, (-np.sin(th) / np.cos(th)))).astype(np.float32)
     if bnd == "weibull_cdf":
         alpha, beta = theta_row[4], theta_row[5]

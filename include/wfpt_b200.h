@@ -163,6 +163,11 @@ int wfpt_dmat_cdf_array_host(const double* h_x, int64_t n, double v, double sv, 
 #define WFPT_SIM_DDM_SDV 6        /* ddm_sdv :876-994             theta = v, a, z, t, sv                                       */
 #define WFPT_SIM_ORNSTEIN 7       /* ornstein_uhlenbeck :1119-1219  theta = v, a, z, g, t                                      */
 #define WFPT_SIM_LEVY 8           /* levy_flexbound :642-741      theta = v, a, z, alpha, t                                    */
+#define WFPT_SIM_GAMMA_DRIFT 9        /* ddm_flex :1001-1113 + gamma_drift        theta = v, a, z, t, shape, scale, c          */
+#define WFPT_SIM_GAMMA_DRIFT_ANGLE 10 /* same, angle bound                         theta = v, a, z, t, theta, shape, scale, c   */
+#define WFPT_SIM_DS_CONFLICT 11       /* ddm_flex + ds_conflict_drift  theta = a, z, t, tinit, dinit, tslope, dslope, tfixedp, tcoh, dcoh */
+#define WFPT_SIM_DS_CONFLICT_ANGLE 12 /* same, angle bound             theta = ... , angle                                     */
+#define WFPT_SIM_DDM_COV 13           /* ddm_cov :384-449              theta = v, a, z, t    bounds [0,a], choices -sign(y)      */
 
 /* Parameters per set of a model id, or -1 for an unknown id. */
 int wfpt_sim_n_params(int model);

@@ -7,6 +7,9 @@
  *   model 3 ddm_flexbound + angle bound, 4 + Weibull bound (graveyard/boundary_functions.py:18-28, :50-63; the
  *           boundary table b[ix] = a (+|*) f(t_s[ix]) is built per parameter set as the reference does, :491-509)
  *   model 5 full_ddm :747-869       6 ddm_sdv :876-994   7 ornstein_uhlenbeck :1119-1219   8 levy_flexbound :642-741
+ *   model 9/10 ddm_flex :1001-1113 with gamma_drift (constant / angle bound), 11/12 with ds_conflict_drift
+ *           (graveyard/drift_functions.py:11-103; the drift table drift[ix] = v + f(t_s[ix]) is built per set, :1054-1056)
+ *   model 13 ddm_cov :384-449
  * Gaussian draws: Marsaglia polar method as in :48-60; alpha-stable draws: :28-40.  The RNG is xoshiro256** instead
  * of C rand(), so results agree with the reference in distribution, not draw by draw.
  *
@@ -63,27 +66,42 @@ static inline int sgn(float x) { return (x > 0) - (x < 0); }
 int orc_sim_run(int model, const float* theta, int n_par, int n_sets, int64_t n_samples, float dt, float max_t, float s,
                 uint64_t seed, float* rts, int32_t* choices)
 {
-    static const int npar[9] = {4, 7, 4, 5, 6, 7, 5, 5, 5};
-    if (model < 0 || model > 8 || n_par != npar[model]) return 1;
+    static const int npar[14] = {4, 7, 4, 5, 6, 7, 5, 5, 5, 7, 8, 10, 11, 4};
+    if (model < 0 || model > 13 || n_par != npar[model]) return 1;
     rng_t R;
     rng_seed(&R, seed);
     const float sqrt_st = (float)sqrt(dt) * s;
     const int nb = (int)((max_t / dt) + 1) + 2;
     float* b = (float*)malloc(sizeof(float) * (size_t)(nb + 1));
-    if (!b) return 2;
+    float* dr = (float*)malloc(sizeof(float) * (size_t)(nb + 1));
+    if (!b || !dr) return 2;
     for (int k = 0; k < n_sets; k++) {
         const float* th = theta + (size_t)k * n_par;
-        const float v = th[0], a = th[1], z = th[2];
-        float t = th[3], g = 0, alpha = 0, dt_alpha = 0;
+        float v = th[0], a = th[1], z = th[2];
+        float t = th[3], g = 0, alpha = 0, dt_alpha = 0, ang = (model == 3) ? th[4] : 0;
+        if (model == 10) ang = th[4];
+        if (model == 11 || model == 12) { v = 0; a = th[0]; z = th[1]; t = th[2]; if (model == 12) ang = th[10]; }
         if (model == 7) { g = th[3]; t = th[4]; }
         if (model == 8) { alpha = th[3]; t = th[4]; dt_alpha = (float)(s * pow(dt, 1.0 / alpha)); }
-        const int zero_a = (model == 0 || model == 1);
+        const int zero_a = (model == 0 || model == 1 || model == 13);
+        const int tdrift = (model >= 9 && model <= 12);
         /* boundary table on t_s = arange(0, max_t + dt, dt).astype(float32)  (:489-509) */
         for (int ix = 0; ix <= nb; ix++) {
             const float ts = (float)((double)ix * (double)dt);
-            if (model == 3) b[ix] = a + ts * (-sinf(th[4]) / cosf(th[4]));
+            if (model == 3 || model == 10 || model == 12) b[ix] = a + ts * (-sinf(ang) / cosf(ang));
             else if (model == 4) b[ix] = (float)(a * exp(-pow((double)ts / th[5], (double)th[4])));
             else b[ix] = a;
+            if (model == 9 || model == 10) {
+                const int o = (model == 10) ? 5 : 4;
+                const double shape = th[o], scale = th[o + 1], cc = th[o + 2];
+                const double num = pow((double)ts, shape - 1) * exp(-(double)ts / scale);
+                const double div = pow(shape - 1, shape - 1) * pow(scale, shape - 1) * exp(-(shape - 1));
+                dr[ix] = (float)(v + cc * (num / div));
+            } else if (model == 11 || model == 12) {
+                const double wt = ((double)th[3] - th[7]) * exp(-((double)th[5] * ts)) + th[7];
+                const double wd = ((double)th[4] - 0) * exp(-((double)th[6] * ts)) + 0;
+                dr[ix] = (float)(v + ((wt * th[8]) + (wd * th[9])));
+            } else dr[ix] = v;
         }
         for (int64_t n = 0; n < n_samples; n++) {
             float y = zero_a ? z * a : (-1) * b[0] + (z * 2 * b[0]);
@@ -100,16 +118,18 @@ int orc_sim_run(int model, const float* theta, int n_par, int n_sets, int64_t n_
             while ((zero_a ? (y >= 0 && y <= a) : (y >= (-1) * b[ix] && y <= b[ix])) && tp <= max_t) {
                 if (model == 8) y += (v * dt) + (dt_alpha * random_stable(&R, alpha));
                 else if (model == 7) y += ((v - (g * y)) * dt) + sqrt_st * random_gaussian(&R);
+                else if (tdrift) y += (dr[ix] * dt) + (sqrt_st * random_gaussian(&R));
                 else y += drift + (sqrt_st * random_gaussian(&R));
                 tp += dt;
                 ix++;
             }
             const size_t o = (size_t)n * n_sets + k;
             rts[o] = tp + t_nd;
-            choices[o] = zero_a ? (y < 0 ? 0 : 1) : sgn(y);
+            choices[o] = (model == 13) ? (-1) * sgn(y) : (zero_a ? (y < 0 ? 0 : 1) : sgn(y));
         }
     }
     free(b);
+    free(dr);
     return 0;
 }
 

@@ -18,6 +18,11 @@ CASES = {
     "ddm_sdv": (6, [0.8, 1.2, 0.5, 0.3, 1.0]),
     "ornstein": (7, [0.5, 1.2, 0.5, 0.6, 0.3]),
     "levy": (8, [0.5, 1.2, 0.5, 1.6, 0.3]),
+    "gamma_drift": (9, [0.3, 1.2, 0.5, 0.3, 3.0, 0.3, 1.5]),
+    "gamma_drift_angle": (10, [0.3, 1.2, 0.5, 0.3, 0.15, 3.0, 0.3, 1.5]),
+    "ds_conflict_drift": (11, [1.3, 0.5, 0.3, 0.5, 2.0, 2.0, 3.0, 1.5, 1.0, -1.0]),
+    "ds_conflict_drift_angle": (12, [1.3, 0.5, 0.3, 0.5, 2.0, 2.0, 3.0, 1.5, 1.0, -1.0, 0.2]),
+    "ddm_cov": (13, [1.0, 2.0, 0.5, 0.3]),
 }
 
 
@@ -106,6 +111,10 @@ def test_shapes_and_metadata_like_reference_test(sims):
         sims.simulator([1.0, 1.0, 0.5], model="angle")
     with pytest.raises(NotImplementedError):
         sims.simulator([0.0] * 8, model="ddm_par2")
+    # ddm_cov codes the lower boundary as +1 (cddm_data_simulation.pyx:437)
+    r0, c0, _ = sims.simulator([2.0, 2.0, 0.5, 0.3], model="ddm_hddm_base", n_samples=4000, random_state=3)
+    r1, c1, _ = sims.simulator([2.0, 2.0, 0.5, 0.3], model="ddm_cov", n_samples=4000, random_state=3)
+    assert np.array_equal(r0, r1) and np.array_equal(c1, np.where(c0 == 1, -1, 1))
 
 
 def test_streams_do_not_depend_on_geometry_or_sharding(sims):

@@ -96,6 +96,68 @@ def test_ornstein_and_levy_vs_reference(oracle, ref_sim):
     _agree(rt[:, 0], ch[:, 0], r[0][:, 0, 0], r[1][:, 0, 0])
 
 
+def gamma_drift(t, shape=2, scale=0.01, c=1.5):
+    # /root/reference/graveyard/drift_functions.py:11-36
+    num_ = np.power(t, shape - 1) * np.exp(np.divide(-t, scale))
+    div_ = np.power(shape - 1, shape - 1) * np.power(scale, shape - 1) * np.exp(-(shape - 1))
+    return c * np.divide(num_, div_)
+
+
+def ds_conflict_drift(t, init_p_t=0, init_p_d=0, slope_t=1, slope_d=1, fixed_p_t=1, coherence_t=1.5, coherence_d=1.5):
+    # drift_functions.py:39-103 (the drift timecourse itself)
+    w_t = (init_p_t - fixed_p_t) * np.exp(-(slope_t * t)) + fixed_p_t
+    w_d = (init_p_d - 0) * np.exp(-(slope_d * t)) + 0
+    return (w_t * coherence_t) + (w_d * coherence_d)
+
+
+def test_ddm_flex_and_ddm_cov_vs_reference(oracle, ref_sim):
+    v, a, z, t = _f32(0.3, 1.2, 0.5, 0.3)
+    dp = {"shape": np.array([3.0], dtype=np.float32), "scale": np.array([0.3], dtype=np.float32), "c": np.array([1.5], dtype=np.float32)}
+    r = ref_sim.ddm_flex(v, a, z, t, n_samples=N, n_trials=1, boundary_fun=angle, drift_fun=gamma_drift, boundary_multiplicative=False,
+                         boundary_params={"theta": np.array([0.15], dtype=np.float32)}, drift_params=dp)
+    rt, ch = oracle.sim_run(10, [0.3, 1.2, 0.5, 0.3, 0.15, 3.0, 0.3, 1.5], N, seed=19)
+    _agree(rt[:, 0], ch[:, 0], r[0][:, 0, 0], r[1][:, 0, 0])
+    th = [1.3, 0.5, 0.3, 0.5, 2.0, 2.0, 3.0, 1.5, 1.0, -1.0]
+    names = ["init_p_t", "init_p_d", "slope_t", "slope_d", "fixed_p_t", "coherence_t", "coherence_d"]
+    dp = {k: np.array([x], dtype=np.float32) for k, x in zip(names, th[3:])}
+    v0, a, z, t = _f32(0.0, th[0], th[1], th[2])
+    r = ref_sim.ddm_flex(v0, a, z, t, n_samples=N, n_trials=1, boundary_fun=constant, drift_fun=ds_conflict_drift,
+                         boundary_multiplicative=True, boundary_params={}, drift_params=dp)
+    rt, ch = oracle.sim_run(11, th, N, seed=20)
+    _agree(rt[:, 0], ch[:, 0], r[0][:, 0, 0], r[1][:, 0, 0])
+    v, a, z, t = _f32(1.0, 2.0, 0.5, 0.3)
+    r = ref_sim.ddm_cov(v, a, z, t, n_samples=N, n_trials=1)
+    rt, ch = oracle.sim_run(13, [1.0, 2.0, 0.5, 0.3], N, seed=21)
+    _agree(rt[:, 0], ch[:, 0], r[0][:, 0, 0], r[1][:, 0, 0])
+
+
+def test_race_and_lca_vs_reference(oracle, ref_sim):
+    n = 20000
+    s3 = np.ones((1, 3), dtype=np.float32)
+    v = np.array([[1.0, 0.5, 0.2]], dtype=np.float32)
+    a = np.array([[2.0]], dtype=np.float32)
+    z = np.array([[0.3, 0.3, 0.3]], dtype=np.float32)
+    t = np.array([[0.3]], dtype=np.float32)
+    r = ref_sim.race_model(v=v, a=a, z=z, t=t, s=s3, n_samples=n, n_trials=1, boundary_fun=constant,
+                           boundary_multiplicative=True, boundary_params={})
+    rt, ch = oracle.sim_race_run(0, 3, 0, [1.0, 0.5, 0.2, 2.0, 0.3, 0.3, 0.3, 0, 0, 0.3, 0], n, seed=22)
+    assert stats.ks_2samp(rt[:, 0], r[0][:, 0, 0]).pvalue > 1e-3
+    for c in range(3):
+        la, ha = _ci(int(np.sum(ch == c)), n)
+        lb, hb = _ci(int(np.sum(r[1] == c)), n)
+        assert la <= hb and lb <= ha
+    g = np.array([[0.5]], dtype=np.float32)
+    b = np.array([[0.3]], dtype=np.float32)
+    r = ref_sim.lca(v=v, a=a, z=z, g=g, b=b, t=t, s=s3, n_samples=n, n_trials=1, boundary_fun=angle,
+                    boundary_multiplicative=False, boundary_params={"theta": np.array([0.2], dtype=np.float32)})
+    rt, ch = oracle.sim_race_run(1, 3, 1, [1.0, 0.5, 0.2, 2.0, 0.3, 0.3, 0.3, 0.5, 0.3, 0.3, 0.2], n, seed=23)
+    assert stats.ks_2samp(rt[:, 0], r[0][:, 0, 0]).pvalue > 1e-3
+    for c in range(3):
+        la, ha = _ci(int(np.sum(ch == c)), n)
+        lb, hb = _ci(int(np.sum(r[1] == c)), n)
+        assert la <= hb and lb <= ha
+
+
 def test_ddm_vs_analytic_wfpt(oracle):
     """Constant bounds: P(upper) from prob_ub (pdf.pxi:67-72) and the RT density from full_pdf, as
     /root/reference/hddm/tests/test_generate.py:33-50 validates its own random walk."""
