@@ -218,8 +218,14 @@ def simulator(theta, model="angle", n_samples=1000, delta_t=0.001, max_t=20, no_
     binned = bin_dim is not None and bin_dim != 0
     if binned and bin_dim < 0:
         return "invalid bin_dim"
+    if binned and bin_pointwise and n_trials > 1 and n_samples > 1:
+        return "currently n_trials > 1 and n_samples > 1 will not work together with bin_pointwise"
     if binned and bin_pointwise:
-        raise NotImplementedError("pointwise binning is a next-row item (SURVEY 8(f) rank 4)")
+        # basic_simulator_old.py:1054-1068: simulate as usual, then replace every RT by its bin number
+        out = simulator(theta, model=model, n_samples=n_samples, delta_t=delta_t, max_t=max_t, no_noise=no_noise,
+                        random_state=seed)
+        b = bin_simulator_output_pointwise(out, nbins=int(bin_dim))
+        return (np.expand_dims(b[:, 0], axis=1), np.expand_dims(b[:, 1], axis=1), out[2])
     if binned and n_trials > 1:
         return "currently binned outputs not implemented for multi-trial simulators"
 
@@ -276,6 +282,24 @@ def bin_simulator_output(out, bin_dt=0.04, nbins=0, max_t=-1, freq_cnt=False):
     if not freq_cnt:
         counts = counts / out[2]["n_samples"]
     return counts
+
+
+def bin_simulator_output_pointwise(out, bin_dt=0.04, nbins=0):
+    """Host restatement of basic_simulator_old.py:27-67: int32 [n, 2] = (bin number of each RT, choice with -1 -> 0).
+    An RT lying exactly on a bin edge keeps its value, as in the reference's strict comparisons."""
+    max_t = out[2]["max_t"]
+    if nbins == 0:
+        nbins = int(max_t / bin_dt)
+    bins = np.zeros(nbins + 1)
+    bins[:nbins] = np.linspace(0, max_t, nbins)
+    bins[nbins] = np.inf
+    rt = np.array(out[0], dtype=np.float64, copy=True)
+    j = np.searchsorted(bins, rt, side="left")            # bins[j-1] < rt <= bins[j]
+    inside = (j >= 1) & (j <= nbins) & (rt < bins[np.minimum(j, nbins)])
+    binned = np.where(inside, j - 1, rt)
+    ch = np.array(out[1], copy=True)
+    ch[ch == -1] = 0
+    return np.concatenate([binned.astype(out[0].dtype), ch.astype(out[0].dtype)], axis=-1).astype(np.int32)
 
 
 def _smoke():
