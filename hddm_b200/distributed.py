@@ -53,6 +53,26 @@ def wiener_like_batch_sharded(x, params, group=None, evaluate=None, **opts):
     return gathered.index_select(0, idx)
 
 
+def wiener_like_batch_trial_sharded(x, params, group=None, evaluate=None, **opts):
+    """Large-N / small-P layout: every rank holds ALL parameter sets and evaluates them on its slice of the trials
+    (rank r takes x[r::W]); the per-set partial sums are combined with an all-reduce(sum).  -inf partials propagate
+    through the sum (a zero-density trial on any rank makes the total -inf, as in the reference); the summation order
+    differs from the single-GPU run by rounding (~1e-16 relative).  All ranks return the full float64[P] vector."""
+    import torch.distributed as dist
+
+    if evaluate is None:
+        from . import wfpt
+
+        evaluate = wfpt.wiener_like_batch
+    world = dist.get_world_size(group) if dist.is_initialized() else 1
+    rank = dist.get_rank(group) if dist.is_initialized() else 0
+    if world == 1:
+        return evaluate(x, params, **opts)
+    part = evaluate(x[rank::world].contiguous(), params, **opts).clone()
+    dist.all_reduce(part, op=dist.ReduceOp.SUM, group=group)
+    return part
+
+
 def merge_histograms(counts, group=None):
     """Sum integer histogram counts over ranks in place (particles sharded over ranks) and return them."""
     import torch.distributed as dist

@@ -40,10 +40,19 @@ def _worker(rank, world, port, P, q):
 
     full = D.wiener_like_batch_sharded(torch.from_numpy(x), torch.from_numpy(prm), evaluate=evaluate)
     want = oracle.wiener_like_batch(x, prm, 1e-4, 2, 2, 0, 1e-3, 0.1)
+    # trial-axis sharding: all-reduce of partial sums; a zero-density trial on one rank makes the total -inf
+    prm2 = prm[:5].copy()
+    prm2[4, 5] = 0.9    # t above some |rt| -> density 0 for those trials; with p_outlier = 0 the sum is -inf
+    prm2[4, 6] = 0.0
+    prm2[4, 7] = 0.0
+    tot = D.wiener_like_batch_trial_sharded(torch.from_numpy(x), torch.from_numpy(prm2), evaluate=evaluate)
+    want2 = oracle.wiener_like_batch(x, prm2, 1e-4, 2, 2, 0, 1e-3, 0.1)
+    ok_trial = bool(np.isneginf(tot.numpy()[4]) and np.isneginf(want2[4]) and
+                    np.allclose(tot.numpy()[:4], want2[:4], rtol=1e-12, atol=0))
     hist = torch.full((4, 8, 2), rank + 1, dtype=torch.int64)
     D.merge_histograms(hist)
-    ok = bool(np.array_equal(full.numpy(), want)) and calls == [len(D.shard_rows(P, rank, world))] and \
-        bool((hist == sum(range(1, world + 1))).all())
+    ok = bool(np.array_equal(full.numpy(), want)) and calls[0] == len(D.shard_rows(P, rank, world)) and \
+        bool((hist == sum(range(1, world + 1))).all()) and ok_trial
     q.put((rank, ok))
     dist.destroy_process_group()
 
