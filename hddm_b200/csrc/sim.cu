@@ -60,35 +60,57 @@ struct Args {
 };
 
 // ---- Philox4x32-10 -------------------------------------------------------------------------------------------------------
+// The ten round keys depend on the seed only: the Weyl sequence k + r*W is computed once per thread (RoundKeys), not per block.
+struct RoundKeys {
+    unsigned int a[10], b[10];
+    __device__ __forceinline__ RoundKeys(unsigned int k0, unsigned int k1)
+    {
+#pragma unroll
+        for (int r = 0; r < 10; r++) {
+            a[r] = k0 + (unsigned int)r * 0x9E3779B9u;
+            b[r] = k1 + (unsigned int)r * 0xBB67AE85u;
+        }
+    }
+};
+
 __device__ __forceinline__ uint4 philox4x32(unsigned int c0, unsigned int c1, unsigned int c2, unsigned int c3,
-                                            unsigned int k0, unsigned int k1)
+                                            const RoundKeys& k)
 {
 #pragma unroll
     for (int r = 0; r < 10; r++) {
-        const unsigned long long p0 = (unsigned long long)0xD2511F53u * c0;
-        const unsigned long long p1 = (unsigned long long)0xCD9E8D57u * c2;
-        const unsigned int n0 = (unsigned int)(p1 >> 32) ^ c1 ^ k0;
-        const unsigned int n2 = (unsigned int)(p0 >> 32) ^ c3 ^ k1;
-        c1 = (unsigned int)p1;
-        c3 = (unsigned int)p0;
-        c0 = n0;
-        c2 = n2;
-        k0 += 0x9E3779B9u;
-        k1 += 0xBB67AE85u;
+        // (separate high / low multiplies: the 64-bit product form costs two extra instructions per multiply here)
+        const unsigned int h0 = __umulhi(0xD2511F53u, c0), l0 = 0xD2511F53u * c0;
+        const unsigned int h1 = __umulhi(0xCD9E8D57u, c2), l1 = 0xCD9E8D57u * c2;
+        c0 = h1 ^ c1 ^ k.a[r];
+        c2 = h0 ^ c3 ^ k.b[r];
+        c1 = l1;
+        c3 = l0;
     }
     return make_uint4(c0, c1, c2, c3);
 }
 
 __device__ __forceinline__ float u01(unsigned int x) { return ((float)x + 0.5f) * 2.3283064365386963e-10f; }  // (0, 1)
 
-// Four standard normals from one Philox block (two Box-Muller pairs, fast intrinsics).
+// Box-Muller radius sqrt(-2 ln u) for u = (x + 0.5) 2^-32 in (0, 1): one lg2 and one rsqrt on the SFU, no special cases
+// (u is never 0, 1 or subnormal, so the guarded library forms of log and sqrt are not needed).
+__device__ __forceinline__ float bm_radius(unsigned int x)
+{
+    const float u = fmaf((float)x, 2.3283064365386963e-10f, 1.1641532182693481e-10f);
+    float l2;
+    asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(l2) : "f"(u));
+    const float q = fmaxf(l2 * -1.3862943611198906f, 1e-30f);   // -2 ln u  (> 0; the floor only guards u rounding to 1)
+    float rs;
+    asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(rs) : "f"(q));
+    return q * rs;
+}
+
+// Four standard normals from one Philox block (two Box-Muller pairs on the special-function unit).
 __device__ __forceinline__ float4 normals4(const uint4 r)
 {
-    const float r0 = sqrtf(-2.0f * __logf(u01(r.x))), r1 = sqrtf(-2.0f * __logf(u01(r.z)));
-    float s0, c0, s1, c1;
-    __sincosf(6.283185307179586f * u01(r.y), &s0, &c0);
-    __sincosf(6.283185307179586f * u01(r.w), &s1, &c1);
-    return make_float4(r0 * c0, r0 * s0, r1 * c1, r1 * s1);
+    const float r0 = bm_radius(r.x), r1 = bm_radius(r.z);
+    const float a0 = fmaf((float)r.y, 1.4629180792671596e-09f, 7.314590396335798e-10f);   // 2 pi (y + 0.5) 2^-32
+    const float a1 = fmaf((float)r.w, 1.4629180792671596e-09f, 7.314590396335798e-10f);
+    return make_float4(r0 * __cosf(a0), r0 * __sinf(a0), r1 * __cosf(a1), r1 * __sinf(a1));
 }
 
 // Chambers-Mallows-Stuck draw as the reference writes it (cddm_data_simulation.pyx:28-40)
@@ -202,14 +224,15 @@ __device__ __forceinline__ float bound_at(const SetConst& c, float fix, float dt
 // steps 4j .. 4j+3 (one normal each; Levy: steps 2j, 2j+1, two uniforms each).  All lanes of a warp fetch their blocks
 // at the same loop iteration: a lane whose particle ends mid-block idles for at most three sub-steps and starts its
 // next particle at the next block boundary, so the Philox rounds and the Box-Muller transform never run diverged.
-template <int MODEL>
+// TRACE: a one-particle instantiation that also writes the path of (set 0, particle 0) -- kept out of the production loop.
+template <int MODEL, bool TRACE>
 __global__ void __launch_bounds__(kSimBlock) sim_kernel(const Args A)
 {
     extern __shared__ unsigned int s_hist[];  // [nbins][2] when A.hist
     __shared__ int s_next;                    // next undistributed particle of the current item
     const int nh = A.hist ? A.nbins * 2 : 0;
     const float sqrt_st = __fmul_rn(sqrtf(A.dt), A.s);
-    const unsigned int k0 = (unsigned int)A.seed, k1 = (unsigned int)(A.seed >> 32);
+    const RoundKeys rk((unsigned int)A.seed, (unsigned int)(A.seed >> 32));
     unsigned long long my_steps = 0;
     const long long n_items = (long long)A.n_sets * A.items_per_set;
 
@@ -232,7 +255,6 @@ __global__ void __launch_bounds__(kSimBlock) sim_kernel(const Args A)
         bool walking = false;
         float y = 0.f, tp = 0.f, fix = 0.f, drift = c.vdt, t_nd = c.t, b = c.a;
         unsigned int blk = 0, plo = 0, phi = 0;
-        bool tracing = false;
         while (active) {
             if (!walking) {
                 // ---- start a particle ----
@@ -248,7 +270,7 @@ __global__ void __launch_bounds__(kSimBlock) sim_kernel(const Args A)
                 if (Traits<MODEL>::zero_a) y = __fmul_rn(c.z, c.a);
                 else y = __fadd_rn(-b, __fmul_rn(__fmul_rn(c.z, 2.f), b));
                 if (Traits<MODEL>::full || Traits<MODEL>::sdv) {
-                    const uint4 r = philox4x32(plo, phi, (unsigned int)set, 0xFFFFFFFFu, k0, k1);
+                    const uint4 r = philox4x32(plo, phi, (unsigned int)set, 0xFFFFFFFFu, rk);
                     const float g = sqrtf(-2.0f * __logf(u01(r.x))) * __cosf(6.283185307179586f * u01(r.y));
                     if (Traits<MODEL>::full) {
                         // theta = v, a, z, t, sz, sv, st  (:228-235, :812-820)
@@ -259,12 +281,11 @@ __global__ void __launch_bounds__(kSimBlock) sim_kernel(const Args A)
                         drift = __fmul_rn(__fadd_rn(c.v, __fmul_rn(c.p4, g)), A.dt);  // theta = v, a, z, t, sv
                     }
                 }
-                tracing = A.traj && set == 0 && gp == 0;
-                if (tracing) A.traj[0] = y;
+                if (TRACE) A.traj[0] = y;
                 walking = true;
             }
             // ---- one Philox block for everybody, then up to four sub-steps ----
-            const uint4 r = philox4x32(plo, phi, (unsigned int)set, blk++, k0, k1);
+            const uint4 r = philox4x32(plo, phi, (unsigned int)set, blk++, rk);
             float4 nn;
             if (MODEL == WFPT_SIM_LEVY) {
                 nn.x = stable_draw(c.alpha, u01(r.x), u01(r.y));
@@ -286,13 +307,18 @@ __global__ void __launch_bounds__(kSimBlock) sim_kernel(const Args A)
                 float det = drift;
                 if (MODEL == WFPT_SIM_ORNSTEIN) det = __fmul_rn(__fsub_rn(c.v, __fmul_rn(c.g, y)), A.dt);
                 if (Traits<MODEL>::tdrift) det = __fmul_rn(drift_at<MODEL>(c, __fmul_rn(fix, A.dt)), A.dt);  // drift[ix] * dt
-                if (in) {
-                    y = __fadd_rn(y, __fadd_rn(det, inc));
-                    tp = __fadd_rn(tp, A.dt);
-                    fix += 1.0f;
-                    if (Traits<MODEL>::moving) b = bound_at<MODEL>(c, fix, A.dt);
-                    if (tracing && (int)fix < A.traj_len) A.traj[(int)fix] = y;
+                // selects, not branches: the four sub-steps stay one basic block
+                const float y_new = __fadd_rn(y, __fadd_rn(det, inc));
+                const float tp_new = __fadd_rn(tp, A.dt);
+                const float fix_new = fix + 1.0f;
+                y = in ? y_new : y;
+                tp = in ? tp_new : tp;
+                fix = in ? fix_new : fix;
+                if (Traits<MODEL>::moving) {
+                    const float b_new = bound_at<MODEL>(c, fix_new, A.dt);
+                    b = in ? b_new : b;
                 }
+                if (TRACE && in && (int)fix < A.traj_len) A.traj[(int)fix] = y;
             }
             if (done) {
                 // ---- record and take the next particle ----
@@ -367,7 +393,7 @@ __global__ void __launch_bounds__(kSimBlock) race_kernel(const Args A)
     __shared__ int s_next;
     const int nh = A.hist ? A.nbins * NP : 0;
     const float sqrt_st = __fmul_rn(sqrtf(A.dt), A.s);
-    const unsigned int k0 = (unsigned int)A.seed, k1 = (unsigned int)(A.seed >> 32);
+    const RoundKeys rk((unsigned int)A.seed, (unsigned int)(A.seed >> 32));
     unsigned long long my_steps = 0;
     const long long item = blockIdx.x;
     const int set = (int)(item / A.items_per_set);
@@ -401,7 +427,7 @@ __global__ void __launch_bounds__(kSimBlock) race_kernel(const Args A)
 #pragma unroll
             for (int j = 0; j < NP; j++) hit |= (y[j] > b);
             if (hit || !(tp <= A.max_t)) break;
-            const float4 nn = normals4(philox4x32((unsigned int)gp, (unsigned int)(gp >> 32), (unsigned int)set, blk++, k0, k1));
+            const float4 nn = normals4(philox4x32((unsigned int)gp, (unsigned int)(gp >> 32), (unsigned int)set, blk++, rk));
             float sum = 0.f;
             if (LCA) {
 #pragma unroll
@@ -483,7 +509,16 @@ template <int MODEL>
 static cudaError_t launch(const Args& A, int blocks, cudaStream_t stream)
 {
     const size_t smem = A.hist ? sizeof(unsigned int) * 2 * (size_t)A.nbins : 0;
-    sim_kernel<MODEL><<<blocks, kSimBlock, smem, stream>>>(A);
+    Args P = A;
+    P.traj = nullptr;
+    sim_kernel<MODEL, false><<<blocks, kSimBlock, smem, stream>>>(P);
+    if (A.traj && A.sample_offset == 0) {
+        // the trajectory of (set 0, particle 0): the same walk again, one particle, path written out
+        Args T = A;
+        T.n_sets = 1; T.n_samples = 1; T.chunk = 1; T.items_per_set = 1;
+        T.rts = nullptr; T.choices = nullptr; T.hist = nullptr; T.nbins = 0; T.steps = nullptr;
+        sim_kernel<MODEL, true><<<1, kSimBlock, 0, stream>>>(T);
+    }
     return cudaGetLastError();
 }
 
