@@ -505,6 +505,119 @@ static cudaError_t launch_race(const Args& A, int angle, int blocks, cudaStream_
     return cudaGetLastError();
 }
 
+// ---- two-stage 4-choice model: ddm_flexbound_par2 (cddm_data_simulation.pyx:1667-1791) ------------------------------------
+// A "high-dimension" walk (v_h, z_h) decides between the option pairs {0,1} and {2,3}; a "low-dimension" walk with the
+// drift / start point of the chosen pair (v_l1, z_l1 or v_l2, z_l2) decides inside the pair.  Both walks start at time 0
+// against the same bound b(t) (each with its own step index); rt = max(t_h, t_l) + t; choice = (y_h < 0 ? 0 : 2) +
+// (sign(y_l) >= 0).  theta (canonical): v_h, v_l1, v_l2, a, z_h, z_l1, z_l2, t, b0, b1; BOUND 0 constant, 1 angle (b0),
+// 2 Weibull (b0 = alpha, b1 = beta).  One Philox stream per particle, consumed in order by the two walks.
+template <int BOUND>
+__global__ void __launch_bounds__(kSimBlock) par2_kernel(const Args A)
+{
+    extern __shared__ unsigned int s_hist[];  // [nbins][4] when A.hist
+    __shared__ int s_next;
+    const int nh = A.hist ? A.nbins * 4 : 0;
+    const float sqrt_st = __fmul_rn(sqrtf(A.dt), A.s);
+    const RoundKeys rk((unsigned int)A.seed, (unsigned int)(A.seed >> 32));
+    unsigned long long my_steps = 0;
+    const long long item = blockIdx.x;
+    const int set = (int)(item / A.items_per_set);
+    const long long beg = (item - (long long)set * A.items_per_set) * A.chunk;
+    const long long end = (beg + A.chunk < A.n_samples) ? beg + A.chunk : A.n_samples;
+    for (int i = threadIdx.x; i < nh; i += kSimBlock) s_hist[i] = 0u;
+    if (threadIdx.x == 0) s_next = kSimBlock;
+    __syncthreads();
+
+    const float* th = A.theta + (size_t)set * A.n_par;
+    const float v_h = th[0], v_l1 = th[1], v_l2 = th[2], a = th[3], z_h = th[4], z_l1 = th[5], z_l2 = th[6], t_nd = th[7];
+    const float sdt = (BOUND == 1) ? (-sinf(th[8]) / cosf(th[8])) * A.dt : 0.f;
+    const float w_alpha = th[8], w_inv_beta = (BOUND == 2) ? 1.0f / th[9] : 0.f;
+    auto bound = [&](float fix) -> float {
+        if (BOUND == 1) return fmaf(fix, sdt, a);
+        if (BOUND == 2) {
+            const float r = (fix * A.dt) * w_inv_beta;
+            const float pw = (r > 0.f) ? exp2f(w_alpha * __log2f(r)) : 0.f;
+            return a * __expf(-pw);
+        }
+        return a;
+    };
+    const float b0 = bound(0.f);
+
+    long long p = beg + threadIdx.x;
+    while (p < end) {
+        const unsigned long long gp = (unsigned long long)(p + A.sample_offset);
+        unsigned int blk = 0;
+        float4 nn = make_float4(0.f, 0.f, 0.f, 0.f);
+        int have = 0;
+        auto normal = [&]() -> float {
+            if (have == 0) {
+                nn = normals4(philox4x32((unsigned int)gp, (unsigned int)(gp >> 32), (unsigned int)set, blk++, rk));
+                have = 4;
+            }
+            have--;
+            return have == 3 ? nn.x : have == 2 ? nn.y : have == 1 ? nn.z : nn.w;
+        };
+        auto walk = [&](float z, float v, float* t_out) -> float {
+            float y = __fadd_rn(-b0, __fmul_rn(__fmul_rn(z, 2.f), b0));
+            float b = b0, tp = 0.f, fix = 0.f;
+            const float vdt = __fmul_rn(v, A.dt);
+            while (y >= -b && y <= b && tp <= A.max_t) {
+                y = __fadd_rn(y, __fadd_rn(vdt, __fmul_rn(sqrt_st, normal())));
+                tp = __fadd_rn(tp, A.dt);
+                fix += 1.0f;
+                if (BOUND != 0) b = bound(fix);
+            }
+            my_steps += (unsigned long long)fix;
+            *t_out = tp;
+            return y;
+        };
+        float t_h, t_l;
+        const float y_h = walk(z_h, v_h, &t_h);
+        const bool lower = y_h < 0.f;                       // sign(y_h) < 0  (:1747)
+        const float y_l = walk(lower ? z_l1 : z_l2, lower ? v_l1 : v_l2, &t_l);
+        const int choice = (lower ? 0 : 2) + ((y_l >= 0.f) ? 1 : 0);
+        const float rt = __fadd_rn(fmaxf(t_h, t_l), t_nd);
+        if (A.rts) {
+            const size_t o = (size_t)p * A.n_sets + set;
+            A.rts[o] = rt;
+            A.choices[o] = choice;
+        }
+        if (A.hist) {
+            const double rd = (double)rt;
+            int bin = (int)(rd / A.hist_step);
+            if (bin > A.nbins - 1) bin = A.nbins - 1;
+            if (bin < 0) bin = 0;
+            const double e_lo = (bin == A.nbins - 1) ? A.hist_max_t : bin * A.hist_step;
+            if (rd < e_lo && bin > 0) bin--;
+            else if (bin < A.nbins - 1) {
+                const double e_hi = (bin + 1 == A.nbins - 1) ? A.hist_max_t : (bin + 1) * A.hist_step;
+                if (rd >= e_hi) bin++;
+            }
+            if (rd >= 0.0) atomicAdd(&s_hist[bin * 4 + choice], 1u);
+        }
+        p = beg + (long long)atomicAdd(&s_next, 1);
+    }
+    __syncthreads();
+    if (A.hist) {
+        unsigned int* gh = A.hist + (size_t)set * nh;
+        for (int i = threadIdx.x; i < nh; i += kSimBlock) {
+            const unsigned int c = s_hist[i];
+            if (c) atomicAdd(&gh[i], c);
+        }
+    }
+    if (A.steps) {
+        __shared__ unsigned long long s_steps[kSimBlock / 32];
+        for (int off = 16; off > 0; off >>= 1) my_steps += __shfl_down_sync(0xffffffffu, my_steps, off);
+        if ((threadIdx.x & 31) == 0) s_steps[threadIdx.x >> 5] = my_steps;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            unsigned long long tot = 0;
+            for (int i = 0; i < kSimBlock / 32; i++) tot += s_steps[i];
+            atomicAdd(A.steps, tot);
+        }
+    }
+}
+
 template <int MODEL>
 static cudaError_t launch(const Args& A, int blocks, cudaStream_t stream)
 {
@@ -696,6 +809,62 @@ extern "C" int wfpt_sim_race_run_host(int lca, int n_particles, int angle, const
         else if (n_particles == 3) e = lca ? sim::launch_race<3, true>(A, angle, blocks, 0) : sim::launch_race<3, false>(A, angle, blocks, 0);
         else e = lca ? sim::launch_race<4, true>(A, angle, blocks, 0) : sim::launch_race<4, false>(A, angle, blocks, 0);
         SCK(e);
+        count_launch(1);
+    }
+    SCK(cudaDeviceSynchronize());
+    if (h_rts) {
+        SCK(cudaMemcpy(h_rts, d_rts, sizeof(float) * n_out, cudaMemcpyDeviceToHost));
+        SCK(cudaMemcpy(h_choices, d_ch, sizeof(int32_t) * n_out, cudaMemcpyDeviceToHost));
+    }
+    if (h_hist) SCK(cudaMemcpy(h_hist, d_hist, sizeof(uint32_t) * hist_n, cudaMemcpyDeviceToHost));
+    if (h_steps) SCK(cudaMemcpy(h_steps, d_steps, sizeof(uint64_t), cudaMemcpyDeviceToHost));
+done:
+    cudaFree(d_theta); cudaFree(d_rts); cudaFree(d_ch); cudaFree(d_hist); cudaFree(d_steps);
+    return rc;
+}
+
+
+extern "C" int wfpt_sim_par2_run_host(int bound_kind, const float* h_theta, int n_sets, int64_t n_samples, int64_t sample_offset,
+                                      float delta_t, float max_t, float s, uint64_t seed, float* h_rts, int32_t* h_choices,
+                                      uint32_t* h_hist, int nbins, float hist_max_t, uint64_t* h_steps)
+{
+    if (bound_kind < 0 || bound_kind > 2) return api_fail("wfpt_sim_par2_run_host: bound_kind must be 0 (constant), 1 (angle) or 2 (Weibull)");
+    if (n_sets < 0 || n_samples < 0) return api_fail("wfpt_sim_par2_run_host: negative size");
+    if (n_sets == 0 || n_samples == 0) return 0;
+    if (!h_theta) return api_fail("wfpt_sim_par2_run_host: null theta");
+    if ((h_rts == nullptr) != (h_choices == nullptr)) return api_fail("wfpt_sim_par2_run_host: rts and choices must be given together");
+    if (!h_rts && !h_hist) return api_fail("wfpt_sim_par2_run_host: nothing to write");
+    if (!(delta_t > 0.f) || !(max_t > 0.f)) return api_fail("wfpt_sim_par2_run_host: delta_t and max_t must be positive");
+    if (h_hist && (nbins < 2 || nbins * 4 > 2 * sim::kMaxBins)) return api_fail("wfpt_sim_par2_run_host: nbins out of range");
+    const int n_par = 10;
+    int rc = 0;
+    float *d_theta = nullptr, *d_rts = nullptr;
+    int32_t* d_ch = nullptr;
+    uint32_t* d_hist = nullptr;
+    uint64_t* d_steps = nullptr;
+    const size_t n_out = (size_t)n_samples * (size_t)n_sets;
+    const size_t hist_n = (size_t)n_sets * (size_t)(nbins > 0 ? nbins : 0) * 4;
+    sim::Args A;
+    SCK(cudaMalloc(&d_theta, sizeof(float) * (size_t)n_sets * n_par));
+    SCK(cudaMemcpy(d_theta, h_theta, sizeof(float) * (size_t)n_sets * n_par, cudaMemcpyHostToDevice));
+    if (h_rts) { SCK(cudaMalloc(&d_rts, sizeof(float) * n_out)); SCK(cudaMalloc(&d_ch, sizeof(int32_t) * n_out)); }
+    if (h_hist) { SCK(cudaMalloc(&d_hist, sizeof(uint32_t) * hist_n)); SCK(cudaMemset(d_hist, 0, sizeof(uint32_t) * hist_n)); }
+    if (h_steps) { SCK(cudaMalloc(&d_steps, sizeof(uint64_t))); SCK(cudaMemset(d_steps, 0, sizeof(uint64_t))); }
+    A.theta = d_theta; A.n_par = n_par; A.n_sets = n_sets; A.n_samples = n_samples; A.sample_offset = sample_offset;
+    A.out_stride_samples = n_samples; A.dt = delta_t; A.max_t = max_t; A.s = s; A.seed = seed; A.rts = d_rts; A.choices = d_ch;
+    A.hist = d_hist; A.nbins = d_hist ? nbins : 0; A.hist_max_t = (double)hist_max_t;
+    A.hist_step = d_hist ? (double)hist_max_t / (double)(nbins - 1) : 1.0;
+    A.steps = (unsigned long long*)d_steps; A.traj = nullptr; A.traj_len = 0;
+    A.chunk = n_samples < 4096 ? n_samples : 4096;
+    A.items_per_set = (n_samples + A.chunk - 1) / A.chunk;
+    {
+        const long long n_items = A.items_per_set * n_sets;
+        if (n_items > 2147483647LL) { rc = api_fail("wfpt_sim_par2_run_host: too many work items; split the call"); goto done; }
+        const size_t smem = A.hist ? sizeof(unsigned int) * 4 * (size_t)A.nbins : 0;
+        if (bound_kind == 0) sim::par2_kernel<0><<<(int)n_items, sim::kSimBlock, smem>>>(A);
+        else if (bound_kind == 1) sim::par2_kernel<1><<<(int)n_items, sim::kSimBlock, smem>>>(A);
+        else sim::par2_kernel<2><<<(int)n_items, sim::kSimBlock, smem>>>(A);
+        SCK(cudaGetLastError());
         count_launch(1);
     }
     SCK(cudaDeviceSynchronize());

@@ -54,9 +54,18 @@ def _race_entries():
 
 _RACE = _race_entries()
 
+# two-stage 4-choice model ddm_flexbound_par2: name -> (bound kind, theta columns); column orders of
+# /root/reference/graveyard/basic_simulator_old.py:795-873 (no_bias variants fix every starting point at 0.5)
+_PAR2 = {
+    "ddm_par2": (0, ["vh", "vl1", "vl2", "a", "zh", "zl1", "zl2", "t"]),
+    "ddm_par2_no_bias": (0, ["vh", "vl1", "vl2", "a", "t"]),
+    "ddm_par2_angle_no_bias": (1, ["vh", "vl1", "vl2", "a", "t", "theta"]),
+    "ddm_par2_weibull_no_bias": (2, ["vh", "vl1", "vl2", "a", "t", "alpha", "beta"]),
+}
+
 _ALIAS = {"ddm_legacy": "ddm_hddm_base", "full_ddm_legacy": "full_ddm_hddm_base", "test": "ddm",
           "weibull_cdf": "weibull"}
-_NEXT = ("ddm_seq2", "ddm_par2", "ddm_mic2_adj", "tradeoff")
+_NEXT = ("ddm_seq2", "ddm_mic2_adj", "tradeoff")
 
 # minimal stand-in for the part of hddm.model_config the simulator boundary needs (params and choices per model)
 model_config = {name: {"params": list(cols), "choices": list(ch), "boundary_name": bnd, "boundary_multiplicative": mult}
@@ -66,9 +75,14 @@ model_config.update({name: {"params": list(cols), "choices": list(range(npar)), 
                      for name, (_, npar, ang, cols) in _RACE.items()})
 
 
+model_config.update({name: {"params": list(cols), "choices": [0, 1, 2, 3],
+                            "boundary_name": ("constant", "angle", "weibull_cdf")[kind], "boundary_multiplicative": kind != 1}
+                     for name, (kind, cols) in _PAR2.items()})
+
+
 def _resolve(model):
     name = _ALIAS.get(model, model)
-    if name in _RACE:
+    if name in _RACE or name in _PAR2:
         return name
     if name not in _M:
         if any(model.startswith(p) for p in _NEXT):
@@ -79,7 +93,7 @@ def _resolve(model):
 
 def _coerce_theta(theta, name):
     """basic_simulator_old.py:208-224."""
-    cols = _RACE[name][3] if name in _RACE else _M[name][1]
+    cols = _RACE[name][3] if name in _RACE else (_PAR2[name][1] if name in _PAR2 else _M[name][1])
     if isinstance(theta, list):
         theta = np.asarray(theta).astype(np.float32)
     elif isinstance(theta, np.ndarray):
@@ -202,6 +216,60 @@ def _simulator_race(name, model, theta, n_samples, delta_t, max_t, s, seed, bin_
     return (rts, choices, meta)
 
 
+def _par2_canonical(name, theta):
+    """Per-model columns -> v_h, v_l1, v_l2, a, z_h, z_l1, z_l2, t, b0, b1 (starting points 0.5 where the model has none)."""
+    kind, cols = _PAR2[name]
+    col = {c: theta[:, i] for i, c in enumerate(cols)}
+    half = np.full(theta.shape[0], 0.5, dtype=np.float32)
+    zero = np.zeros(theta.shape[0], dtype=np.float32)
+    b0 = col.get("theta", col.get("alpha", zero))
+    out = [col["vh"], col["vl1"], col["vl2"], col["a"], col.get("zh", half), col.get("zl1", half), col.get("zl2", half),
+           col["t"], b0, col.get("beta", zero)]
+    return np.ascontiguousarray(np.stack(out, axis=1), dtype=np.float32)
+
+
+def _run_par2(name, theta, n_samples, delta_t, max_t, s, seed, want_raw, nbins, sample_offset=0):
+    L = _lib.load()
+    kind = _PAR2[name][0]
+    canon = _par2_canonical(name, theta)
+    n_sets = canon.shape[0]
+    rts = choices = hist = None
+    steps = np.zeros(1, dtype=np.uint64)
+    if want_raw:
+        rts = np.empty((n_samples, n_sets, 1), dtype=np.float32)
+        choices = np.empty((n_samples, n_sets, 1), dtype=np.int32)
+    if nbins:
+        hist = np.zeros((n_sets, nbins, 4), dtype=np.uint32)
+
+    def p(a):
+        return a.ctypes.data_as(C.c_void_p) if a is not None else None
+
+    _lib.check(L.wfpt_sim_par2_run_host(kind, p(canon), n_sets, int(n_samples), int(sample_offset), float(delta_t), float(max_t),
+                                        float(s), seed, p(rts), p(choices), p(hist), int(nbins or 0), float(max_t), p(steps)))
+    return rts, choices, hist, int(steps[0])
+
+
+def _simulator_par2(name, model, theta, n_samples, delta_t, max_t, s, seed, bin_dim, binned):
+    kind, cols = _PAR2[name]
+    n_trials = theta.shape[0]
+    rts, choices, hist, steps = _run_par2(name, theta, n_samples, delta_t, max_t, s, seed, True, int(bin_dim) if binned else 0)
+    canon = _par2_canonical(name, theta)
+    meta = {c: theta[:, i].copy() for i, c in enumerate(cols)}
+    for key, j in (("zh", 4), ("zl1", 5), ("zl2", 6)):   # the reference's metadata always carries them (:1771-1777)
+        meta.setdefault(key, canon[:, j].copy())
+    meta.update({"s": s, "delta_t": delta_t, "max_t": max_t, "n_samples": n_samples, "simulator": "ddm_flexbound",
+                 "boundary_fun_type": ("constant", "angle", "weibull_cdf")[kind], "possible_choices": [0, 1, 2, 3],
+                 "trajectory": "This simulator does not yet allow for trajectory simulation", "model": model,
+                 "n_euler_steps": steps, "seed": seed})
+    if binned:
+        return (hist[0].astype(np.float64) / n_samples, meta)
+    if n_trials == 1:
+        rts, choices = np.squeeze(rts, axis=1), np.squeeze(choices, axis=1)
+    elif n_samples == 1:
+        rts, choices = np.squeeze(rts, axis=0), np.squeeze(choices, axis=0)
+    return (rts, choices, meta)
+
+
 def simulator(theta, model="angle", n_samples=1000, delta_t=0.001, max_t=20, no_noise=False, bin_dim=None,
               bin_pointwise=False, random_state=None, **ignored):
     """(rts, choices, metadata), or (histogram, metadata) when bin_dim > 0 -- see the module docstring.
@@ -231,6 +299,8 @@ def simulator(theta, model="angle", n_samples=1000, delta_t=0.001, max_t=20, no_
 
     if name in _RACE:
         return _simulator_race(name, model, theta, n_samples, delta_t, max_t, s, seed, bin_dim, binned)
+    if name in _PAR2:
+        return _simulator_par2(name, model, theta, n_samples, delta_t, max_t, s, seed, bin_dim, binned)
     rts, choices, hist, traj, steps = _run(name, theta, n_samples, delta_t, max_t, s, seed, True,
                                            int(bin_dim) if binned else 0, want_traj=True)
     _, cols, sim_name, bnd, mult, ch = _M[name]
@@ -258,9 +328,10 @@ def simulate_histograms(theta, model="angle", n_samples=100000, nbins=512, delta
     merge with hddm_b200.distributed.merge_histograms)."""
     name = _resolve(model)
     theta = _coerce_theta(theta, name)
-    if name in _RACE:
-        _, _, hist, steps = _run_race(name, theta, int(n_samples), delta_t, max_t, 0.0 if no_noise else 1.0,
-                                      _seed(random_state), False, int(nbins), sample_offset=sample_offset)
+    if name in _RACE or name in _PAR2:
+        run = _run_race if name in _RACE else _run_par2
+        _, _, hist, steps = run(name, theta, int(n_samples), delta_t, max_t, 0.0 if no_noise else 1.0,
+                                _seed(random_state), False, int(nbins), sample_offset=sample_offset)
         return hist, steps
     _, _, hist, _, steps = _run(name, theta, int(n_samples), delta_t, max_t, 0.0 if no_noise else 1.0,
                                 _seed(random_state), False, int(nbins), sample_offset=sample_offset)

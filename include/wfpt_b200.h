@@ -197,6 +197,14 @@ int wfpt_sim_race_run_host(int lca, int n_particles, int angle, const float* h_t
                            int64_t sample_offset, float delta_t, float max_t, float s, uint64_t seed, float* h_rts,
                            int32_t* h_choices, uint32_t* h_hist, int nbins, float hist_max_t, uint64_t* h_steps);
 
+/* Two-stage 4-choice simulator ddm_flexbound_par2 (src/cddm_data_simulation.pyx:1667-1791): theta is float32
+ * [n_sets][10] = v_h, v_l1, v_l2, a, z_h, z_l1, z_l2, t, b0, b1 with bound_kind 0 constant, 1 angle (b0 = theta),
+ * 2 Weibull (b0 = alpha, b1 = beta); choices 0..3; hist is uint32 [n_sets][nbins][4].  Other arguments as in
+ * wfpt_sim_run. */
+int wfpt_sim_par2_run_host(int bound_kind, const float* h_theta, int n_sets, int64_t n_samples, int64_t sample_offset,
+                           float delta_t, float max_t, float s, uint64_t seed, float* h_rts, int32_t* h_choices,
+                           uint32_t* h_hist, int nbins, float hist_max_t, uint64_t* h_steps);
+
 #ifdef __cplusplus
 }
 #endif

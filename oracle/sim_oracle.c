@@ -189,3 +189,52 @@ int orc_sim_race_run(int lca, int np, int angle, const float* theta, int n_sets,
     free(b);
     return 0;
 }
+
+/* ddm_flexbound_par2 (:1667-1791).  theta per set (10 floats): v_h, v_l1, v_l2, a, z_h, z_l1, z_l2, t, b0, b1;
+ * bound_kind 0 constant, 1 angle (b0), 2 Weibull (b0 = alpha, b1 = beta).  choice = (y_h < 0 ? 0 : 2) + (sign(y_l) >= 0). */
+int orc_sim_par2_run(int bound_kind, const float* theta, int n_sets, int64_t n_samples, float dt, float max_t, float s,
+                     uint64_t seed, float* rts, int32_t* choices)
+{
+    rng_t R;
+    rng_seed(&R, seed);
+    const float sqrt_st = (float)sqrt(dt) * s;
+    const int nb = (int)((max_t / dt) + 1) + 2;
+    float* b = (float*)malloc(sizeof(float) * (size_t)(nb + 1));
+    if (!b) return 2;
+    for (int k = 0; k < n_sets; k++) {
+        const float* th = theta + (size_t)k * 10;
+        const float a = th[3], t = th[7];
+        for (int ix = 0; ix <= nb; ix++) {
+            const float ts = (float)((double)ix * (double)dt);
+            if (bound_kind == 1) b[ix] = a + ts * (-sinf(th[8]) / cosf(th[8]));
+            else if (bound_kind == 2) b[ix] = (float)(a * exp(-pow((double)ts / th[9], (double)th[8])));
+            else b[ix] = a;
+        }
+        for (int64_t n = 0; n < n_samples; n++) {
+            float t_h = 0.0f, t_l = 0.0f;
+            int ix = 0;
+            float y_h = (-1) * b[0] + (th[4] * 2 * b[0]);
+            while (y_h >= (-1) * b[ix] && y_h <= b[ix] && t_h <= max_t) {
+                y_h += (th[0] * dt) + (sqrt_st * random_gaussian(&R));
+                t_h += dt;
+                ix++;
+            }
+            int choice;
+            float y_l, v_l;
+            if (sgn(y_h) < 0) { choice = 0; y_l = (-1) * b[0] + (th[5] * 2 * b[0]); v_l = th[1]; }
+            else { choice = 2; y_l = (-1) * b[0] + (th[6] * 2 * b[0]); v_l = th[2]; }
+            ix = 0;
+            while (y_l >= (-1) * b[ix] && y_l <= b[ix] && t_l <= max_t) {
+                y_l += (v_l * dt) + (sqrt_st * random_gaussian(&R));
+                t_l += dt;
+                ix++;
+            }
+            const size_t o = (size_t)n * n_sets + k;
+            rts[o] = fmaxf(t_h, t_l) + t;
+            if (sgn(y_l) >= 0) choice += 1;
+            choices[o] = choice;
+        }
+    }
+    free(b);
+    return 0;
+}

@@ -93,6 +93,34 @@ def test_race_and_lca_match_oracle(model, sims, oracle):
     assert np.array_equal(hist[0].astype(np.float64), sims.bin_simulator_output(out, nbins=128, freq_cnt=True))
 
 
+PAR2_CASES = {
+    "ddm_par2": [1.0, 0.5, -0.5, 1.2, 0.55, 0.45, 0.5, 0.3],
+    "ddm_par2_no_bias": [1.0, 0.5, -0.5, 1.2, 0.3],
+    "ddm_par2_angle_no_bias": [1.0, 0.5, -0.5, 1.2, 0.3, 0.2],
+    "ddm_par2_weibull_no_bias": [1.0, 0.5, -0.5, 1.2, 0.3, 2.0, 1.5],
+}
+
+
+@pytest.mark.parametrize("model", list(PAR2_CASES))
+def test_par2_matches_oracle(model, sims, oracle):
+    theta = np.asarray(PAR2_CASES[model], dtype=np.float32)
+    kind, cols = sims._PAR2[model]
+    n_gpu, n_cpu = 300000, 60000
+    rts, ch, meta = sims.simulator(theta, model=model, n_samples=n_gpu, random_state=51)
+    ort, och = oracle.sim_par2_run(kind, sims._par2_canonical(model, theta[None, :]), n_cpu, seed=52)
+    assert rts.shape == (n_gpu, 1) and meta["possible_choices"] == [0, 1, 2, 3]
+    assert stats.ks_2samp(rts[:, 0], ort[:, 0]).pvalue > 1e-3
+    for c in range(4):
+        la, ha = _ci(int(np.sum(ch == c)), n_gpu)
+        lb, hb = _ci(int(np.sum(och == c)), n_cpu)
+        assert la <= hb and lb <= ha, (model, c)
+    for p_name in cols + ["zh", "zl1", "zl2"]:
+        assert p_name in meta
+    r2, c2, hist, steps = sims._run_par2(model, theta[None, :], 20000, 0.001, 20.0, 1.0, 7, True, 128)
+    out = (r2[:, 0, :], c2[:, 0, :], {"max_t": 20.0, "possible_choices": [0, 1, 2, 3], "n_samples": 20000})
+    assert np.array_equal(hist[0].astype(np.float64), sims.bin_simulator_output(out, nbins=128, freq_cnt=True))
+
+
 def test_shapes_and_metadata_like_reference_test(sims):
     """/root/reference/hddm/tests/test_simulators.py:65-87."""
     n_samples, n_trials = 100, 7
@@ -110,7 +138,7 @@ def test_shapes_and_metadata_like_reference_test(sims):
     with pytest.raises(ValueError):
         sims.simulator([1.0, 1.0, 0.5], model="angle")
     with pytest.raises(NotImplementedError):
-        sims.simulator([0.0] * 8, model="ddm_par2")
+        sims.simulator([0.0] * 8, model="ddm_seq2")
     # ddm_cov codes the lower boundary as +1 (cddm_data_simulation.pyx:437)
     r0, c0, _ = sims.simulator([2.0, 2.0, 0.5, 0.3], model="ddm_hddm_base", n_samples=4000, random_state=3)
     r1, c1, _ = sims.simulator([2.0, 2.0, 0.5, 0.3], model="ddm_cov", n_samples=4000, random_state=3)

@@ -44,6 +44,8 @@ def test_theta_coercion_and_model_table():
     assert S._resolve("weibull_cdf") == "weibull" and S._resolve("full_ddm_legacy") == "full_ddm_hddm_base"
     with pytest.raises(NotImplementedError):
         S._resolve("ddm_seq2_no_bias")
+    assert S._par2_canonical("ddm_par2_weibull_no_bias", np.arange(7, dtype=np.float32)[None, :]).tolist() == \
+        [[0, 1, 2, 3, 0.5, 0.5, 0.5, 4, 5, 6]]
     with pytest.raises(ValueError):
         S._resolve("no_such_model")
     # parameter lists follow /root/reference/hddm/model_config.py

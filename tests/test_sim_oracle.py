@@ -158,6 +158,20 @@ def test_race_and_lca_vs_reference(oracle, ref_sim):
         assert la <= hb and lb <= ha
 
 
+def test_par2_vs_reference(oracle, ref_sim):
+    n = 20000
+    th = [1.0, 0.5, -0.5, 1.2, 0.55, 0.45, 0.5, 0.3]
+    arrs = _f32(*th)
+    r = ref_sim.ddm_flexbound_par2(*arrs, n_samples=n, n_trials=1, boundary_fun=angle, boundary_multiplicative=False,
+                                   boundary_params={"theta": np.array([0.2], dtype=np.float32)})
+    rt, ch = oracle.sim_par2_run(1, th + [0.2, 0.0], n, seed=24)
+    assert stats.ks_2samp(rt[:, 0], r[0][:, 0, 0]).pvalue > 1e-3
+    for c in range(4):
+        la, ha = _ci(int(np.sum(ch == c)), n)
+        lb, hb = _ci(int(np.sum(r[1] == c)), n)
+        assert la <= hb and lb <= ha, c
+
+
 def test_ddm_vs_analytic_wfpt(oracle):
     """Constant bounds: P(upper) from prob_ub (pdf.pxi:67-72) and the RT density from full_pdf, as
     /root/reference/hddm/tests/test_generate.py:33-50 validates its own random walk."""
