@@ -18,12 +18,14 @@ import numpy as np
 
 from . import _lib
 from ._lib import FAITHFUL, FAST, WfptError  # noqa: F401
+from .lan import *  # noqa: F401,F403  (network-likelihood wrappers, host-only; `src/wfpt.pyx:156-267,436-514,633-753`)
+from .lan import __all__ as _lan_all
 
 __all__ = [
     "pdf_array", "wiener_like", "wiener_like_rlddm", "wiener_like_rl", "wiener_like_multi", "wiener_like_multi_rlddm",
     "wiener_like_contaminant", "gen_rts_from_cdf", "gen_cdf_using_pdf", "split_cdf", "full_pdf", "wiener_like_batch", "sort_rts",
     "set_variant", "get_variant", "ResidentData", "wiener_like_segments",
-]
+] + list(_lan_all)
 
 _variant = FAST
 

@@ -53,7 +53,9 @@ def test_top_level_module_name_and_callables():
 
     for name in ("wiener_like", "wiener_like_multi", "pdf_array", "wiener_like_rlddm", "full_pdf", "gen_rts_from_cdf",
                  "gen_cdf_using_pdf", "split_cdf", "wiener_like_contaminant", "wiener_like_rl",
-                 "wiener_like_multi_rlddm"):
+                 "wiener_like_multi_rlddm", "wiener_like_nn_mlp", "wiener_like_nn_mlp_info", "wiener_like_nn_mlp_pdf",
+                 "wiener_like_multi_nn_mlp", "wiener_like_multi_nn_mlp_pdf", "wiener_like_rlssm_nn",
+                 "wiener_like_rlssm_nn_reg"):
         assert callable(getattr(wfpt, name)), name
 
 
