@@ -373,6 +373,42 @@ def bin_simulator_output_pointwise(out, bin_dt=0.04, nbins=0):
     return np.concatenate([binned.astype(out[0].dtype), ch.astype(out[0].dtype)], axis=-1).astype(np.int32)
 
 
+def hddm_preprocess(simulator_data=None, subj_id="none", keep_negative_responses=False, add_model_parameters=False,
+                    keep_subj_idx=True):
+    """`(rts, choices, metadata)` -> the data frame HDDM fits (`hddm/simulators/hddm_dataset_generators.py:12-53`):
+    `rt` float64, `response` int with -1 mapped to 0 unless asked otherwise, optional `subj_idx` and one column per
+    model parameter (scalar for a single parameter set, per-row otherwise)."""
+    import pandas as pd
+
+    rts, choices, meta = simulator_data
+    df = pd.DataFrame({"rt": np.asarray(rts, dtype=np.double).reshape(-1),
+                       "response": np.asarray(choices).astype(int).reshape(-1)})
+    if not keep_negative_responses:
+        df.loc[df["response"] == -1, "response"] = 0
+    if keep_subj_idx:
+        df["subj_idx"] = subj_id
+    if add_model_parameters:
+        for name in model_config[meta["model"]]["params"]:
+            val = np.atleast_1d(meta[name])
+            df[name] = val if val.shape[0] > 1 else val[0]
+    return df
+
+
+def _add_outliers(sim_out=None, p_outlier=None, max_rt_outlier=10.0):
+    """Replace the last Binomial(n, p_outlier) samples by outliers: RT uniform on [0, max_rt_outlier], choice uniform
+    over `possible_choices` (`hddm_dataset_generators.py:56-101`).  Draws come from NumPy's global generator in the
+    reference's order (binomial, uniform, choice), so a seeded caller gets the reference's outliers; in place."""
+    if p_outlier == 0:
+        return sim_out
+    k = np.random.binomial(n=sim_out[0].shape[0], p=p_outlier)
+    if k > 0:
+        rt_out = np.random.uniform(low=0.0, high=max_rt_outlier, size=k)
+        ch_out = np.random.choice(sim_out[2]["possible_choices"], size=k)
+        sim_out[0][-k:, 0] = rt_out
+        sim_out[1][-k:, 0] = ch_out
+    return sim_out
+
+
 def _smoke():
     rts, ch, meta = simulator([1.0, 1.0, 0.5, 0.3, 0.2], model="angle", n_samples=20000, random_state=1)
     assert rts.shape == (20000, 1) and ch.shape == (20000, 1) and meta["possible_choices"] == [-1, 1]

@@ -54,3 +54,31 @@ def test_theta_coercion_and_model_table():
     assert S.model_config["race_no_bias_3"]["choices"] == [0, 1, 2]
     c = S._race_canonical("lca_no_bias_angle_4", np.arange(10, dtype=np.float32)[None, :])
     assert c.tolist() == [[0, 1, 2, 3, 4, 5, 5, 5, 5, 6, 7, 8, 9]]
+
+
+def test_preprocess_and_outliers():
+    """`hddm_dataset_generators.py:12-101`: frame layout, -1 -> 0, outliers replace the tail using NumPy's global RNG."""
+    n = 500
+    rts = np.linspace(0.3, 2.0, n, dtype=np.float32)[:, None]
+    ch = np.where(np.arange(n) % 3 == 0, -1, 1).astype(np.int32)[:, None]
+    meta = {"model": "angle", "possible_choices": [-1, 1], "max_t": 20.0, "n_samples": n,
+            "v": np.array([1.0], np.float32), "a": np.array([1.5], np.float32), "z": np.array([0.5], np.float32),
+            "t": np.array([0.3], np.float32), "theta": np.array([0.2], np.float32)}
+    df = S.hddm_preprocess((rts, ch, meta), subj_id=3, add_model_parameters=True)
+    assert list(df.columns) == ["rt", "response", "subj_idx", "v", "a", "z", "t", "theta"]
+    assert df["rt"].dtype == np.float64 and set(df["response"]) == {0, 1} and (df["subj_idx"] == 3).all()
+    assert np.isclose(df["theta"].iloc[0], 0.2)
+    keep = S.hddm_preprocess((rts, ch, meta), keep_negative_responses=True, keep_subj_idx=False)
+    assert set(keep["response"]) == {-1, 1} and "subj_idx" not in keep
+
+    assert S._add_outliers((rts, ch, meta), p_outlier=0) [0] is rts
+    np.random.seed(11)
+    k = np.random.binomial(n=n, p=0.1)
+    want_rt = np.random.uniform(0.0, 10.0, k)
+    want_ch = np.random.choice([-1, 1], size=k)
+    r2, c2 = rts.copy(), ch.copy()
+    np.random.seed(11)
+    out = S._add_outliers((r2, c2, meta), p_outlier=0.1, max_rt_outlier=10.0)
+    assert out[0] is r2 and k > 0
+    assert np.array_equal(r2[-k:, 0], want_rt.astype(np.float32)) and np.array_equal(c2[-k:, 0], want_ch)
+    assert np.array_equal(r2[:-k], rts[:-k]) and np.array_equal(c2[:-k], ch[:-k])
