@@ -71,6 +71,8 @@ def _declare(L):
     L.wfpt_sim_race_run_host.restype = i
     L.wfpt_sim_par2_run_host.argtypes = [i, vp, i, i64, i64, f, f, f, C.c_uint64, vp, vp, vp, i, f, vp]
     L.wfpt_sim_par2_run_host.restype = i
+    L.wfpt_sim_hier_run_host.argtypes = [i, i, vp, i, i64, i64, f, f, f, C.c_uint64, vp, vp, vp, i, f, vp]
+    L.wfpt_sim_hier_run_host.restype = i
     L.wfpt_sim_n_params.argtypes = [i]
     L.wfpt_sim_n_params.restype = i
 

@@ -27,6 +27,7 @@
 // another without waiting for its warp neighbours (a finished lane picks up its next particle at the next Philox
 // block boundary, at most three sub-steps later); bounds are evaluated in registers.
 #include <cstdio>
+#include <string>
 
 #include "../../include/wfpt_b200.h"
 #include "common.cuh"
@@ -511,8 +512,10 @@ static cudaError_t launch_race(const Args& A, int angle, int blocks, cudaStream_
 // against the same bound b(t) (each with its own step index); rt = max(t_h, t_l) + t; choice = (y_h < 0 ? 0 : 2) +
 // (sign(y_l) >= 0).  theta (canonical): v_h, v_l1, v_l2, a, z_h, z_l1, z_l2, t, b0, b1; BOUND 0 constant, 1 angle (b0),
 // 2 Weibull (b0 = alpha, b1 = beta).  One Philox stream per particle, consumed in order by the two walks.
-template <int BOUND>
-__global__ void __launch_bounds__(kSimBlock) par2_kernel(const Args A)
+// KIND 0 is par2; KIND 1 / 2 / 3 are its siblings ddm_flexbound_seq2 / _mic2_adj / _tradeoff (theta gains an 11th column d),
+// described where they branch off below.
+template <int KIND, int BOUND>
+__global__ void __launch_bounds__(kSimBlock) hier_kernel(const Args A)
 {
     extern __shared__ unsigned int s_hist[];  // [nbins][4] when A.hist
     __shared__ int s_next;
@@ -530,8 +533,12 @@ __global__ void __launch_bounds__(kSimBlock) par2_kernel(const Args A)
 
     const float* th = A.theta + (size_t)set * A.n_par;
     const float v_h = th[0], v_l1 = th[1], v_l2 = th[2], a = th[3], z_h = th[4], z_l1 = th[5], z_l2 = th[6], t_nd = th[7];
-    const float sdt = (BOUND == 1) ? (-sinf(th[8]) / cosf(th[8])) * A.dt : 0.f;
+    const float sdt = (BOUND == 1 || BOUND == 3) ? (-sinf(th[8]) / cosf(th[8])) * A.dt : 0.f;
     const float w_alpha = th[8], w_inv_beta = (BOUND == 2) ? 1.0f / th[9] : 0.f;
+    // conflict-gamma bound (graveyard/boundary_functions.py:66-97): max(a + scale * gamma_pdf(t; shape, scale_g) + t * slope, 0)
+    const float g_scale = (BOUND == 3) ? th[9] : 0.f, g_shape_m1 = (BOUND == 3) ? th[11] - 1.f : 0.f;
+    const float g_inv_sg = (BOUND == 3) ? 1.0f / th[12] : 0.f;
+    const float g_lognorm = (BOUND == 3) ? -lgammaf(th[11]) + logf(g_inv_sg) : 0.f;
     auto bound = [&](float fix) -> float {
         if (BOUND == 1) return fmaf(fix, sdt, a);
         if (BOUND == 2) {
@@ -539,44 +546,181 @@ __global__ void __launch_bounds__(kSimBlock) par2_kernel(const Args A)
             const float pw = (r > 0.f) ? exp2f(w_alpha * __log2f(r)) : 0.f;
             return a * __expf(-pw);
         }
+        if (BOUND == 3) {
+            const float x = (fix * A.dt) * g_inv_sg;
+            float pdf;
+            if (x > 0.f) pdf = __expf(fmaf(g_shape_m1, __logf(x), g_lognorm - x));
+            else pdf = (g_shape_m1 > 0.f) ? 0.f : (g_shape_m1 == 0.f ? g_inv_sg : __int_as_float(0x7f800000));
+            return fmaxf(fmaf(g_scale, pdf, fmaf(fix, sdt, a)), 0.f);
+        }
         return a;
     };
     const float b0 = bound(0.f);
 
+    // Counter word 3 = block index | stream << 28: separate streams for the high-dimension walk (0), the low-dimension
+    // walk (1) and the uniforms (2), so that the high-dimension path can be regenerated while the low one runs.
+    struct Stream {
+        unsigned int blk;
+        int have;
+        float4 nn;
+    };
+    const float d_damp = (KIND >= 2) ? th[10] : 0.f;
+    const float vdt_h = __fmul_rn(v_h, A.dt);
+
     long long p = beg + threadIdx.x;
     while (p < end) {
         const unsigned long long gp = (unsigned long long)(p + A.sample_offset);
-        unsigned int blk = 0;
-        float4 nn = make_float4(0.f, 0.f, 0.f, 0.f);
-        int have = 0;
-        auto normal = [&]() -> float {
-            if (have == 0) {
-                nn = normals4(philox4x32((unsigned int)gp, (unsigned int)(gp >> 32), (unsigned int)set, blk++, rk));
-                have = 4;
+        float rt;
+        int choice;
+        if (KIND == 0) {
+            Stream S = {0u, 0, make_float4(0.f, 0.f, 0.f, 0.f)};
+            auto normal = [&]() -> float {
+                if (S.have == 0) {
+                    S.nn = normals4(philox4x32((unsigned int)gp, (unsigned int)(gp >> 32), (unsigned int)set, S.blk++, rk));
+                    S.have = 4;
+                }
+                S.have--;
+                return S.have == 3 ? S.nn.x : S.have == 2 ? S.nn.y : S.have == 1 ? S.nn.z : S.nn.w;
+            };
+            auto walk = [&](float z, float v, float* t_out) -> float {
+                float y = __fadd_rn(-b0, __fmul_rn(__fmul_rn(z, 2.f), b0));
+                float b = b0, tp = 0.f, fix = 0.f;
+                const float vdt = __fmul_rn(v, A.dt);
+                while (y >= -b && y <= b && tp <= A.max_t) {
+                    y = __fadd_rn(y, __fadd_rn(vdt, __fmul_rn(sqrt_st, normal())));
+                    tp = __fadd_rn(tp, A.dt);
+                    fix += 1.0f;
+                    if (BOUND != 0) b = bound(fix);
+                }
+                my_steps += (unsigned long long)fix;
+                *t_out = tp;
+                return y;
+            };
+            float t_h, t_l;
+            const float y_h = walk(z_h, v_h, &t_h);
+            const bool lower = y_h < 0.f;                       // sign(y_h) < 0  (:1747)
+            const float y_l = walk(lower ? z_l1 : z_l2, lower ? v_l1 : v_l2, &t_l);
+            choice = (lower ? 0 : 2) + ((y_l >= 0.f) ? 1 : 0);
+            rt = __fadd_rn(fmaxf(t_h, t_l), t_nd);
+        } else {
+            auto draw = [&](Stream& S, unsigned long long q, unsigned int stream) -> float {
+                if (S.have == 0) {
+                    S.nn = normals4(philox4x32((unsigned int)q, (unsigned int)(q >> 32), (unsigned int)set,
+                                               (S.blk++) | (stream << 28), rk));
+                    S.have = 4;
+                }
+                S.have--;
+                return S.have == 3 ? S.nn.x : S.have == 2 ? S.nn.y : S.have == 1 ? S.nn.z : S.nn.w;
+            };
+            auto uniforms = [&](unsigned long long q) -> uint4 {
+                return philox4x32((unsigned int)q, (unsigned int)(q >> 32), (unsigned int)set, 2u << 28, rk);
+            };
+            if (KIND == 1) {
+                // seq2 (:1523-1661): the low-dimension walk continues on the clock and bound index of the high one.  On the
+                // time-out and collapsed-bound branches the reference leaves y_l as the previous particle left it, so the
+                // last increment reads the predecessor's final y_l: replay predecessors (by particle index) until one of
+                // them ran its own low-dimension walk.  Particle 0 has none: y_l = 0 there.
+                auto particle = [&](unsigned long long q, float& rt_q, int& base_q, bool& yl_nonneg, bool count) -> bool {
+                    Stream H = {0u, 0, make_float4(0.f, 0.f, 0.f, 0.f)};
+                    float y = __fadd_rn(-b0, __fmul_rn(__fmul_rn(z_h, 2.f), b0));
+                    float b = b0, tp = 0.f, fix = 0.f;
+                    while (y >= -b && y <= b && tp <= A.max_t) {
+                        y = __fadd_rn(y, __fadd_rn(vdt_h, __fmul_rn(sqrt_st, draw(H, q, 0u))));
+                        tp = __fadd_rn(tp, A.dt);
+                        fix += 1.0f;
+                        if (BOUND != 0) b = bound(fix);
+                    }
+                    bool stale;
+                    float y_l = 0.f;
+                    if (tp >= A.max_t) {
+                        base_q = (u01(uniforms(q).x) > 0.5f) ? 1 : 0;
+                        stale = true;
+                    } else {
+                        const bool lower = y < 0.f;
+                        const float z_l = lower ? z_l1 : z_l2;
+                        base_q = lower ? 0 : 2;
+                        if (b <= 0.f) {
+                            if (u01(uniforms(q).x) < z_l) base_q += 1;
+                            stale = true;
+                        } else {
+                            stale = false;
+                            y_l = __fadd_rn(-b, __fmul_rn(__fmul_rn(z_l, 2.f), b));
+                            const float vdt = __fmul_rn(lower ? v_l1 : v_l2, A.dt);
+                            Stream Lw = {0u, 0, make_float4(0.f, 0.f, 0.f, 0.f)};
+                            while (y_l >= -b && y_l <= b && tp <= A.max_t) {
+                                y_l = __fadd_rn(y_l, __fadd_rn(vdt, __fmul_rn(sqrt_st, draw(Lw, q, 1u))));
+                                tp = __fadd_rn(tp, A.dt);
+                                fix += 1.0f;
+                                if (BOUND != 0) b = bound(fix);
+                            }
+                        }
+                    }
+                    if (count) my_steps += (unsigned long long)fix;
+                    rt_q = __fadd_rn(tp, t_nd);
+                    yl_nonneg = y_l >= 0.f;
+                    return stale;
+                };
+                bool nonneg;
+                bool stale = particle(gp, rt, choice, nonneg, true);
+                unsigned long long q = gp;
+                for (int depth = 0; stale; depth++) {
+                    if (q == 0ull || depth == 256) { nonneg = true; break; }
+                    q--;
+                    float rt_q;
+                    int base_q;
+                    stale = particle(q, rt_q, base_q, nonneg, false);
+                }
+                choice += nonneg ? 1 : 0;
+            } else {
+                // mic2_adj (:1797-1960) / tradeoff (:1966-2137): both walks start at time 0; while the high-dimension walk
+                // is still running, the low one is slowed by the high walker's normalised position ("bias trace").  The
+                // trace is not stored: the high walk is regenerated from its own stream next to the low walk.  Entry n_h
+                // of the reference's trace is left over from the previous particle; it is taken as "already decided".
+                Stream H = {0u, 0, make_float4(0.f, 0.f, 0.f, 0.f)};
+                float y = __fadd_rn(-b0, __fmul_rn(__fmul_rn(z_h, 2.f), b0));
+                float b = b0, t_h = 0.f, n_h = 0.f;
+                while (y >= -b && y <= b && t_h <= A.max_t) {
+                    y = __fadd_rn(y, __fadd_rn(vdt_h, __fmul_rn(sqrt_st, draw(H, gp, 0u))));
+                    t_h = __fadd_rn(t_h, A.dt);
+                    n_h += 1.0f;
+                    if (BOUND != 0) b = bound(n_h);
+                }
+                const uint4 uu = uniforms(gp);
+                const bool upper = u01(uu.x) <= __fdiv_rn(__fadd_rn(y, b), __fmul_rn(2.f, b));
+                const float v_l = upper ? v_l2 : v_l1;
+                const float vdt_l = __fmul_rn(v_l, A.dt);
+                float y_l = __fadd_rn(-b0, __fmul_rn(__fmul_rn(upper ? z_l2 : z_l1, 2.f), b0));
+                Stream H2 = {0u, 0, make_float4(0.f, 0.f, 0.f, 0.f)}, Lw = H2;
+                float y2 = __fadd_rn(-b0, __fmul_rn(__fmul_rn(z_h, 2.f), b0));
+                float t_l = 0.f, fix = 0.f;
+                b = b0;
+                const float inv_2md = __fdiv_rn(1.f, __fsub_rn(2.f, d_damp));
+                while (y_l >= -b && y_l <= b && t_l <= A.max_t) {
+                    float tr = 1.f;
+                    if (fix < n_h) {
+                        y2 = __fadd_rn(y2, __fadd_rn(vdt_h, __fmul_rn(sqrt_st, draw(H2, gp, 0u))));
+                        tr = __fdiv_rn(__fadd_rn(y2, b), __fmul_rn(2.f, b));
+                        if (!upper) tr = __fsub_rn(1.f, tr);
+                    }
+                    const bool before = (tr < 1.f) && (tr > 0.f);
+                    const float g = draw(Lw, gp, 1u);
+                    if (KIND == 2) {
+                        y_l = __fadd_rn(y_l, before ? __fmul_rn(__fmul_rn(__fmul_rn(v_l, tr), d_damp), A.dt) : vdt_l);
+                        y_l = __fadd_rn(y_l, __fmul_rn(sqrt_st, g));
+                    } else {
+                        const float pos = before ? __fmul_rn(__fadd_rn(1.f, __fmul_rn(d_damp, __fsub_rn(tr, 1.f))), inv_2md) : 1.f;
+                        y_l = __fadd_rn(y_l, __fmul_rn(pos, vdt_l));
+                        y_l = __fadd_rn(y_l, __fmul_rn(__fmul_rn(pos, sqrt_st), g));
+                    }
+                    t_l = __fadd_rn(t_l, A.dt);
+                    fix += 1.0f;
+                    if (BOUND != 0) b = bound(fix);
+                }
+                my_steps += (unsigned long long)n_h + (unsigned long long)fix;
+                choice = (upper ? 2 : 0) + ((u01(uu.y) <= __fdiv_rn(__fadd_rn(y_l, b), __fmul_rn(2.f, b))) ? 1 : 0);
+                rt = __fadd_rn(fmaxf(t_h, t_l), t_nd);
             }
-            have--;
-            return have == 3 ? nn.x : have == 2 ? nn.y : have == 1 ? nn.z : nn.w;
-        };
-        auto walk = [&](float z, float v, float* t_out) -> float {
-            float y = __fadd_rn(-b0, __fmul_rn(__fmul_rn(z, 2.f), b0));
-            float b = b0, tp = 0.f, fix = 0.f;
-            const float vdt = __fmul_rn(v, A.dt);
-            while (y >= -b && y <= b && tp <= A.max_t) {
-                y = __fadd_rn(y, __fadd_rn(vdt, __fmul_rn(sqrt_st, normal())));
-                tp = __fadd_rn(tp, A.dt);
-                fix += 1.0f;
-                if (BOUND != 0) b = bound(fix);
-            }
-            my_steps += (unsigned long long)fix;
-            *t_out = tp;
-            return y;
-        };
-        float t_h, t_l;
-        const float y_h = walk(z_h, v_h, &t_h);
-        const bool lower = y_h < 0.f;                       // sign(y_h) < 0  (:1747)
-        const float y_l = walk(lower ? z_l1 : z_l2, lower ? v_l1 : v_l2, &t_l);
-        const int choice = (lower ? 0 : 2) + ((y_l >= 0.f) ? 1 : 0);
-        const float rt = __fadd_rn(fmaxf(t_h, t_l), t_nd);
+        }
         if (A.rts) {
             const size_t o = (size_t)p * A.n_sets + set;
             A.rts[o] = rt;
@@ -824,19 +968,19 @@ done:
 }
 
 
-extern "C" int wfpt_sim_par2_run_host(int bound_kind, const float* h_theta, int n_sets, int64_t n_samples, int64_t sample_offset,
-                                      float delta_t, float max_t, float s, uint64_t seed, float* h_rts, int32_t* h_choices,
-                                      uint32_t* h_hist, int nbins, float hist_max_t, uint64_t* h_steps)
+static int run_hier_host(const char* who, int kind, int bound_kind, const float* h_theta, int n_sets, int64_t n_samples,
+                         int64_t sample_offset, float delta_t, float max_t, float s, uint64_t seed, float* h_rts,
+                         int32_t* h_choices, uint32_t* h_hist, int nbins, float hist_max_t, uint64_t* h_steps)
 {
-    if (bound_kind < 0 || bound_kind > 2) return api_fail("wfpt_sim_par2_run_host: bound_kind must be 0 (constant), 1 (angle) or 2 (Weibull)");
-    if (n_sets < 0 || n_samples < 0) return api_fail("wfpt_sim_par2_run_host: negative size");
+    if (bound_kind < 0 || bound_kind > (kind == 0 ? 2 : 3)) return api_fail((std::string(who) + ": bound_kind out of range").c_str());
+    if (n_sets < 0 || n_samples < 0) return api_fail((std::string(who) + ": negative size").c_str());
     if (n_sets == 0 || n_samples == 0) return 0;
-    if (!h_theta) return api_fail("wfpt_sim_par2_run_host: null theta");
-    if ((h_rts == nullptr) != (h_choices == nullptr)) return api_fail("wfpt_sim_par2_run_host: rts and choices must be given together");
-    if (!h_rts && !h_hist) return api_fail("wfpt_sim_par2_run_host: nothing to write");
-    if (!(delta_t > 0.f) || !(max_t > 0.f)) return api_fail("wfpt_sim_par2_run_host: delta_t and max_t must be positive");
-    if (h_hist && (nbins < 2 || nbins * 4 > 2 * sim::kMaxBins)) return api_fail("wfpt_sim_par2_run_host: nbins out of range");
-    const int n_par = 10;
+    if (!h_theta) return api_fail((std::string(who) + ": null theta").c_str());
+    if ((h_rts == nullptr) != (h_choices == nullptr)) return api_fail((std::string(who) + ": rts and choices must be given together").c_str());
+    if (!h_rts && !h_hist) return api_fail((std::string(who) + ": nothing to write").c_str());
+    if (!(delta_t > 0.f) || !(max_t > 0.f)) return api_fail((std::string(who) + ": delta_t and max_t must be positive").c_str());
+    if (h_hist && (nbins < 2 || nbins * 4 > 2 * sim::kMaxBins)) return api_fail((std::string(who) + ": nbins out of range").c_str());
+    const int n_par = kind == 0 ? 10 : 13;
     int rc = 0;
     float *d_theta = nullptr, *d_rts = nullptr;
     int32_t* d_ch = nullptr;
@@ -859,11 +1003,20 @@ extern "C" int wfpt_sim_par2_run_host(int bound_kind, const float* h_theta, int 
     A.items_per_set = (n_samples + A.chunk - 1) / A.chunk;
     {
         const long long n_items = A.items_per_set * n_sets;
-        if (n_items > 2147483647LL) { rc = api_fail("wfpt_sim_par2_run_host: too many work items; split the call"); goto done; }
+        if (n_items > 2147483647LL) { rc = api_fail((std::string(who) + ": too many work items; split the call").c_str()); goto done; }
         const size_t smem = A.hist ? sizeof(unsigned int) * 4 * (size_t)A.nbins : 0;
-        if (bound_kind == 0) sim::par2_kernel<0><<<(int)n_items, sim::kSimBlock, smem>>>(A);
-        else if (bound_kind == 1) sim::par2_kernel<1><<<(int)n_items, sim::kSimBlock, smem>>>(A);
-        else sim::par2_kernel<2><<<(int)n_items, sim::kSimBlock, smem>>>(A);
+#define HIER_LAUNCH(K)                                                                           \
+    do {                                                                                         \
+        if (bound_kind == 0) sim::hier_kernel<K, 0><<<(int)n_items, sim::kSimBlock, smem>>>(A);  \
+        else if (bound_kind == 1) sim::hier_kernel<K, 1><<<(int)n_items, sim::kSimBlock, smem>>>(A); \
+        else if (bound_kind == 2) sim::hier_kernel<K, 2><<<(int)n_items, sim::kSimBlock, smem>>>(A); \
+        else sim::hier_kernel<K, 3><<<(int)n_items, sim::kSimBlock, smem>>>(A);                  \
+    } while (0)
+        if (kind == 0) HIER_LAUNCH(0);
+        else if (kind == 1) HIER_LAUNCH(1);
+        else if (kind == 2) HIER_LAUNCH(2);
+        else HIER_LAUNCH(3);
+#undef HIER_LAUNCH
         SCK(cudaGetLastError());
         count_launch(1);
     }
@@ -877,4 +1030,21 @@ extern "C" int wfpt_sim_par2_run_host(int bound_kind, const float* h_theta, int 
 done:
     cudaFree(d_theta); cudaFree(d_rts); cudaFree(d_ch); cudaFree(d_hist); cudaFree(d_steps);
     return rc;
+}
+
+extern "C" int wfpt_sim_par2_run_host(int bound_kind, const float* h_theta, int n_sets, int64_t n_samples, int64_t sample_offset,
+                                      float delta_t, float max_t, float s, uint64_t seed, float* h_rts, int32_t* h_choices,
+                                      uint32_t* h_hist, int nbins, float hist_max_t, uint64_t* h_steps)
+{
+    return run_hier_host("wfpt_sim_par2_run_host", 0, bound_kind, h_theta, n_sets, n_samples, sample_offset, delta_t, max_t, s,
+                         seed, h_rts, h_choices, h_hist, nbins, hist_max_t, h_steps);
+}
+
+extern "C" int wfpt_sim_hier_run_host(int kind, int bound_kind, const float* h_theta, int n_sets, int64_t n_samples,
+                                      int64_t sample_offset, float delta_t, float max_t, float s, uint64_t seed, float* h_rts,
+                                      int32_t* h_choices, uint32_t* h_hist, int nbins, float hist_max_t, uint64_t* h_steps)
+{
+    if (kind < 1 || kind > 3) return api_fail("wfpt_sim_hier_run_host: kind must be 1 (seq2), 2 (mic2_adj) or 3 (tradeoff)");
+    return run_hier_host("wfpt_sim_hier_run_host", kind, bound_kind, h_theta, n_sets, n_samples, sample_offset, delta_t, max_t, s,
+                         seed, h_rts, h_choices, h_hist, nbins, hist_max_t, h_steps);
 }

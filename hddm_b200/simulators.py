@@ -63,9 +63,27 @@ _PAR2 = {
     "ddm_par2_weibull_no_bias": (2, ["vh", "vl1", "vl2", "a", "t", "alpha", "beta"]),
 }
 
+# siblings of par2 (kind 1 seq2, 2 mic2_adj, 3 tradeoff): name -> (kind, bound kind, theta columns); column orders of
+# /root/reference/graveyard/basic_simulator_old.py:715-793, 875-1040.  Bound kind 3 is the conflict-gamma bound.
+def _hier_entries():
+    out = {}
+    for kind, stem, extra in ((1, "ddm_seq2", []), (2, "ddm_mic2_adj", ["d"]), (3, "tradeoff", ["d"])):
+        base = ["vh", "vl1", "vl2", "a"]
+        if kind != 3:
+            out[stem] = (kind, 0, base + ["zh", "zl1", "zl2"] + extra + ["t"])
+        out[stem + "_no_bias"] = (kind, 0, base + extra + ["t"])
+        out[stem + "_angle_no_bias"] = (kind, 1, base + extra + ["t", "theta"])
+        out[stem + "_weibull_no_bias"] = (kind, 2, base + extra + ["t", "alpha", "beta"])
+    out["tradeoff_conflict_gamma_no_bias"] = (3, 3, ["vh", "vl1", "vl2", "d", "t", "a", "theta", "scale", "alphagamma",
+                                                     "scalegamma"])
+    return out
+
+
+_HIER = _hier_entries()
+_BOUND_NAMES = ("constant", "angle", "weibull_cdf", "conflict_gamma_bound")
+
 _ALIAS = {"ddm_legacy": "ddm_hddm_base", "full_ddm_legacy": "full_ddm_hddm_base", "test": "ddm",
           "weibull_cdf": "weibull"}
-_NEXT = ("ddm_seq2", "ddm_mic2_adj", "tradeoff")
 
 # minimal stand-in for the part of hddm.model_config the simulator boundary needs (params and choices per model)
 model_config = {name: {"params": list(cols), "choices": list(ch), "boundary_name": bnd, "boundary_multiplicative": mult}
@@ -80,20 +98,24 @@ model_config.update({name: {"params": list(cols), "choices": [0, 1, 2, 3],
                      for name, (kind, cols) in _PAR2.items()})
 
 
+model_config.update({name: {"params": list(cols), "choices": [0, 1, 2, 3], "boundary_name": _BOUND_NAMES[bk],
+                            "boundary_multiplicative": bk in (0, 2)}
+                     for name, (kind, bk, cols) in _HIER.items()})
+
+
 def _resolve(model):
     name = _ALIAS.get(model, model)
-    if name in _RACE or name in _PAR2:
+    if name in _RACE or name in _PAR2 or name in _HIER:
         return name
     if name not in _M:
-        if any(model.startswith(p) for p in _NEXT):
-            raise NotImplementedError(f"simulator model '{model}' is a next-row model (SURVEY 8(f) rank 4), not built yet")
         raise ValueError(f"unknown simulator model '{model}'")
     return name
 
 
 def _coerce_theta(theta, name):
     """basic_simulator_old.py:208-224."""
-    cols = _RACE[name][3] if name in _RACE else (_PAR2[name][1] if name in _PAR2 else _M[name][1])
+    cols = (_RACE[name][3] if name in _RACE else _PAR2[name][1] if name in _PAR2 else _HIER[name][2] if name in _HIER
+            else _M[name][1])
     if isinstance(theta, list):
         theta = np.asarray(theta).astype(np.float32)
     elif isinstance(theta, np.ndarray):
@@ -216,21 +238,32 @@ def _simulator_race(name, model, theta, n_samples, delta_t, max_t, s, seed, bin_
     return (rts, choices, meta)
 
 
+def _two_stage(name):
+    """(kind, bound kind, theta columns) of a two-stage 4-choice model; kind 0 = par2."""
+    if name in _PAR2:
+        return (0,) + tuple(_PAR2[name])
+    return _HIER[name]
+
+
 def _par2_canonical(name, theta):
-    """Per-model columns -> v_h, v_l1, v_l2, a, z_h, z_l1, z_l2, t, b0, b1 (starting points 0.5 where the model has none)."""
-    kind, cols = _PAR2[name]
+    """Per-model columns -> v_h, v_l1, v_l2, a, z_h, z_l1, z_l2, t, b0, b1 (starting points 0.5 where the model has none);
+    the par2 siblings append d, b2, b3 (13 columns)."""
+    kind, bk, cols = _two_stage(name)
     col = {c: theta[:, i] for i, c in enumerate(cols)}
     half = np.full(theta.shape[0], 0.5, dtype=np.float32)
     zero = np.zeros(theta.shape[0], dtype=np.float32)
     b0 = col.get("theta", col.get("alpha", zero))
+    b1 = col.get("scale", col.get("beta", zero))
     out = [col["vh"], col["vl1"], col["vl2"], col["a"], col.get("zh", half), col.get("zl1", half), col.get("zl2", half),
-           col["t"], b0, col.get("beta", zero)]
+           col["t"], b0, b1]
+    if kind:
+        out += [col.get("d", zero), col.get("alphagamma", zero), col.get("scalegamma", zero)]
     return np.ascontiguousarray(np.stack(out, axis=1), dtype=np.float32)
 
 
 def _run_par2(name, theta, n_samples, delta_t, max_t, s, seed, want_raw, nbins, sample_offset=0):
     L = _lib.load()
-    kind = _PAR2[name][0]
+    kind, bk, _ = _two_stage(name)
     canon = _par2_canonical(name, theta)
     n_sets = canon.shape[0]
     rts = choices = hist = None
@@ -244,21 +277,23 @@ def _run_par2(name, theta, n_samples, delta_t, max_t, s, seed, want_raw, nbins, 
     def p(a):
         return a.ctypes.data_as(C.c_void_p) if a is not None else None
 
-    _lib.check(L.wfpt_sim_par2_run_host(kind, p(canon), n_sets, int(n_samples), int(sample_offset), float(delta_t), float(max_t),
-                                        float(s), seed, p(rts), p(choices), p(hist), int(nbins or 0), float(max_t), p(steps)))
+    tail = (p(canon), n_sets, int(n_samples), int(sample_offset), float(delta_t), float(max_t), float(s), seed, p(rts),
+            p(choices), p(hist), int(nbins or 0), float(max_t), p(steps))
+    _lib.check(L.wfpt_sim_par2_run_host(bk, *tail) if kind == 0 else L.wfpt_sim_hier_run_host(kind, bk, *tail))
     return rts, choices, hist, int(steps[0])
 
 
 def _simulator_par2(name, model, theta, n_samples, delta_t, max_t, s, seed, bin_dim, binned):
-    kind, cols = _PAR2[name]
+    kind, bk, cols = _two_stage(name)
     n_trials = theta.shape[0]
     rts, choices, hist, steps = _run_par2(name, theta, n_samples, delta_t, max_t, s, seed, True, int(bin_dim) if binned else 0)
     canon = _par2_canonical(name, theta)
     meta = {c: theta[:, i].copy() for i, c in enumerate(cols)}
     for key, j in (("zh", 4), ("zl1", 5), ("zl2", 6)):   # the reference's metadata always carries them (:1771-1777)
         meta.setdefault(key, canon[:, j].copy())
-    meta.update({"s": s, "delta_t": delta_t, "max_t": max_t, "n_samples": n_samples, "simulator": "ddm_flexbound",
-                 "boundary_fun_type": ("constant", "angle", "weibull_cdf")[kind], "possible_choices": [0, 1, 2, 3],
+    meta.update({"s": s, "delta_t": delta_t, "max_t": max_t, "n_samples": n_samples,
+                 "simulator": "ddm_flexbound_mic2_adj" if kind == 3 else "ddm_flexbound",   # sic (:2131)
+                 "boundary_fun_type": _BOUND_NAMES[bk], "possible_choices": [0, 1, 2, 3],
                  "trajectory": "This simulator does not yet allow for trajectory simulation", "model": model,
                  "n_euler_steps": steps, "seed": seed})
     if binned:
@@ -299,7 +334,7 @@ def simulator(theta, model="angle", n_samples=1000, delta_t=0.001, max_t=20, no_
 
     if name in _RACE:
         return _simulator_race(name, model, theta, n_samples, delta_t, max_t, s, seed, bin_dim, binned)
-    if name in _PAR2:
+    if name in _PAR2 or name in _HIER:
         return _simulator_par2(name, model, theta, n_samples, delta_t, max_t, s, seed, bin_dim, binned)
     rts, choices, hist, traj, steps = _run(name, theta, n_samples, delta_t, max_t, s, seed, True,
                                            int(bin_dim) if binned else 0, want_traj=True)
@@ -328,7 +363,7 @@ def simulate_histograms(theta, model="angle", n_samples=100000, nbins=512, delta
     merge with hddm_b200.distributed.merge_histograms)."""
     name = _resolve(model)
     theta = _coerce_theta(theta, name)
-    if name in _RACE or name in _PAR2:
+    if name in _RACE or name in _PAR2 or name in _HIER:
         run = _run_race if name in _RACE else _run_par2
         _, _, hist, steps = run(name, theta, int(n_samples), delta_t, max_t, 0.0 if no_noise else 1.0,
                                 _seed(random_state), False, int(nbins), sample_offset=sample_offset)

@@ -205,6 +205,17 @@ int wfpt_sim_par2_run_host(int bound_kind, const float* h_theta, int n_sets, int
                            float delta_t, float max_t, float s, uint64_t seed, float* h_rts, int32_t* h_choices,
                            uint32_t* h_hist, int nbins, float hist_max_t, uint64_t* h_steps);
 
+/* Siblings of the two-stage model: kind 1 = ddm_flexbound_seq2 (src/cddm_data_simulation.pyx:1523-1661; the
+ * low-dimension walk starts when and where the high one ends), 2 = ddm_flexbound_mic2_adj (:1797-1960) and
+ * 3 = ddm_flexbound_tradeoff (:1966-2137) (both walks start at time 0, the low one damped by the high walker's
+ * position through d).  theta rows carry 13 floats: v_h, v_l1, v_l2, a, z_h, z_l1, z_l2, t, b0, b1, d, b2, b3.
+ * bound_kind 0 / 1 / 2 as above, and 3 = the conflict-gamma bound of `tradeoff_conflict_gamma_no_bias`
+ * (graveyard/boundary_functions.py:66-97): max(a + b1 * gamma_pdf(t; shape b2, scale b3) + t * (-tan b0), 0).
+ * Everything else as wfpt_sim_par2_run_host. */
+int wfpt_sim_hier_run_host(int kind, int bound_kind, const float* h_theta, int n_sets, int64_t n_samples,
+                           int64_t sample_offset, float delta_t, float max_t, float s, uint64_t seed, float* h_rts,
+                           int32_t* h_choices, uint32_t* h_hist, int nbins, float hist_max_t, uint64_t* h_steps);
+
 #ifdef __cplusplus
 }
 #endif

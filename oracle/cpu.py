@@ -291,6 +291,25 @@ def sim_par2_run(bound_kind, theta, n_samples, delta_t=0.001, max_t=20.0, s=1.0,
     return rts, ch
 
 
+def sim_hier_run(kind, bound_kind, theta, n_samples, delta_t=0.001, max_t=20.0, s=1.0, seed=0):
+    """ddm_flexbound_seq2 / _mic2_adj / _tradeoff (kind 1 / 2 / 3) from oracle/sim_oracle.c; theta rows:
+    v_h, v_l1, v_l2, a, z_h, z_l1, z_l2, t, b0, b1, d, b2, b3 (bound_kind 3 = conflict-gamma bound)."""
+    theta = np.ascontiguousarray(np.atleast_2d(np.asarray(theta, dtype=np.float32)))
+    n_sets = theta.shape[0]
+    assert theta.shape[1] == 13
+    rts = np.empty((n_samples, n_sets), dtype=np.float32)
+    ch = np.empty((n_samples, n_sets), dtype=np.int32)
+    f = lib().orc_sim_hier_run
+    f.restype = C.c_int
+    f.argtypes = [C.c_int, C.c_int, C.POINTER(C.c_float), C.c_int, C.c_int64, C.c_float, C.c_float, C.c_float, C.c_uint64,
+                  C.POINTER(C.c_float), C.POINTER(C.c_int32)]
+    rc = f(int(kind), int(bound_kind), theta.ctypes.data_as(C.POINTER(C.c_float)), n_sets, n_samples, delta_t, max_t, s,
+           seed, rts.ctypes.data_as(C.POINTER(C.c_float)), ch.ctypes.data_as(C.POINTER(C.c_int32)))
+    if rc:
+        raise ValueError(f"orc_sim_hier_run failed ({rc})")
+    return rts, ch
+
+
 def dmat_cdf_array_ref(x, v, sv, a, z, sz, t, st, p_outlier, w_outlier):
     """hddm.cdfdif.dmat_cdf_array with the reference's own C (oracle/_ref/libcdfdif_ref.so, built from
     /root/reference/src/cdfdif.c as it lies) and the wrapper's arithmetic (src/cdfdif_wrapper.pyx:36-51) restated."""

@@ -238,3 +238,123 @@ int orc_sim_par2_run(int bound_kind, const float* theta, int n_sets, int64_t n_s
     free(b);
     return 0;
 }
+
+/* ddm_flexbound_seq2 (:1523-1661), ddm_flexbound_mic2_adj (:1797-1960), ddm_flexbound_tradeoff (:1966-2137).
+ * kind 1 / 2 / 3.  theta per set (13 floats): v_h, v_l1, v_l2, a, z_h, z_l1, z_l2, t, b0, b1, d, b2, b3.
+ * bound_kind 0 constant, 1 angle (b0), 2 Weibull (b0 = alpha, b1 = beta), 3 conflict-gamma (graveyard/boundary_functions.py:
+ * 66-97: max(a + scale * gamma_pdf(t; shape, scale_gamma) + t * (-tan(theta)), 0) with b0 = theta, b1 = scale, b2 = shape,
+ * b3 = scale_gamma).
+ * Literal about the state the reference carries from one particle into the next: seq2 leaves y_l / v_l untouched on
+ * its time-out and collapsed-bound branches, and the other two never rewrite bias_trace[n_h] (n_h = number of
+ * high-dimension steps of the current particle).  Before the first particle that state is taken as zero. */
+int orc_sim_hier_run(int kind, int bound_kind, const float* theta, int n_sets, int64_t n_samples, float dt, float max_t,
+                     float s, uint64_t seed, float* rts, int32_t* choices)
+{
+    rng_t R;
+    rng_seed(&R, seed);
+    const float sqrt_st = (float)sqrt(dt) * s;
+    const int num_draws = (int)((max_t / dt) + 1);
+    const int nb = num_draws + 2;
+    float* b = (float*)malloc(sizeof(float) * (size_t)(nb + 1));
+    float* trace = (float*)calloc((size_t)(nb + 1), sizeof(float));
+    if (!b || !trace) { free(b); free(trace); return 2; }
+    float y_l = 0.0f, v_l = 0.0f;
+    for (int k = 0; k < n_sets; k++) {
+        const float* th = theta + (size_t)k * 13;
+        const float a = th[3], t = th[7], d = th[10];
+        for (int ix = 0; ix <= nb; ix++) {
+            const float ts = (float)((double)ix * (double)dt);
+            if (bound_kind == 1) b[ix] = a + ts * (-sinf(th[8]) / cosf(th[8]));
+            else if (bound_kind == 2) b[ix] = (float)(a * exp(-pow((double)ts / th[9], (double)th[8])));
+            else if (bound_kind == 3) {
+                const double shape = th[11], sg = th[12], x = (double)ts / sg;
+                double pdf;
+                if (x > 0) pdf = exp((shape - 1.0) * log(x) - x - lgamma(shape)) / sg;
+                else pdf = (shape > 1.0) ? 0.0 : (shape == 1.0 ? 1.0 / sg : INFINITY);
+                const double v = (double)a + (double)th[9] * pdf + (double)ts * (-sin((double)th[8]) / cos((double)th[8]));
+                b[ix] = (float)(v > 0 ? v : 0);
+            } else b[ix] = a;
+        }
+        for (int64_t n = 0; n < n_samples; n++) {
+            const size_t o = (size_t)n * n_sets + k;
+            int choice = 0, ix = 0;
+            float y_h = (-1) * b[0] + (th[4] * 2 * b[0]);
+            if (kind == 1) {
+                float tp = 0.0f;
+                while (y_h >= (-1) * b[ix] && y_h <= b[ix] && tp <= max_t) {
+                    y_h += (th[0] * dt) + (sqrt_st * random_gaussian(&R));
+                    tp += dt;
+                    ix++;
+                }
+                if (tp >= max_t) {
+                    if (random_uniform(&R) > 0.5f) choice += 1;
+                } else {
+                    const int lower = sgn(y_h) < 0;
+                    const float z_l = lower ? th[5] : th[6];
+                    choice = lower ? 0 : 2;
+                    if (b[ix] <= 0) {
+                        if (random_uniform(&R) < z_l) choice += 1;
+                    } else {
+                        y_l = (-1) * b[ix] + (z_l * 2 * b[ix]);
+                        v_l = lower ? th[1] : th[2];
+                    }
+                }
+                while (y_l >= (-1) * b[ix] && y_l <= b[ix] && tp <= max_t) {
+                    y_l += (v_l * dt) + (sqrt_st * random_gaussian(&R));
+                    tp += dt;
+                    ix++;
+                }
+                rts[o] = tp + t;
+                if (sgn(y_l) >= 0) choice += 1;
+                choices[o] = choice;
+                continue;
+            }
+            float t_h = 0.0f, t_l = 0.0f;
+            trace[0] = (y_h + b[0]) / (2 * b[0]);
+            while (y_h >= (-1) * b[ix] && y_h <= b[ix] && t_h <= max_t) {
+                y_h += (th[0] * dt) + (sqrt_st * random_gaussian(&R));
+                trace[ix] = (y_h + b[ix]) / (2 * b[ix]);
+                t_h += dt;
+                ix++;
+            }
+            if (random_uniform(&R) <= ((y_h + b[ix]) / (2 * b[ix]))) choice += 2;
+            if (choice == 2) {
+                y_l = (-1) * b[0] + (th[6] * 2 * b[0]);
+                v_l = th[2];
+                for (int j = ix + 1; j < num_draws; j++) trace[j] = 1.0f;
+            } else {
+                y_l = (-1) * b[0] + (th[5] * 2 * b[0]);
+                v_l = th[1];
+                for (int j = ix + 1; j < num_draws; j++) trace[j] = 0.0f;
+                for (int j = 0; j < num_draws; j++) trace[j] = 1.0f - trace[j];
+            }
+            ix = 0;
+            while (y_l >= (-1) * b[ix] && y_l <= b[ix] && t_l <= max_t) {
+                const int before = (trace[ix] < 1) && (trace[ix] > 0);
+                if (kind == 2) {
+                    if (before) y_l += ((v_l * trace[ix] * d) * dt);
+                    else y_l += (v_l * dt);
+                    y_l += (sqrt_st * random_gaussian(&R));
+                } else {
+                    const float pos = (float)((1 + ((double)d * ((double)trace[ix] - 1.0))) / (double)(2 - d));
+                    const float g = random_gaussian(&R);
+                    if (before) {
+                        y_l += pos * (v_l * dt);
+                        y_l += pos * sqrt_st * g;
+                    } else {
+                        y_l += (v_l * dt);
+                        y_l += sqrt_st * g;
+                    }
+                }
+                t_l += dt;
+                ix++;
+            }
+            rts[o] = fmaxf(t_h, t_l) + t;
+            if (random_uniform(&R) <= ((y_l + b[ix]) / (2 * b[ix]))) choice += 1;
+            choices[o] = choice;
+        }
+    }
+    free(b);
+    free(trace);
+    return 0;
+}

@@ -121,6 +121,43 @@ def test_par2_matches_oracle(model, sims, oracle):
     assert np.array_equal(hist[0].astype(np.float64), sims.bin_simulator_output(out, nbins=128, freq_cnt=True))
 
 
+HIER_CASES = {
+    "ddm_seq2": [1.0, 0.5, -0.5, 1.2, 0.55, 0.45, 0.5, 0.3],
+    "ddm_seq2_angle_no_bias": [0.4, 0.5, -0.5, 1.0, 0.3, 0.6],        # bound collapses early: the carried-over y_l matters
+    "ddm_seq2_weibull_no_bias": [1.0, 0.5, -0.5, 1.2, 0.3, 2.0, 1.5],
+    "ddm_mic2_adj": [1.0, 0.8, -0.8, 1.2, 0.55, 0.45, 0.5, 0.6, 0.3],
+    "ddm_mic2_adj_angle_no_bias": [0.6, 0.8, -0.8, 1.0, 0.4, 0.3, 0.4],
+    "tradeoff_no_bias": [1.0, 0.8, -0.8, 1.2, 0.6, 0.3],
+    "tradeoff_weibull_no_bias": [1.0, 0.8, -0.8, 1.2, 0.6, 0.3, 2.0, 1.5],
+    "tradeoff_conflict_gamma_no_bias": [1.0, 0.8, -0.8, 0.6, 0.3, 0.8, 0.3, 1.5, 2.0, 0.6],
+}
+
+
+@pytest.mark.parametrize("model", list(HIER_CASES))
+def test_hier_matches_oracle(model, sims, oracle):
+    """seq2 / mic2_adj / tradeoff against the serial CPU restatement (which keeps the reference's carried-over state)."""
+    theta = np.asarray(HIER_CASES[model], dtype=np.float32)
+    kind, bk, cols = sims._HIER[model]
+    n_gpu, n_cpu = 300000, 60000
+    rts, ch, meta = sims.simulator(theta, model=model, n_samples=n_gpu, random_state=61)
+    ort, och = oracle.sim_hier_run(kind, bk, sims._par2_canonical(model, theta[None, :]), n_cpu, seed=62)
+    assert rts.shape == (n_gpu, 1) and meta["possible_choices"] == [0, 1, 2, 3]
+    assert stats.ks_2samp(rts[:, 0], ort[:, 0]).pvalue > 1e-3
+    for c in range(4):
+        la, ha = _ci(int(np.sum(ch == c)), n_gpu)
+        lb, hb = _ci(int(np.sum(och == c)), n_cpu)
+        assert la <= hb and lb <= ha, (model, c)
+        sel_g, sel_c = rts[:, 0][ch[:, 0] == c], ort[:, 0][och[:, 0] == c]
+        if min(sel_g.size, sel_c.size) > 2000:
+            assert stats.ks_2samp(sel_g, sel_c).pvalue > 1e-4, (model, c)
+    for p_name in cols + ["zh", "zl1", "zl2"]:
+        assert p_name in meta
+    # same particles for any sharding of the particle axis (the predecessor replay of seq2 is keyed by global index)
+    full = sims._run_par2(model, theta[None, :], 6000, 0.001, 20.0, 1.0, 9, True, 0)
+    tail = sims._run_par2(model, theta[None, :], 2000, 0.001, 20.0, 1.0, 9, True, 0, sample_offset=4000)
+    assert np.array_equal(full[0][4000:], tail[0]) and np.array_equal(full[1][4000:], tail[1])
+
+
 def test_shapes_and_metadata_like_reference_test(sims):
     """/root/reference/hddm/tests/test_simulators.py:65-87."""
     n_samples, n_trials = 100, 7
@@ -137,8 +174,8 @@ def test_shapes_and_metadata_like_reference_test(sims):
     assert sims.simulator(np.tile([1.0, 1.0, 0.5, 0.3, 0.2], (9, 1)), model="angle", n_samples=1)[0].shape == (9, 1)
     with pytest.raises(ValueError):
         sims.simulator([1.0, 1.0, 0.5], model="angle")
-    with pytest.raises(NotImplementedError):
-        sims.simulator([0.0] * 8, model="ddm_seq2")
+    with pytest.raises(ValueError):
+        sims.simulator([0.0] * 8, model="ddm_seq3")
     # ddm_cov codes the lower boundary as +1 (cddm_data_simulation.pyx:437)
     r0, c0, _ = sims.simulator([2.0, 2.0, 0.5, 0.3], model="ddm_hddm_base", n_samples=4000, random_state=3)
     r1, c1, _ = sims.simulator([2.0, 2.0, 0.5, 0.3], model="ddm_cov", n_samples=4000, random_state=3)

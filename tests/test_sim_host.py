@@ -42,8 +42,11 @@ def test_theta_coercion_and_model_table():
     with pytest.raises(ValueError):
         S._coerce_theta(np.zeros((3, 4)), "angle")
     assert S._resolve("weibull_cdf") == "weibull" and S._resolve("full_ddm_legacy") == "full_ddm_hddm_base"
-    with pytest.raises(NotImplementedError):
-        S._resolve("ddm_seq2_no_bias")
+    assert S._resolve("ddm_seq2_no_bias") == "ddm_seq2_no_bias" and len(S.model_config) == 42
+    assert S._par2_canonical("tradeoff_conflict_gamma_no_bias", np.arange(10, dtype=np.float32)[None, :]).tolist() == \
+        [[0, 1, 2, 5, 0.5, 0.5, 0.5, 4, 6, 7, 3, 8, 9]]
+    assert S._par2_canonical("ddm_mic2_adj", np.arange(9, dtype=np.float32)[None, :]).tolist() == \
+        [[0, 1, 2, 3, 4, 5, 6, 8, 0, 0, 7, 0, 0]]
     assert S._par2_canonical("ddm_par2_weibull_no_bias", np.arange(7, dtype=np.float32)[None, :]).tolist() == \
         [[0, 1, 2, 3, 0.5, 0.5, 0.5, 4, 5, 6]]
     with pytest.raises(ValueError):

@@ -172,6 +172,46 @@ def test_par2_vs_reference(oracle, ref_sim):
         assert la <= hb and lb <= ha, c
 
 
+def _conflict_gamma_bound(t=0, a=0.5, theta=0.5, scale=1, alphagamma=1.01, scalegamma=0.3):
+    # graveyard/boundary_functions.py:66-97
+    return np.maximum(a + scale * stats.gamma.pdf(t, a=alphagamma, loc=0, scale=scalegamma)
+                      + np.multiply(t, (-np.sin(theta) / np.cos(theta))), 0)
+
+
+def _constant(t=0):
+    return 1
+
+
+@pytest.mark.parametrize("kind,fn", [(1, "ddm_flexbound_seq2"), (2, "ddm_flexbound_mic2_adj"), (3, "ddm_flexbound_tradeoff")])
+@pytest.mark.parametrize("bk", [0, 1, 3])
+def test_hier_vs_reference(oracle, ref_sim, kind, fn, bk):
+    n = 20000
+    th = [0.6, 0.5, -0.5, 1.1, 0.55, 0.45, 0.5, 0.3]
+    d = 0.6
+    arrs = _f32(*th[:7]) + (_f32(d) if kind > 1 else []) + _f32(th[7])
+    a_arg = th[3]
+    if bk == 0:
+        bnd, canon_b = dict(boundary_fun=_constant, boundary_multiplicative=True, boundary_params={}), [0, 0, 0, 0]
+    elif bk == 1:
+        bnd = dict(boundary_fun=angle, boundary_multiplicative=False, boundary_params={"theta": np.array([0.5], dtype=np.float32)})
+        canon_b = [0.5, 0, 0, 0]
+    else:
+        bp = {"a": [th[3]], "theta": [0.3], "scale": [1.5], "alphagamma": [2.0], "scalegamma": [0.6]}
+        bnd = dict(boundary_fun=_conflict_gamma_bound, boundary_multiplicative=False,
+                   boundary_params={k: np.array(v, dtype=np.float32) for k, v in bp.items()})
+        canon_b = [0.3, 1.5, 2.0, 0.6]
+        arrs[3] = np.zeros(1, dtype=np.float32)      # the dispatch passes a zero vector; the bound carries its own a
+    r = getattr(ref_sim, fn)(*arrs, n_samples=n, n_trials=1, **bnd)
+    r_rt, r_ch = (r["rts"], r["choices"]) if isinstance(r, dict) else (r[0], r[1])
+    canon = th + [canon_b[0], canon_b[1], d, canon_b[2], canon_b[3]]
+    rt, ch = oracle.sim_hier_run(kind, bk, canon, n, seed=31 + kind)
+    assert stats.ks_2samp(rt[:, 0], r_rt[:, 0, 0]).pvalue > 1e-3
+    for c in range(4):
+        la, ha = _ci(int(np.sum(ch == c)), n)
+        lb, hb = _ci(int(np.sum(r_ch == c)), n)
+        assert la <= hb and lb <= ha, c
+
+
 def test_ddm_vs_analytic_wfpt(oracle):
     """Constant bounds: P(upper) from prob_ub (pdf.pxi:67-72) and the RT density from full_pdf, as
     /root/reference/hddm/tests/test_generate.py:33-50 validates its own random walk."""
