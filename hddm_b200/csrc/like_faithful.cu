@@ -27,6 +27,7 @@ struct FaithfulImpl {
         bool d;
         return density<true>(x, s, c, &d);
     }
+    __device__ static __forceinline__ bool whole_set_generic(const Set&) { return false; }
     static constexpr bool kParks = false;
     static constexpr int kParkCapacity = 0;
     __device__ static __forceinline__ bool may_park(const Set&) { return false; }

@@ -20,6 +20,8 @@ struct FastImpl {
     {
         return fast::density_generic(x, s);
     }
+    // parameter sets without a table (err / layout not covered): the kernels route every trial to density_generic
+    __device__ static __forceinline__ bool whole_set_generic(const Set& s) { return s.mode == fast::kModeGeneric; }
     static constexpr bool kParks = true;
     static constexpr int kParkCapacity = fast::kQueue;
     // only adaptive (refinement) and table-less parameter sets ever defer a trial

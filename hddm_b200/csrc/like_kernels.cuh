@@ -112,6 +112,17 @@ __global__ void __launch_bounds__(kBlock, MINB) like_batch_kernel(const double* 
             acc_slow += log(p0);
         }
     };
+    if (Impl::whole_set_generic(set)) {
+        // No table covers this parameter set: every trial goes through the operation-for-operation evaluator.  Kept apart
+        // from the loop below so that the hot loop of the fixed-grid instantiation contains no call at all (a call site
+        // there makes the register allocation of the whole loop depend on the callee).
+#pragma unroll 1
+        for (int64_t i = beg + threadIdx.x; i < end; i += kBlock) {
+            const double p0 = mix_outlier(Impl::density_generic(x[i], set, ctx), omp, wp);
+            zero |= (p0 == 0);
+            acc_slow += log(p0);
+        }
+    } else {
 #pragma unroll 1
     for (int64_t r = 0; r < rounds; r++) {
         double v0 = 0.0, v1 = 0.0;
@@ -131,11 +142,13 @@ __global__ void __launch_bounds__(kBlock, MINB) like_batch_kernel(const double* 
             const double xv = h ? v1 : v0;
             bool defer;
             double dens = Impl::template density<ADAPT>(xv, set, ctx, &defer);
-            if (defer) {
-                // park the trial; evaluated by the whole CTA.  (A full lot cannot happen with the drain below; the
-                // inline evaluation is the safety net.)
-                if (ADAPT && Impl::park(set, xv)) continue;
-                dens = Impl::density_generic(xv, set, ctx);
+            if (ADAPT && defer) {
+                // park the trial; evaluated by the whole CTA between rounds.  The lot is drained whenever fewer than one
+                // round's worth of slots (two per thread) is left, so it cannot be full here; should that invariant ever
+                // be broken the kernel stops loudly instead of evaluating inline (a call site in this loop costs the
+                // common path registers) or dropping the trial.
+                if (!Impl::park(set, xv)) __trap();
+                continue;
             }
             lp.add(mix_outlier(dens, omp, wp), zero);
         }
@@ -147,6 +160,7 @@ __global__ void __launch_bounds__(kBlock, MINB) like_batch_kernel(const double* 
                 Impl::parked_reset(set);                   // barriers inside
             }
         }
+    }
     }
     // remaining parked trials: dense pass through the generic evaluator
     if (ADAPT && Impl::kParks && Impl::may_park(set)) drain(Impl::parked_count(set));
@@ -181,8 +195,9 @@ __global__ void __launch_bounds__(kBlock) pdf_array_kernel(const double* __restr
     // wfpt.pyx:44: y * (1 - p_outlier) + (w_outlier * p_outlier), then optionally np.log
     const double wp = __dmul_rn(w_outlier, prm.p_outlier);
     const double omp = __dsub_rn(1.0, prm.p_outlier);
-    bool defer;
-    double dens = Impl::template density<ADAPT>(x[i], set, ctx, &defer);
+    bool defer = true;
+    double dens = 0.0;
+    if (!Impl::whole_set_generic(set)) dens = Impl::template density<ADAPT>(x[i], set, ctx, &defer);
     if (defer) dens = Impl::density_generic(x[i], set, ctx);
     const double p = mix_outlier(dens, omp, wp);
     y[i] = logp ? log(p) : p;

@@ -61,7 +61,8 @@ __device__ __forceinline__ double pdf(double x, double v, double a, double w, do
     return p * exp(-v * a * w - (v * v) * x / 2.) / (a * a);
 }
 
-__device__ __forceinline__ double pdf_sv(double x, double v, double sv, double a, double z, double err)
+// out of line: it is reached from several quadrature walkers, and one copy keeps the slow paths' code footprint small
+static __device__ __noinline__ double pdf_sv(double x, double v, double sv, double a, double z, double err)
 {
     if (x <= 0) return 0;
     if (sv == 0) return pdf(x, v, a, z, err);
@@ -93,11 +94,11 @@ template <class F>
 __device__ __forceinline__ double simpson_fixed(const F& f, double lb, double ub, int n)
 {
     const double h = (ub - lb) / n;
-    double S = f(lb);
+    double S = 0;
     double y = 0;
-    for (int i = 1; i <= n; i++) {
-        y = f(lb + h * i);
-        S += (i & 1) ? (4 * y) : (2 * y);
+    for (int i = 0; i <= n; i++) {   // node 0 is f(lb) with weight 1; one evaluation site for all nodes
+        y = f(i == 0 ? lb : lb + h * i);
+        S = (i == 0) ? y : S + ((i & 1) ? (4 * y) : (2 * y));
     }
     S = S - y;
     S = S / (ub - lb);
@@ -119,19 +120,29 @@ __device__ __forceinline__ double simpson_adaptive(const F& f, double lb, double
     int sp = 0;
 
     const double h0 = ub - lb;
-    double fb = f(lb) / ZT;
-    double fe = f(ub) / ZT;
-    double fm = f((lb + ub) / 2.) / ZT;
-    double S = (h0 / 6) * (fb + 4 * fm + fe);
+    double fb = 0, fe = 0, fm = 0, fd = 0, S = 0;
     double err = simps_err;
-
+    // The integrand is evaluated at ONE place in the code (it is large, and when it is itself an adaptive integral it
+    // contains another copy of this walk): stage 0-2 are the three nodes of the whole interval, 3 and 4 the two new
+    // midpoints of the current one.
+    int stage = 0;
     for (;;) {
-        const double h = ub - lb;
         const double c = (ub + lb) / 2.;
-        const double d = (lb + c) / 2.;
-        const double e = (c + ub) / 2.;
-        const double fd = f(d) / ZT;
-        const double fee = f(e) / ZT;
+        const double at = (stage == 0) ? lb : (stage == 1) ? ub : (stage == 2) ? c : (stage == 3) ? (lb + c) / 2. : (c + ub) / 2.;
+        const double val = f(at) / ZT;
+        if (stage < 4) {
+            if (stage == 0) fb = val;
+            else if (stage == 1) fe = val;
+            else if (stage == 2) {
+                fm = val;
+                S = (h0 / 6) * (fb + 4 * fm + fe);
+            } else fd = val;
+            stage++;
+            continue;
+        }
+        stage = 3;
+        const double fee = val;
+        const double h = ub - lb;
         const double Sl = (h / 12) * (fb + 4 * fd + fm);
         const double Sr = (h / 12) * (fm + 4 * fee + fe);
         const double S2 = Sl + Sr;
@@ -194,33 +205,26 @@ __device__ __forceinline__ double full_pdf(double x, double v, double sv, double
     if (sz < 1e-3) sz = 0;
 
     const Trial q{x, v, sv, a, o.err};
-    if (sz == 0) {
-        if (st == 0) return pdf_sv(x - t, v, sv, a, z, o.err);
-        const double lb_t = t - st / 2., ub_t = t + st / 2.;
-        if (o.use_adaptive > 0) {
-            // adaptiveSimpsons_1D picks the axis by (ub_t - lb_t) == 0 (integrate.pxi:120)
-            if ((ub_t - lb_t) == 0) {
-                Axis ax{q, t, true};
-                return simpson_adaptive(ax, z, z, 0.0, o.simps_err, o.n_st);
-            }
-            Axis ax{q, z, false};
-            return simpson_adaptive(ax, lb_t, ub_t, ub_t - lb_t, o.simps_err, o.n_st);
-        }
-        // simpson_1D(..., n_sz=0, ..., n_st): n = max(n_st, 0); axis picked by n_st == 0 (integrate.pxi:17-28)
-        if (o.n_st == 0) {
-            Axis ax{q, t, true};
-            return simpson_fixed(ax, z, z, o.n_st > 0 ? o.n_st : 0);
-        }
-        Axis ax{q, z, false};
-        return simpson_fixed(ax, lb_t, ub_t, o.n_st > 0 ? o.n_st : 0);
-    }
-    const double lb_z = z - sz / 2., ub_z = z + sz / 2.;
-    if (st == 0) {
-        Axis ax{q, t, true};
-        if (o.use_adaptive) return simpson_adaptive(ax, lb_z, ub_z, ub_z - lb_z, o.simps_err, o.n_sz);
-        return simpson_fixed(ax, lb_z, ub_z, o.n_sz > 0 ? o.n_sz : 0);
-    }
+    if (sz == 0 && st == 0) return pdf_sv(x - t, v, sv, a, z, o.err);
     const double lb_t = t - st / 2., ub_t = t + st / 2.;
+    const double lb_z = z - sz / 2., ub_z = z + sz / 2.;
+    if (sz == 0 || st == 0) {
+        // one axis.  sz == 0: adaptiveSimpsons_1D picks the axis by (ub_t - lb_t) == 0 (integrate.pxi:120), simpson_1D
+        // by n_st == 0 (integrate.pxi:17-28); both then integrate "over z" on the empty interval [z, z].
+        const bool adapt = o.use_adaptive > 0 || (st == 0 && o.use_adaptive);
+        bool over_z;
+        double lo, hi;
+        int n;
+        if (st == 0) {
+            over_z = true; lo = lb_z; hi = ub_z; n = o.n_sz;
+        } else {
+            over_z = adapt ? ((ub_t - lb_t) == 0) : (o.n_st == 0);
+            lo = over_z ? z : lb_t; hi = over_z ? z : ub_t; n = o.n_st;
+        }
+        const Axis ax{q, over_z ? t : z, over_z};
+        if (adapt) return simpson_adaptive(ax, lo, hi, (st == 0) ? ub_z - lb_z : (over_z ? 0.0 : ub_t - lb_t), o.simps_err, n);
+        return simpson_fixed(ax, lo, hi, n > 0 ? n : 0);
+    }
     if (o.use_adaptive) {
         InnerAdaptive in{q, lb_z, ub_z, o.simps_err, o.n_sz};
         return simpson_adaptive(in, lb_t, ub_t, ub_t - lb_t, o.simps_err, o.n_st);

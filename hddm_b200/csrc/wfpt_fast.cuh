@@ -568,7 +568,7 @@ __device__ __forceinline__ double density(double x, Set& s, bool* defer)
 {
     *defer = false;
     if (s.mode == kModeZero) return 0.0;
-    if (s.mode == kModeGeneric) return generic_full_pdf(x, s.tab->prm, s.tab->o);  // no table for this err / layout
+    // (kModeGeneric never gets here: the kernels send such sets to density_generic, see whole_set_generic)
     const double ax = fabs(x);
     if ((ax - s.tlo) < 0) return 0.0;  // pdf.pxi:112, the trial-dependent part
     const int sign = x > 0;
@@ -698,24 +698,86 @@ static __device__ __noinline__ double adaptive_full_pdf(double x, const Tables* 
     c.asv2 = c.a2 * c.sv2; c.sv_nonzero = (p.sv != 0); c.T = Tp;
     const double lb_z = __dsub_rn(z, __ddiv_rn(sz, 2.)), ub_z = __dadd_rn(z, __ddiv_rn(sz, 2.));
     const double lb_t = __dsub_rn(t, __ddiv_rn(st, 2.)), ub_t = __dadd_rn(t, __ddiv_rn(st, 2.));
-    if (sz == 0) {
-        AdhocAxis ax{c, x, z, false};
-        return faithful::simpson_adaptive(ax, lb_t, ub_t, __dsub_rn(ub_t, lb_t), T.o.simps_err, T.o.n_st);
-    }
-    if (st == 0) {
-        AdhocAxis ax{c, x, t, true};
-        return faithful::simpson_adaptive(ax, lb_z, ub_z, __dsub_rn(ub_z, lb_z), T.o.simps_err, T.o.n_sz);
+    if (sz == 0 || st == 0) {   // one axis: along t at fixed z, or along z at fixed t
+        const bool over_z = (sz != 0);
+        const AdhocAxis ax{c, x, over_z ? t : z, over_z};
+        const double lo = over_z ? lb_z : lb_t, hi = over_z ? ub_z : ub_t;
+        return faithful::simpson_adaptive(ax, lo, hi, __dsub_rn(hi, lo), T.o.simps_err, over_z ? T.o.n_sz : T.o.n_st);
     }
     AdhocInner in{c, x, lb_z, ub_z, T.o.simps_err, T.o.n_sz};
     return faithful::simpson_adaptive(in, lb_t, ub_t, __dsub_rn(ub_t, lb_t), T.o.simps_err, T.o.n_st);
 }
 
-// The full reference recursion for one trial: the table-driven walker for adaptive parameter sets, the
+// Refinement along t with the staged z-nodes.  Nearly every trial that fails the first-level test does so on the t axis
+// (an RT close to t +- st/2, where the integrand switches on), while each inner z-integral still stops at its first
+// level.  Such a trial needs the reference's walk over t only, and every new t-node costs what a staged one costs:
+// the inner integral at an arbitrary t-node is inner_t on the staged z lattice.  When an inner integral does ask for
+// refinement the whole trial goes to the node-by-node walker above.
+template <int NZN>
+static __device__ __noinline__ double staged_inner(double t_node, double ax, int sign, Set& s, bool* ok, int* neg)
+{
+    TNode tn;
+    make_tnode(tn, ax - t_node, s);
+    return inner_t<NZN>(tn, s, sign, ok, *neg);
+}
+template <int NZN>
+struct StagedInner {
+    Set* s;
+    double ax;
+    int sign;
+    bool* ok;
+    int* neg;
+    __device__ __forceinline__ double operator()(double t_node) const
+    {
+        return staged_inner<NZN>(t_node, ax, sign, *s, ok, neg);
+    }
+};
+
+static __device__ __noinline__ double adaptive_refine(double x, const Tables* Tp, int kind, int kl_max)
+{
+    const Tables& T = *Tp;
+    if (kind == 4) return adaptive_full_pdf(x, Tp);   // z-only integration: nothing staged helps below the first level
+    const Params& p = T.prm;
+    Set s;                                            // private copy: the caller's stays in registers
+    s.mode = kModeAdaptive;
+    s.nz = (kind == 3) ? 4 : 0;
+    s.nt = 4;
+    s.sv_nonzero = (p.sv != 0);
+    s.kl_max = kl_max;
+    s.kind = kind;
+    s.piece = 0;
+    s.piece_desc = 0;
+    s.lo_b = 1;
+    s.hi_b = 0;
+    s.tlo = T.tn[0];
+    s.v2 = p.v * p.v;
+    s.sv2 = p.sv * p.sv;
+    s.a2 = p.a * p.a;
+    s.inv_a2 = 1.0 / s.a2;
+    s.tab = Tp;
+    bool ok = true;
+    int neg = 0;
+    const double ax = fabs(x);
+    const int sign = x > 0;
+    double r;
+    if (kind == 3) {
+        StagedInner<5> f{&s, ax, sign, &ok, &neg};
+        r = faithful::simpson_adaptive(f, T.tn[0], T.tn[4], T.wt, T.simps_err, T.depth_t);
+    } else {
+        StagedInner<1> f{&s, ax, sign, &ok, &neg};
+        r = faithful::simpson_adaptive(f, T.tn[0], T.tn[4], T.wt, T.simps_err, T.depth_t);
+    }
+    if (!ok) return adaptive_full_pdf(x, Tp);
+    if (s.sv_nonzero && neg < 0) r = CUDART_NAN;
+    return r;
+}
+
+// The full reference recursion for one trial: the table-driven walkers for adaptive parameter sets, the
 // operation-for-operation evaluator for everything the tables do not cover.
 __device__ __forceinline__ double density_generic(double x, const Set& s)
 {
     const Tables& T = *s.tab;
-    if (s.mode == kModeAdaptive) return adaptive_full_pdf(x, s.tab);
+    if (s.mode == kModeAdaptive) return adaptive_refine(x, s.tab, s.kind, s.kl_max);
     return generic_full_pdf(x, T.prm, T.o);
 }
 
