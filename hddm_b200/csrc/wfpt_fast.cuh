@@ -666,14 +666,20 @@ struct AdhocAxis {  // integrand along one axis (cf. faithful::Axis)
         return over_z ? pdf_sv_adhoc(c, x - fixed, s) : pdf_sv_adhoc(c, x - s, fixed);
     }
 };
+// Adaptive Simpson along one axis, node by node (one copy in the kernel: every caller goes through here).
+static __device__ __noinline__ double adhoc_axis_integral(const AdhocAxis& ax, double lo, double hi, double width,
+                                                          double simps_err, int depth)
+{
+    return faithful::simpson_adaptive(ax, lo, hi, width, simps_err, depth);
+}
 struct AdhocInner {  // adaptive z-integral as the integrand of the t-integral (integrate.pxi:143-206)
     AdhocCtx c;
     double x, lb_z, ub_z, simps_err;
     int depth_sz;
     __device__ __forceinline__ double operator()(double t_node) const
     {
-        AdhocAxis ax{c, x, t_node, true};
-        return faithful::simpson_adaptive(ax, lb_z, ub_z, ub_z - lb_z, simps_err, depth_sz);
+        const AdhocAxis ax{c, x, t_node, true};
+        return adhoc_axis_integral(ax, lb_z, ub_z, ub_z - lb_z, simps_err, depth_sz);
     }
 };
 
@@ -702,7 +708,7 @@ static __device__ __noinline__ double adaptive_full_pdf(double x, const Tables* 
         const bool over_z = (sz != 0);
         const AdhocAxis ax{c, x, over_z ? t : z, over_z};
         const double lo = over_z ? lb_z : lb_t, hi = over_z ? ub_z : ub_t;
-        return faithful::simpson_adaptive(ax, lo, hi, __dsub_rn(hi, lo), T.o.simps_err, over_z ? T.o.n_sz : T.o.n_st);
+        return adhoc_axis_integral(ax, lo, hi, __dsub_rn(hi, lo), T.o.simps_err, over_z ? T.o.n_sz : T.o.n_st);
     }
     AdhocInner in{c, x, lb_z, ub_z, T.o.simps_err, T.o.n_sz};
     return faithful::simpson_adaptive(in, lb_t, ub_t, __dsub_rn(ub_t, lb_t), T.o.simps_err, T.o.n_st);
@@ -711,27 +717,85 @@ static __device__ __noinline__ double adaptive_full_pdf(double x, const Tables* 
 // Refinement along t with the staged z-nodes.  Nearly every trial that fails the first-level test does so on the t axis
 // (an RT close to t +- st/2, where the integrand switches on), while each inner z-integral still stops at its first
 // level.  Such a trial needs the reference's walk over t only, and every new t-node costs what a staged one costs:
-// the inner integral at an arbitrary t-node is inner_t on the staged z lattice.  When an inner integral does ask for
-// refinement the whole trial goes to the node-by-node walker above.
+// the inner integral at an arbitrary t-node is inner_t on the staged z lattice.  When one inner integral does ask for
+// refinement, that integral alone is redone node by node.
+//
+// The reference's walk over t for a recursion budget of 2 (what HDDM passes, likelihoods.py:105-113), written level by
+// level: the five nodes of the first level, the four of the second, and -- for each half that asks for it -- the four
+// of the third, after which the budget is spent and the half is accepted as it is.  The 17 candidate nodes are visited
+// in one loop with one evaluation site, so the lanes of a warp (one parked trial each) stay in step: they differ only
+// in whether they take part in the last eight iterations.  Sums are formed in the reference's order
+// (left + right at every level).
 template <int NZN>
-static __device__ __noinline__ double staged_inner(double t_node, double ax, int sign, Set& s, bool* ok, int* neg)
+__device__ __forceinline__ double refine_t_depth2(double ax, int sign, Set& s, const AdhocCtx& c, int* neg)
 {
-    TNode tn;
-    make_tnode(tn, ax - t_node, s);
-    return inner_t<NZN>(tn, s, sign, ok, *neg);
-}
-template <int NZN>
-struct StagedInner {
-    Set* s;
-    double ax;
-    int sign;
-    bool* ok;
-    int* neg;
-    __device__ __forceinline__ double operator()(double t_node) const
-    {
-        return staged_inner<NZN>(t_node, ax, sign, *s, ok, neg);
+    const Tables& T = *s.tab;
+    double t[17], g[17];
+    t[0] = T.tn[0]; t[4] = T.tn[1]; t[8] = T.tn[2]; t[12] = T.tn[3]; t[16] = T.tn[4];
+#pragma unroll
+    for (int j = 2; j < 16; j += 4) t[j] = (t[j - 2] + t[j + 2]) / 2.;
+#pragma unroll
+    for (int j = 1; j < 16; j += 2) t[j] = (t[j - 1] + t[j + 1]) / 2.;
+    double part[4] = {0.0, 0.0, 0.0, 0.0};  // level-2 Simpson pieces per quarter: [0,4] [4,8] [8,12] [12,16]
+    double half_ret[2] = {0.0, 0.0};
+    bool deeper[2] = {false, false};
+#pragma unroll 1
+    for (int it = 0; it < 17; it++) {
+        // it 0..4 -> j = 4 it;  5..8 -> j = 4 (it - 5) + 2;  9..16 -> j = 2 (it - 9) + 1
+        const int j = (it < 5) ? 4 * it : (it < 9) ? 4 * (it - 5) + 2 : 2 * (it - 9) + 1;
+        if (it == 5) {
+            // first level again: a trial parked for an inner integral alone may pass it with the refined values
+            double r1;
+            if (adaptive_level1(g[0], g[4], g[8], g[12], g[16], T.wt, T.simps_err, T.depth_t, &r1)) return r1;
+        }
+        if (it == 9) {
+            // second level (integrate.pxi:99-112 with bottom = 1, simps_err / 2) on both halves
+            const double H = t[16] - t[0], h = t[8] - t[0], h2 = t[16] - t[8];
+            const double S_l = (H / 12) * (g[0] + 4 * g[4] + g[8]);    // Sleft / Sright of the first level
+            const double S_r = (H / 12) * (g[8] + 4 * g[12] + g[16]);
+            part[0] = (h / 12) * (g[0] + 4 * g[2] + g[4]);
+            part[1] = (h / 12) * (g[4] + 4 * g[6] + g[8]);
+            part[2] = (h2 / 12) * (g[8] + 4 * g[10] + g[12]);
+            part[3] = (h2 / 12) * (g[12] + 4 * g[14] + g[16]);
+            const double S2l = part[0] + part[1], S2r = part[2] + part[3];
+            const double e2 = 15 * (T.simps_err / 2);
+            deeper[0] = !(fabs(S2l - S_l) <= e2);
+            deeper[1] = !(fabs(S2r - S_r) <= e2);
+            half_ret[0] = S2l + (S2l - S_l) / 15;
+            half_ret[1] = S2r + (S2r - S_r) / 15;
+            if (!deeper[0] && !deeper[1]) break;
+        }
+        if (it >= 9 && !deeper[(it - 9) >> 2]) continue;
+        TNode tn;
+        make_tnode(tn, ax - t[j], s);
+        bool inner_ok = true;
+        double val = inner_t<NZN>(tn, s, sign, &inner_ok, *neg);
+        if (NZN == 5 && !inner_ok) {
+            // this node's z-integral wants more than its first level: walk it node by node (integrate.pxi:114-141)
+            const AdhocAxis az{c, ax, t[j], true};
+            val = adhoc_axis_integral(az, T.z[sign][0].u[1], T.z[sign][4].u[1], T.wz[sign], T.simps_err, T.depth_z);
+        }
+        g[j] = val * T.inv_wt;
     }
-};
+    // third level (bottom = 0: accepted whatever the difference), quarter by quarter
+#pragma unroll
+    for (int hlf = 0; hlf < 2; hlf++) {
+        if (!deeper[hlf]) continue;
+        double sum = 0.0;
+#pragma unroll
+        for (int q = 0; q < 2; q++) {
+            const int j0 = 8 * hlf + 4 * q;                          // quarter [t[j0], t[j0 + 4]]
+            const double h = t[j0 + 4] - t[j0];
+            const double Sl = (h / 12) * (g[j0] + 4 * g[j0 + 1] + g[j0 + 2]);
+            const double Sr = (h / 12) * (g[j0 + 2] + 4 * g[j0 + 3] + g[j0 + 4]);
+            const double S2 = Sl + Sr;
+            const double ret = S2 + (S2 - part[2 * hlf + q]) / 15;
+            sum = q ? sum + ret : ret;
+        }
+        half_ret[hlf] = sum;
+    }
+    return half_ret[0] + half_ret[1];
+}
 
 static __device__ __noinline__ double adaptive_refine(double x, const Tables* Tp, int kind, int kl_max)
 {
@@ -755,19 +819,14 @@ static __device__ __noinline__ double adaptive_refine(double x, const Tables* Tp
     s.a2 = p.a * p.a;
     s.inv_a2 = 1.0 / s.a2;
     s.tab = Tp;
-    bool ok = true;
     int neg = 0;
     const double ax = fabs(x);
     const int sign = x > 0;
-    double r;
-    if (kind == 3) {
-        StagedInner<5> f{&s, ax, sign, &ok, &neg};
-        r = faithful::simpson_adaptive(f, T.tn[0], T.tn[4], T.wt, T.simps_err, T.depth_t);
-    } else {
-        StagedInner<1> f{&s, ax, sign, &ok, &neg};
-        r = faithful::simpson_adaptive(f, T.tn[0], T.tn[4], T.wt, T.simps_err, T.depth_t);
-    }
-    if (!ok) return adaptive_full_pdf(x, Tp);
+    if (T.depth_t != 2) return adaptive_full_pdf(x, Tp);   // other budgets: the general walker
+    AdhocCtx c;                                           // for z-integrals that need their own refinement
+    c.v = sign ? -p.v : p.v; c.v2 = s.v2; c.sv2 = s.sv2; c.a = p.a; c.a2 = s.a2; c.inv_a2 = s.inv_a2;
+    c.asv2 = c.a2 * c.sv2; c.sv_nonzero = s.sv_nonzero; c.T = Tp;
+    double r = (kind == 3) ? refine_t_depth2<5>(ax, sign, s, c, &neg) : refine_t_depth2<1>(ax, sign, s, c, &neg);
     if (s.sv_nonzero && neg < 0) r = CUDART_NAN;
     return r;
 }
