@@ -24,6 +24,7 @@ struct FastImpl {
     __device__ static __forceinline__ bool whole_set_generic(const Set& s) { return s.mode == fast::kModeGeneric; }
     static constexpr bool kParks = true;
     static constexpr int kParkCapacity = fast::kQueue;
+    static_assert(fast::kQueue > kParkCheck * 2 * kBlock, "parking lot smaller than what can arrive between two checks");
     // only adaptive (refinement) and table-less parameter sets ever defer a trial
     __device__ static __forceinline__ bool may_park(const Set& s) { return s.mode == fast::kModeAdaptive; }
     __device__ static __forceinline__ void parked_reset(const Set&)

@@ -47,6 +47,8 @@ struct LogProduct {
 // ADAPT: the launch uses adaptive Simpson (use_adaptive != 0).  Only then can a trial be deferred (refinement below
 // the first level), so only that instantiation carries the parking lot, the round structure and the adaptive
 // evaluators; the fixed-grid instantiation stays lean.
+constexpr int kParkCheck = 3;   // rounds between two looks at the parking lot (capacity must exceed kParkCheck * 2 * kBlock)
+
 template <class Impl, bool ADAPT, int MINB = 4>
 __global__ void __launch_bounds__(kBlock, MINB) like_batch_kernel(const double* __restrict__ x, int64_t n,
                                                           const double* __restrict__ params, int64_t P, Opts o,
@@ -152,10 +154,11 @@ __global__ void __launch_bounds__(kBlock, MINB) like_batch_kernel(const double* 
             }
             lp.add(mix_outlier(dens, omp, wp), zero);
         }
-        if (ADAPT && Impl::kParks && Impl::may_park(set)) {   // uniform over the CTA
-            // room for one more round (two trials per thread)?  If not, everybody evaluates the parked trials now.
+        if (ADAPT && Impl::kParks && Impl::may_park(set) && (r % kParkCheck) == kParkCheck - 1) {   // uniform over the CTA
+            // Room for kParkCheck more rounds (two trials per thread each)?  If not, everybody evaluates the parked trials
+            // now.  Looking only every kParkCheck-th round keeps the barrier this needs out of most rounds.
             const int parked = Impl::parked_count(set);   // barrier inside
-            if (parked > Impl::kParkCapacity - 2 * kBlock) {
+            if (parked > Impl::kParkCapacity - kParkCheck * 2 * kBlock) {
                 drain(parked);
                 Impl::parked_reset(set);                   // barriers inside
             }
