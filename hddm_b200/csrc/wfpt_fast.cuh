@@ -44,10 +44,10 @@ enum Mode : int {
 };
 
 // Per (response sign, z-node) constants.
-struct NodeTab {
-    double A;                 // (a z sv)^2 - 2 a v' z
+struct alignas(16) NodeTab {   // field order and alignment chosen so that the node loop can fetch pairs (16-byte loads)
     double u[4];              // z + 2k,        k = -1, 0, 1, 2
-    double uh[4];             // -(z + 2k)^2/2
+    double A;                 // (a z sv)^2 - 2 a v' z
+    double uh1;               // -z^2/2
     double S[kMaxKLarge];     // k sin(k pi z), k = 1..kl_max
 };
 
@@ -104,7 +104,7 @@ __device__ __forceinline__ Tables& tables()
 
 // ---- exp ------------------------------------------------------------------------------------------------------------------
 // exp(x) = 2^e * 2^(j/64) * exp(r),  k = rint(64 x / ln 2) = 64 e + j,  r = x - k ln2/64, |r| <= 0.0055.
-// Branch-free; valid for |x| < 708 (normal results).  Max error 0.98 ulp (checked against mpmath).
+// Branch-free; valid for |x| < 708 (normal results).  Max error 1.24 ulp (checked against mpmath with exact-FMA emulation).
 // The coefficients sit in constant memory: as literals the compiler re-materialises each one with two 32-bit moves
 // every time register pressure evicts it (16 % of the trial loop's instructions in the profile of the literal form).
 __constant__ double kExpC[10] = {
@@ -121,14 +121,18 @@ __device__ __forceinline__ double exp_core(double x, const double* __restrict__ 
     const double kd = t - kExpC[1];
     double r = fma(kd, kExpC[2], x);
     r = fma(kd, kExpC[3], r);
-    double p = fma(r, kExpC[4], kExpC[5]);
-    p = fma(p, r, kExpC[6]);
-    p = fma(p, r, kExpC[7]);
-    p = fma(p, r, kExpC[8]);
-    p = p * r;                                            // exp(r) - 1
+    // exp(r) - 1 = r + r^2 (1/2 + r/6 + r^2 (1/24 + r/120)), Estrin form: the kernel waits on dependent FP64 results far
+    // more than on issue slots, and this chain is two steps shorter than Horner's for the same number of operations
+    const double r2 = r * r;
+    const double ph = fma(r, kExpC[4], kExpC[5]);
+    const double pl = fma(r, kExpC[6], kExpC[7]);
+    const double p = fma(r2, fma(ph, r2, pl), r);
     const double T = tab[ki & 63];
     const double res = fma(T, p, T);
-    return __hiloint2double(__double2hiint(res) + ((ki << 14) & 0xfff00000), __double2loint(res));
+    // add e = k >> 6 to the exponent field: one mask and one multiply-add (k - j is a multiple of 64, times 2^14 = e << 20)
+    int hi;
+    asm("mad.lo.s32 %0, %1, 16384, %2;" : "=r"(hi) : "r"(ki & ~63), "r"(__double2hiint(res)));
+    return __hiloint2double(hi, __double2loint(res));
 }
 // |x| < 708 (and not NaN), tested on the high word so that it costs no FP64-pipe slot
 __device__ __forceinline__ bool exp_arg_ok(double x) { return (unsigned)(__double2hiint(x) & 0x7fffffff) < 0x40862000u; }
@@ -273,7 +277,7 @@ __device__ __forceinline__ void nodes(const TNode& tn, const Set& s, int sign, i
         double e0[N];
 #pragma unroll
         for (int n = 0; n < N; n++) {
-            const double a = fma(Z[n].uh[1], tau, E[n]);
+            const double a = fma(Z[n].uh1, tau, E[n]);
             ok &= exp_arg_ok(a);
             e0[n] = exp_core(a, tab);
         }
@@ -482,7 +486,7 @@ __device__ __forceinline__ void prepare(Set& s, const Params& prm, const Opts& o
         if (slot < 4) {
             const double u = zj + 2.0 * (slot - 1);
             Z.u[slot] = u;
-            Z.uh[slot] = -0.5 * u * u;
+            if (slot == 1) Z.uh1 = -0.5 * u * u;
         } else if (slot == 4) {
             const double vv = sign ? -prm.v : prm.v;
             const double azsv = a * zj * sv;
