@@ -35,7 +35,7 @@ static int fail(const char* fmt, ...)
 void count_launch(int k) { g_launches.fetch_add(k, std::memory_order_relaxed); }
 
 // ---- per-device grow-only scratch ------------------------------------------------------------------------------------
-enum Slot { kPartSum = 0, kPartZero, kStageX, kStageParams, kStageOut, kStageAux0, kStageAux1, kStageAux2, kStageAux3,
+enum Slot { kPartSum = 0, kPartZero, kDone, kStageX, kStageParams, kStageOut, kStageAux0, kStageAux1, kStageAux2, kStageAux3,
             kStageAux4, kStageAux5, kStageAux6, kStageAux7, kStageAux8, kStageAux9, kStageAux10, kStageAux11, kNumSlots };
 constexpr int kMaxDev = 16;
 struct Buf { void* p = nullptr; size_t cap = 0; };
@@ -56,8 +56,46 @@ static int scratch(int slot, size_t bytes, void** out)
         size_t cap = bytes < 4096 ? 4096 : bytes + bytes / 4;
         CK(cudaMalloc(&b.p, cap));
         b.cap = cap;
+        if (slot == kDone) {   // arrival counters: zero between launches by construction; zeroed before any stream can use them
+            CK(cudaMemset(b.p, 0, cap));
+            CK(cudaDeviceSynchronize());
+        }
     }
     *out = b.p;
+    return 0;
+}
+
+// ---- pinned, device-mapped host staging for small host-buffer calls ------------------------------------------------------
+// A `wiener_like` call from a sampler moves a few KB in and 8 bytes out; done with pageable buffers that is three
+// driver-staged copies, each costing more than the kernel.  Small calls pack their inputs into this pinned block (one
+// truly asynchronous copy in) and have the kernel write the results into its mapped head (no copy out).
+constexpr size_t kPinOutBytes = 4096;          // results: up to 512 parameter sets
+constexpr size_t kPinMaxIn = (size_t)1 << 20;  // larger inputs amortise the pageable path
+struct Pin { char* h = nullptr; char* d = nullptr; size_t cap = 0; };
+static Pin g_pin[kMaxDev];
+
+static int pinned(size_t in_bytes, char** h, char** d)
+{
+    int dev = 0;
+    CK(cudaGetDevice(&dev));
+    if (dev >= kMaxDev) return fail("device index %d beyond the %d this library tracks", dev, kMaxDev);
+    std::lock_guard<std::mutex> lk(g_mu);
+    Pin& b = g_pin[dev];
+    const size_t need = kPinOutBytes + in_bytes;
+    if (b.cap < need) {
+        if (b.h) CK(cudaFreeHost(b.h));
+        b = Pin();
+        size_t cap = need < 65536 ? 65536 : need + need / 4;
+        void* hp = nullptr;
+        void* dp = nullptr;
+        CK(cudaHostAlloc(&hp, cap, cudaHostAllocMapped));
+        CK(cudaHostGetDevicePointer(&dp, hp, 0));
+        b.h = (char*)hp;
+        b.d = (char*)dp;
+        b.cap = cap;
+    }
+    *h = b.h;
+    *d = b.d;
     return 0;
 }
 
@@ -279,6 +317,8 @@ int wfpt_release_scratch(void)
         if (g_buf[dev][s].p) cudaFree(g_buf[dev][s].p);
         g_buf[dev][s] = Buf();
     }
+    if (g_pin[dev].h) cudaFreeHost(g_pin[dev].h);
+    g_pin[dev] = Pin();
     return 0;
 }
 
@@ -325,19 +365,16 @@ int wfpt_like_batch(const double* d_x, int64_t n, const double* d_params, int64_
     a.part_sum = nullptr;
     a.part_zero = nullptr;
     if (a.slices > 1) {
-        void *ps, *pz;
+        void *ps, *pz, *dn;
         if (scratch(kPartSum, sizeof(double) * (size_t)P * a.slices, &ps)) return 1;
         if (scratch(kPartZero, sizeof(int) * (size_t)P * a.slices, &pz)) return 1;
+        if (scratch(kDone, sizeof(int) * (size_t)P, &dn)) return 1;
         a.part_sum = (double*)ps;
         a.part_zero = (int*)pz;
+        a.done = (int*)dn;   // the last slice of each set sums the partials: one launch in all
     }
     CK(variant == WFPT_VARIANT_FAITHFUL ? launch_like_batch_faithful(a) : launch_like_batch_fast(a));
     count_launch(1);
-    if (a.slices > 1) {
-        finalize_kernel<<<(unsigned)((P + 127) / 128), 128, 0, a.stream>>>(a.part_sum, a.part_zero, P, a.slices, 1, d_out);
-        CK(cudaGetLastError());
-        count_launch(1);
-    }
     return 0;
 }
 
@@ -348,6 +385,22 @@ int wfpt_like_batch_host(const double* h_x, int64_t n, const double* h_params, i
     if (P == 0) return 0;
     if (!h_params || !h_out || (n > 0 && !h_x)) return fail("null pointer argument");
     void *dx, *dp, *dout;
+    const size_t in_bytes = sizeof(double) * (8 * (size_t)P + (size_t)n);
+    if (sizeof(double) * (size_t)P <= kPinOutBytes && in_bytes <= kPinMaxIn) {
+        // small call: [params | x] through the pinned block in one copy, results straight into its mapped head
+        char *ph, *pd;
+        if (pinned(in_bytes, &ph, &pd)) return 1;
+        if (scratch(kStageX, in_bytes, &dx)) return 1;
+        memcpy(ph + kPinOutBytes, h_params, sizeof(double) * 8 * (size_t)P);
+        if (n > 0) memcpy(ph + kPinOutBytes + sizeof(double) * 8 * (size_t)P, h_x, sizeof(double) * (size_t)n);
+        CK(cudaMemcpyAsync(dx, ph + kPinOutBytes, in_bytes, cudaMemcpyHostToDevice, 0));
+        if (wfpt_like_batch((const double*)dx + 8 * P, n, (const double*)dx, P, err, n_st, n_sz, use_adaptive, simps_err,
+                            w_outlier, variant, (double*)pd, nullptr))
+            return 1;
+        CK(cudaStreamSynchronize(0));
+        memcpy(h_out, ph, sizeof(double) * (size_t)P);
+        return 0;
+    }
     if (scratch(kStageX, sizeof(double) * (size_t)(n > 0 ? n : 1), &dx)) return 1;
     if (scratch(kStageParams, sizeof(double) * 8 * (size_t)P, &dp)) return 1;
     if (scratch(kStageOut, sizeof(double) * (size_t)P, &dout)) return 1;

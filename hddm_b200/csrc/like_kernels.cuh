@@ -54,7 +54,8 @@ __global__ void __launch_bounds__(kBlock, MINB) like_batch_kernel(const double* 
                                                           const double* __restrict__ params, int64_t P, Opts o,
                                                           double w_outlier, int slices, int64_t chunk,
                                                           double* __restrict__ out_sum, int* __restrict__ out_zero,
-                                                          const int64_t* __restrict__ seg,
+                                                          const int64_t* __restrict__ seg, int* __restrict__ done,
+                                                          double* __restrict__ final_out,
                                                           const __grid_constant__ typename Impl::Ctx ctx)
 {
     const int64_t bid = blockIdx.x;
@@ -79,6 +80,7 @@ __global__ void __launch_bounds__(kBlock, MINB) like_batch_kernel(const double* 
         if (threadIdx.x == 0) {
             if (out_zero) { out_sum[bid] = 0.0; out_zero[bid] = 1; }
             else out_sum[bid] = -CUDART_INF;
+            if (out_zero && done) final_out[p] = -CUDART_INF;   // every slice of the set comes through here: no counting
         }
         return;
     }
@@ -175,6 +177,22 @@ __global__ void __launch_bounds__(kBlock, MINB) like_batch_kernel(const double* 
         if (out_zero) {
             out_sum[bid] = tot;
             out_zero[bid] = any_zero;
+            if (done) {
+                // fused finalize: whoever finishes last adds the set's partials up in slice order (same order and
+                // result as finalize_kernel, whatever the arrival order) and leaves the counter at zero for the next launch
+                __threadfence();
+                if (atomicAdd(&done[p], 1) == slices - 1) {
+                    __threadfence();
+                    double sum = 0.0;
+                    int z = 0;
+                    for (int k = 0; k < slices; k++) {
+                        sum += __ldcg(&out_sum[p * slices + k]);
+                        z |= __ldcg(&out_zero[p * slices + k]);
+                    }
+                    final_out[p] = z ? -CUDART_INF : sum;
+                    done[p] = 0;
+                }
+            }
         } else {
             // wfpt.pyx:71-72: the first p == 0 returns -inf (a NaN elsewhere never gets to overrule it)
             out_sum[bid] = any_zero ? -CUDART_INF : tot;

@@ -156,16 +156,30 @@ def wiener_like_batch(x, params, err=1e-4, n_st=2, n_sz=2, use_adaptive=1, simps
 
 
 # ---- src/wfpt.pyx:54-76 --------------------------------------------------------------------------------------------------
+_F64 = np.dtype(np.float64)
+_Prm8 = C.c_double * 8
+
+
 def wiener_like(x, v, sv, a, z, sz, t, st, err, n_st=10, n_sz=10, use_adaptive=1, simps_err=1e-8, p_outlier=0,
                 w_outlier=0.1):
-    x = _buffer(x, "x")
-    prm = np.array([[float(v), float(sv), float(a), float(z), float(sz), float(t), float(st), float(p_outlier)]],
-                   dtype=np.double)
-    res = np.empty(1, dtype=np.double)
-    L = _lib.load()
-    _lib.check(L.wfpt_like_batch_host(_ptr(x), x.shape[0], _ptr(prm), 1, *_opts(err, n_st, n_sz, use_adaptive, simps_err),
-                                      float(w_outlier), _variant, _ptr(res)))
-    return float(res[0])
+    # The call a sampler makes millions of times: keep the Python side to a handful of microseconds.
+    if type(x) is not np.ndarray or x.dtype != _F64 or x.ndim != 1 or not x.flags.c_contiguous:
+        x = _buffer(x, "x")                      # the reference's TypeError / ValueError, or a contiguous copy
+    try:
+        prm = _Prm8(v, sv, a, z, sz, t, st, p_outlier)
+    except TypeError:                            # 0-d arrays and other things float() accepts
+        prm = _Prm8(float(v), float(sv), float(a), float(z), float(sz), float(t), float(st), float(p_outlier))
+    res = C.c_double()
+    fn = _lib.load().wfpt_like_batch_host
+    try:
+        rc = fn(x.ctypes.data, x.shape[0], prm, 1, err, n_st, n_sz, 1 if use_adaptive else 0, simps_err, w_outlier,
+                _variant, C.byref(res))
+    except C.ArgumentError:                      # options given as 0-d arrays etc.
+        rc = fn(x.ctypes.data, x.shape[0], prm, 1, *_opts(err, n_st, n_sz, use_adaptive, simps_err), float(w_outlier),
+                _variant, C.byref(res))
+    if rc:
+        _lib.check(rc)
+    return res.value
 
 
 # ---- src/wfpt.pyx:357-387 ------------------------------------------------------------------------------------------------
