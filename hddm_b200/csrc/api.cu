@@ -361,6 +361,17 @@ int wfpt_like_batch(const double* d_x, int64_t n, const double* d_params, int64_
     a.x = d_x; a.n = n; a.params = d_params; a.P = P; a.o = o; a.w_outlier = w_outlier; a.out = d_out;
     a.stream = (cudaStream_t)stream;
     plan_slices(n, P, &a.slices, &a.chunk);
+    if (P * (int64_t)a.slices * 2 <= (int64_t)sm_count() && n > kBlock) {
+        // a grid that cannot even put one CTA on every SM with two RTs per thread (a single `wiener_like` call): what
+        // matters is the latency of the call, so give every thread one RT and use twice as many CTAs
+        int64_t s = (n + kBlock - 1) / kBlock;
+        if (s * P > (int64_t)sm_count() * 2) s = (int64_t)sm_count() * 2 / P;
+        if (s < 1) s = 1;
+        int64_t c = (n + s - 1) / s;
+        a.slices = (int)((n + c - 1) / c);
+        a.chunk = c;
+        a.one_each = 1;
+    }
     if ((double)P * a.slices > 2.0e9) return fail("P*slices too large for one launch (P=%lld)", (long long)P);
     a.part_sum = nullptr;
     a.part_zero = nullptr;

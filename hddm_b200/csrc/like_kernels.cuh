@@ -55,7 +55,7 @@ __global__ void __launch_bounds__(kBlock, MINB) like_batch_kernel(const double* 
                                                           double w_outlier, int slices, int64_t chunk,
                                                           double* __restrict__ out_sum, int* __restrict__ out_zero,
                                                           const int64_t* __restrict__ seg, int* __restrict__ done,
-                                                          double* __restrict__ final_out,
+                                                          double* __restrict__ final_out, int one_each,
                                                           const __grid_constant__ typename Impl::Ctx ctx)
 {
     const int64_t bid = blockIdx.x;
@@ -106,7 +106,9 @@ __global__ void __launch_bounds__(kBlock, MINB) like_batch_kernel(const double* 
     const double2* x2 = reinterpret_cast<const double2*>(x + b);
     // CTA-uniform trip count (every thread runs the same number of rounds, the last ones possibly empty-handed), so
     // that the parking lot can be drained by the whole CTA between rounds before it overflows.
-    const int64_t rounds = (npair + kBlock - 1) / kBlock + 1;   // + 1: the head / tail elements
+    // one_each (small grids, where latency counts rather than throughput): one RT per thread and round, 8-byte loads
+    const int64_t rounds = one_each ? (end - beg + kBlock - 1) / kBlock
+                                    : (npair + kBlock - 1) / kBlock + 1;   // + 1: the head / tail elements
     double acc_slow = 0.0;
     auto drain = [&](int parked) {
 #pragma unroll 1
@@ -132,7 +134,9 @@ __global__ void __launch_bounds__(kBlock, MINB) like_batch_kernel(const double* 
         double v0 = 0.0, v1 = 0.0;
         int cnt = 0;
         const int64_t i = r * kBlock + threadIdx.x;
-        if (i < npair) {
+        if (one_each) {
+            if (beg + i < end) { v0 = x[beg + i]; cnt = 1; }
+        } else if (i < npair) {
             const double2 xx = __ldg(x2 + i);
             v0 = xx.x;
             v1 = xx.y;
