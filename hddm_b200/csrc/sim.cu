@@ -58,20 +58,24 @@ struct Args {
     int traj_len;
     long long chunk;           // particles per work item
     long long items_per_set;
+    unsigned int key_a[10], key_b[10];   // Philox round keys of `seed`
+    void set_seed(unsigned long long sd)
+    {
+        seed = sd;
+        for (int r = 0; r < 10; r++) {
+            key_a[r] = (unsigned int)sd + (unsigned int)r * 0x9E3779B9u;
+            key_b[r] = (unsigned int)(sd >> 32) + (unsigned int)r * 0xBB67AE85u;
+        }
+    }
 };
 
 // ---- Philox4x32-10 -------------------------------------------------------------------------------------------------------
-// The ten round keys depend on the seed only: the Weyl sequence k + r*W is computed once per thread (RoundKeys), not per block.
+// The ten round keys (the Weyl sequence k + r*W) depend on the seed only.  The host computes them into the kernel
+// arguments (Args::set_seed), i.e. into the constant bank, where the round's XOR reads them as an operand: no
+// instruction and no register is spent on them.
 struct RoundKeys {
-    unsigned int a[10], b[10];
-    __device__ __forceinline__ RoundKeys(unsigned int k0, unsigned int k1)
-    {
-#pragma unroll
-        for (int r = 0; r < 10; r++) {
-            a[r] = k0 + (unsigned int)r * 0x9E3779B9u;
-            b[r] = k1 + (unsigned int)r * 0xBB67AE85u;
-        }
-    }
+    const unsigned int *a, *b;
+    __device__ __forceinline__ RoundKeys(const Args& A) : a(A.key_a), b(A.key_b) {}
 };
 
 __device__ __forceinline__ uint4 philox4x32(unsigned int c0, unsigned int c1, unsigned int c2, unsigned int c3,
@@ -233,7 +237,7 @@ __global__ void __launch_bounds__(kSimBlock) sim_kernel(const Args A)
     __shared__ int s_next;                    // next undistributed particle of the current item
     const int nh = A.hist ? A.nbins * 2 : 0;
     const float sqrt_st = __fmul_rn(sqrtf(A.dt), A.s);
-    const RoundKeys rk((unsigned int)A.seed, (unsigned int)(A.seed >> 32));
+    const RoundKeys rk(A);
     unsigned long long my_steps = 0;
     const long long n_items = (long long)A.n_sets * A.items_per_set;
 
@@ -394,7 +398,7 @@ __global__ void __launch_bounds__(kSimBlock) race_kernel(const Args A)
     __shared__ int s_next;
     const int nh = A.hist ? A.nbins * NP : 0;
     const float sqrt_st = __fmul_rn(sqrtf(A.dt), A.s);
-    const RoundKeys rk((unsigned int)A.seed, (unsigned int)(A.seed >> 32));
+    const RoundKeys rk(A);
     unsigned long long my_steps = 0;
     const long long item = blockIdx.x;
     const int set = (int)(item / A.items_per_set);
@@ -521,7 +525,7 @@ __global__ void __launch_bounds__(kSimBlock) hier_kernel(const Args A)
     __shared__ int s_next;
     const int nh = A.hist ? A.nbins * 4 : 0;
     const float sqrt_st = __fmul_rn(sqrtf(A.dt), A.s);
-    const RoundKeys rk((unsigned int)A.seed, (unsigned int)(A.seed >> 32));
+    const RoundKeys rk(A);
     unsigned long long my_steps = 0;
     const long long item = blockIdx.x;
     const int set = (int)(item / A.items_per_set);
@@ -821,7 +825,7 @@ extern "C" int wfpt_sim_run(int model, const float* d_theta, int n_par, int n_se
     sim::Args A;
     A.theta = d_theta; A.n_par = n_par; A.n_sets = n_sets; A.n_samples = n_samples; A.sample_offset = sample_offset;
     A.out_stride_samples = n_samples;
-    A.dt = delta_t; A.max_t = max_t; A.s = s; A.seed = seed; A.rts = d_rts; A.choices = d_choices;
+    A.dt = delta_t; A.max_t = max_t; A.s = s; A.set_seed(seed); A.rts = d_rts; A.choices = d_choices;
     A.hist = d_hist; A.nbins = d_hist ? nbins : 0;
     A.hist_max_t = (double)hist_max_t;
     A.hist_step = d_hist ? (double)hist_max_t / (double)(nbins - 1) : 1.0;
@@ -939,7 +943,7 @@ extern "C" int wfpt_sim_race_run_host(int lca, int n_particles, int angle, const
     if (h_hist) { SCK(cudaMalloc(&d_hist, sizeof(uint32_t) * hist_n)); SCK(cudaMemset(d_hist, 0, sizeof(uint32_t) * hist_n)); }
     if (h_steps) { SCK(cudaMalloc(&d_steps, sizeof(uint64_t))); SCK(cudaMemset(d_steps, 0, sizeof(uint64_t))); }
     A.theta = d_theta; A.n_par = n_par; A.n_sets = n_sets; A.n_samples = n_samples; A.sample_offset = sample_offset;
-    A.out_stride_samples = n_samples; A.dt = delta_t; A.max_t = max_t; A.s = s; A.seed = seed; A.rts = d_rts; A.choices = d_ch;
+    A.out_stride_samples = n_samples; A.dt = delta_t; A.max_t = max_t; A.s = s; A.set_seed(seed); A.rts = d_rts; A.choices = d_ch;
     A.hist = d_hist; A.nbins = d_hist ? nbins : 0; A.hist_max_t = (double)hist_max_t;
     A.hist_step = d_hist ? (double)hist_max_t / (double)(nbins - 1) : 1.0;
     A.steps = (unsigned long long*)d_steps; A.traj = nullptr; A.traj_len = 0;
@@ -995,7 +999,7 @@ static int run_hier_host(const char* who, int kind, int bound_kind, const float*
     if (h_hist) { SCK(cudaMalloc(&d_hist, sizeof(uint32_t) * hist_n)); SCK(cudaMemset(d_hist, 0, sizeof(uint32_t) * hist_n)); }
     if (h_steps) { SCK(cudaMalloc(&d_steps, sizeof(uint64_t))); SCK(cudaMemset(d_steps, 0, sizeof(uint64_t))); }
     A.theta = d_theta; A.n_par = n_par; A.n_sets = n_sets; A.n_samples = n_samples; A.sample_offset = sample_offset;
-    A.out_stride_samples = n_samples; A.dt = delta_t; A.max_t = max_t; A.s = s; A.seed = seed; A.rts = d_rts; A.choices = d_ch;
+    A.out_stride_samples = n_samples; A.dt = delta_t; A.max_t = max_t; A.s = s; A.set_seed(seed); A.rts = d_rts; A.choices = d_ch;
     A.hist = d_hist; A.nbins = d_hist ? nbins : 0; A.hist_max_t = (double)hist_max_t;
     A.hist_step = d_hist ? (double)hist_max_t / (double)(nbins - 1) : 1.0;
     A.steps = (unsigned long long*)d_steps; A.traj = nullptr; A.traj_len = 0;

@@ -1,18 +1,20 @@
 """Source-line profile of like_batch_kernel<FastImpl>: merges an ncu --set full capture (per-SASS-instruction executed
 counts, `--import-source on`) with nvdisasm line info of the object file the profiled library was linked from.
-Usage: python scripts/line_profile.py <prof.ncu-rep> [evals_per_launch]   (run before rebuilding the library)"""
+Usage: python scripts/line_profile.py <prof.ncu-rep> [units_per_launch] [object-stem] [kernel-substring ...]
+(run before rebuilding the library; defaults: like_fast, "like_batch_kernel" "FastImpl")"""
 import collections, csv, glob, os, re, subprocess, sys, tempfile
 
 rep = sys.argv[1]
 evals = float(sys.argv[2]) if len(sys.argv) > 2 else 4096 * 10000
 root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-obj = os.path.join(root, "hddm_b200", "csrc", "_obj", "like_fast.o")
+obj = os.path.join(root, "hddm_b200", "csrc", "_obj", (sys.argv[3] if len(sys.argv) > 3 else "like_fast") + ".o")
+pats = sys.argv[4:] if len(sys.argv) > 4 else ["like_batch_kernel", "FastImpl"]
 tmp = tempfile.mkdtemp()
 subprocess.run(["cuobjdump", "-xelf", "all", obj], cwd=tmp, check=True, capture_output=True)
 cubin = glob.glob(os.path.join(tmp, "*.cubin"))[0]
 dis = subprocess.run(["nvdisasm", "-g", "-c", cubin], capture_output=True, text=True).stdout.splitlines()
 # locate the batch kernel section
-start = next(i for i, l in enumerate(dis) if l.startswith("//---") and "like_batch_kernel" in l and "FastImpl" in l)
+start = next(i for i, l in enumerate(dis) if l.startswith("//---") and all(p in l for p in pats))
 end = next((i for i in range(start + 1, len(dis)) if dis[i].startswith("//---")), len(dis))
 lines = []  # per instruction: (file, line, outermost inlined-at line)
 cur = ("?", 0)
