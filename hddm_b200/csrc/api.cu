@@ -69,7 +69,7 @@ static int scratch(int slot, size_t bytes, void** out)
 // A `wiener_like` call from a sampler moves a few KB in and 8 bytes out; done with pageable buffers that is three
 // driver-staged copies, each costing more than the kernel.  Small calls pack their inputs into this pinned block (one
 // truly asynchronous copy in) and have the kernel write the results into its mapped head (no copy out).
-constexpr size_t kPinOutBytes = 4096;          // results: up to 512 parameter sets
+constexpr size_t kPinOutBytes = 65536;         // results: up to 8,192 parameter sets
 constexpr size_t kPinMaxIn = (size_t)1 << 20;  // larger inputs amortise the pageable path
 struct Pin { char* h = nullptr; char* d = nullptr; size_t cap = 0; };
 static Pin g_pin[kMaxDev];
@@ -264,6 +264,22 @@ static void plan_slices(int64_t n, int64_t P, int* slices, int64_t* chunk)
     *chunk = c;
 }
 
+// A grid that cannot put two CTAs on every SM with two RTs per thread (a single `wiener_like` call, one sweep over the
+// nodes of a small hierarchical model): what matters is the latency of the call, so give every thread one RT and use
+// more CTAs (up to four per SM).
+static void plan_small_grid(int64_t n, int64_t P, BatchArgs* a)
+{
+    const int64_t sms = sm_count();
+    if (P * (int64_t)a->slices > 2 * sms || n <= kBlock) return;
+    int64_t s = (n + kBlock - 1) / kBlock;
+    if (s * P > 4 * sms) s = 4 * sms / P;
+    if (s < 1) s = 1;
+    const int64_t c = (n + s - 1) / s;
+    a->slices = (int)((n + c - 1) / c);
+    a->chunk = c;
+    a->one_each = 1;
+}
+
 // ---- hooks for sibling translation units ---------------------------------------------------------------------------------
 int api_fail(const char* msg) { return fail("%s", msg); }
 int api_check_opts(double err, int n_st, int n_sz, int use_adaptive, double simps_err, int variant, Opts* o)
@@ -361,17 +377,7 @@ int wfpt_like_batch(const double* d_x, int64_t n, const double* d_params, int64_
     a.x = d_x; a.n = n; a.params = d_params; a.P = P; a.o = o; a.w_outlier = w_outlier; a.out = d_out;
     a.stream = (cudaStream_t)stream;
     plan_slices(n, P, &a.slices, &a.chunk);
-    if (P * (int64_t)a.slices * 2 <= (int64_t)sm_count() && n > kBlock) {
-        // a grid that cannot even put one CTA on every SM with two RTs per thread (a single `wiener_like` call): what
-        // matters is the latency of the call, so give every thread one RT and use twice as many CTAs
-        int64_t s = (n + kBlock - 1) / kBlock;
-        if (s * P > (int64_t)sm_count() * 2) s = (int64_t)sm_count() * 2 / P;
-        if (s < 1) s = 1;
-        int64_t c = (n + s - 1) / s;
-        a.slices = (int)((n + c - 1) / c);
-        a.chunk = c;
-        a.one_each = 1;
-    }
+    plan_small_grid(n, P, &a);
     if ((double)P * a.slices > 2.0e9) return fail("P*slices too large for one launch (P=%lld)", (long long)P);
     a.part_sum = nullptr;
     a.part_zero = nullptr;
@@ -602,22 +608,54 @@ int wfpt_like_segments(const double* d_x, const int64_t* d_seg, int64_t mean_len
     a.stream = (cudaStream_t)stream;
     a.seg = d_seg;
     plan_slices(mean_len, P, &a.slices, &a.chunk);
+    plan_small_grid(mean_len, P, &a);
     a.part_sum = nullptr;
     a.part_zero = nullptr;
     if (a.slices > 1) {
-        void *ps, *pz;
+        void *ps, *pz, *dn;
         if (scratch(kPartSum, sizeof(double) * (size_t)P * a.slices, &ps)) return 1;
         if (scratch(kPartZero, sizeof(int) * (size_t)P * a.slices, &pz)) return 1;
+        if (scratch(kDone, sizeof(int) * (size_t)P, &dn)) return 1;
         a.part_sum = (double*)ps;
         a.part_zero = (int*)pz;
+        a.done = (int*)dn;
     }
     CK(variant == WFPT_VARIANT_FAITHFUL ? launch_like_batch_faithful(a) : launch_like_batch_fast(a));
     count_launch(1);
-    if (a.slices > 1) {
-        finalize_kernel<<<(unsigned)((P + 127) / 128), 128, 0, a.stream>>>(a.part_sum, a.part_zero, P, a.slices, 1, d_out);
-        CK(cudaGetLastError());
-        count_launch(1);
+    return 0;
+}
+
+int wfpt_like_segments_resident(const double* d_x, const int64_t* d_seg, int64_t mean_len, const double* h_params,
+                                int64_t P, double err, int n_st, int n_sz, int use_adaptive, double simps_err,
+                                double w_outlier, int variant, double* h_out)
+{
+    if (P < 0) return fail("negative size");
+    if (P == 0) return 0;
+    if (!h_params || !h_out) return fail("null pointer argument");
+    const size_t pbytes = sizeof(double) * 8 * (size_t)P, obytes = sizeof(double) * (size_t)P;
+    void* dp;
+    if (scratch(kStageParams, pbytes, &dp)) return 1;
+    if (obytes <= kPinOutBytes && pbytes <= kPinMaxIn) {
+        // parameters through the pinned block (one asynchronous copy), results written straight into its mapped head
+        char *ph, *pd;
+        if (pinned(pbytes, &ph, &pd)) return 1;
+        memcpy(ph + kPinOutBytes, h_params, pbytes);
+        CK(cudaMemcpyAsync(dp, ph + kPinOutBytes, pbytes, cudaMemcpyHostToDevice, 0));
+        if (wfpt_like_segments(d_x, d_seg, mean_len, (const double*)dp, P, err, n_st, n_sz, use_adaptive, simps_err,
+                               w_outlier, variant, (double*)pd, nullptr))
+            return 1;
+        CK(cudaStreamSynchronize(0));
+        memcpy(h_out, ph, obytes);
+        return 0;
     }
+    void* dout;
+    if (scratch(kStageOut, obytes, &dout)) return 1;
+    CK(cudaMemcpyAsync(dp, h_params, pbytes, cudaMemcpyHostToDevice, 0));
+    if (wfpt_like_segments(d_x, d_seg, mean_len, (const double*)dp, P, err, n_st, n_sz, use_adaptive, simps_err, w_outlier,
+                           variant, (double*)dout, nullptr))
+        return 1;
+    CK(cudaMemcpyAsync(h_out, dout, obytes, cudaMemcpyDeviceToHost, 0));
+    CK(cudaStreamSynchronize(0));
     return 0;
 }
 

@@ -67,7 +67,8 @@ __global__ void __launch_bounds__(kBlock, MINB) like_batch_kernel(const double* 
         const int64_t s0 = seg[2 * p];
         x += s0;
         n = seg[2 * p + 1] - s0;
-        chunk = (((n + slices - 1) / slices) + 1) & ~(int64_t)1;
+        chunk = (n + slices - 1) / slices;
+        if (!one_each) chunk = (chunk + 1) & ~(int64_t)1;   // even, so that 16-byte loads stay aligned across slices
         if (chunk < 2) chunk = 2;
     }
 

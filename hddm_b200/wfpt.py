@@ -331,6 +331,9 @@ class ResidentData:
         self.starts = starts[:-1].copy()
         self.x = torch.from_numpy(packed).to(self.device)
         self._seg_all = self._segments(np.arange(len(arrs)))
+        self._dseg_all = torch.from_numpy(self._seg_all.reshape(-1).copy()).to(self.device)   # (empty for no arrays)
+        self._x_ptr, self._dseg_ptr = self.x.data_ptr(), self._dseg_all.data_ptr()
+        self._dev_index = self.device.index if self.device.index is not None else torch.cuda.current_device()
         self.mean_len = int(max(1, self.lengths.mean())) if len(arrs) else 1
 
     def _segments(self, nodes):
@@ -341,26 +344,43 @@ class ResidentData:
              variant=None):
         torch = self._torch
         var = _variant if variant is None else variant
-        seg = self._seg_all if nodes is None else self._segments(np.asarray(nodes, dtype=np.int64))
-        P = seg.shape[0]
-        if isinstance(params, np.ndarray):
-            ps = torch.from_numpy(np.ascontiguousarray(params, dtype=np.double)).to(self.device)
-            as_numpy = True
+        if nodes is None:
+            P, dseg_ptr, keep = self._seg_all.shape[0], self._dseg_ptr, None
         else:
-            ps, as_numpy = params.contiguous(), False
+            seg = self._segments(np.asarray(nodes, dtype=np.int64))
+            keep = torch.from_numpy(seg.reshape(-1)).to(self.device)
+            P, dseg_ptr = seg.shape[0], keep.data_ptr()
+        L = _lib.load()
+        o = _opts(err, n_st, n_sz, use_adaptive, simps_err)
+        # (torch's device context manager and stream lookup cost tens of microseconds: only used when actually needed)
+        same_dev = torch.cuda.current_device() == self._dev_index
+        if isinstance(params, np.ndarray):
+            # host parameters in, host log-likelihoods out: the library stages both through pinned memory
+            ps = params if (params.dtype == _F64 and params.flags.c_contiguous) else np.ascontiguousarray(params, dtype=np.double)
+            if ps.shape != (P, 8):
+                raise ValueError(f"params must have shape ({P}, 8)")
+            res = np.empty(P, dtype=np.double)
+            if P:
+                args = (self._x_ptr, dseg_ptr, self.mean_len, ps.ctypes.data, P, *o, float(w_outlier), var, res.ctypes.data)
+                if same_dev:
+                    rc = L.wfpt_like_segments_resident(*args)
+                else:
+                    with torch.cuda.device(self.device):
+                        rc = L.wfpt_like_segments_resident(*args)
+                if rc:
+                    _lib.check(rc)
+            return res
+        ps = params.contiguous()
         if ps.shape != (P, 8):
             raise ValueError(f"params must have shape ({P}, 8)")
         out = torch.empty(P, dtype=torch.float64, device=self.device)
         if P == 0:
-            return out.cpu().numpy() if as_numpy else out
-        dseg = torch.from_numpy(seg.reshape(-1)).to(self.device)
-        L = _lib.load()
+            return out
         with torch.cuda.device(self.device):
             s = torch.cuda.current_stream().cuda_stream
-            _lib.check(L.wfpt_like_segments(self.x.data_ptr(), dseg.data_ptr(), self.mean_len, ps.data_ptr(), P,
-                                            *_opts(err, n_st, n_sz, use_adaptive, simps_err), float(w_outlier), var,
-                                            out.data_ptr(), s))
-        return out.cpu().numpy() if as_numpy else out
+            _lib.check(L.wfpt_like_segments(self._x_ptr, dseg_ptr, self.mean_len, ps.data_ptr(), P, *o,
+                                            float(w_outlier), var, out.data_ptr(), s))
+        return out
 
 
 def wiener_like_segments(arrays, params, **kw):

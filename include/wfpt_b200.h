@@ -124,6 +124,13 @@ int wfpt_like_segments_host(const double* h_x, const int64_t* h_seg, const doubl
                             int n_st, int n_sz, int use_adaptive, double simps_err, double w_outlier, int variant,
                             double* h_out);
 
+/* The sampler's form of the above: RTs and segments already resident on the device (uploaded once before sampling),
+ * parameters in a host buffer, log-likelihoods back into a host buffer -- one sweep over the nodes of a hierarchical
+ * model (hddm/models/hddm_info.py:539-558 evaluates them one wiener_like at a time).  Synchronous. */
+int wfpt_like_segments_resident(const double* d_x, const int64_t* d_seg, int64_t mean_len, const double* h_params,
+                                int64_t P, double err, int n_st, int n_sz, int use_adaptive, double simps_err,
+                                double w_outlier, int variant, double* h_out);
+
 /* Replaces src/wfpt.pyx:551-580 (wiener_like_contaminant): trials with cont_x == 0 enter the diffusion likelihood (no
  * outlier mix, -inf on the first zero density), the others contribute n_cont * log(0.5 / (t_max - t_min)). */
 int wfpt_like_contaminant_host(const double* h_x, const int32_t* h_cont, int64_t n, double v, double sv, double a, double z,

@@ -234,3 +234,65 @@ def test_full_size_properties(golden, wfpt_gpu):
     assert rel_err(a + b, full) < 1e-12
     faithful = wfpt_gpu.wiener_like_batch(x2, prm, variant=1, **kw)
     assert rel_err(full, faithful) <= TOL
+
+
+def test_refinement_paths_vs_oracle(oracle, wfpt_gpu):
+    """Adaptive recursion below the first level (config 4 over the whole param_bounds box: RTs inside the t +- st/2
+    window switch the integrand on inside the interval, which is what makes the reference refine): per-trial densities
+    and summed log-likelihoods against the oracle, for the HDDM budget (2, 2) and for deeper / asymmetric budgets."""
+    rng = np.random.default_rng(33)
+    P, n = 96, 700
+    prm = np.stack([rng.uniform(-5, 5, P), rng.uniform(0, 4, P), rng.uniform(0.1, 5, P), rng.uniform(0.3, 0.7, P),
+                    rng.uniform(0, 0.25, P), rng.uniform(0.25, 2.25, P), rng.uniform(0, 0.25, P), np.full(P, 0.05)], axis=1)
+    prm[::7, 4] = 0.0    # t-only integration
+    prm[3::7, 6] = 0.0   # z-only integration
+    x = np.where(rng.random(n) < 0.7, 1.0, -1.0) * rng.uniform(0.3, 3.0, n)
+    for n_st, n_sz, se in ((2, 2, 1e-3), (2, 2, 1e-6), (2, 3, 1e-4), (3, 2, 1e-4)):
+        want = oracle.wiener_like_batch(x, prm, 1e-4, n_st, n_sz, 1, se, 0.1)
+        got = wfpt_gpu.wiener_like_batch(x, prm, 1e-4, n_st, n_sz, 1, se, 0.1, variant=wfpt_gpu.FAST)
+        assert np.array_equal(np.isfinite(got), np.isfinite(want)), (n_st, n_sz, se)
+        ok = np.isfinite(want)
+        assert rel_err(got[ok], want[ok]) < TOL, (n_st, n_sz, se)
+    # per-trial values for a few sets (a wrong node anywhere shows up undiluted)
+    refined = 0
+    for row in prm[:12]:
+        oracle.nodes_reset()
+        want = oracle.pdf_array(x, *row[:7], 1e-4, 0, 2, 2, 1, 1e-3, 0.0, 0.0)
+        first_level = (5 if row[4] >= 1e-3 else 1) * (5 if row[6] >= 1e-3 else 1)
+        refined += oracle.nodes_get() > first_level * int(np.sum(np.abs(x) - (row[5] - row[6] / 2) >= 0))
+        got = wfpt_gpu.pdf_array(x, *row[:7], 1e-4, 0, 2, 2, 1, 1e-3, 0.0, 0.0)
+        assert np.array_equal(got == 0, want == 0)
+        nz = np.abs(want) > 1e-290      # (subnormal results carry only a few digits in either implementation)
+        assert np.max(np.abs(got[nz] - want[nz]) / np.abs(want[nz])) < 1e-9
+        assert np.all(np.abs(got[~nz] - want[~nz]) < 1e-290)
+    assert refined >= 6   # the case really exercises the levels below the first
+
+
+@pytest.mark.parametrize("n", [1, 2, 127, 128, 129, 255, 256, 257, 1000, 4099, 20001])
+def test_single_call_sizes(oracle, wfpt_gpu, n, variant):
+    """One wiener_like call at sizes around the launch-geometry switches (one RT per thread for small grids, pairs
+    otherwise; pinned staging), odd lengths and unaligned views included."""
+    rng = np.random.default_rng(n)
+    buf = np.where(rng.random(n + 1) < 0.8, 1.0, -1.0) * rng.uniform(0.35, 4.0, n + 1)
+    for x in (np.ascontiguousarray(buf[:n]), buf[1:]):      # the second view starts 8 bytes off a 16-byte boundary
+        for args, kw in (((1.0, 0.0, 2.0, 0.5, 0.0, 0.3, 0.0, 1e-4), {}),
+                         ((0.7, 1.1, 1.8, 0.45, 0.2, 0.3, 0.1, 1e-4),
+                          dict(n_st=2, n_sz=2, use_adaptive=1, simps_err=1e-3, p_outlier=0.05, w_outlier=0.1)),
+                         ((0.7, 1.1, 1.8, 0.45, 0.2, 0.3, 0.1, 1e-4), dict(n_st=2, n_sz=2, use_adaptive=0, simps_err=1e-3))):
+            want = oracle.wiener_like(x, *args, **kw)
+            got = wfpt_gpu.wiener_like(x, *args, **kw)
+            assert abs(got - want) <= TOL * abs(want), (n, args)
+
+
+def test_batch_host_sizes_through_both_staging_paths(oracle, wfpt_gpu):
+    """P on both sides of the pinned-staging limits (results block 8,192 sets, input block 1 MiB)."""
+    rng = np.random.default_rng(9)
+    x = np.where(rng.random(64) < 0.8, 1.0, -1.0) * rng.uniform(0.4, 3.0, 64)
+    for P in (1, 511, 513, 8192, 8193, 20000):
+        prm = np.stack([rng.uniform(-2, 2, P), rng.uniform(0, 2, P), rng.uniform(1, 3, P), rng.uniform(0.3, 0.7, P),
+                        rng.uniform(0, 0.2, P), rng.uniform(0.1, 0.3, P), rng.uniform(0, 0.2, P), np.full(P, 0.05)], axis=1)
+        got = wfpt_gpu.wiener_like_batch(x, prm, 1e-4, 2, 2, 1, 1e-3, 0.1)
+        idx = rng.choice(P, size=min(P, 40), replace=False)
+        want = oracle.wiener_like_batch(x, prm[idx], 1e-4, 2, 2, 1, 1e-3, 0.1)
+        assert rel_err(got[idx], want) < TOL, P
+        assert np.all(np.isfinite(got))
