@@ -28,6 +28,8 @@ struct FaithfulImpl {
         return density<true>(x, s, c, &d);
     }
     __device__ static __forceinline__ bool whole_set_generic(const Set&) { return false; }
+    __device__ static __forceinline__ bool coop_applies(const Set&, int) { return false; }
+    __device__ static __forceinline__ double density_coop(double, const Set&) { return 0.0; }
     static constexpr bool kParks = false;
     static constexpr int kParkCapacity = 0;
     __device__ static __forceinline__ bool may_park(const Set&) { return false; }

@@ -22,6 +22,16 @@ struct FastImpl {
     }
     // parameter sets without a table (err / layout not covered): the kernels route every trial to density_generic
     __device__ static __forceinline__ bool whole_set_generic(const Set& s) { return s.mode == fast::kModeGeneric; }
+    // Few parked trials: one warp per trial instead of one thread per trial (see fast::refine_coop).  Every thread of
+    // the CTA calls it; returns the density of parked trial q to every lane of the warp that took it.
+    __device__ static __forceinline__ bool coop_applies(const Set& s, int parked)
+    {
+        return parked <= 32 && s.mode == fast::kModeAdaptive && s.kind != 4 && s.tab->depth_t == 2;
+    }
+    __device__ static __forceinline__ double density_coop(double x, const Set& s)
+    {
+        return fast::refine_coop(x, s.tab, s.kind, s.kl_max);
+    }
     static constexpr bool kParks = true;
     static constexpr int kParkCapacity = fast::kQueue;
     static_assert(fast::kQueue > kParkCheck * 2 * kBlock, "parking lot smaller than what can arrive between two checks");

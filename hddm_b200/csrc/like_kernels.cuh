@@ -112,6 +112,18 @@ __global__ void __launch_bounds__(kBlock, MINB) like_batch_kernel(const double* 
                                     : (npair + kBlock - 1) / kBlock + 1;   // + 1: the head / tail elements
     double acc_slow = 0.0;
     auto drain = [&](int parked) {
+        if (Impl::coop_applies(set, parked)) {   // uniform over the CTA
+            // a handful of parked trials: one warp each, the warp's lanes sharing the trial's quadrature nodes
+#pragma unroll 1
+            for (int q = threadIdx.x >> 5; q < parked; q += kBlock / 32) {
+                const double p0 = mix_outlier(Impl::density_coop(Impl::parked(set, q), set), omp, wp);
+                if ((threadIdx.x & 31) == 0) {
+                    zero |= (p0 == 0);
+                    acc_slow += log(p0);
+                }
+            }
+            return;
+        }
 #pragma unroll 1
         for (int q = threadIdx.x; q < parked; q += kBlock) {
             const double p0 = mix_outlier(Impl::density_generic(Impl::parked(set, q), set, ctx), omp, wp);

@@ -72,6 +72,9 @@ struct Tables {
     int npieces;              // thresholds in the series-term table
     double simps_err;
     double queue[kQueue];
+    double coop_g[4][18];     // warp-cooperative refinement: node values and flags of the trial each warp works on
+    double coop_z[4][18];     // ... and of the z-integral being refined
+    int coop_f[4][18];
 };
 
 // Per-thread (register) view of the parameter set; everything bulky lives in Tables.
@@ -801,12 +804,11 @@ __device__ __forceinline__ double refine_t_depth2(double ax, int sign, Set& s, c
     return half_ret[0] + half_ret[1];
 }
 
-static __device__ __noinline__ double adaptive_refine(double x, const Tables* Tp, int kind, int kl_max)
+// Per-thread view of the staged parameter set rebuilt from the shared tables (the slow paths keep their own copy so that
+// the caller's stays in registers).
+__device__ __forceinline__ void rebuild_set(Set& s, const Tables* Tp, int kind, int kl_max)
 {
-    const Tables& T = *Tp;
-    if (kind == 4) return adaptive_full_pdf(x, Tp);   // z-only integration: nothing staged helps below the first level
-    const Params& p = T.prm;
-    Set s;                                            // private copy: the caller's stays in registers
+    const Params& p = Tp->prm;
     s.mode = kModeAdaptive;
     s.nz = (kind == 3) ? 4 : 0;
     s.nt = 4;
@@ -817,12 +819,155 @@ static __device__ __noinline__ double adaptive_refine(double x, const Tables* Tp
     s.piece_desc = 0;
     s.lo_b = 1;
     s.hi_b = 0;
-    s.tlo = T.tn[0];
+    s.tlo = Tp->tn[0];
     s.v2 = p.v * p.v;
     s.sv2 = p.sv * p.sv;
     s.a2 = p.a * p.a;
     s.inv_a2 = 1.0 / s.a2;
     s.tab = Tp;
+}
+
+// The reference's adaptive Simpson walk for a budget of 2 on values that are already there: g[j] = f(pos[j]) / ZT on the
+// 17 dyadic points of the interval (0, 4, .. 16 first level; 2, 6, .. second; odd third).  Reads only the points the
+// walk visits and reports them in *used (bit j), so that callers may fill the others speculatively or not at all.
+__device__ __forceinline__ double walk_depth2(const double* g, const double* pos, double width, double simps_err,
+                                              int budget, unsigned* used)
+{
+    double result;
+    *used = 0x11111u;
+    if (adaptive_level1(g[0], g[4], g[8], g[12], g[16], width, simps_err, budget, &result)) return result;
+    *used |= 0x4444u;
+    const double H = pos[16] - pos[0], h = pos[8] - pos[0], h2 = pos[16] - pos[8];
+    const double S_l = (H / 12) * (g[0] + 4 * g[4] + g[8]);    // Sleft / Sright of the first level
+    const double S_r = (H / 12) * (g[8] + 4 * g[12] + g[16]);
+    const double part0 = (h / 12) * (g[0] + 4 * g[2] + g[4]);
+    const double part1 = (h / 12) * (g[4] + 4 * g[6] + g[8]);
+    const double part2 = (h2 / 12) * (g[8] + 4 * g[10] + g[12]);
+    const double part3 = (h2 / 12) * (g[12] + 4 * g[14] + g[16]);
+    const double S2l = part0 + part1, S2r = part2 + part3;
+    const double e2 = 15 * (simps_err / 2);
+    double ret0 = S2l + (S2l - S_l) / 15, ret1 = S2r + (S2r - S_r) / 15;
+    auto quarter = [&](int j0, double parent) {                // budget spent: accepted whatever the difference
+        const double hq = pos[j0 + 4] - pos[j0];
+        const double Sl = (hq / 12) * (g[j0] + 4 * g[j0 + 1] + g[j0 + 2]);
+        const double Sr = (hq / 12) * (g[j0 + 2] + 4 * g[j0 + 3] + g[j0 + 4]);
+        const double S2 = Sl + Sr;
+        return S2 + (S2 - parent) / 15;
+    };
+    if (!(fabs(S2l - S_l) <= e2)) {
+        *used |= 0xaau;
+        const double q0 = quarter(0, part0);
+        ret0 = q0 + quarter(4, part1);
+    }
+    if (!(fabs(S2r - S_r) <= e2)) {
+        *used |= 0xaa00u;
+        const double q0 = quarter(8, part2);
+        ret1 = q0 + quarter(12, part3);
+    }
+    return ret0 + ret1;
+}
+
+__device__ __forceinline__ void dyadic17(double* pos, double p0, double p4, double p8, double p12, double p16)
+{
+    pos[0] = p0; pos[4] = p4; pos[8] = p8; pos[12] = p12; pos[16] = p16;
+#pragma unroll
+    for (int j = 2; j < 16; j += 4) pos[j] = (pos[j - 2] + pos[j + 2]) / 2.;
+#pragma unroll
+    for (int j = 1; j < 16; j += 2) pos[j] = (pos[j - 1] + pos[j + 1]) / 2.;
+}
+
+// The same walk, one WARP per trial: lane j < 17 evaluates t-node j (all 17 candidates at once, whether or not the
+// walk will ask for them), the decisions are then taken on the shared values.  A thread working through a parked trial
+// alone needs 9 to 17 node evaluations one after the other (tens of microseconds); this takes the time of one, which is
+// what counts when a CTA has only a handful of parked trials (one sweep over the nodes of a hierarchical model, a single
+// wiener_like call).  A t-node whose z-integral wants refinement gets the same treatment along z, the whole warp
+// working on that node.  Nodes the walk does not visit contribute neither values nor NaN flags.  Every lane of the
+// warp must call it with the same x; the result is valid in every lane.
+static __device__ __noinline__ double refine_coop(double x, const Tables* Tp, int kind, int kl_max)
+{
+    Tables& T = *const_cast<Tables*>(Tp);
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    double* g = T.coop_g[w];
+    double* gz = T.coop_z[w];
+    int* fl = T.coop_f[w];            // bit 0: inner integral wants refinement, bit 1: negative series seen
+    const double ax = fabs(x);
+    const int sign = x > 0;
+    Set s;
+    rebuild_set(s, Tp, kind, kl_max);
+    const Params& p = T.prm;
+    AdhocCtx c;
+    c.v = sign ? -p.v : p.v; c.v2 = s.v2; c.sv2 = s.sv2; c.a = p.a; c.a2 = s.a2; c.inv_a2 = s.inv_a2;
+    c.asv2 = c.a2 * c.sv2; c.sv_nonzero = s.sv_nonzero; c.T = Tp;
+    double t[17];
+    dyadic17(t, T.tn[0], T.tn[1], T.tn[2], T.tn[3], T.tn[4]);
+    double tj = t[0];
+#pragma unroll
+    for (int j = 1; j < 17; j++) tj = (lane == j) ? t[j] : tj;
+    int my = 0;
+    if (lane < 17) {
+        TNode tn;
+        make_tnode(tn, ax - tj, s);
+        bool inner_ok = true;
+        int neg = 0;
+        const double val = (kind == 3) ? inner_t<5>(tn, s, sign, &inner_ok, neg) : inner_t<1>(tn, s, sign, &inner_ok, neg);
+        my = (inner_ok ? 0 : 1) | ((s.sv_nonzero && neg < 0) ? 2 : 0);
+        g[lane] = val * T.inv_wt;
+        fl[lane] = my;
+    }
+    // z-integrals that want more than their first level (integrate.pxi:114-141), one t-node at a time, all lanes on it
+    auto redo = [&](unsigned want) {
+        unsigned todo = __ballot_sync(0xffffffffu, (lane < 17) && (my & 1) && ((want >> lane) & 1u));
+        if (!todo) return;
+        double zp[17];
+        const NodeTab* Z = T.z[sign];
+        dyadic17(zp, Z[0].u[1], Z[1].u[1], Z[2].u[1], Z[3].u[1], Z[4].u[1]);
+        double zj = zp[0];
+#pragma unroll
+        for (int j = 1; j < 17; j++) zj = (lane == j) ? zp[j] : zj;
+        while (todo) {
+            const int src = __ffs(todo) - 1;
+            todo &= todo - 1;
+            const double t_src = __shfl_sync(0xffffffffu, tj, src);
+            if (T.depth_z == 2) {
+                if (lane < 17) gz[lane] = pdf_sv_adhoc(c, ax - t_src, zj) / T.wz[sign];
+                __syncwarp();
+                unsigned used;
+                const double v = walk_depth2(gz, zp, T.wz[sign], T.simps_err, T.depth_z, &used);
+                __syncwarp();
+                if (lane == src) { g[src] = v * T.inv_wt; fl[src] = 0; my = 0; }
+            } else if (lane == src) {   // other budgets: this lane alone, node by node
+                const AdhocAxis az{c, ax, tj, true};
+                g[src] = adhoc_axis_integral(az, zp[0], zp[16], T.wz[sign], T.simps_err, T.depth_z) * T.inv_wt;
+                fl[src] = 0;
+                my = 0;
+            }
+        }
+    };
+    redo(0x15555u);                    // levels 1 and 2 (even nodes) are visited whenever the first level fails
+    __syncwarp();
+    unsigned used;
+    double result = walk_depth2(g, t, T.wt, T.simps_err, T.depth_t, &used);
+    if (__any_sync(0xffffffffu, (lane < 17) && (my & 1) && ((used >> lane) & 1u))) {
+        __syncwarp();
+        redo(used);                    // third-level nodes of the halves that asked for them
+        __syncwarp();
+        result = walk_depth2(g, t, T.wt, T.simps_err, T.depth_t, &used);
+    }
+    int bad = 0;
+#pragma unroll
+    for (int j = 0; j < 17; j++) bad |= ((used >> j) & 1u) ? fl[j] : 0;
+    if (bad & 2) result = CUDART_NAN;
+    __syncwarp();   // g / fl are reused for the warp's next trial
+    return result;
+}
+
+static __device__ __noinline__ double adaptive_refine(double x, const Tables* Tp, int kind, int kl_max)
+{
+    const Tables& T = *Tp;
+    if (kind == 4) return adaptive_full_pdf(x, Tp);   // z-only integration: nothing staged helps below the first level
+    const Params& p = T.prm;
+    Set s;                                            // private copy: the caller's stays in registers
+    rebuild_set(s, Tp, kind, kl_max);
     int neg = 0;
     const double ax = fabs(x);
     const int sign = x > 0;
