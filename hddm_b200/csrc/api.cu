@@ -264,15 +264,15 @@ static void plan_slices(int64_t n, int64_t P, int* slices, int64_t* chunk)
     *chunk = c;
 }
 
-// A grid that cannot put two CTAs on every SM with two RTs per thread (a single `wiener_like` call, one sweep over the
-// nodes of a small hierarchical model): what matters is the latency of the call, so give every thread one RT and use
-// more CTAs (up to four per SM).
+// A grid of at most a couple of waves with two RTs per thread (a single `wiener_like` call, one sweep over the nodes
+// of a hierarchical model): what matters is the latency of the call, so give every thread one RT and use more CTAs
+// (up to sixteen per SM, four waves), the slices of a set interleaved.
 static void plan_small_grid(int64_t n, int64_t P, BatchArgs* a)
 {
     const int64_t sms = sm_count();
-    if (P * (int64_t)a->slices > 2 * sms || n <= kBlock) return;
+    if (n <= 0 || P * (int64_t)a->slices > 8 * sms) return;
     int64_t s = (n + kBlock - 1) / kBlock;
-    if (s * P > 4 * sms) s = 4 * sms / P;
+    if (s * P > 16 * sms) s = 16 * sms / P;
     if (s < 1) s = 1;
     const int64_t c = (n + s - 1) / s;
     a->slices = (int)((n + c - 1) / c);

@@ -108,7 +108,10 @@ __global__ void __launch_bounds__(kBlock, MINB) like_batch_kernel(const double* 
     // CTA-uniform trip count (every thread runs the same number of rounds, the last ones possibly empty-handed), so
     // that the parking lot can be drained by the whole CTA between rounds before it overflows.
     // one_each (small grids, where latency counts rather than throughput): one RT per thread and round, 8-byte loads
-    const int64_t rounds = one_each ? (end - beg + kBlock - 1) / kBlock
+    // In that mode the slices of a set interleave (slice s takes trials s, s + slices, ...): trials that need refinement
+    // are neighbours in the |rt|-sorted array, and this spreads them over all the CTAs of the set.
+    const int64_t mine = (n > s) ? (n - s + slices - 1) / slices : 0;
+    const int64_t rounds = one_each ? (mine + kBlock - 1) / kBlock
                                     : (npair + kBlock - 1) / kBlock + 1;   // + 1: the head / tail elements
     double acc_slow = 0.0;
     auto drain = [&](int parked) {
@@ -148,7 +151,7 @@ __global__ void __launch_bounds__(kBlock, MINB) like_batch_kernel(const double* 
         int cnt = 0;
         const int64_t i = r * kBlock + threadIdx.x;
         if (one_each) {
-            if (beg + i < end) { v0 = x[beg + i]; cnt = 1; }
+            if (i < mine) { v0 = x[i * slices + s]; cnt = 1; }
         } else if (i < npair) {
             const double2 xx = __ldg(x2 + i);
             v0 = xx.x;
