@@ -71,6 +71,7 @@ static int scratch(int slot, size_t bytes, void** out)
 // truly asynchronous copy in) and have the kernel write the results into its mapped head (no copy out).
 constexpr size_t kPinOutBytes = 65536;         // results: up to 8,192 parameter sets
 constexpr size_t kPinMaxIn = (size_t)1 << 20;  // larger inputs amortise the pageable path
+constexpr size_t kZeroCopyMax = (size_t)1 << 17;  // inputs the kernel reads directly from the mapped block (no copy in)
 struct Pin { char* h = nullptr; char* d = nullptr; size_t cap = 0; };
 static Pin g_pin[kMaxDev];
 
@@ -410,9 +411,11 @@ int wfpt_like_batch_host(const double* h_x, int64_t n, const double* h_params, i
         if (scratch(kStageX, in_bytes, &dx)) return 1;
         memcpy(ph + kPinOutBytes, h_params, sizeof(double) * 8 * (size_t)P);
         if (n > 0) memcpy(ph + kPinOutBytes + sizeof(double) * 8 * (size_t)P, h_x, sizeof(double) * (size_t)n);
-        CK(cudaMemcpyAsync(dx, ph + kPinOutBytes, in_bytes, cudaMemcpyHostToDevice, 0));
-        if (wfpt_like_batch((const double*)dx + 8 * P, n, (const double*)dx, P, err, n_st, n_sz, use_adaptive, simps_err,
-                            w_outlier, variant, (double*)pd, nullptr))
+        const double* in_dev = (const double*)dx;
+        CK(cudaMemcpyAsync(dx, ph + kPinOutBytes, in_bytes, cudaMemcpyHostToDevice, 0));   // (reading the RTs through the
+        // mapped block instead was measured slower: every thread then waits on the bus before its first trial)
+        if (wfpt_like_batch(in_dev + 8 * P, n, in_dev, P, err, n_st, n_sz, use_adaptive, simps_err, w_outlier, variant,
+                            (double*)pd, nullptr))
             return 1;
         CK(cudaStreamSynchronize(0));
         memcpy(h_out, ph, sizeof(double) * (size_t)P);
@@ -640,9 +643,14 @@ int wfpt_like_segments_resident(const double* d_x, const int64_t* d_seg, int64_t
         char *ph, *pd;
         if (pinned(pbytes, &ph, &pd)) return 1;
         memcpy(ph + kPinOutBytes, h_params, pbytes);
-        CK(cudaMemcpyAsync(dp, ph + kPinOutBytes, pbytes, cudaMemcpyHostToDevice, 0));
-        if (wfpt_like_segments(d_x, d_seg, mean_len, (const double*)dp, P, err, n_st, n_sz, use_adaptive, simps_err,
-                               w_outlier, variant, (double*)pd, nullptr))
+        const double* params_dev = (const double*)dp;
+        if (pbytes <= kZeroCopyMax) {
+            params_dev = (const double*)(pd + kPinOutBytes);   // each CTA reads its 64-byte row straight from the mapped block
+        } else {
+            CK(cudaMemcpyAsync(dp, ph + kPinOutBytes, pbytes, cudaMemcpyHostToDevice, 0));
+        }
+        if (wfpt_like_segments(d_x, d_seg, mean_len, params_dev, P, err, n_st, n_sz, use_adaptive, simps_err, w_outlier,
+                               variant, (double*)pd, nullptr))
             return 1;
         CK(cudaStreamSynchronize(0));
         memcpy(h_out, ph, obytes);
