@@ -518,6 +518,33 @@ int wfpt_like_multi_host(const double* h_x, int64_t n, const double* const h_per
     if (!h_out || !scalars || (n > 0 && !h_x)) return fail("null pointer argument");
     void *dx, *dout;
     const size_t bytes = sizeof(double) * (size_t)(n > 0 ? n : 1);
+    int n_arrays = 1;
+    for (int k = 0; k < 7; k++) n_arrays += (h_per_trial && h_per_trial[k]) ? 1 : 0;
+    if (n > 0 && bytes * (size_t)n_arrays <= kPinMaxIn) {
+        // small call (a regression model's likelihood node): x and the per-trial parameter columns packed into the
+        // pinned block, one copy in, the result written into its mapped head
+        char *ph, *pd;
+        if (pinned(bytes * (size_t)n_arrays, &ph, &pd)) return 1;
+        if (scratch(kStageX, bytes * (size_t)n_arrays, &dx)) return 1;
+        const double* dcol[7];
+        memcpy(ph + kPinOutBytes, h_x, bytes);
+        int slot = 1;
+        for (int k = 0; k < 7; k++) {
+            dcol[k] = nullptr;
+            if (h_per_trial && h_per_trial[k]) {
+                memcpy(ph + kPinOutBytes + bytes * (size_t)slot, h_per_trial[k], bytes);
+                dcol[k] = (const double*)dx + (size_t)n * (size_t)slot;
+                slot++;
+            }
+        }
+        CK(cudaMemcpyAsync(dx, ph + kPinOutBytes, bytes * (size_t)n_arrays, cudaMemcpyHostToDevice, 0));
+        if (wfpt_like_multi((const double*)dx, n, dcol, scalars, err, n_st, n_sz, use_adaptive, simps_err, p_outlier,
+                            w_outlier, variant, (double*)pd, nullptr))
+            return 1;
+        CK(cudaStreamSynchronize(0));
+        memcpy(h_out, ph, sizeof(double));
+        return 0;
+    }
     if (scratch(kStageX, bytes, &dx)) return 1;
     if (scratch(kStageOut, sizeof(double), &dout)) return 1;
     if (n > 0) CK(cudaMemcpyAsync(dx, h_x, sizeof(double) * (size_t)n, cudaMemcpyHostToDevice, 0));

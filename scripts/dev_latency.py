@@ -25,3 +25,5 @@ px, pp, pr = x1.ctypes.data, prm.ctypes.data, res.ctypes.data
 print("C call alone, cfg1           %.1f us" % per_call(lambda: L.wfpt_like_batch_host(px, 1000, pp, 1, 1e-4, 10, 10, 1, 1e-8, 0.1, 0, pr)))
 print("pdf_array 1000               %.1f us" % per_call(lambda: wfpt.pdf_array(x1, 1, 0, 2, 0.5, 0, 0.3, 0, 1e-4)))
 print(wfpt.wiener_like(x1, 1, 0, 2, 0.5, 0, 0.3, 0, 1e-4), float(g["cfg1"]) if "cfg1" in g else "")
+vv = np.linspace(0.5, 1.5, 1000); tt = np.full(1000, 0.3)
+print("wiener_like_multi 1000 (v, t) %.1f us" % per_call(lambda: wfpt.wiener_like_multi(x1, vv, 0, 2, 0.5, 0, tt, 0, 1e-4, multi=["v", "t"], p_outlier=0.05, w_outlier=0.1)))
