@@ -255,6 +255,8 @@ static void plan_slices(int64_t n, int64_t P, int* slices, int64_t* chunk)
     int64_t s = (P >= target) ? 1 : (target + P - 1) / (P > 0 ? P : 1);
     const int64_t max_s = (n + 2 * kBlock - 1) / (2 * kBlock);
     if (s > max_s) s = max_s;
+    const int64_t min_s = (n >> 30) + 1;   // the kernel counts a slice's RTs in 32 bits
+    if (s < min_s) s = min_s;
     if (s < 1) s = 1;
     int64_t c = (n + s - 1) / s;
     if (c & 1) c++;

@@ -112,9 +112,11 @@ __global__ void __launch_bounds__(kBlock, MINB) like_batch_kernel(const double* 
     // one_each (small grids, where latency counts rather than throughput): one RT per thread and round, 8-byte loads
     // In that mode the slices of a set interleave (slice s takes trials s, s + slices, ...): trials that need refinement
     // are neighbours in the |rt|-sorted array, and this spreads them over all the CTAs of the set.
-    const int64_t mine = (n > s) ? (n - s + slices - 1) / slices : 0;
-    const int64_t rounds = one_each ? (mine + kBlock - 1) / kBlock
-                                    : (npair + kBlock - 1) / kBlock + 1;   // + 1: the head / tail elements
+    // (32-bit counters: a slice never holds 2^30 RTs, see plan_slices)
+    const int mine = (n > s) ? (int)((n - s + slices - 1) / slices) : 0;
+    const int npair32 = (int)npair;
+    const int rounds = one_each ? (mine + kBlock - 1) / kBlock
+                                : (npair32 + kBlock - 1) / kBlock + 1;   // + 1: the head / tail elements
     double acc_slow = 0.0;
     auto drain = [&](int parked) {
         if (Impl::coop_applies(set, parked)) {   // uniform over the CTA
@@ -148,13 +150,13 @@ __global__ void __launch_bounds__(kBlock, MINB) like_batch_kernel(const double* 
         }
     } else {
 #pragma unroll 1
-    for (int64_t r = 0; r < rounds; r++) {
+    for (int r = 0; r < rounds; r++) {
         double v0 = 0.0, v1 = 0.0;
         int cnt = 0;
-        const int64_t i = r * kBlock + threadIdx.x;
+        const int i = r * kBlock + threadIdx.x;
         if (one_each) {
-            if (i < mine) { v0 = x[i * slices + s]; cnt = 1; }
-        } else if (i < npair) {
+            if (i < mine) { v0 = x[(int64_t)i * slices + s]; cnt = 1; }
+        } else if (i < npair32) {
             const double2 xx = __ldg(x2 + i);
             v0 = xx.x;
             v1 = xx.y;
