@@ -146,6 +146,43 @@ __device__ __forceinline__ double exp_core_or_zero(double x, const double* __res
     return exp_arg_ok(x) ? v : 0.0;
 }
 
+// M exps at once, written stage by stage: the M dependent chains (8 FP64 results deep each) then sit next to each other in
+// the instruction stream and overlap, instead of running one after the other.  Same arithmetic as exp_core.
+template <int M>
+__device__ __forceinline__ void exp_core_batch(const double (&x)[M], double (&out)[M], const double* __restrict__ tab)
+{
+    double t[M], r[M], p[M], T[M];
+    int ki[M];
+#pragma unroll
+    for (int i = 0; i < M; i++) t[i] = fma(x[i], kExpC[0], kExpC[1]);
+#pragma unroll
+    for (int i = 0; i < M; i++) {
+        ki[i] = __double2loint(t[i]);
+        t[i] = t[i] - kExpC[1];
+    }
+#pragma unroll
+    for (int i = 0; i < M; i++) r[i] = fma(t[i], kExpC[2], x[i]);
+#pragma unroll
+    for (int i = 0; i < M; i++) {
+        r[i] = fma(t[i], kExpC[3], r[i]);
+        T[i] = tab[ki[i] & 63];
+    }
+#pragma unroll
+    for (int i = 0; i < M; i++) {
+        const double r2 = r[i] * r[i];
+        const double ph = fma(r[i], kExpC[4], kExpC[5]);
+        const double pl = fma(r[i], kExpC[6], kExpC[7]);
+        p[i] = fma(r2, fma(ph, r2, pl), r[i]);
+    }
+#pragma unroll
+    for (int i = 0; i < M; i++) {
+        const double res = fma(T[i], p[i], T[i]);
+        int hi;
+        asm("mad.lo.s32 %0, %1, 16384, %2;" : "=r"(hi) : "r"(ki[i] & ~63), "r"(__double2hiint(res)));
+        out[i] = __hiloint2double(hi, __double2loint(res));
+    }
+}
+
 // 1/sqrt(x) for normal positive x: hardware seed + two Newton steps (straight-line; <= 2 ulp)
 __device__ __forceinline__ double rsqrt_fast(double x)
 {
@@ -278,17 +315,25 @@ __device__ __forceinline__ void nodes(const TNode& tn, const Set& s, int sign, i
         const double tau = tn.inv_tt, m2t = -2.0 * tau;
         bool ok = (K <= 4);
         double e0[N];
+        // the N + 3 exps of the node set as one batch: e0_n, then R, Q and rho
+        constexpr int M = N + (N > 1 ? 3 : 2);
+        double arg[M], val[M];
 #pragma unroll
         for (int n = 0; n < N; n++) {
-            const double a = fma(Z[n].uh1, tau, E[n]);
-            ok &= exp_arg_ok(a);
-            e0[n] = exp_core(a, tab);
+            arg[n] = fma(Z[n].uh1, tau, E[n]);
+            ok &= exp_arg_ok(arg[n]);
         }
         const double z_first = Z[0].u[1], z_last = Z[N - 1].u[1];
-        double R = exp_core_or_zero(fma(m2t, z_first, m2t), tab);            // exp(-2 (z_0 + 1) / tt)
-        double Q = exp_core_or_zero(fma(-m2t, z_last, m2t), tab);            // exp(-2 (1 - z_last) / tt)
+        arg[N] = fma(m2t, z_first, m2t);                                     // R = exp(-2 (z_0 + 1) / tt)
+        arg[N + 1] = fma(-m2t, z_last, m2t);                                 // Q = exp(-2 (1 - z_last) / tt)
+        if (N > 1) arg[M - 1] = m2t * T.zstep[sign];                         // rho = exp(-2 step / tt)
+        exp_core_batch<M>(arg, val, tab);
+#pragma unroll
+        for (int n = 0; n < N; n++) e0[n] = val[n];
+        double R = exp_arg_ok(arg[N]) ? val[N] : 0.0;                        // (true value underflows: 0)
+        double Q = exp_arg_ok(arg[N + 1]) ? val[N + 1] : 0.0;
         if (K < 3) Q = 0.0;                                                  // K == 2 sums k = 0, 1 only
-        const double rho = (N > 1) ? exp_core_or_zero(m2t * T.zstep[sign], tab) : 1.0;
+        const double rho = (N > 1) ? (exp_arg_ok(arg[M - 1]) ? val[M - 1] : 0.0) : 1.0;
         double Rn[N], Qn[N];
         Rn[0] = R;
         Qn[N - 1] = Q;
@@ -313,10 +358,8 @@ __device__ __forceinline__ void nodes(const TNode& tn, const Set& s, int sign, i
         bool ok = true;
         double ex[N];
 #pragma unroll
-        for (int n = 0; n < N; n++) {
-            ok &= exp_arg_ok(E[n]);
-            ex[n] = exp_core(E[n], tab);
-        }
+        for (int n = 0; n < N; n++) ok &= exp_arg_ok(E[n]);
+        exp_core_batch<N>(E, ex, tab);
         if (!ok) {
 #pragma unroll
             for (int n = 0; n < N; n++) ex[n] = exp(E[n]);
