@@ -36,7 +36,8 @@ void count_launch(int k) { g_launches.fetch_add(k, std::memory_order_relaxed); }
 
 // ---- per-device grow-only scratch ------------------------------------------------------------------------------------
 enum Slot { kPartSum = 0, kPartZero, kDone, kStageX, kStageParams, kStageOut, kStageAux0, kStageAux1, kStageAux2, kStageAux3,
-            kStageAux4, kStageAux5, kStageAux6, kStageAux7, kStageAux8, kStageAux9, kStageAux10, kStageAux11, kNumSlots };
+            kStageAux4, kStageAux5, kStageAux6, kStageAux7, kStageAux8, kStageAux9, kStageAux10, kStageAux11, kSim0, kSim1, kSim2,
+            kSim3, kSim4, kSim5, kNumSlots };
 constexpr int kMaxDev = 16;
 struct Buf { void* p = nullptr; size_t cap = 0; };
 static Buf g_buf[kMaxDev][kNumSlots];
@@ -285,6 +286,12 @@ static void plan_small_grid(int64_t n, int64_t P, BatchArgs* a)
 
 // ---- hooks for sibling translation units ---------------------------------------------------------------------------------
 int api_fail(const char* msg) { return fail("%s", msg); }
+int api_sim_scratch(int which, size_t bytes, void** out)
+{
+    if (which < 0 || which > 5) return fail("bad simulator scratch slot");
+    return scratch(kSim0 + which, bytes < 16 ? 16 : bytes, out);
+}
+int api_sm_count() { return sm_count(); }
 int api_check_opts(double err, int n_st, int n_sz, int use_adaptive, double simps_err, int variant, Opts* o)
 {
     return check_opts(err, n_st, n_sz, use_adaptive, simps_err, variant, o);

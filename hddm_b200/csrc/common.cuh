@@ -77,6 +77,8 @@ cudaError_t launch_like_multi_fast(const MultiArgs& a);
 
 // ---- hooks exported by api.cu for sibling translation units -------------------------------------------------------------
 int api_fail(const char* msg);
+int api_sim_scratch(int which, size_t bytes, void** out);   // grow-only device buffers of the simulator entry points (0..5)
+int api_sm_count();
 int api_check_opts(double err, int n_st, int n_sz, int use_adaptive, double simps_err, int variant, Opts* o);
 void api_plan_slices(int64_t n, int64_t P, int* slices, int64_t* chunk);
 cudaError_t api_launch_finalize(const double* part_sum, const int* part_zero, int64_t P, int slices, int early_exit,

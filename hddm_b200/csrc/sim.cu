@@ -766,6 +766,22 @@ __global__ void __launch_bounds__(kSimBlock) hier_kernel(const Args A)
     }
 }
 
+// Particles per work item (one CTA each): 4,096 for large runs; for small ones fewer, so that a call with a few thousand
+// particles still spreads over the machine instead of running on a single SM (results do not depend on it: the random
+// streams are keyed by particle index).
+static long long pick_chunk(long long n_samples, long long n_sets)
+{
+    long long chunk = 4096;
+    const long long want_items = (long long)api_sm_count() * 4;
+    if (n_sets * ((n_samples + chunk - 1) / chunk) < want_items) {
+        chunk = (n_samples * n_sets + want_items - 1) / want_items;
+        if (chunk < kSimBlock) chunk = kSimBlock;
+        if (chunk > 4096) chunk = 4096;
+    }
+    if (chunk > n_samples) chunk = n_samples;
+    return chunk;
+}
+
 template <int MODEL>
 static cudaError_t launch(const Args& A, int blocks, cudaStream_t stream)
 {
@@ -837,8 +853,7 @@ extern "C" int wfpt_sim_run(int model, const float* d_theta, int n_par, int n_se
     // work items: (parameter set, chunk of its particles), one CTA each.  Chunks of at most 4,096 particles keep the
     // hardware block scheduler busy balancing cheap and expensive parameter sets, while inside a CTA the shared
     // particle counter keeps all lanes busy until the chunk is done.
-    long long chunk = 4096;
-    if (chunk > n_samples) chunk = n_samples;
+    const long long chunk = sim::pick_chunk(n_samples, n_sets);
     A.chunk = chunk;
     A.items_per_set = (n_samples + chunk - 1) / chunk;
     const long long n_items = A.items_per_set * n_sets;
@@ -875,6 +890,11 @@ extern "C" int wfpt_sim_run(int model, const float* d_theta, int n_par, int n_se
         if (e__ != cudaSuccess) { rc = api_fail(cudaGetErrorString(e__)); goto done; } \
     } while (0)
 
+#define SCK_RC(call)                        \
+    do {                                    \
+        if ((call) != 0) { rc = 1; goto done; } \
+    } while (0)
+
 extern "C" int wfpt_sim_run_host(int model, const float* h_theta, int n_par, int n_sets, int64_t n_samples, int64_t sample_offset,
                                  float delta_t, float max_t, float s, uint64_t seed, float* h_rts, int32_t* h_choices,
                                  uint32_t* h_hist, int nbins, float hist_max_t, uint64_t* h_steps, float* h_traj, int traj_len)
@@ -888,13 +908,13 @@ extern "C" int wfpt_sim_run_host(int model, const float* h_theta, int n_par, int
     uint64_t* d_steps = nullptr;
     const size_t n_out = (size_t)n_samples * (size_t)n_sets;
     const size_t hist_n = (size_t)n_sets * (size_t)(nbins > 0 ? nbins : 0) * 2;
-    SCK(cudaMalloc(&d_theta, sizeof(float) * (size_t)n_sets * n_par));
+    SCK_RC(api_sim_scratch(0, sizeof(float) * (size_t)n_sets * n_par, (void**)&d_theta));
     SCK(cudaMemcpy(d_theta, h_theta, sizeof(float) * (size_t)n_sets * n_par, cudaMemcpyHostToDevice));
-    if (h_rts) { SCK(cudaMalloc(&d_rts, sizeof(float) * n_out)); SCK(cudaMalloc(&d_ch, sizeof(int32_t) * n_out)); }
-    if (h_hist) { SCK(cudaMalloc(&d_hist, sizeof(uint32_t) * hist_n)); SCK(cudaMemset(d_hist, 0, sizeof(uint32_t) * hist_n)); }
-    if (h_steps) { SCK(cudaMalloc(&d_steps, sizeof(uint64_t))); SCK(cudaMemset(d_steps, 0, sizeof(uint64_t))); }
+    if (h_rts) { SCK_RC(api_sim_scratch(1, sizeof(float) * n_out, (void**)&d_rts)); SCK_RC(api_sim_scratch(2, sizeof(int32_t) * n_out, (void**)&d_ch)); }
+    if (h_hist) { SCK_RC(api_sim_scratch(3, sizeof(uint32_t) * hist_n, (void**)&d_hist)); SCK(cudaMemset(d_hist, 0, sizeof(uint32_t) * hist_n)); }
+    if (h_steps) { SCK_RC(api_sim_scratch(4, sizeof(uint64_t), (void**)&d_steps)); SCK(cudaMemset(d_steps, 0, sizeof(uint64_t))); }
     if (h_traj && traj_len > 0) {
-        SCK(cudaMalloc(&d_traj, sizeof(float) * (size_t)traj_len));
+        SCK_RC(api_sim_scratch(5, sizeof(float) * (size_t)traj_len, (void**)&d_traj));
         // the reference pre-fills the trajectory with -999 (cddm_data_simulation.pyx:318-319)
         SCK(cudaMemcpy(d_traj, h_traj, sizeof(float) * (size_t)traj_len, cudaMemcpyHostToDevice));
     }
@@ -910,7 +930,6 @@ extern "C" int wfpt_sim_run_host(int model, const float* h_theta, int n_par, int
     if (h_steps) SCK(cudaMemcpy(h_steps, d_steps, sizeof(uint64_t), cudaMemcpyDeviceToHost));
     if (d_traj) SCK(cudaMemcpy(h_traj, d_traj, sizeof(float) * (size_t)traj_len, cudaMemcpyDeviceToHost));
 done:
-    cudaFree(d_theta); cudaFree(d_rts); cudaFree(d_ch); cudaFree(d_hist); cudaFree(d_steps); cudaFree(d_traj);
     return rc;
 }
 
@@ -937,17 +956,17 @@ extern "C" int wfpt_sim_race_run_host(int lca, int n_particles, int angle, const
     const size_t hist_n = (size_t)n_sets * (size_t)(nbins > 0 ? nbins : 0) * n_particles;
     sim::Args A;
     cudaError_t e = cudaSuccess;
-    SCK(cudaMalloc(&d_theta, sizeof(float) * (size_t)n_sets * n_par));
+    SCK_RC(api_sim_scratch(0, sizeof(float) * (size_t)n_sets * n_par, (void**)&d_theta));
     SCK(cudaMemcpy(d_theta, h_theta, sizeof(float) * (size_t)n_sets * n_par, cudaMemcpyHostToDevice));
-    if (h_rts) { SCK(cudaMalloc(&d_rts, sizeof(float) * n_out)); SCK(cudaMalloc(&d_ch, sizeof(int32_t) * n_out)); }
-    if (h_hist) { SCK(cudaMalloc(&d_hist, sizeof(uint32_t) * hist_n)); SCK(cudaMemset(d_hist, 0, sizeof(uint32_t) * hist_n)); }
-    if (h_steps) { SCK(cudaMalloc(&d_steps, sizeof(uint64_t))); SCK(cudaMemset(d_steps, 0, sizeof(uint64_t))); }
+    if (h_rts) { SCK_RC(api_sim_scratch(1, sizeof(float) * n_out, (void**)&d_rts)); SCK_RC(api_sim_scratch(2, sizeof(int32_t) * n_out, (void**)&d_ch)); }
+    if (h_hist) { SCK_RC(api_sim_scratch(3, sizeof(uint32_t) * hist_n, (void**)&d_hist)); SCK(cudaMemset(d_hist, 0, sizeof(uint32_t) * hist_n)); }
+    if (h_steps) { SCK_RC(api_sim_scratch(4, sizeof(uint64_t), (void**)&d_steps)); SCK(cudaMemset(d_steps, 0, sizeof(uint64_t))); }
     A.theta = d_theta; A.n_par = n_par; A.n_sets = n_sets; A.n_samples = n_samples; A.sample_offset = sample_offset;
     A.out_stride_samples = n_samples; A.dt = delta_t; A.max_t = max_t; A.s = s; A.set_seed(seed); A.rts = d_rts; A.choices = d_ch;
     A.hist = d_hist; A.nbins = d_hist ? nbins : 0; A.hist_max_t = (double)hist_max_t;
     A.hist_step = d_hist ? (double)hist_max_t / (double)(nbins - 1) : 1.0;
     A.steps = (unsigned long long*)d_steps; A.traj = nullptr; A.traj_len = 0;
-    A.chunk = n_samples < 4096 ? n_samples : 4096;
+    A.chunk = sim::pick_chunk(n_samples, n_sets);
     A.items_per_set = (n_samples + A.chunk - 1) / A.chunk;
     {
         const long long n_items = A.items_per_set * n_sets;
@@ -967,7 +986,6 @@ extern "C" int wfpt_sim_race_run_host(int lca, int n_particles, int angle, const
     if (h_hist) SCK(cudaMemcpy(h_hist, d_hist, sizeof(uint32_t) * hist_n, cudaMemcpyDeviceToHost));
     if (h_steps) SCK(cudaMemcpy(h_steps, d_steps, sizeof(uint64_t), cudaMemcpyDeviceToHost));
 done:
-    cudaFree(d_theta); cudaFree(d_rts); cudaFree(d_ch); cudaFree(d_hist); cudaFree(d_steps);
     return rc;
 }
 
@@ -993,17 +1011,17 @@ static int run_hier_host(const char* who, int kind, int bound_kind, const float*
     const size_t n_out = (size_t)n_samples * (size_t)n_sets;
     const size_t hist_n = (size_t)n_sets * (size_t)(nbins > 0 ? nbins : 0) * 4;
     sim::Args A;
-    SCK(cudaMalloc(&d_theta, sizeof(float) * (size_t)n_sets * n_par));
+    SCK_RC(api_sim_scratch(0, sizeof(float) * (size_t)n_sets * n_par, (void**)&d_theta));
     SCK(cudaMemcpy(d_theta, h_theta, sizeof(float) * (size_t)n_sets * n_par, cudaMemcpyHostToDevice));
-    if (h_rts) { SCK(cudaMalloc(&d_rts, sizeof(float) * n_out)); SCK(cudaMalloc(&d_ch, sizeof(int32_t) * n_out)); }
-    if (h_hist) { SCK(cudaMalloc(&d_hist, sizeof(uint32_t) * hist_n)); SCK(cudaMemset(d_hist, 0, sizeof(uint32_t) * hist_n)); }
-    if (h_steps) { SCK(cudaMalloc(&d_steps, sizeof(uint64_t))); SCK(cudaMemset(d_steps, 0, sizeof(uint64_t))); }
+    if (h_rts) { SCK_RC(api_sim_scratch(1, sizeof(float) * n_out, (void**)&d_rts)); SCK_RC(api_sim_scratch(2, sizeof(int32_t) * n_out, (void**)&d_ch)); }
+    if (h_hist) { SCK_RC(api_sim_scratch(3, sizeof(uint32_t) * hist_n, (void**)&d_hist)); SCK(cudaMemset(d_hist, 0, sizeof(uint32_t) * hist_n)); }
+    if (h_steps) { SCK_RC(api_sim_scratch(4, sizeof(uint64_t), (void**)&d_steps)); SCK(cudaMemset(d_steps, 0, sizeof(uint64_t))); }
     A.theta = d_theta; A.n_par = n_par; A.n_sets = n_sets; A.n_samples = n_samples; A.sample_offset = sample_offset;
     A.out_stride_samples = n_samples; A.dt = delta_t; A.max_t = max_t; A.s = s; A.set_seed(seed); A.rts = d_rts; A.choices = d_ch;
     A.hist = d_hist; A.nbins = d_hist ? nbins : 0; A.hist_max_t = (double)hist_max_t;
     A.hist_step = d_hist ? (double)hist_max_t / (double)(nbins - 1) : 1.0;
     A.steps = (unsigned long long*)d_steps; A.traj = nullptr; A.traj_len = 0;
-    A.chunk = n_samples < 4096 ? n_samples : 4096;
+    A.chunk = sim::pick_chunk(n_samples, n_sets);
     A.items_per_set = (n_samples + A.chunk - 1) / A.chunk;
     {
         const long long n_items = A.items_per_set * n_sets;
@@ -1032,7 +1050,6 @@ static int run_hier_host(const char* who, int kind, int bound_kind, const float*
     if (h_hist) SCK(cudaMemcpy(h_hist, d_hist, sizeof(uint32_t) * hist_n, cudaMemcpyDeviceToHost));
     if (h_steps) SCK(cudaMemcpy(h_steps, d_steps, sizeof(uint64_t), cudaMemcpyDeviceToHost));
 done:
-    cudaFree(d_theta); cudaFree(d_rts); cudaFree(d_ch); cudaFree(d_hist); cudaFree(d_steps);
     return rc;
 }
 
