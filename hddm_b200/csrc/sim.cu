@@ -788,14 +788,32 @@ static cudaError_t launch(const Args& A, int blocks, cudaStream_t stream)
     const size_t smem = A.hist ? sizeof(unsigned int) * 2 * (size_t)A.nbins : 0;
     Args P = A;
     P.traj = nullptr;
-    sim_kernel<MODEL, false><<<blocks, kSimBlock, smem, stream>>>(P);
     if (A.traj && A.sample_offset == 0) {
-        // the trajectory of (set 0, particle 0): the same walk again, one particle, path written out
+        // the trajectory of (set 0, particle 0): the same walk again, one particle, path written out.  One thread
+        // stepping through a whole walk takes as long as a small production launch, so it runs beside it on a stream
+        // of its own (forked from and joined back into the caller's stream with events).
+        static cudaStream_t side[16] = {};
+        static cudaEvent_t fork_ev[16] = {}, join_ev[16] = {};
+        int dev = 0;
+        cudaGetDevice(&dev);
+        dev &= 15;
+        if (!side[dev]) {
+            cudaStreamCreateWithFlags(&side[dev], cudaStreamNonBlocking);
+            cudaEventCreateWithFlags(&fork_ev[dev], cudaEventDisableTiming);
+            cudaEventCreateWithFlags(&join_ev[dev], cudaEventDisableTiming);
+        }
         Args T = A;
         T.n_sets = 1; T.n_samples = 1; T.chunk = 1; T.items_per_set = 1;
         T.rts = nullptr; T.choices = nullptr; T.hist = nullptr; T.nbins = 0; T.steps = nullptr;
-        sim_kernel<MODEL, true><<<1, kSimBlock, 0, stream>>>(T);
+        cudaEventRecord(fork_ev[dev], stream);            // inputs (theta, the -999 prefill) are ready at this point
+        cudaStreamWaitEvent(side[dev], fork_ev[dev], 0);
+        sim_kernel<MODEL, true><<<1, kSimBlock, 0, side[dev]>>>(T);
+        cudaEventRecord(join_ev[dev], side[dev]);
+        sim_kernel<MODEL, false><<<blocks, kSimBlock, smem, stream>>>(P);
+        cudaStreamWaitEvent(stream, join_ev[dev], 0);
+        return cudaGetLastError();
     }
+    sim_kernel<MODEL, false><<<blocks, kSimBlock, smem, stream>>>(P);
     return cudaGetLastError();
 }
 
