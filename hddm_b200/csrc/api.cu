@@ -101,6 +101,40 @@ static int pinned(size_t in_bytes, char** h, char** d)
     return 0;
 }
 
+// Several host arrays to the device: packed into the pinned block and copied with ONE asynchronous copy when they fit
+// (16-byte aligned pieces of scratch slot `slot0`), one copy each into slots slot0.. otherwise.  *mapped_out receives the
+// device address of the mapped result area when the pinned block was used (nullptr otherwise).
+static int stage_in(int k, const void* const* src, const size_t* bytes, int slot0, void** dev, double** mapped_out,
+                    char** host_out)
+{
+    size_t total = 0, off[8];
+    for (int i = 0; i < k; i++) {
+        off[i] = total;
+        total += (bytes[i] + 15) & ~(size_t)15;
+    }
+    *mapped_out = nullptr;
+    *host_out = nullptr;
+    if (total <= kPinMaxIn) {
+        char *ph, *pd;
+        void* base;
+        if (pinned(total, &ph, &pd)) return 1;
+        if (scratch(slot0, total, &base)) return 1;
+        for (int i = 0; i < k; i++) {
+            memcpy(ph + kPinOutBytes + off[i], src[i], bytes[i]);
+            dev[i] = (char*)base + off[i];
+        }
+        CK(cudaMemcpyAsync(base, ph + kPinOutBytes, total, cudaMemcpyHostToDevice, 0));
+        *mapped_out = (double*)pd;
+        *host_out = ph;
+        return 0;
+    }
+    for (int i = 0; i < k; i++) {
+        if (scratch(slot0 + i, bytes[i], &dev[i])) return 1;
+        CK(cudaMemcpyAsync(dev[i], src[i], bytes[i], cudaMemcpyHostToDevice, 0));
+    }
+    return 0;
+}
+
 // ---- small kernels ---------------------------------------------------------------------------------------------------------
 __global__ void finalize_kernel(const double* __restrict__ part_sum, const int* __restrict__ part_zero, int64_t P,
                                 int slices, int early_exit, double* __restrict__ out)
@@ -124,23 +158,43 @@ __global__ void rl_q_kernel(const int64_t* __restrict__ response, const double* 
                             double q, double alpha, double pos_alfa, double* __restrict__ vscale,
                             uint8_t* __restrict__ skip)
 {
-    const int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    // One WARP per group.  The recurrence is sequential, but its inputs are not: the lanes fetch 32 trials at a time
+    // (so no memory latency sits in the dependent chain), every lane then steps through them with shuffles, and lane k
+    // keeps the value seen before trial k.
+    const int lane = threadIdx.x & 31;
+    const int64_t g = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     if (g >= n_groups) return;
     // alfa = B^alpha / (1 + B^alpha) with the reference's truncated base B = 2.718281828459 (wfpt.pyx:122-124)
     const double ea = pow(2.718281828459, alpha), ep = pow(2.718281828459, pos_alfa);
     const double rate_neg = __ddiv_rn(ea, __dadd_rn(1.0, ea));
     const double rate_pos = __ddiv_rn(ep, __dadd_rn(1.0, ep));
     double qs0 = q, qs1 = q;
-    for (int64_t i = starts[g]; i < starts[g + 1]; i++) {
-        const int64_t j = order[i];
-        vscale[j] = __dsub_rn(qs1, qs0);
-        skip[j] = (i == starts[g]) ? 1 : 0;
-        const int64_t r = response[j];
-        const double fb = feedback[j];
-        const double cur = r ? qs1 : qs0;
-        const double alfa = (fb > cur) ? rate_pos : rate_neg;
-        const double upd = __dadd_rn(cur, __dmul_rn(alfa, __dsub_rn(fb, cur)));
-        if (r) qs1 = upd; else qs0 = upd;
+    const int64_t beg = starts[g], end = starts[g + 1];
+    for (int64_t base = beg; base < end; base += 32) {
+        const int64_t i = base + lane;
+        int64_t j = 0;
+        int r = 0;
+        double fb = 0.0;
+        if (i < end) {
+            j = order[i];
+            r = response[j] != 0;
+            fb = feedback[j];
+        }
+        const int cnt = (end - base < 32) ? (int)(end - base) : 32;
+        double mine = 0.0;
+        for (int k = 0; k < cnt; k++) {
+            const int rk = __shfl_sync(0xffffffffu, r, k);
+            const double fk = __shfl_sync(0xffffffffu, fb, k);
+            if (lane == k) mine = __dsub_rn(qs1, qs0);
+            const double cur = rk ? qs1 : qs0;
+            const double alfa = (fk > cur) ? rate_pos : rate_neg;
+            const double upd = __dadd_rn(cur, __dmul_rn(alfa, __dsub_rn(fk, cur)));
+            if (rk) qs1 = upd; else qs0 = upd;
+        }
+        if (i < end) {
+            vscale[j] = mine;
+            skip[j] = (i == beg) ? 1 : 0;
+        }
     }
 }
 
@@ -167,18 +221,34 @@ __global__ void rl_q_runs_kernel(const int64_t* __restrict__ response, const dou
                                  const int64_t* __restrict__ run_starts, int64_t n_runs, double q,
                                  const double* __restrict__ alpha_arr, double alpha_scalar, double* __restrict__ vscale)
 {
-    const int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    // one warp per run, inputs (and the per-trial learning rates, computed in parallel) handed round with shuffles
+    const int lane = threadIdx.x & 31;
+    const int64_t g = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     if (g >= n_runs) return;
     double qs0 = q, qs1 = q;
-    for (int64_t i = run_starts[g]; i < run_starts[g + 1]; i++) {
-        vscale[i] = __dsub_rn(qs1, qs0);
-        const double al = alpha_arr ? alpha_arr[i] : alpha_scalar;
-        const double ea = pow(2.718281828459, al);
-        const double alfa = __ddiv_rn(ea, __dadd_rn(1.0, ea));
-        const int64_t r = response[i];
-        const double cur = r ? qs1 : qs0;
-        const double upd = __dadd_rn(cur, __dmul_rn(alfa, __dsub_rn(feedback[i], cur)));
-        if (r) qs1 = upd; else qs0 = upd;
+    const int64_t beg = run_starts[g], end = run_starts[g + 1];
+    for (int64_t base = beg; base < end; base += 32) {
+        const int64_t i = base + lane;
+        int r = 0;
+        double fb = 0.0, alfa = 0.0;
+        if (i < end) {
+            r = response[i] != 0;
+            fb = feedback[i];
+            const double ea = pow(2.718281828459, alpha_arr ? alpha_arr[i] : alpha_scalar);
+            alfa = __ddiv_rn(ea, __dadd_rn(1.0, ea));
+        }
+        const int cnt = (end - base < 32) ? (int)(end - base) : 32;
+        double mine = 0.0;
+        for (int k = 0; k < cnt; k++) {
+            const int rk = __shfl_sync(0xffffffffu, r, k);
+            const double fk = __shfl_sync(0xffffffffu, fb, k);
+            const double ak = __shfl_sync(0xffffffffu, alfa, k);
+            if (lane == k) mine = __dsub_rn(qs1, qs0);
+            const double cur = rk ? qs1 : qs0;
+            const double upd = __dadd_rn(cur, __dmul_rn(ak, __dsub_rn(fk, cur)));
+            if (rk) qs1 = upd; else qs0 = upd;
+        }
+        if (i < end) vscale[i] = mine;
     }
 }
 
@@ -604,21 +674,22 @@ int wfpt_like_rlddm_host(const double* h_x, const int64_t* h_response, const dou
     const double pos_alfa = (pos_alpha == 100.00) ? alpha : pos_alpha;  // wfpt.pyx:104-107
 
     void *dx, *dresp, *dfb, *dord, *dst, *dvs, *dskip, *dout;
-    if (scratch(kStageX, sizeof(double) * (size_t)n, &dx)) return 1;
-    if (scratch(kStageAux0, sizeof(int64_t) * (size_t)n, &dresp)) return 1;
-    if (scratch(kStageAux1, sizeof(double) * (size_t)n, &dfb)) return 1;
-    if (scratch(kStageAux2, sizeof(int64_t) * (size_t)n, &dord)) return 1;
-    if (scratch(kStageAux3, sizeof(int64_t) * (size_t)(n_groups + 1), &dst)) return 1;
+    double* mapped;
+    char* pin_host;
+    {
+        const void* src[5] = {h_x, h_response, h_feedback, h_order, h_starts};
+        const size_t nb8 = sizeof(double) * (size_t)n;
+        const size_t bytes[5] = {nb8, nb8, nb8, nb8, sizeof(int64_t) * (size_t)(n_groups + 1)};
+        void* dev[5];
+        if (stage_in(5, src, bytes, kStageAux6, dev, &mapped, &pin_host)) return 1;
+        dx = dev[0]; dresp = dev[1]; dfb = dev[2]; dord = dev[3]; dst = dev[4];
+    }
     if (scratch(kStageAux4, sizeof(double) * (size_t)n, &dvs)) return 1;
     if (scratch(kStageAux5, (size_t)n, &dskip)) return 1;
     if (scratch(kStageOut, sizeof(double), &dout)) return 1;
-    CK(cudaMemcpyAsync(dx, h_x, sizeof(double) * (size_t)n, cudaMemcpyHostToDevice, 0));
-    CK(cudaMemcpyAsync(dresp, h_response, sizeof(int64_t) * (size_t)n, cudaMemcpyHostToDevice, 0));
-    CK(cudaMemcpyAsync(dfb, h_feedback, sizeof(double) * (size_t)n, cudaMemcpyHostToDevice, 0));
-    CK(cudaMemcpyAsync(dord, h_order, sizeof(int64_t) * (size_t)n, cudaMemcpyHostToDevice, 0));
-    CK(cudaMemcpyAsync(dst, h_starts, sizeof(int64_t) * (size_t)(n_groups + 1), cudaMemcpyHostToDevice, 0));
+    if (mapped) dout = mapped;   // the result goes straight into mapped host memory
     CK(cudaMemsetAsync(dskip, 1, (size_t)n, 0));  // trials not named by `order` contribute nothing
-    rl_q_kernel<<<(unsigned)((n_groups + 63) / 64), 64>>>((const int64_t*)dresp, (const double*)dfb, (const int64_t*)dord,
+    rl_q_kernel<<<(unsigned)((n_groups + 3) / 4), 128>>>((const int64_t*)dresp, (const double*)dfb, (const int64_t*)dord,
                                                         (const int64_t*)dst, n_groups, q, alpha, pos_alfa, (double*)dvs,
                                                         (uint8_t*)dskip);
     CK(cudaGetLastError());
@@ -627,6 +698,11 @@ int wfpt_like_rlddm_host(const double* h_x, const int64_t* h_response, const dou
     if (run_multi((const double*)dx, n, nullptr, scalars, o, p_outlier, w_outlier, (const double*)dvs,
                   (const uint8_t*)dskip, 1, 0, variant, (double*)dout, 0))
         return 1;
+    if (mapped) {
+        CK(cudaStreamSynchronize(0));
+        memcpy(h_out, pin_host, sizeof(double));
+        return 0;
+    }
     CK(cudaMemcpyAsync(h_out, dout, sizeof(double), cudaMemcpyDeviceToHost, 0));
     CK(cudaStreamSynchronize(0));
     return 0;
@@ -786,10 +862,16 @@ int wfpt_like_rl_host(const int64_t* h_response, const double* h_feedback, const
         if (h_response[i] != 0 && h_response[i] != 1) return fail("response[%lld] is not 0/1", (long long)i);
     const double pos_alfa = (pos_alpha == 100.00) ? alpha : pos_alpha;
     void *dresp, *dfb, *dord, *dst, *dvs, *dskip, *dout, *ps, *pz;
-    if (scratch(kStageAux0, sizeof(int64_t) * (size_t)n, &dresp)) return 1;
-    if (scratch(kStageAux1, sizeof(double) * (size_t)n, &dfb)) return 1;
-    if (scratch(kStageAux2, sizeof(int64_t) * (size_t)n, &dord)) return 1;
-    if (scratch(kStageAux3, sizeof(int64_t) * (size_t)(n_groups + 1), &dst)) return 1;
+    double* mapped;
+    char* pin_host;
+    {
+        const void* src[4] = {h_response, h_feedback, h_order, h_starts};
+        const size_t nb8 = sizeof(double) * (size_t)n;
+        const size_t bytes[4] = {nb8, nb8, nb8, sizeof(int64_t) * (size_t)(n_groups + 1)};
+        void* dev[4];
+        if (stage_in(4, src, bytes, kStageAux6, dev, &mapped, &pin_host)) return 1;
+        dresp = dev[0]; dfb = dev[1]; dord = dev[2]; dst = dev[3];
+    }
     if (scratch(kStageAux4, sizeof(double) * (size_t)n, &dvs)) return 1;
     if (scratch(kStageAux5, (size_t)n, &dskip)) return 1;
     if (scratch(kStageOut, sizeof(double), &dout)) return 1;
@@ -797,12 +879,9 @@ int wfpt_like_rl_host(const int64_t* h_response, const double* h_feedback, const
     if (nb > (int64_t)sm_count() * 16) nb = (int64_t)sm_count() * 16;
     if (scratch(kPartSum, sizeof(double) * (size_t)nb, &ps)) return 1;
     if (scratch(kPartZero, sizeof(int) * (size_t)nb, &pz)) return 1;
-    CK(cudaMemcpyAsync(dresp, h_response, sizeof(int64_t) * (size_t)n, cudaMemcpyHostToDevice, 0));
-    CK(cudaMemcpyAsync(dfb, h_feedback, sizeof(double) * (size_t)n, cudaMemcpyHostToDevice, 0));
-    CK(cudaMemcpyAsync(dord, h_order, sizeof(int64_t) * (size_t)n, cudaMemcpyHostToDevice, 0));
-    CK(cudaMemcpyAsync(dst, h_starts, sizeof(int64_t) * (size_t)(n_groups + 1), cudaMemcpyHostToDevice, 0));
+    if (mapped) dout = mapped;
     CK(cudaMemsetAsync(dskip, 1, (size_t)n, 0));
-    rl_q_kernel<<<(unsigned)((n_groups + 63) / 64), 64>>>((const int64_t*)dresp, (const double*)dfb, (const int64_t*)dord,
+    rl_q_kernel<<<(unsigned)((n_groups + 3) / 4), 128>>>((const int64_t*)dresp, (const double*)dfb, (const int64_t*)dord,
                                                         (const int64_t*)dst, n_groups, q, alpha, pos_alfa, (double*)dvs,
                                                         (uint8_t*)dskip);
     CK(cudaGetLastError());
@@ -812,6 +891,11 @@ int wfpt_like_rl_host(const int64_t* h_response, const double* h_feedback, const
     finalize_kernel<<<1, 32>>>((const double*)ps, (const int*)pz, 1, (int)nb, 1, (double*)dout);
     CK(cudaGetLastError());
     count_launch(3);
+    if (mapped) {
+        CK(cudaStreamSynchronize(0));
+        memcpy(h_out, pin_host, sizeof(double));
+        return 0;
+    }
     CK(cudaMemcpyAsync(h_out, dout, sizeof(double), cudaMemcpyDeviceToHost, 0));
     CK(cudaStreamSynchronize(0));
     return 0;
@@ -867,7 +951,7 @@ int wfpt_like_multi_rlddm_host(const double* h_x, const int64_t* h_response, con
         if (scratch(kStageAux11, bytes, &dalpha)) return 1;
         CK(cudaMemcpy(dalpha, h_per_trial[7], bytes, cudaMemcpyHostToDevice));
     }
-    rl_q_runs_kernel<<<(unsigned)((n_runs + 63) / 64), 64>>>((const int64_t*)dresp, (const double*)dfb, (const int64_t*)druns,
+    rl_q_runs_kernel<<<(unsigned)((n_runs + 3) / 4), 128>>>((const int64_t*)dresp, (const double*)dfb, (const int64_t*)druns,
                                                            n_runs, q, (const double*)dalpha, scalars[7], (double*)dvs);
     CK(cudaGetLastError());
     count_launch(1);
