@@ -290,6 +290,72 @@ __global__ void __launch_bounds__(kBlock) rl_choice_kernel(const int64_t* __rest
     }
 }
 
+// rl_q_kernel and rl_choice_kernel in one launch for host calls (a choice-only model evaluates a few thousand trials per
+// call: launches, not arithmetic, are what it pays for).  One warp per group; lane k turns the drift scale it sees
+// before trial k into that trial's log-probability; per-group partials in out_sum / out_zero.
+__global__ void rl_choice_fused_kernel(const int64_t* __restrict__ response, const double* __restrict__ feedback,
+                                       const int64_t* __restrict__ order, const int64_t* __restrict__ starts,
+                                       int64_t n_groups, double q, double alpha, double pos_alfa, double v, double z,
+                                       double p_outlier, double w_outlier, double* __restrict__ out_sum,
+                                       int* __restrict__ out_zero)
+{
+    const int lane = threadIdx.x & 31;
+    const int64_t g = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (g >= n_groups) return;
+    const double wp = __dmul_rn(w_outlier, p_outlier);
+    const double omp = __dsub_rn(1.0, p_outlier);
+    const double ea = pow(2.718281828459, alpha), ep = pow(2.718281828459, pos_alfa);
+    const double rate_neg = __ddiv_rn(ea, __dadd_rn(1.0, ea));
+    const double rate_pos = __ddiv_rn(ep, __dadd_rn(1.0, ep));
+    double qs0 = q, qs1 = q, acc = 0.0;
+    int zero = 0;
+    const int64_t beg = starts[g], end = starts[g + 1];
+    for (int64_t base = beg; base < end; base += 32) {
+        const int64_t i = base + lane;
+        int r = 0;
+        double fb = 0.0;
+        if (i < end) {
+            const int64_t j = order[i];
+            r = response[j] != 0;
+            fb = feedback[j];
+        }
+        const int cnt = (end - base < 32) ? (int)(end - base) : 32;
+        double mine = 0.0;
+        for (int k = 0; k < cnt; k++) {
+            const int rk = __shfl_sync(0xffffffffu, r, k);
+            const double fk = __shfl_sync(0xffffffffu, fb, k);
+            if (lane == k) mine = __dsub_rn(qs1, qs0);
+            const double cur = rk ? qs1 : qs0;
+            const double alfa = (fk > cur) ? rate_pos : rate_neg;
+            const double upd = __dadd_rn(cur, __dmul_rn(alfa, __dsub_rn(fk, cur)));
+            if (rk) qs1 = upd; else qs0 = upd;
+        }
+        if (i < end && i != beg) {   // the first trial of a group only updates Q (wfpt.pyx:309-316)
+            const double drift = __dmul_rn(mine, v);
+            double p;
+            if (drift == 0) {
+                p = 0.5;
+            } else {
+                const double num = __dsub_rn(pow(2.718281828459, __dmul_rn(__dmul_rn(-2, z), drift)), 1.0);
+                const double den = __dsub_rn(pow(2.718281828459, __dmul_rn(-2, drift)), 1.0);
+                p = __ddiv_rn(num, den);
+                if (!r) p = __dsub_rn(1.0, p);
+            }
+            p = __dadd_rn(__dmul_rn(p, omp), wp);
+            zero |= (p == 0);
+            acc += log(p);
+        }
+    }
+    for (int off = 16; off > 0; off >>= 1) {
+        acc += __shfl_down_sync(0xffffffffu, acc, off);
+        zero |= __shfl_down_sync(0xffffffffu, zero, off);
+    }
+    if (lane == 0) {
+        out_sum[g] = acc;
+        out_zero[g] = zero;
+    }
+}
+
 // ---- helpers -------------------------------------------------------------------------------------------------------------
 static int check_opts(double err, int n_st, int n_sz, int use_adaptive, double simps_err, int variant, Opts* o)
 {
@@ -880,6 +946,22 @@ int wfpt_like_rl_host(const int64_t* h_response, const double* h_feedback, const
     if (scratch(kPartSum, sizeof(double) * (size_t)nb, &ps)) return 1;
     if (scratch(kPartZero, sizeof(int) * (size_t)nb, &pz)) return 1;
     if (mapped) dout = mapped;
+    if (n_groups <= 4096) {
+        // recurrence and choice likelihood in one launch, then the fixed-order sum of the per-group partials
+        if (scratch(kPartSum, sizeof(double) * (size_t)n_groups, &ps)) return 1;
+        if (scratch(kPartZero, sizeof(int) * (size_t)n_groups, &pz)) return 1;
+        rl_choice_fused_kernel<<<(unsigned)((n_groups + 3) / 4), 128>>>(
+            (const int64_t*)dresp, (const double*)dfb, (const int64_t*)dord, (const int64_t*)dst, n_groups, q, alpha, pos_alfa,
+            v, z, p_outlier, w_outlier, (double*)ps, (int*)pz);
+        CK(cudaGetLastError());
+        finalize_kernel<<<1, 32>>>((const double*)ps, (const int*)pz, 1, (int)n_groups, 1, (double*)dout);
+        CK(cudaGetLastError());
+        count_launch(2);
+        CK(cudaStreamSynchronize(0));
+        if (mapped) memcpy(h_out, pin_host, sizeof(double));
+        else CK(cudaMemcpy(h_out, dout, sizeof(double), cudaMemcpyDeviceToHost));
+        return 0;
+    }
     CK(cudaMemsetAsync(dskip, 1, (size_t)n, 0));
     rl_q_kernel<<<(unsigned)((n_groups + 3) / 4), 128>>>((const int64_t*)dresp, (const double*)dfb, (const int64_t*)dord,
                                                         (const int64_t*)dst, n_groups, q, alpha, pos_alfa, (double*)dvs,
