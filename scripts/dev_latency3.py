@@ -20,3 +20,15 @@ print("pdf_array 1000               %.1f us" % per_call(lambda: wfpt.pdf_array(x
 print("simulator ddm 1000 samples   %.1f us" % per_call(lambda: S.simulator([1.0, 1.5, 0.5, 0.3], model="ddm", n_samples=1000), 50))
 print("simulator angle 1e5 samples  %.1f us" % per_call(lambda: S.simulator([1.0, 1.5, 0.5, 0.3, 0.2], model="angle", n_samples=100000), 20))
 print("simulator race_3 1000        %.1f us" % per_call(lambda: S.simulator([1.0, 1.2, 0.8, 1.5, 0.5, 0.5, 0.5, 0.3], model="race_3", n_samples=1000), 50))
+try:
+    from oracle.build_ref import load_ref
+    ref = load_ref()[0]
+    vv = np.linspace(0.5, 1.5, 1000); tt = np.full(1000, 0.3)
+    print("reference Cython on this host:")
+    print("  wiener_like_rlddm 1000       %.1f us" % per_call(lambda: ref.wiener_like_rlddm(x1, resp, fb, split, 0.5, 0.1, 100.0, 1.0, 0.0, 2.0, 0.5, 0.0, 0.3, 0.0, 1e-4, p_outlier=0.05, w_outlier=0.1), 50))
+    print("  wiener_like_rl 1000          %.1f us" % per_call(lambda: ref.wiener_like_rl(resp, fb, split, 0.5, 0.1, 100.0, 1.0, 0.5), 50))
+    print("  wiener_like_contaminant 1000 %.1f us" % per_call(lambda: ref.wiener_like_contaminant(x1, np.zeros(n, dtype=np.int32), 1.0, 0.0, 2.0, 0.5, 0.0, 0.3, 0.0, 0.1, 5.0, 1e-4), 50))
+    print("  wiener_like_multi 1000 (v,t) %.1f us" % per_call(lambda: ref.wiener_like_multi(x1, vv, 0, 2, 0.5, 0, tt, 0, 1e-4, multi=["v", "t"], p_outlier=0.05, w_outlier=0.1), 50))
+    print("  pdf_array 1000               %.1f us" % per_call(lambda: ref.pdf_array(x1, 1, 0, 2, 0.5, 0, 0.3, 0, 1e-4), 50))
+except Exception as exc:
+    print("reference unavailable:", exc)
