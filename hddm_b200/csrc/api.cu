@@ -487,7 +487,7 @@ int wfpt_release_scratch(void)
 int wfpt_fp64_peak(int iters, double* dfma_per_s, double* ms_out)
 {
     if (iters <= 0) iters = 4096;
-    void* sink;
+    void* sink = nullptr;
     if (scratch(kStageOut, 64, &sink)) return 1;
     const int blocks = sm_count() * 8, threads = 256;
     cudaEvent_t e0, e1;
