@@ -56,6 +56,8 @@ def _declare(L):
     L.wfpt_like_segments_resident.argtypes = [vp, vp, i64, vp, i64] + opts + [d, i, vp]
     L.wfpt_like_contaminant_host.argtypes = [vp, vp, i64] + [d] * 9 + opts + [i, vp]
     L.wfpt_like_rl_host.argtypes = [vp, vp, vp, vp, i64, i64] + [d] * 7 + [vp]
+    L.wfpt_group_by_split.argtypes = [vp, i64, vp, vp, vp]
+    L.wfpt_group_by_split.restype = i
     L.wfpt_like_multi_rlddm_host.argtypes = [vp, vp, vp, vp, i64, d, C.POINTER(vp), c_double_p] + opts + [d, d, i, vp]
     for name in ("wfpt_like_segments", "wfpt_like_segments_host", "wfpt_like_segments_resident", "wfpt_like_contaminant_host", "wfpt_like_rl_host",
                  "wfpt_like_multi_rlddm_host"):

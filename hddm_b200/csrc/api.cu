@@ -1,6 +1,7 @@
 // extern "C" surface of libwfpt_b200.so (declared in include/wfpt_b200.h): argument checks, scratch management,
 // host<->device staging for the `_host` entry points, launch geometry, and the few small kernels that are not
 // density evaluators (second-stage sum, RL Q-recurrence, FP64 issue-rate probe).
+#include <algorithm>
 #include <atomic>
 #include <cmath>
 #include <cstdarg>
@@ -913,6 +914,44 @@ int wfpt_like_contaminant_host(const double* h_x, const int32_t* h_cont, int64_t
 }
 
 // ---- choice-only RL (wfpt.pyx:270-354) -------------------------------------------------------------------------------------
+int wfpt_group_by_split(const int64_t* h_split_by, int64_t n, int64_t* h_order, int64_t* h_starts, int64_t* n_groups)
+{
+    if (n < 0) return fail("negative size");
+    if (!n_groups || !h_starts || (n > 0 && (!h_split_by || !h_order))) return fail("null pointer argument");
+    *n_groups = 0;
+    h_starts[0] = 0;
+    if (n == 0) return 0;
+    int64_t lo = h_split_by[0], hi = h_split_by[0];
+    for (int64_t i = 1; i < n; i++) {
+        lo = h_split_by[i] < lo ? h_split_by[i] : lo;
+        hi = h_split_by[i] > hi ? h_split_by[i] : hi;
+    }
+    if ((uint64_t)(hi - lo) < 65536u) {
+        // the usual case (conditions numbered 0, 1, 2, ...): counting sort, stable by construction
+        const int64_t span = hi - lo + 1;
+        int64_t* cnt = (int64_t*)calloc((size_t)span + 1, sizeof(int64_t));
+        if (!cnt) return fail("out of host memory");
+        for (int64_t i = 0; i < n; i++) cnt[h_split_by[i] - lo + 1]++;
+        int64_t g = 0;
+        for (int64_t v = 0; v < span; v++) {
+            const int64_t c = cnt[v + 1];
+            cnt[v + 1] = cnt[v] + c;              // cnt[v] = first slot of value v
+            if (c) h_starts[++g] = cnt[v + 1];
+        }
+        for (int64_t i = 0; i < n; i++) h_order[cnt[h_split_by[i] - lo]++] = i;
+        *n_groups = g;
+        free(cnt);
+        return 0;
+    }
+    for (int64_t i = 0; i < n; i++) h_order[i] = i;
+    std::stable_sort(h_order, h_order + n, [&](int64_t a, int64_t b) { return h_split_by[a] < h_split_by[b]; });
+    int64_t g = 0;
+    for (int64_t i = 1; i <= n; i++)
+        if (i == n || h_split_by[h_order[i]] != h_split_by[h_order[i - 1]]) h_starts[++g] = i;
+    *n_groups = g;
+    return 0;
+}
+
 int wfpt_like_rl_host(const int64_t* h_response, const double* h_feedback, const int64_t* h_order, const int64_t* h_starts,
                       int64_t n_groups, int64_t n, double q, double alpha, double pos_alpha, double v, double z,
                       double p_outlier, double w_outlier, double* h_out)

@@ -224,12 +224,14 @@ def wiener_like_multi(x, v, sv, a, z, sz, t, st, err, multi=None, n_st=10, n_sz=
 
 # ---- src/wfpt.pyx:78-153 -------------------------------------------------------------------------------------------------
 def _group_by_split(split_by):
-    """The grouping `for s in np.unique(split_by): mask = split_by == s` (wfpt.pyx:99,109-116) as index lists."""
-    order = np.argsort(split_by, kind="stable").astype(np.int64)
-    uniq, counts = np.unique(split_by, return_counts=True)
-    starts = np.zeros(len(uniq) + 1, dtype=np.int64)
-    np.cumsum(counts, out=starts[1:])
-    return order, starts
+    """The grouping `for s in np.unique(split_by): mask = split_by == s` (wfpt.pyx:99,109-116) as index lists (the
+    library's host utility: a counting sort, a few microseconds instead of NumPy's argsort + unique)."""
+    n = split_by.shape[0]
+    order = np.empty(n, dtype=np.int64)
+    starts = np.empty(n + 1, dtype=np.int64)
+    ng = C.c_int64()
+    _lib.check(_lib.load().wfpt_group_by_split(split_by.ctypes.data, n, order.ctypes.data, starts.ctypes.data, C.byref(ng)))
+    return order, starts[:ng.value + 1]
 
 
 def wiener_like_rlddm(x, response, feedback, split_by, q, alpha, pos_alpha, v, sv, a, z, sz, t, st, err, n_st=10,

@@ -143,6 +143,12 @@ int wfpt_like_rl_host(const int64_t* h_response, const double* h_feedback, const
                       int64_t n_groups, int64_t n, double q, double alpha, double pos_alpha, double v, double z,
                       double p_outlier, double w_outlier, double* h_out);
 
+/* Host utility for the callers of the two functions above: the grouping `for s in np.unique(split_by): mask = split_by == s`
+ * (src/wfpt.pyx:99,109-116) as index lists -- order[n] = trial indices group by group (groups by ascending split_by
+ * value, trials in array order inside a group), starts[0..n_groups] = group boundaries in `order`.  starts must hold
+ * n + 1 entries.  No device work. */
+int wfpt_group_by_split(const int64_t* h_split_by, int64_t n, int64_t* h_order, int64_t* h_starts, int64_t* n_groups);
+
 /* Replaces src/wfpt.pyx:390-433 (wiener_like_multi_rlddm): trials in array order, Q reset where split_by changes,
  * per-trial parameters; per_trial[0..6] = v, sv, a, z, sz, t, st and per_trial[7] = alpha (NULL -> scalars[k]). */
 int wfpt_like_multi_rlddm_host(const double* h_x, const int64_t* h_response, const double* h_feedback,

@@ -124,3 +124,19 @@ def test_import_is_lazy():
     code = "import sys; sys.path.insert(0, %r); import wfpt, hddm_b200._lib as L; assert L._lib is None; print('ok')" % ROOT
     out = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True)
     assert out.returncode == 0 and "ok" in out.stdout, out.stderr
+
+
+def test_group_by_split_matches_numpy():
+    """wfpt_group_by_split (host utility, no device work) == np.argsort(kind='stable') + np.unique, the grouping of
+    /root/reference/src/wfpt.pyx:99,109-116."""
+    from hddm_b200 import wfpt as W
+
+    rng = np.random.default_rng(0)
+    cases = [rng.integers(0, 3, 1000), rng.integers(-5, 7, 517), rng.integers(0, 2**40, 300) * 3, np.zeros(5),
+             np.array([]), np.array([7, 7, 2, 9, 2])]
+    for split in cases:
+        split = np.ascontiguousarray(split, dtype=np.int64)
+        order, starts = W._group_by_split(split)
+        uniq, counts = np.unique(split, return_counts=True)
+        assert np.array_equal(order, np.argsort(split, kind="stable"))
+        assert np.array_equal(starts, np.concatenate([[0], np.cumsum(counts)]))
