@@ -60,6 +60,8 @@ struct Tables {
     double cz[2], ct;         // hz/(3 wz) per sign and ht/(3 wt): the fixed-grid Simpson scale as one multiplier
     double inv_wz[2], inv_wt; // reciprocal widths (first adaptive level)
     double zstep[2];          // spacing of the staged z nodes per sign (lattice factor exp(-2 step / tt))
+    double zq[2][4];          // per sign: the exponent of node n is quadratic in n; coefficients of tau and c in its
+                              // linear (beta: [2] tau, [3] c) and quadratic (gamma: [0] tau, [1] c) terms
     double wts_t[kMaxNodes];  // Simpson weights 1 4 2 ... 4 1 along t (fixed grid)
     double wts_z[kMaxNodes];  // same along z
     double exptab[64];        // 2^(j/64)
@@ -315,25 +317,55 @@ __device__ __forceinline__ void nodes(const TNode& tn, const Set& s, int sign, i
         const double tau = tn.inv_tt, m2t = -2.0 * tau;
         bool ok = (K <= 4);
         double e0[N];
-        // the N + 3 exps of the node set as one batch: e0_n, then R, Q and rho
-        constexpr int M = N + (N > 1 ? 3 : 2);
-        double arg[M], val[M];
-#pragma unroll
-        for (int n = 0; n < N; n++) {
-            arg[n] = fma(Z[n].uh1, tau, E[n]);
-            ok &= exp_arg_ok(arg[n]);
-        }
         const double z_first = Z[0].u[1], z_last = Z[N - 1].u[1];
-        arg[N] = fma(m2t, z_first, m2t);                                     // R = exp(-2 (z_0 + 1) / tt)
-        arg[N + 1] = fma(-m2t, z_last, m2t);                                 // Q = exp(-2 (1 - z_last) / tt)
-        if (N > 1) arg[M - 1] = m2t * T.zstep[sign];                         // rho = exp(-2 step / tt)
-        exp_core_batch<M>(arg, val, tab);
+        double R, Q, rho;
+        if (N == 5) {
+            // Five equally spaced nodes (first adaptive level): the exponent of e0_n is quadratic in n,
+            // a_n = a_0 + n beta + n^2 gamma, so e0_{n+1} / e0_n = exp(beta + gamma) exp(2 gamma)^n: three exps and a few
+            // products instead of five exps.  Six exps in all for the node set (with R, Q, rho).
+            const double* zq = T.zq[sign];
+            const double gam = fma(zq[1], tn.c, zq[0] * tau), bet = fma(zq[3], tn.c, zq[2] * tau);
+            double arg[6], val[6];
+            arg[0] = fma(Z[0].uh1, tau, E[0]);
+            arg[1] = bet + gam;                                              // a_1 - a_0
+            arg[2] = 2.0 * gam;
+            arg[3] = fma(m2t, z_first, m2t);                                 // R = exp(-2 (z_0 + 1) / tt)
+            arg[4] = fma(-m2t, z_last, m2t);                                 // Q = exp(-2 (1 - z_last) / tt)
+            arg[5] = m2t * T.zstep[sign];                                    // rho = exp(-2 step / tt)
+            // every e0_n and every ratio between neighbours must be inside the exp kernel's range
+            ok &= exp_arg_ok(arg[0]) & exp_arg_ok(fma(4.0, bet, fma(16.0, gam, arg[0])));
+            ok &= (fabs(arg[1]) < 700.0) & (fabs(fma(7.0, gam, bet)) < 700.0);
+            exp_core_batch<6>(arg, val, tab);
+            double ratio = val[1];
+            e0[0] = val[0];
 #pragma unroll
-        for (int n = 0; n < N; n++) e0[n] = val[n];
-        double R = exp_arg_ok(arg[N]) ? val[N] : 0.0;                        // (true value underflows: 0)
-        double Q = exp_arg_ok(arg[N + 1]) ? val[N + 1] : 0.0;
+            for (int n = 1; n < 5; n++) {
+                e0[n] = e0[n - 1] * ratio;
+                ratio *= val[2];
+            }
+            R = exp_arg_ok(arg[3]) ? val[3] : 0.0;                           // (true value underflows: 0)
+            Q = exp_arg_ok(arg[4]) ? val[4] : 0.0;
+            rho = exp_arg_ok(arg[5]) ? val[5] : 0.0;
+        } else {
+            // the N + 3 exps of the node set as one batch: e0_n, then R, Q and rho
+            constexpr int M = N + (N > 1 ? 3 : 2);
+            double arg[M], val[M];
+#pragma unroll
+            for (int n = 0; n < N; n++) {
+                arg[n] = fma(Z[n].uh1, tau, E[n]);
+                ok &= exp_arg_ok(arg[n]);
+            }
+            arg[N] = fma(m2t, z_first, m2t);                                 // R = exp(-2 (z_0 + 1) / tt)
+            arg[N + 1] = fma(-m2t, z_last, m2t);                             // Q = exp(-2 (1 - z_last) / tt)
+            if (N > 1) arg[M - 1] = m2t * T.zstep[sign];                     // rho = exp(-2 step / tt)
+            exp_core_batch<M>(arg, val, tab);
+#pragma unroll
+            for (int n = 0; n < N; n++) e0[n] = val[n];
+            R = exp_arg_ok(arg[N]) ? val[N] : 0.0;                           // (true value underflows: 0)
+            Q = exp_arg_ok(arg[N + 1]) ? val[N + 1] : 0.0;
+            rho = (N > 1) ? (exp_arg_ok(arg[M - 1]) ? val[M - 1] : 0.0) : 1.0;
+        }
         if (K < 3) Q = 0.0;                                                  // K == 2 sums k = 0, 1 only
-        const double rho = (N > 1) ? (exp_arg_ok(arg[M - 1]) ? val[M - 1] : 0.0) : 1.0;
         double Rn[N], Qn[N];
         Rn[0] = R;
         Qn[N - 1] = Q;
@@ -357,9 +389,26 @@ __device__ __forceinline__ void nodes(const TNode& tn, const Set& s, int sign, i
     } else {
         bool ok = true;
         double ex[N];
+        if (N == 5) {
+            // as above for exp(E_n): E_n = E_0 + n beta + n^2 gamma with the c-parts of beta and gamma only
+            const double* zq = T.zq[sign];
+            const double gam = zq[1] * tn.c, bet = zq[3] * tn.c;
+            double arg[3] = {E[0], bet + gam, 2.0 * gam}, val[3];
+            ok &= exp_arg_ok(E[0]) & exp_arg_ok(E[4]);
+            ok &= (fabs(arg[1]) < 700.0) & (fabs(fma(7.0, gam, bet)) < 700.0);
+            exp_core_batch<3>(arg, val, tab);
+            double ratio = val[1];
+            ex[0] = val[0];
 #pragma unroll
-        for (int n = 0; n < N; n++) ok &= exp_arg_ok(E[n]);
-        exp_core_batch<N>(E, ex, tab);
+            for (int n = 1; n < 5; n++) {
+                ex[n] = ex[n - 1] * ratio;
+                ratio *= val[2];
+            }
+        } else {
+#pragma unroll
+            for (int n = 0; n < N; n++) ok &= exp_arg_ok(E[n]);
+            exp_core_batch<N>(E, ex, tab);
+        }
         if (!ok) {
 #pragma unroll
             for (int n = 0; n < N; n++) ex[n] = exp(E[n]);
@@ -517,6 +566,13 @@ __device__ __forceinline__ void prepare(Set& s, const Params& prm, const Opts& o
         const double hz = (mode == kModeFixed && nz_div > 0) ? __ddiv_rn(w, (double)nz_div) : 0.0;
         T.hz[sign] = hz;
         T.zstep[sign] = (nzn > 1) ? w / (double)(nzn - 1) : 0.0;
+        {
+            const double h = T.zstep[sign], z0 = znode(sign, 0, &w), asv = a * sv, vv = sign ? -prm.v : prm.v;
+            T.zq[sign][0] = -0.5 * h * h;
+            T.zq[sign][1] = (asv * h) * (asv * h);
+            T.zq[sign][2] = -z0 * h;
+            T.zq[sign][3] = 2.0 * asv * asv * z0 * h - 2.0 * a * vv * h;
+        }
         T.cz[sign] = hz / (3.0 * w);
         T.inv_wz[sign] = 1.0 / w;
     }
