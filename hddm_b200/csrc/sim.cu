@@ -773,6 +773,8 @@ static long long pick_chunk(long long n_samples, long long n_sets)
 {
     long long chunk = 4096;
     const long long want_items = (long long)api_sm_count() * 4;
+    // plenty of work: longer items, so that the tail of an item (lanes waiting for its last walks) weighs less
+    while (chunk < 32768 && n_sets * ((n_samples + 2 * chunk - 1) / (2 * chunk)) >= 16 * want_items) chunk *= 2;
     if (n_sets * ((n_samples + chunk - 1) / chunk) < want_items) {
         chunk = (n_samples * n_sets + want_items - 1) / want_items;
         if (chunk < kSimBlock) chunk = kSimBlock;
