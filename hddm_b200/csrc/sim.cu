@@ -52,6 +52,7 @@ struct Args {
     unsigned int* hist;        // [n_sets][nbins][2] or nullptr
     int nbins;
     double hist_step;          // max_t_hist / (nbins - 1)
+    float hist_inv_step;       // its reciprocal in float32: first guess of the bin, corrected against the exact edges
     double hist_max_t;
     unsigned long long* steps; // optional: total Euler steps
     float* traj;               // optional: trajectory of (set 0, particle 0): [int(max_t/dt)+1]
@@ -327,7 +328,7 @@ __global__ void __launch_bounds__(kSimBlock) sim_kernel(const Args A)
             }
             if (done) {
                 // ---- record and take the next particle ----
-                my_steps += (unsigned long long)fix;
+                my_steps += (unsigned int)fix;
                 const float rt = __fadd_rn(tp, t_nd);
                 int choice;
                 if (MODEL == WFPT_SIM_DDM_COV) choice = (y < 0.f) - (y > 0.f);   // -sign(y)
@@ -343,7 +344,7 @@ __global__ void __launch_bounds__(kSimBlock) sim_kernel(const Args A)
                     if (col >= 0) {
                         // np.histogram on edges linspace(0, max_t, nbins) + [inf] (basic_simulator_old.py:99-114)
                         const double rd = (double)rt;
-                        int bin = (int)(rd / A.hist_step);
+                        int bin = (int)(rt * A.hist_inv_step);   // within one bin of the truth; settled below
                         if (bin > A.nbins - 1) bin = A.nbins - 1;
                         if (bin < 0) bin = 0;
                         const double e_lo = (bin == A.nbins - 1) ? A.hist_max_t : bin * A.hist_step;
@@ -453,7 +454,7 @@ __global__ void __launch_bounds__(kSimBlock) race_kernel(const Args A)
             fix += 1.0f;
             if (ANGLE) b = fmaf(fix, sdt, a);
         }
-        my_steps += (unsigned long long)fix;
+        my_steps += (unsigned int)fix;
         int choice = 0;                       // np.argmax: first index of the maximum
         float best = y[0];
 #pragma unroll
@@ -467,7 +468,7 @@ __global__ void __launch_bounds__(kSimBlock) race_kernel(const Args A)
         }
         if (A.hist) {
             const double rd = (double)rt;
-            int bin = (int)(rd / A.hist_step);
+            int bin = (int)(rt * A.hist_inv_step);   // within one bin of the truth; settled below
             if (bin > A.nbins - 1) bin = A.nbins - 1;
             if (bin < 0) bin = 0;
             const double e_lo = (bin == A.nbins - 1) ? A.hist_max_t : bin * A.hist_step;
@@ -596,7 +597,7 @@ __global__ void __launch_bounds__(kSimBlock) hier_kernel(const Args A)
                     fix += 1.0f;
                     if (BOUND != 0) b = bound(fix);
                 }
-                my_steps += (unsigned long long)fix;
+                my_steps += (unsigned int)fix;
                 *t_out = tp;
                 return y;
             };
@@ -659,7 +660,7 @@ __global__ void __launch_bounds__(kSimBlock) hier_kernel(const Args A)
                             }
                         }
                     }
-                    if (count) my_steps += (unsigned long long)fix;
+                    if (count) my_steps += (unsigned int)fix;
                     rt_q = __fadd_rn(tp, t_nd);
                     yl_nonneg = y_l >= 0.f;
                     return stale;
@@ -732,7 +733,7 @@ __global__ void __launch_bounds__(kSimBlock) hier_kernel(const Args A)
         }
         if (A.hist) {
             const double rd = (double)rt;
-            int bin = (int)(rd / A.hist_step);
+            int bin = (int)(rt * A.hist_inv_step);   // within one bin of the truth; settled below
             if (bin > A.nbins - 1) bin = A.nbins - 1;
             if (bin < 0) bin = 0;
             const double e_lo = (bin == A.nbins - 1) ? A.hist_max_t : bin * A.hist_step;
@@ -865,6 +866,7 @@ extern "C" int wfpt_sim_run(int model, const float* d_theta, int n_par, int n_se
     A.hist = d_hist; A.nbins = d_hist ? nbins : 0;
     A.hist_max_t = (double)hist_max_t;
     A.hist_step = d_hist ? (double)hist_max_t / (double)(nbins - 1) : 1.0;
+    A.hist_inv_step = (float)(1.0 / A.hist_step);
     A.steps = (unsigned long long*)d_steps;
     A.traj = d_traj; A.traj_len = traj_len;
 
@@ -985,6 +987,7 @@ extern "C" int wfpt_sim_race_run_host(int lca, int n_particles, int angle, const
     A.out_stride_samples = n_samples; A.dt = delta_t; A.max_t = max_t; A.s = s; A.set_seed(seed); A.rts = d_rts; A.choices = d_ch;
     A.hist = d_hist; A.nbins = d_hist ? nbins : 0; A.hist_max_t = (double)hist_max_t;
     A.hist_step = d_hist ? (double)hist_max_t / (double)(nbins - 1) : 1.0;
+    A.hist_inv_step = (float)(1.0 / A.hist_step);
     A.steps = (unsigned long long*)d_steps; A.traj = nullptr; A.traj_len = 0;
     A.chunk = sim::pick_chunk(n_samples, n_sets);
     A.items_per_set = (n_samples + A.chunk - 1) / A.chunk;
@@ -1040,6 +1043,7 @@ static int run_hier_host(const char* who, int kind, int bound_kind, const float*
     A.out_stride_samples = n_samples; A.dt = delta_t; A.max_t = max_t; A.s = s; A.set_seed(seed); A.rts = d_rts; A.choices = d_ch;
     A.hist = d_hist; A.nbins = d_hist ? nbins : 0; A.hist_max_t = (double)hist_max_t;
     A.hist_step = d_hist ? (double)hist_max_t / (double)(nbins - 1) : 1.0;
+    A.hist_inv_step = (float)(1.0 / A.hist_step);
     A.steps = (unsigned long long*)d_steps; A.traj = nullptr; A.traj_len = 0;
     A.chunk = sim::pick_chunk(n_samples, n_sets);
     A.items_per_set = (n_samples + A.chunk - 1) / A.chunk;
