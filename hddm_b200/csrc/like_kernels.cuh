@@ -3,12 +3,14 @@
 //   like_batch_kernel   wiener_like for P parameter sets on one RT array      (/root/reference/src/wfpt.pyx:54-76)
 //   pdf_array_kernel    per-trial densities                                      (wfpt.pyx:32-48)
 //   like_multi_kernel   per-trial parameters, +-999 coding, RL-DDM drift scaling (wfpt.pyx:357-387, :78-153)
-//   finalize_kernel     second stage of the deterministic two-stage trial sum
+//   finalize_kernel     second stage of the deterministic two-stage trial sum, for callers that do not pass arrival
+//                       counters (like_batch_kernel otherwise does it itself: the slice that finishes last sums)
 //
 // Data layout in HBM: RTs are one contiguous float64[n]; parameter sets are float64[P][8] rows
 // (v, sv, a, z, sz, t, st, p_outlier); outputs float64[P].  One CTA = (one parameter set, one slice of trials);
-// its 128 threads walk the slice with coalesced 16-byte loads (two RTs per thread per step), reduce with warp
-// shuffles, and either write the final sum (slices == 1) or a partial into scratch (slices > 1).
+// its 128 threads walk the slice with coalesced 16-byte loads (two RTs per thread per step; one RT per thread and
+// interleaved slices for small grids), reduce with warp shuffles, and either write the final sum (slices == 1) or a
+// partial into scratch (slices > 1).
 #pragma once
 #include "common.cuh"
 
