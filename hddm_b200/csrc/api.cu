@@ -604,6 +604,23 @@ int wfpt_pdf_array_host(const double* h_x, int64_t n, const double* params8, dou
     if (n == 0) return 0;
     if (!h_x || !h_y) return fail("null pointer argument");
     void *dx, *dy;
+    if (sizeof(double) * (size_t)n <= kPinOutBytes) {
+        // small call: x through the pinned block, densities written straight into its mapped head
+        const void* src[1] = {h_x};
+        const size_t bytes[1] = {sizeof(double) * (size_t)n};
+        void* dev[1];
+        double* mapped;
+        char* pin_host;
+        if (stage_in(1, src, bytes, kStageX, dev, &mapped, &pin_host)) return 1;
+        if (mapped) {
+            if (wfpt_pdf_array((const double*)dev[0], n, params8, err, n_st, n_sz, use_adaptive, simps_err, w_outlier, logp,
+                               variant, mapped, nullptr))
+                return 1;
+            CK(cudaStreamSynchronize(0));
+            memcpy(h_y, pin_host, sizeof(double) * (size_t)n);
+            return 0;
+        }
+    }
     if (scratch(kStageX, sizeof(double) * (size_t)n, &dx)) return 1;
     if (scratch(kStageOut, sizeof(double) * (size_t)n, &dy)) return 1;
     CK(cudaMemcpyAsync(dx, h_x, sizeof(double) * (size_t)n, cudaMemcpyHostToDevice, 0));
