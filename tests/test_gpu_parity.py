@@ -296,3 +296,32 @@ def test_batch_host_sizes_through_both_staging_paths(oracle, wfpt_gpu):
         want = oracle.wiener_like_batch(x, prm[idx], 1e-4, 2, 2, 1, 1e-3, 0.1)
         assert rel_err(got[idx], want) < TOL, P
         assert np.all(np.isfinite(got))
+
+
+def test_random_option_sweep_vs_oracle(oracle, wfpt_gpu):
+    """Random calls over the option space (sizes around the launch-plan switches, fixed / adaptive integration with
+    budgets 0..4 and grids 2..6, err, simps_err, sv/sz/st on or off, presorted or not): same NaN / inf pattern as the
+    oracle, finite values within TOL."""
+    rng = np.random.default_rng(77)
+    for _ in range(150):
+        n = int(rng.choice([1, 3, 17, 128, 129, 300, 1000, 2500]))
+        x = np.where(rng.random(n) < 0.7, 1.0, -1.0) * rng.uniform(0.25, 3.5, n)
+        P = int(rng.choice([1, 1, 2, 7, 33]))
+        prm = np.stack([rng.uniform(-4, 4, P), rng.choice([0.0, 1.0], P) * rng.uniform(0, 3, P), rng.uniform(0.4, 4, P),
+                        rng.uniform(0.25, 0.75, P), rng.choice([0.0, 1.0], P) * rng.uniform(0, 0.3, P),
+                        rng.uniform(0.05, 1.5, P), rng.choice([0.0, 1.0], P) * rng.uniform(0, 0.3, P),
+                        rng.choice([0.0, 0.05], P)], axis=1)
+        ad = int(rng.integers(0, 2))
+        if ad:
+            n_st, n_sz = int(rng.integers(0, 5)), int(rng.integers(0, 5))
+        else:
+            n_st, n_sz = int(rng.choice([2, 4, 6])), int(rng.choice([2, 4]))
+        se, err = float(rng.choice([1e-2, 1e-3, 1e-5, 1e-8])), float(rng.choice([1e-3, 1e-4, 1e-6]))
+        want = oracle.wiener_like_batch(x, prm, err, n_st, n_sz, ad, se, 0.1)
+        got = wfpt_gpu.wiener_like_batch(x, prm, err, n_st, n_sz, ad, se, 0.1, presort=bool(rng.integers(0, 2)))
+        ctx = dict(n=n, P=P, ad=ad, n_st=n_st, n_sz=n_sz, se=se, err=err)
+        assert np.array_equal(np.isnan(got), np.isnan(want)), ctx
+        assert np.array_equal(np.isinf(got), np.isinf(want)), ctx
+        fin = np.isfinite(want)
+        if fin.any():
+            assert rel_err(got[fin], want[fin]) < TOL, ctx
