@@ -247,3 +247,28 @@ def test_choice_probability_at_1e7_particles(sims, oracle):
     assert abs(p3 - p_gpu) < 5 * np.sqrt(2 * p_true * (1 - p_true) / n)
     ks = np.max(np.abs(np.cumsum(hist[0].sum(1).astype(np.int64)) - np.cumsum(hist3[0].sum(1).astype(np.int64)))) / n
     assert ks < 1.95 * np.sqrt(2 / n)  # two-sample KS at alpha = 0.001 on the binned RTs
+
+
+def test_every_model_name_runs(sims):
+    """All 42 names of the simulator boundary: shapes, finite positive RTs, choices inside `possible_choices`, and every
+    parameter name in the metadata (hddm/tests/test_simulators.py:78-87 does this for the reference's list)."""
+    defaults = {"v": 0.8, "a": 1.3, "z": 0.5, "t": 0.3, "theta": 0.3, "alpha": 1.8, "beta": 2.0, "sz": 0.1, "sv": 0.5, "st": 0.1,
+                "g": 0.3, "b": 0.2, "shape": 2.0, "scale": 1.5, "c": 1.0, "tinit": 0.5, "dinit": 0.5, "tslope": 1.0,
+                "dslope": 1.0, "tfixedp": 1.0, "tcoh": 0.5, "dcoh": 0.5, "angle": 0.3, "vh": 0.8, "vl1": 0.5, "vl2": -0.5,
+                "zh": 0.5, "zl1": 0.5, "zl2": 0.5, "d": 0.5, "alphagamma": 2.0, "scalegamma": 0.6}
+    assert len(sims.model_config) == 42
+    for name, cfg in sims.model_config.items():
+        th = []
+        for p_name in cfg["params"]:
+            if p_name in defaults:
+                th.append(defaults[p_name])
+            elif p_name[0] == "v":
+                th.append(0.5 + 0.3 * int(p_name[1:]))
+            else:
+                assert p_name[0] == "z", p_name
+                th.append(0.3)
+        rts, ch, meta = sims.simulator(th, model=name, n_samples=1500, random_state=1)
+        assert rts.shape == (1500, 1) and ch.shape == (1500, 1), name
+        assert np.isfinite(rts).all() and (rts > 0).all(), name
+        assert set(np.unique(ch).tolist()) <= set(meta["possible_choices"]), name
+        assert meta["model"] == name and all(p_name in meta for p_name in cfg["params"]), name
