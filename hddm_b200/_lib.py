@@ -54,6 +54,12 @@ def _declare(L):
     L.wfpt_like_segments.argtypes = [vp, vp, i64, vp, i64] + opts + [d, i, vp, vp]
     L.wfpt_like_segments_host.argtypes = [vp, vp, vp, i64] + opts + [d, i, vp]
     L.wfpt_like_segments_resident.argtypes = [vp, vp, i64, vp, i64] + opts + [d, i, vp]
+    L.wfpt_resident_create.argtypes = [vp, i64, vp, i64, vp]
+    L.wfpt_resident_logp.argtypes = [C.c_uint64, vp, vp, i64] + opts + [d, i, vp]
+    L.wfpt_resident_pointers.argtypes = [C.c_uint64, vp, vp, vp, vp]
+    L.wfpt_resident_release.argtypes = [C.c_uint64]
+    for name in ("wfpt_resident_create", "wfpt_resident_logp", "wfpt_resident_pointers", "wfpt_resident_release"):
+        getattr(L, name).restype = i
     L.wfpt_like_contaminant_host.argtypes = [vp, vp, i64] + [d] * 9 + opts + [i, vp]
     L.wfpt_like_rl_host.argtypes = [vp, vp, vp, vp, i64, i64] + [d] * 7 + [vp]
     L.wfpt_group_by_split.argtypes = [vp, i64, vp, vp, vp]

@@ -9,6 +9,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <mutex>
+#include <new>
 
 #include "../../include/wfpt_b200.h"
 #include "common.cuh"
@@ -859,6 +860,120 @@ int wfpt_like_segments_resident(const double* d_x, const int64_t* d_seg, int64_t
                            variant, (double*)dout, nullptr))
         return 1;
     CK(cudaMemcpyAsync(h_out, dout, obytes, cudaMemcpyDeviceToHost, 0));
+    CK(cudaStreamSynchronize(0));
+    return 0;
+}
+
+// ---- resident data behind a handle (no device pointers cross the boundary) ------------------------------------------------
+struct Resident {
+    int dev = 0;
+    double* d_x = nullptr;
+    int64_t* d_seg = nullptr;      // [n_nodes][2]
+    int64_t* h_seg = nullptr;      // host copy, for subsets
+    int64_t n_nodes = 0, mean_len = 1;
+};
+
+int wfpt_resident_create(const double* h_x, int64_t total, const int64_t* h_seg, int64_t n_nodes, uint64_t* handle)
+{
+    if (!handle) return fail("null pointer argument");
+    *handle = 0;
+    if (total < 0 || n_nodes < 0) return fail("negative size");
+    if ((total > 0 && !h_x) || (n_nodes > 0 && !h_seg)) return fail("null pointer argument");
+    int64_t sum = 0;
+    for (int64_t p = 0; p < n_nodes; p++) {
+        if (h_seg[2 * p] < 0 || h_seg[2 * p + 1] < h_seg[2 * p] || h_seg[2 * p + 1] > total)
+            return fail("segment %lld is not inside the RT array", (long long)p);
+        sum += h_seg[2 * p + 1] - h_seg[2 * p];
+    }
+    Resident* r = new (std::nothrow) Resident();
+    if (!r) return fail("out of host memory");
+    cudaGetDevice(&r->dev);
+    r->n_nodes = n_nodes;
+    r->mean_len = n_nodes > 0 && sum / n_nodes > 0 ? sum / n_nodes : 1;
+    const size_t xb = sizeof(double) * (size_t)(total > 0 ? total : 1), sb = sizeof(int64_t) * 2 * (size_t)(n_nodes > 0 ? n_nodes : 1);
+    r->h_seg = (int64_t*)malloc(sb);
+    cudaError_t e = r->h_seg ? cudaMalloc(&r->d_x, xb) : cudaErrorMemoryAllocation;
+    if (e == cudaSuccess) e = cudaMalloc(&r->d_seg, sb);
+    if (e == cudaSuccess && total > 0) e = cudaMemcpy(r->d_x, h_x, sizeof(double) * (size_t)total, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess && n_nodes > 0) {
+        memcpy(r->h_seg, h_seg, sizeof(int64_t) * 2 * (size_t)n_nodes);
+        e = cudaMemcpy(r->d_seg, h_seg, sizeof(int64_t) * 2 * (size_t)n_nodes, cudaMemcpyHostToDevice);
+    }
+    if (e != cudaSuccess) {
+        cudaFree(r->d_x); cudaFree(r->d_seg); free(r->h_seg);
+        delete r;
+        return fail("%s", cudaGetErrorString(e));
+    }
+    *handle = (uint64_t)(uintptr_t)r;
+    return 0;
+}
+
+int wfpt_resident_release(uint64_t handle)
+{
+    Resident* r = (Resident*)(uintptr_t)handle;
+    if (!r) return 0;
+    cudaFree(r->d_x); cudaFree(r->d_seg); free(r->h_seg);
+    delete r;
+    return 0;
+}
+
+int wfpt_resident_pointers(uint64_t handle, const double** d_x, const int64_t** d_seg, int64_t* n_nodes, int64_t* mean_len)
+{
+    Resident* r = (Resident*)(uintptr_t)handle;
+    if (!r) return fail("null handle");
+    if (d_x) *d_x = r->d_x;
+    if (d_seg) *d_seg = r->d_seg;
+    if (n_nodes) *n_nodes = r->n_nodes;
+    if (mean_len) *mean_len = r->mean_len;
+    return 0;
+}
+
+int wfpt_resident_logp(uint64_t handle, const int64_t* h_nodes, const double* h_params, int64_t P, double err, int n_st,
+                       int n_sz, int use_adaptive, double simps_err, double w_outlier, int variant, double* h_out)
+{
+    Resident* r = (Resident*)(uintptr_t)handle;
+    if (!r) return fail("null handle");
+    if (P < 0) return fail("negative size");
+    if (P == 0) return 0;
+    if (!h_params || !h_out) return fail("null pointer argument");
+    if (!h_nodes) {
+        if (P != r->n_nodes) return fail("params has %lld rows for %lld resident nodes", (long long)P, (long long)r->n_nodes);
+        return wfpt_like_segments_resident(r->d_x, r->d_seg, r->mean_len, h_params, P, err, n_st, n_sz, use_adaptive,
+                                           simps_err, w_outlier, variant, h_out);
+    }
+    // a subset / several proposals per node: segment rows picked on the host, staged together with the parameters
+    const size_t pbytes = sizeof(double) * 8 * (size_t)P, sbytes = sizeof(int64_t) * 2 * (size_t)P;
+    int64_t* seg = (int64_t*)malloc(sbytes);
+    if (!seg) return fail("out of host memory");
+    int64_t sum = 0;
+    for (int64_t i = 0; i < P; i++) {
+        const int64_t k = h_nodes[i];
+        if (k < 0 || k >= r->n_nodes) { free(seg); return fail("node index %lld out of range", (long long)k); }
+        seg[2 * i] = r->h_seg[2 * k];
+        seg[2 * i + 1] = r->h_seg[2 * k + 1];
+        sum += seg[2 * i + 1] - seg[2 * i];
+    }
+    const void* src[2] = {h_params, seg};
+    const size_t bytes[2] = {pbytes, sbytes};
+    void* dev[2];
+    double* mapped;
+    char* pin_host;
+    int rc = stage_in(2, src, bytes, kStageAux6, dev, &mapped, &pin_host);
+    free(seg);
+    if (rc) return 1;
+    void* dout = nullptr;
+    const bool direct = mapped && sizeof(double) * (size_t)P <= kPinOutBytes;
+    if (!direct && scratch(kStageOut, sizeof(double) * (size_t)P, &dout)) return 1;
+    const int64_t mean_len = sum / P > 0 ? sum / P : 1;
+    if (wfpt_like_segments(r->d_x, (const int64_t*)dev[1], mean_len, (const double*)dev[0], P, err, n_st, n_sz, use_adaptive,
+                           simps_err, w_outlier, variant, direct ? mapped : (double*)dout, nullptr))
+        return 1;
+    if (direct) {
+        CK(cudaStreamSynchronize(0));
+        memcpy(h_out, pin_host, sizeof(double) * (size_t)P);
+        return 0;
+    }
+    CK(cudaMemcpyAsync(h_out, dout, sizeof(double) * (size_t)P, cudaMemcpyDeviceToHost, 0));
     CK(cudaStreamSynchronize(0));
     return 0;
 }

@@ -312,13 +312,11 @@ class ResidentData:
     uploads the arrays once (each |rt|-sorted, packed back to back on even offsets); `logp(params)` evaluates
     wiener_like for every node -- params[i] belongs to arrays[i] -- in ONE kernel launch and returns float64[len(arrays)].
     `logp(params, nodes=idx)` evaluates a subset (params[i] belongs to arrays[idx[i]]; a node may appear many times,
-    e.g. several proposals for the same node).  Needs torch (device memory and streams only)."""
+    e.g. several proposals for the same node).  The device memory belongs to the library (`wfpt_resident_*`): NumPy in,
+    NumPy out needs nothing but ctypes; torch CUDA tensors as `params` are accepted too (result stays on the device,
+    enqueued on torch's current stream)."""
 
     def __init__(self, arrays, device=None):
-        import torch
-
-        self._torch = torch
-        self.device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
         arrs = [sort_rts(_buffer(np.asarray(a), "x")) for a in arrays]
         self.lengths = np.array([len(a) for a in arrs], dtype=np.int64)
         starts = np.zeros(len(arrs) + 1, dtype=np.int64)
@@ -331,57 +329,86 @@ class ResidentData:
         for a, s0 in zip(arrs, starts[:-1]):
             packed[s0:s0 + len(a)] = a
         self.starts = starts[:-1].copy()
-        self.x = torch.from_numpy(packed).to(self.device)
-        self._seg_all = self._segments(np.arange(len(arrs)))
-        self._dseg_all = torch.from_numpy(self._seg_all.reshape(-1).copy()).to(self.device)   # (empty for no arrays)
-        self._x_ptr, self._dseg_ptr = self.x.data_ptr(), self._dseg_all.data_ptr()
-        self._dev_index = self.device.index if self.device.index is not None else torch.cuda.current_device()
+        self.n_nodes = len(arrs)
+        seg = np.ascontiguousarray(np.stack([self.starts, self.starts + self.lengths], axis=1), dtype=np.int64) \
+            if arrs else np.zeros((0, 2), dtype=np.int64)
+        self._seg_all = seg
         self.mean_len = int(max(1, self.lengths.mean())) if len(arrs) else 1
+        self._device = None
+        if device is not None:
+            import torch
 
-    def _segments(self, nodes):
-        st = self.starts[nodes]
-        return np.ascontiguousarray(np.stack([st, st + self.lengths[nodes]], axis=1), dtype=np.int64)
+            self._device = torch.device(device)
+        L = _lib.load()
+        h = C.c_uint64()
+        with self._on_device():
+            _lib.check(L.wfpt_resident_create(packed.ctypes.data, packed.shape[0], seg.ctypes.data, self.n_nodes, C.byref(h)))
+        self._h = h
+        dx, dseg = C.c_void_p(), C.c_void_p()
+        _lib.check(L.wfpt_resident_pointers(h, C.byref(dx), C.byref(dseg), None, None))
+        self._x_ptr, self._dseg_ptr = dx.value, dseg.value
+
+    def _on_device(self):
+        """Context for library calls: torch's device guard when a device was named, nothing otherwise (the library
+        then works on the CUDA runtime's current device, as every other entry point does)."""
+        if self._device is None:
+            import contextlib
+
+            return contextlib.nullcontext()
+        import torch
+
+        return torch.cuda.device(self._device)
+
+    def close(self):
+        h, self._h = getattr(self, "_h", None), None
+        if h is not None:
+            try:
+                _lib.load().wfpt_resident_release(h)
+            except Exception:  # interpreter shutdown
+                pass
+
+    __del__ = close
 
     def logp(self, params, nodes=None, err=1e-4, n_st=2, n_sz=2, use_adaptive=1, simps_err=1e-3, w_outlier=0.1,
              variant=None):
-        torch = self._torch
         var = _variant if variant is None else variant
-        if nodes is None:
-            P, dseg_ptr, keep = self._seg_all.shape[0], self._dseg_ptr, None
-        else:
-            seg = self._segments(np.asarray(nodes, dtype=np.int64))
-            keep = torch.from_numpy(seg.reshape(-1)).to(self.device)
-            P, dseg_ptr = seg.shape[0], keep.data_ptr()
         L = _lib.load()
         o = _opts(err, n_st, n_sz, use_adaptive, simps_err)
-        # (torch's device context manager and stream lookup cost tens of microseconds: only used when actually needed)
-        same_dev = torch.cuda.current_device() == self._dev_index
+        idx = None if nodes is None else np.ascontiguousarray(nodes, dtype=np.int64)
+        P = self.n_nodes if idx is None else idx.shape[0]
         if isinstance(params, np.ndarray):
-            # host parameters in, host log-likelihoods out: the library stages both through pinned memory
             ps = params if (params.dtype == _F64 and params.flags.c_contiguous) else np.ascontiguousarray(params, dtype=np.double)
             if ps.shape != (P, 8):
                 raise ValueError(f"params must have shape ({P}, 8)")
             res = np.empty(P, dtype=np.double)
             if P:
-                args = (self._x_ptr, dseg_ptr, self.mean_len, ps.ctypes.data, P, *o, float(w_outlier), var, res.ctypes.data)
-                if same_dev:
-                    rc = L.wfpt_like_segments_resident(*args)
+                args = (self._h, None if idx is None else idx.ctypes.data, ps.ctypes.data, P, *o, float(w_outlier), var,
+                        res.ctypes.data)
+                if self._device is None:
+                    rc = L.wfpt_resident_logp(*args)
                 else:
-                    with torch.cuda.device(self.device):
-                        rc = L.wfpt_like_segments_resident(*args)
+                    with self._on_device():
+                        rc = L.wfpt_resident_logp(*args)
                 if rc:
                     _lib.check(rc)
             return res
+        import torch  # device-resident parameters: torch owns them and the stream
+
         ps = params.contiguous()
         if ps.shape != (P, 8):
             raise ValueError(f"params must have shape ({P}, 8)")
-        out = torch.empty(P, dtype=torch.float64, device=self.device)
+        out = torch.empty(P, dtype=torch.float64, device=ps.device)
         if P == 0:
             return out
-        with torch.cuda.device(self.device):
+        if idx is None:
+            dseg_ptr, mean_len, keep = self._dseg_ptr, self.mean_len, None
+        else:
+            keep = torch.from_numpy(self._seg_all[idx].reshape(-1)).to(ps.device)
+            dseg_ptr, mean_len = keep.data_ptr(), int(max(1, self.lengths[idx].mean()))
+        with torch.cuda.device(ps.device):
             s = torch.cuda.current_stream().cuda_stream
-            _lib.check(L.wfpt_like_segments(self._x_ptr, dseg_ptr, self.mean_len, ps.data_ptr(), P, *o,
-                                            float(w_outlier), var, out.data_ptr(), s))
+            _lib.check(L.wfpt_like_segments(self._x_ptr, dseg_ptr, mean_len, ps.data_ptr(), P, *o, float(w_outlier), var,
+                                            out.data_ptr(), s))
         return out
 
 

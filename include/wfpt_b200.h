@@ -131,6 +131,20 @@ int wfpt_like_segments_resident(const double* d_x, const int64_t* d_seg, int64_t
                                 int64_t P, double err, int n_st, int n_sz, int use_adaptive, double simps_err,
                                 double w_outlier, int variant, double* h_out);
 
+/* The same behind a handle, for callers that hold no device pointers (a sampler driving the library through ctypes
+ * only): wfpt_resident_create uploads the packed RT array (each node's RTs |rt|-sorted by the caller, see
+ * hddm_b200.wfpt.sort_rts) and the node table seg[n_nodes][2] once; wfpt_resident_logp evaluates one parameter row
+ * per node (h_nodes == NULL, P == n_nodes) or per entry of h_nodes (a node may be named several times: several
+ * proposals for it), host parameters in, host log-likelihoods out; wfpt_resident_release frees the device memory.
+ * wfpt_resident_pointers exposes the device addresses for callers that want to pass device-resident parameters to
+ * wfpt_like_segments themselves.  One RT array per likelihood node of a hierarchical model
+ * (hddm/models/base.py:1488-1493); no reference counterpart at this level. */
+int wfpt_resident_create(const double* h_x, int64_t total, const int64_t* h_seg, int64_t n_nodes, uint64_t* handle);
+int wfpt_resident_logp(uint64_t handle, const int64_t* h_nodes, const double* h_params, int64_t P, double err, int n_st,
+                       int n_sz, int use_adaptive, double simps_err, double w_outlier, int variant, double* h_out);
+int wfpt_resident_pointers(uint64_t handle, const double** d_x, const int64_t** d_seg, int64_t* n_nodes, int64_t* mean_len);
+int wfpt_resident_release(uint64_t handle);
+
 /* Replaces src/wfpt.pyx:551-580 (wiener_like_contaminant): trials with cont_x == 0 enter the diffusion likelihood (no
  * outlier mix, -inf on the first zero density), the others contribute n_cont * log(0.5 / (t_max - t_min)). */
 int wfpt_like_contaminant_host(const double* h_x, const int32_t* h_cont, int64_t n, double v, double sv, double a, double z,

@@ -181,6 +181,16 @@ def test_segments_resident_data(oracle, wfpt_gpu, variant):
     idx = np.array([3, 3, 59, 0, 3])
     got = rd.logp(prm[idx], nodes=idx, variant=variant, **kw)
     assert rel_err(got, want[idx]) <= TOL
+    # device-resident parameters (torch tensors) through the same handle's device pointers
+    import torch
+
+    got_t = rd.logp(torch.from_numpy(prm).cuda(), variant=variant, **kw)
+    assert got_t.is_cuda and np.array_equal(got_t.cpu().numpy(), rd.logp(prm, variant=variant, **kw))
+    got_t = rd.logp(torch.from_numpy(prm[idx]).cuda(), nodes=idx, variant=variant, **kw)
+    assert rel_err(got_t.cpu().numpy(), want[idx]) <= TOL
+    with pytest.raises(wfpt_gpu.WfptError):
+        rd.logp(prm[:2], nodes=np.array([0, 60]), variant=variant, **kw)
+    rd.close()
     got = wfpt_gpu.wiener_like_segments(arrays[:5], prm[:5], variant=variant, **kw)
     assert rel_err(got, want[:5]) <= TOL
     # one long node: the segment is cut into many slices
