@@ -47,6 +47,10 @@ def _declare(L):
     L.wfpt_ktable.restype = i
     L.wfpt_ktable_decision.argtypes = [d, d]
     L.wfpt_ktable_decision.restype = i
+    L.wfpt_ktable_decision_array.argtypes = [vp, i64, d, vp]
+    L.wfpt_ktable_decision_array.restype = i
+    L.wfpt_kflip_census.argtypes = [vp, i64, vp, i64, d, i, i, i, vp, vp]
+    L.wfpt_kflip_census.restype = i
     for name in ("wfpt_device_info", "wfpt_release_scratch", "wfpt_fp64_peak", "wfpt_like_batch",
                  "wfpt_like_batch_host", "wfpt_pdf_array", "wfpt_pdf_array_host", "wfpt_like_multi",
                  "wfpt_like_multi_host", "wfpt_like_rlddm_host"):
@@ -135,6 +139,16 @@ def ktable(err: float) -> dict:
 
 def ktable_decision(tt: float, err: float) -> int:
     return int(load().wfpt_ktable_decision(float(tt), float(err)))
+
+
+def ktable_decision_array(tt, err: float):
+    """The reference's series-term decision (host libm, src/pdf.pxi:35-60) for an array of tt; int32 descriptors."""
+    import numpy as np
+
+    tt = np.ascontiguousarray(tt, dtype=np.float64)
+    out = np.empty(tt.shape[0], dtype=np.int32)
+    check(load().wfpt_ktable_decision_array(tt.ctypes.data, tt.shape[0], float(err), out.ctypes.data))
+    return out
 
 
 def fp64_peak(iters: int = 8192) -> dict:

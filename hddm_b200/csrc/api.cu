@@ -44,6 +44,16 @@ constexpr int kMaxDev = 16;
 struct Buf { void* p = nullptr; size_t cap = 0; };
 static Buf g_buf[kMaxDev][kNumSlots];
 static std::mutex g_mu;
+static std::recursive_mutex g_call_mu[kMaxDev + 1];   // [kMaxDev]: devices beyond the tracked range (calls fail anyway)
+
+HostCall::HostCall()
+{
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= kMaxDev) dev = kMaxDev;
+    dev_ = dev;
+    g_call_mu[dev_].lock();
+}
+HostCall::~HostCall() { g_call_mu[dev_].unlock(); }
 
 static int scratch(int slot, size_t bytes, void** out)
 {
@@ -430,6 +440,10 @@ int api_sim_scratch(int which, size_t bytes, void** out)
     return scratch(kSim0 + which, bytes < 16 ? 16 : bytes, out);
 }
 int api_sm_count() { return sm_count(); }
+int api_scratch_pair(size_t bytes0, size_t bytes1, void** p0, void** p1)
+{
+    return scratch(kStageX, bytes0 < 16 ? 16 : bytes0, p0) || scratch(kStageOut, bytes1 < 16 ? 16 : bytes1, p1);
+}
 int api_check_opts(double err, int n_st, int n_sz, int use_adaptive, double simps_err, int variant, Opts* o)
 {
     return check_opts(err, n_st, n_sz, use_adaptive, simps_err, variant, o);
@@ -488,6 +502,7 @@ int wfpt_release_scratch(void)
 
 int wfpt_fp64_peak(int iters, double* dfma_per_s, double* ms_out)
 {
+    HostCall guard_;
     if (iters <= 0) iters = 4096;
     void* sink = nullptr;
     if (scratch(kStageOut, 64, &sink)) return 1;
@@ -546,6 +561,7 @@ int wfpt_like_batch(const double* d_x, int64_t n, const double* d_params, int64_
 int wfpt_like_batch_host(const double* h_x, int64_t n, const double* h_params, int64_t P, double err, int n_st,
                          int n_sz, int use_adaptive, double simps_err, double w_outlier, int variant, double* h_out)
 {
+    HostCall guard_;
     if (n < 0 || P < 0) return fail("negative size");
     if (P == 0) return 0;
     if (!h_params || !h_out || (n > 0 && !h_x)) return fail("null pointer argument");
@@ -581,6 +597,19 @@ int wfpt_like_batch_host(const double* h_x, int64_t n, const double* h_params, i
     return 0;
 }
 
+// ---- series-term decision census (diagnostic) -------------------------------------------------------------------------
+int wfpt_kflip_census(const double* d_x, int64_t n, const double* d_params, int64_t P, double err, int n_st, int n_sz,
+                      int use_adaptive, uint64_t* d_counts3, void* stream)
+{
+    Opts o;
+    if (check_opts(err, n_st, n_sz, use_adaptive, 1e-3, WFPT_VARIANT_FAST, &o)) return 1;
+    if (n < 0 || P < 0) return fail("negative size");
+    if (!d_counts3 || (P > 0 && !d_params) || (n > 0 && !d_x)) return fail("null pointer argument");
+    CK(launch_kflip_census(d_x, n, d_params, P, o, (unsigned long long*)d_counts3, (cudaStream_t)stream));
+    count_launch(P > 0 ? 1 : 0);
+    return 0;
+}
+
 // ---- pdf_array -----------------------------------------------------------------------------------------------------------
 int wfpt_pdf_array(const double* d_x, int64_t n, const double* params8, double err, int n_st, int n_sz,
                    int use_adaptive, double simps_err, double w_outlier, int logp, int variant, double* d_y, void* stream)
@@ -601,6 +630,7 @@ int wfpt_pdf_array(const double* d_x, int64_t n, const double* params8, double e
 int wfpt_pdf_array_host(const double* h_x, int64_t n, const double* params8, double err, int n_st, int n_sz,
                         int use_adaptive, double simps_err, double w_outlier, int logp, int variant, double* h_y)
 {
+    HostCall guard_;
     if (n < 0) return fail("negative size");
     if (n == 0) return 0;
     if (!h_x || !h_y) return fail("null pointer argument");
@@ -678,6 +708,7 @@ int wfpt_like_multi_host(const double* h_x, int64_t n, const double* const h_per
                          double err, int n_st, int n_sz, int use_adaptive, double simps_err, double p_outlier,
                          double w_outlier, int variant, double* h_out)
 {
+    HostCall guard_;
     if (n < 0) return fail("negative size");
     if (!h_out || !scalars || (n > 0 && !h_x)) return fail("null pointer argument");
     void *dx, *dout;
@@ -737,6 +768,7 @@ int wfpt_like_rlddm_host(const double* h_x, const int64_t* h_response, const dou
                          int n_sz, int use_adaptive, double simps_err, double p_outlier, double w_outlier, int variant,
                          double* h_out)
 {
+    HostCall guard_;
     Opts o;
     if (check_opts(err, n_st, n_sz, use_adaptive, simps_err, variant, &o)) return 1;
     if (n < 0 || n_groups < 0) return fail("negative size");
@@ -829,6 +861,7 @@ int wfpt_like_segments_resident(const double* d_x, const int64_t* d_seg, int64_t
                                 int64_t P, double err, int n_st, int n_sz, int use_adaptive, double simps_err,
                                 double w_outlier, int variant, double* h_out)
 {
+    HostCall guard_;
     if (P < 0) return fail("negative size");
     if (P == 0) return 0;
     if (!h_params || !h_out) return fail("null pointer argument");
@@ -931,6 +964,7 @@ int wfpt_resident_pointers(uint64_t handle, const double** d_x, const int64_t** 
 int wfpt_resident_logp(uint64_t handle, const int64_t* h_nodes, const double* h_params, int64_t P, double err, int n_st,
                        int n_sz, int use_adaptive, double simps_err, double w_outlier, int variant, double* h_out)
 {
+    HostCall guard_;
     Resident* r = (Resident*)(uintptr_t)handle;
     if (!r) return fail("null handle");
     if (P < 0) return fail("negative size");
@@ -982,6 +1016,7 @@ int wfpt_like_segments_host(const double* h_x, const int64_t* h_seg, const doubl
                             int n_st, int n_sz, int use_adaptive, double simps_err, double w_outlier, int variant,
                             double* h_out)
 {
+    HostCall guard_;
     if (P < 0) return fail("negative size");
     if (P == 0) return 0;
     if (!h_seg || !h_params || !h_out) return fail("null pointer argument");
@@ -1013,6 +1048,7 @@ int wfpt_like_contaminant_host(const double* h_x, const int32_t* h_cont, int64_t
                                double sz, double t, double st, double t_min, double t_max, double err, int n_st, int n_sz,
                                int use_adaptive, double simps_err, int variant, double* h_out)
 {
+    HostCall guard_;
     Opts o;
     if (check_opts(err, n_st, n_sz, use_adaptive, simps_err, variant, &o)) return 1;
     if (n < 0) return fail("negative size");
@@ -1088,6 +1124,7 @@ int wfpt_like_rl_host(const int64_t* h_response, const double* h_feedback, const
                       int64_t n_groups, int64_t n, double q, double alpha, double pos_alpha, double v, double z,
                       double p_outlier, double w_outlier, double* h_out)
 {
+    HostCall guard_;
     if (n < 0 || n_groups < 0) return fail("negative size");
     if (!h_out) return fail("null pointer argument");
     if (!((p_outlier >= 0) & (p_outlier <= 1))) { *h_out = -HUGE_VAL; return 0; }
@@ -1160,6 +1197,7 @@ int wfpt_like_multi_rlddm_host(const double* h_x, const int64_t* h_response, con
                                const double scalars[8], double err, int n_st, int n_sz, int use_adaptive,
                                double simps_err, double p_outlier, double w_outlier, int variant, double* h_out)
 {
+    HostCall guard_;
     Opts o;
     if (check_opts(err, n_st, n_sz, use_adaptive, simps_err, variant, &o)) return 1;
     if (n < 0) return fail("negative size");

@@ -209,18 +209,19 @@ extern "C" int wfpt_dmat_cdf_array_host(const double* h_x, int64_t n, double v, 
     if (n < 0) return api_fail("wfpt_dmat_cdf_array_host: negative size");
     if (n == 0) return 0;
     if (!h_x || !h_y) return api_fail("wfpt_dmat_cdf_array_host: null pointer argument");
-    double *dx = nullptr, *dy = nullptr;
-    cudaError_t e = cudaMalloc(&dx, sizeof(double) * (size_t)n);
-    if (e == cudaSuccess) e = cudaMalloc(&dy, sizeof(double) * (size_t)n);
-    if (e == cudaSuccess) e = cudaMemcpy(dx, h_x, sizeof(double) * (size_t)n, cudaMemcpyHostToDevice);
+    HostCall guard_;
+    // staging in the library's grow-only scratch (as every other host entry point): no allocation after the first call
+    void *px = nullptr, *py = nullptr;
+    if (api_scratch_pair(sizeof(double) * (size_t)n, sizeof(double) * (size_t)n, &px, &py)) return 1;
+    double *dx = (double*)px, *dy = (double*)py;
+    cudaError_t e = cudaMemcpyAsync(dx, h_x, sizeof(double) * (size_t)n, cudaMemcpyHostToDevice, 0);
     if (e == cudaSuccess) {
         cdf::dmat_cdf_kernel<<<(unsigned)((n + 63) / 64), 64>>>(dx, n, v, sv, a, z, sz, t, st, p_outlier, w_outlier, dy);
         e = cudaGetLastError();
         count_launch(1);
     }
-    if (e == cudaSuccess) e = cudaMemcpy(h_y, dy, sizeof(double) * (size_t)n, cudaMemcpyDeviceToHost);
-    cudaFree(dx);
-    cudaFree(dy);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(h_y, dy, sizeof(double) * (size_t)n, cudaMemcpyDeviceToHost, 0);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(0);
     if (e != cudaSuccess) return api_fail(cudaGetErrorString(e));
     return 0;
 }

@@ -57,6 +57,9 @@ struct BatchArgs {
 cudaError_t launch_like_batch_faithful(const BatchArgs& a);
 cudaError_t launch_like_batch_fast(const BatchArgs& a);
 
+cudaError_t launch_kflip_census(const double* x, int64_t n, const double* params, int64_t P, const Opts& o,
+                                unsigned long long* counts, cudaStream_t stream);
+
 struct PdfArrayArgs {
     const double* x; int64_t n; Params prm; Opts o; double w_outlier; int logp; double* y; cudaStream_t stream;
 };
@@ -79,6 +82,18 @@ cudaError_t launch_like_multi_fast(const MultiArgs& a);
 int api_fail(const char* msg);
 int api_sim_scratch(int which, size_t bytes, void** out);   // grow-only device buffers of the simulator entry points (0..5)
 int api_sm_count();
+int api_scratch_pair(size_t bytes0, size_t bytes1, void** p0, void** p1);   // two grow-only staging buffers (kStageX / kStageOut)
+// Held for the whole body of every `_host` entry point (stage in, launch, synchronise, copy out): those calls share one
+// pinned staging block, the grow-only scratch and stream 0 per device, so two host threads inside them at once would
+// overwrite each other's inputs and read each other's results.  Per device, re-entrant (host entry points call each other).
+struct HostCall {
+    HostCall();
+    ~HostCall();
+    HostCall(const HostCall&) = delete;
+    HostCall& operator=(const HostCall&) = delete;
+private:
+    int dev_;
+};
 int api_check_opts(double err, int n_st, int n_sz, int use_adaptive, double simps_err, int variant, Opts* o);
 void api_plan_slices(int64_t n, int64_t P, int* slices, int64_t* chunk);
 cudaError_t api_launch_finalize(const double* part_sum, const int* part_zero, int64_t P, int slices, int early_exit,

@@ -120,7 +120,7 @@ static KTable build_ktable(double err)
     return kt;
 }
 
-const KTable& get_ktable(double err)
+KTable get_ktable(double err)
 {
     static std::mutex mu;
     static std::map<long long, KTable> cache;
@@ -139,7 +139,7 @@ const KTable& get_ktable(double err)
 // C hooks for the tests (declared in include/wfpt_b200.h)
 extern "C" int wfpt_ktable(double err, int* n, int* kl_max, int* ks_max, int* desc0, double* thr, int* desc, int cap)
 {
-    const wfpt::KTable& kt = wfpt::get_ktable(err);
+    const wfpt::KTable kt = wfpt::get_ktable(err);
     if (n) *n = kt.n;
     if (kl_max) *kl_max = kt.kl_max;
     if (ks_max) *ks_max = kt.ks_max;
@@ -152,3 +152,9 @@ extern "C" int wfpt_ktable(double err, int* n, int* kl_max, int* ks_max, int* de
 }
 
 extern "C" int wfpt_ktable_decision(double tt, double err) { return wfpt::ktable_reference_decision(tt, err); }
+
+extern "C" int wfpt_ktable_decision_array(const double* tt, int64_t n, double err, int* out)
+{
+    for (int64_t i = 0; i < n; i++) out[i] = wfpt::ktable_reference_decision(tt[i], err);
+    return 0;
+}

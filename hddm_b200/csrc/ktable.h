@@ -21,8 +21,9 @@ struct KTable {
     int desc[kMaxPieces];         // descriptor of the piece starting at thr[i]:  (small ? 0x100 : 0) | K
 };
 
-// Host only.  Returns a table for `err` (cached per distinct err value; thread-safe).
-const KTable& get_ktable(double err);
+// Host only.  Returns a copy of the table for `err` (cached per distinct err value; copied under the cache's lock, so a
+// later eviction cannot touch what a caller holds).
+KTable get_ktable(double err);
 
 // The reference decision itself (host libm), exposed for tests: returns (small ? 0x100 : 0) | K.
 int ktable_reference_decision(double tt, double err);

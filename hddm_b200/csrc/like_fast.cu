@@ -81,6 +81,60 @@ cudaError_t launch_like_batch_fast(const BatchArgs& a)
     return cudaGetLastError();
 }
 
+// Census of series-term decisions (SURVEY 7 "measure, don't assume"): the fast evaluator decides the expansion and K on
+// tt = x'/a^2 formed from a reciprocal and one residual correction (fast::make_tnode), the reference on the IEEE quotient
+// x' / pow(a, 2) (/root/reference/src/pdf.pxi:35-60).  For every (parameter set, trial, staged t-node) this kernel forms
+// both, looks both up in the same table and counts (0) the pairs visited, (1) pairs whose two tt differ in any bit,
+// (2) pairs whose descriptors differ -- a "K flip", which would move that density by up to `err`.  One CTA per set.
+__global__ void __launch_bounds__(kBlock) kflip_census_kernel(const double* __restrict__ x, int64_t n,
+                                                             const double* __restrict__ params, int64_t P, Opts o,
+                                                             unsigned long long* __restrict__ counts,
+                                                             const __grid_constant__ KTable kt)
+{
+    const int64_t p = blockIdx.x;
+    if (p >= P) return;
+    const double* row = params + 8 * p;
+    Params prm{row[0], row[1], row[2], row[3], row[4], row[5], row[6], row[7]};
+    fast::Set set;
+    fast::prepare(set, prm, o, kt);
+    if (set.mode != fast::kModePoint && set.mode != fast::kModeFixed && set.mode != fast::kModeAdaptive) return;
+    const fast::Tables& T = *set.tab;
+    const double a2_ref = __dmul_rn(prm.a, prm.a);   // pow(a, 2.0) is a*a correctly rounded (checked on the host for every a)
+    unsigned long long seen = 0, tt_diff = 0, flips = 0;
+    for (int64_t i = threadIdx.x; i < n; i += kBlock) {
+        const double ax = fabs(x[i]);
+        if ((ax - set.tlo) < 0) continue;
+        for (int k = 0; k <= set.nt; k++) {
+            const double xp = ax - T.tn[k];
+            if (!(xp > 0)) continue;
+            const double q0 = xp * set.inv_a2;
+            const double tt_fast = fma(fma(-q0, set.a2, xp), set.inv_a2, q0);
+            const double tt_ref = __ddiv_rn(xp, a2_ref);
+            seen++;
+            tt_diff += (__double_as_longlong(tt_fast) != __double_as_longlong(tt_ref));
+            flips += (fast::klookup_scan(kt, tt_fast) != fast::klookup_scan(kt, tt_ref));
+        }
+    }
+    for (int off = 16; off > 0; off >>= 1) {
+        seen += __shfl_down_sync(0xffffffffu, seen, off);
+        tt_diff += __shfl_down_sync(0xffffffffu, tt_diff, off);
+        flips += __shfl_down_sync(0xffffffffu, flips, off);
+    }
+    if ((threadIdx.x & 31) == 0) {
+        atomicAdd(&counts[0], seen);
+        atomicAdd(&counts[1], tt_diff);
+        atomicAdd(&counts[2], flips);
+    }
+}
+
+cudaError_t launch_kflip_census(const double* x, int64_t n, const double* params, int64_t P, const Opts& o,
+                                unsigned long long* counts, cudaStream_t stream)
+{
+    if (P == 0) return cudaSuccess;
+    kflip_census_kernel<<<(unsigned)P, kBlock, 0, stream>>>(x, n, params, P, o, counts, get_ktable(o.err));
+    return cudaGetLastError();
+}
+
 cudaError_t launch_pdf_array_fast(const PdfArrayArgs& a)
 {
     if (a.n == 0) return cudaSuccess;

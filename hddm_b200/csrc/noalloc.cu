@@ -9,8 +9,10 @@
 // fixed array inside the library image instead.
 //
 // Cost and limits: every GPU that loads libwfpt_b200.so carries the array (kNoAllocSlots * 12 bytes = 192 KiB) until
-// the process exits.  A call needs P * slices slots, where `slices` is the trial slicing wfpt_like_batch would pick
-// for the same (n, P); calls needing more than kNoAllocSlots are refused with an error, never truncated.
+// the process exits.  A call needs P * slices slots, where `slices` comes from the library's general slicing rule
+// (api_plan_slices) WITHOUT the small-grid re-plan wfpt_like_batch adds for latency-bound grids: for those the two
+// entry points cut the trials differently and agree to rounding, not to the last bit.  Calls needing more than
+// kNoAllocSlots are refused with an error, never truncated.
 //
 // Sharing: all calls on a device use the same array and it still holds the previous call's partials on entry.
 // Nothing in it has to start at zero -- the first-stage kernel overwrites every slot the second stage reads -- so no
@@ -18,7 +20,9 @@
 // on the array and corrupt each other's sums: serialise them.
 //
 // Set-up: the device address of the array is looked up (cudaGetSymbolAddress, with that device current) by the first
-// call on each device and cached.  Make that first call on each device before any stream capture begins.
+// call on each device and cached.  Make that first call on each device before any stream capture begins.  The cached
+// address belongs to the device's primary context: after cudaDeviceReset it is stale, and this entry point must not be
+// used again in that process.
 #include <cstdio>
 #include <mutex>
 

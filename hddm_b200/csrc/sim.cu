@@ -921,6 +921,7 @@ extern "C" int wfpt_sim_run_host(int model, const float* h_theta, int n_par, int
                                  float delta_t, float max_t, float s, uint64_t seed, float* h_rts, int32_t* h_choices,
                                  uint32_t* h_hist, int nbins, float hist_max_t, uint64_t* h_steps, float* h_traj, int traj_len)
 {
+    wfpt::HostCall guard_;
     if (n_sets <= 0 || n_samples <= 0) return wfpt_sim_run(model, nullptr, n_par, n_sets, n_samples, sample_offset, delta_t, max_t, s, seed,
                                                            nullptr, nullptr, nullptr, nbins, hist_max_t, nullptr, nullptr, 0, nullptr);
     int rc = 0;
@@ -960,6 +961,7 @@ extern "C" int wfpt_sim_race_run_host(int lca, int n_particles, int angle, const
                                       int64_t sample_offset, float delta_t, float max_t, float s, uint64_t seed, float* h_rts,
                                       int32_t* h_choices, uint32_t* h_hist, int nbins, float hist_max_t, uint64_t* h_steps)
 {
+    wfpt::HostCall guard_;
     if (n_particles < 2 || n_particles > 4) return api_fail("wfpt_sim_race_run_host: n_particles must be 2, 3 or 4");
     if (n_sets < 0 || n_samples < 0) return api_fail("wfpt_sim_race_run_host: negative size");
     if (n_sets == 0 || n_samples == 0) return 0;
@@ -1081,6 +1083,7 @@ extern "C" int wfpt_sim_par2_run_host(int bound_kind, const float* h_theta, int 
                                       float delta_t, float max_t, float s, uint64_t seed, float* h_rts, int32_t* h_choices,
                                       uint32_t* h_hist, int nbins, float hist_max_t, uint64_t* h_steps)
 {
+    wfpt::HostCall guard_;
     return run_hier_host("wfpt_sim_par2_run_host", 0, bound_kind, h_theta, n_sets, n_samples, sample_offset, delta_t, max_t, s,
                          seed, h_rts, h_choices, h_hist, nbins, hist_max_t, h_steps);
 }
@@ -1089,6 +1092,7 @@ extern "C" int wfpt_sim_hier_run_host(int kind, int bound_kind, const float* h_t
                                       int64_t sample_offset, float delta_t, float max_t, float s, uint64_t seed, float* h_rts,
                                       int32_t* h_choices, uint32_t* h_hist, int nbins, float hist_max_t, uint64_t* h_steps)
 {
+    wfpt::HostCall guard_;
     if (kind < 1 || kind > 3) return api_fail("wfpt_sim_hier_run_host: kind must be 1 (seq2), 2 (mic2_adj) or 3 (tradeoff)");
     return run_hier_host("wfpt_sim_hier_run_host", kind, bound_kind, h_theta, n_sets, n_samples, sample_offset, delta_t, max_t, s,
                          seed, h_rts, h_choices, h_hist, nbins, hist_max_t, h_steps);

@@ -532,7 +532,9 @@ __device__ __forceinline__ void prepare(Set& s, const Params& prm, const Opts& o
             T.inv_wt = 1.0 / wt;
         }
         for (int i = threadIdx.x; i < ntn; i += blockDim.x) {
-            T.wts_t[i] = (i == 0 || i == ntn - 1) ? 1.0 : ((i & 1) ? 4.0 : 2.0);
+            // integrate.pxi:38-43: 4 on odd nodes, 2 on even ones, then "S - y" takes one f(b) back: the last node weighs
+            // 1 for an even number of intervals and 3 for an odd one (the reference's "n even" asserts are commented out)
+            T.wts_t[i] = (i == 0) ? 1.0 : (i == ntn - 1) ? ((i & 1) ? 3.0 : 1.0) : ((i & 1) ? 4.0 : 2.0);
             double ti;
             if (ntn == 1) ti = t;
             else if (mode == kModeFixed) ti = __dadd_rn(lb, __dmul_rn(ht, (double)i));
@@ -578,7 +580,8 @@ __device__ __forceinline__ void prepare(Set& s, const Params& prm, const Opts& o
     }
     // one (sign, node, slot) entry per thread: slots 0..3 = lattice k = -1..2, slot 4 = A, slots 5.. = sines
     constexpr int kSlots = 5 + kMaxKLarge;
-    for (int j = threadIdx.x; j < nzn; j += blockDim.x) T.wts_z[j] = (j == 0 || j == nzn - 1) ? 1.0 : ((j & 1) ? 4.0 : 2.0);
+    for (int j = threadIdx.x; j < nzn; j += blockDim.x)
+        T.wts_z[j] = (j == 0) ? 1.0 : (j == nzn - 1) ? ((j & 1) ? 3.0 : 1.0) : ((j & 1) ? 4.0 : 2.0);
     for (int idx = threadIdx.x; idx < 2 * nzn * kSlots; idx += blockDim.x) {
         const int slot = idx % kSlots, r = idx / kSlots;
         const int sign = r / nzn, j = r - sign * nzn;

@@ -55,8 +55,9 @@ def wiener_like_batch_sharded(x, params, group=None, evaluate=None, **opts):
 
 def wiener_like_batch_trial_sharded(x, params, group=None, evaluate=None, **opts):
     """Large-N / small-P layout: every rank holds ALL parameter sets and evaluates them on its slice of the trials
-    (rank r takes x[r::W]); the per-set partial sums are combined with an all-reduce(sum).  -inf partials propagate
-    through the sum (a zero-density trial on any rank makes the total -inf, as in the reference); the summation order
+    (rank r takes x[r::W]); the per-set partial sums are combined with an all-reduce(sum) and a "some rank saw a zero
+    density" flag with an all-reduce(max): a zero-density trial on any rank makes the total -inf even when another rank
+    produced NaN, as in the reference and in the single-GPU kernel; the summation order
     differs from the single-GPU run by rounding (~1e-16 relative).  All ranks return the full float64[P] vector."""
     import torch.distributed as dist
 
@@ -68,9 +69,16 @@ def wiener_like_batch_trial_sharded(x, params, group=None, evaluate=None, **opts
     rank = dist.get_rank(group) if dist.is_initialized() else 0
     if world == 1:
         return evaluate(x, params, **opts)
+    import torch
+
     part = evaluate(x[rank::world].contiguous(), params, **opts).clone()
+    # wfpt.pyx:71-72: the first zero density returns -inf whatever the other trials give.  A plain sum would turn
+    # "-inf on one rank, NaN or +inf on another" into NaN, so the "saw a zero" flag travels with the sums (max over ranks)
+    # and wins, as it does inside the single-GPU kernel.
+    zero = torch.isneginf(part).to(torch.float64)
     dist.all_reduce(part, op=dist.ReduceOp.SUM, group=group)
-    return part
+    dist.all_reduce(zero, op=dist.ReduceOp.MAX, group=group)
+    return torch.where(zero > 0, torch.full_like(part, float("-inf")), part)
 
 
 def merge_histograms(counts, group=None):

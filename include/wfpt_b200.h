@@ -19,6 +19,12 @@
  *   - parameter-set rows are double[8] = {v, sv, a, z, sz, t, st, p_outlier}.
  *   - integration options, as in every reference signature: err, n_st, n_sz, use_adaptive, simps_err
  *     (src/pdf.pxi:104-108).  With use_adaptive != 0, n_st/n_sz are recursion depths and must be <= 24.
+ *   - threads and streams: `_host` functions hold a per-device lock for their whole body (they share one staging block,
+ *     the library's scratch and stream 0), so they may be called from several host threads; calls on one device simply
+ *     run one after another.  Device-pointer functions are asynchronous and share, per device, the scratch that holds the
+ *     per-slice partial sums and the arrival counters of the trial reduction (wfpt_like_batch / wfpt_like_segments whenever a
+ *     set's trials are cut into more than one slice, wfpt_like_multi always): two such calls whose kernels can overlap on the
+ *     GPU (different streams, or different host threads) race on it -- enqueue them on one stream or order them with events.
  *   - `variant`: WFPT_VARIANT_FAST (default product path) or WFPT_VARIANT_FAITHFUL (operation-for-operation
  *     evaluation without FMA contraction; slower; kept as the on-device cross-check).
  */
@@ -56,6 +62,16 @@ int wfpt_fp64_peak(int iters, double* dfma_per_s, double* ms);
  * wfpt_ktable_decision evaluates the reference decision for one tt (same descriptor encoding, -1 if out of range). */
 int wfpt_ktable(double err, int* n, int* kl_max, int* ks_max, int* desc0, double* thr, int* desc, int cap);
 int wfpt_ktable_decision(double tt, double err);
+int wfpt_ktable_decision_array(const double* tt, int64_t n, double err, int* out);   /* the same for n values */
+
+/* Diagnostic: census of the fast variant's series-term decisions against the reference's.  The reference decides the
+ * expansion and K on tt = x'/pow(a,2) (src/pdf.pxi:35-60); the fast kernels on a tt built from a reciprocal.  For every
+ * (parameter set, trial inside the support, staged t-node of the integration grid the options select) the kernel forms
+ * both and adds to d_counts3[0] the pairs visited, to [1] the pairs whose two tt differ in any bit, to [2] the pairs whose
+ * table descriptors differ ("K flips": each would move one density by up to err).  d_counts3 is uint64[3] on the device,
+ * zeroed by the caller.  No reference counterpart (the reference has one arithmetic). */
+int wfpt_kflip_census(const double* d_x, int64_t n, const double* d_params, int64_t P, double err, int n_st, int n_sz,
+                      int use_adaptive, uint64_t* d_counts3, void* stream);
 
 /* Likelihood ------------------------------------------------------------------------------------------------- */
 
@@ -68,16 +84,20 @@ int wfpt_like_batch(const double* d_x, int64_t n, const double* d_params, int64_
 int wfpt_like_batch_host(const double* h_x, int64_t n, const double* h_params, int64_t P, double err, int n_st,
                          int n_sz, int use_adaptive, double simps_err, double w_outlier, int variant, double* h_out);
 
-/* Same computation and same results as wfpt_like_batch, for callers that cannot allocate device memory (a process
- * whose GPU memory is already owned by another pool, a latency-bound caller that cannot afford cudaMalloc's device
- * synchronisation, a context in which allocation calls are not permitted).  It has no counterpart in the reference.
+/* The computation of wfpt_like_batch for callers that cannot allocate device memory (a process whose GPU memory is
+ * already owned by another pool, a latency-bound caller that cannot afford cudaMalloc's device synchronisation, a
+ * context in which allocation calls are not permitted).  It has no counterpart in the reference.
  * The partial sums of the two-stage trial reduction live in a fixed array inside the library image
  * (WFPT_NOALLOC_MAX_SLOTS slots, 192 KiB, held by every GPU that loads the library until process exit) and the
- * function makes no cudaMalloc/cudaFree call.  A call needs P x slices slots (slices = the trial slicing
- * wfpt_like_batch picks for the same n and P; P slots when one slice covers all trials); more than
- * WFPT_NOALLOC_MAX_SLOTS is refused with an error.  All calls on a device share the array, so calls whose kernels
- * overlap on the GPU race; run them one after another.  The first call on each device looks the array's device
- * address up and should be made before any stream capture. */
+ * function makes no cudaMalloc/cudaFree call.  A call needs P x slices slots, where slices is the library's general
+ * trial slicing for (n, P) (one slice once P reaches eight CTAs per SM, otherwise enough slices to get there, at least
+ * 256 RTs each); the small-grid re-plan wfpt_like_batch applies on top of that is NOT applied here, so for small grids
+ * the two functions cut the trials differently and their sums agree to rounding (<= 1e-13 relative), not bit for bit.
+ * More than WFPT_NOALLOC_MAX_SLOTS slots is refused with an error.  All calls on a device share the array, so calls
+ * whose kernels overlap on the GPU race; run them one after another.  The first call on each device looks the array's
+ * device address up and should be made before any stream capture; the address is cached per device for the life of the
+ * process, so after a cudaDeviceReset (which destroys the context the address belongs to) this entry point must not
+ * be used again in that process. */
 #define WFPT_NOALLOC_MAX_SLOTS 16384
 int wfpt_like_batch_noalloc(const double* d_x, int64_t n, const double* d_params, int64_t P, double err, int n_st,
                             int n_sz, int use_adaptive, double simps_err, double w_outlier, int variant,

@@ -21,6 +21,24 @@ def golden():
 
 
 @pytest.fixture(scope="session")
+def grid_golden():
+    """Reference answers for the whole benchmark grids (tests/golden/make_grid_golden.py) with the grids themselves,
+    regenerated from their seeds and checked against the digests stored beside the answers."""
+    import hashlib
+
+    import bench
+
+    g = dict(np.load(os.path.join(GOLDEN, "grid_golden.npz")))
+    x, benign = bench.workload(bench.P_FULL)
+    bounds = bench.param_bounds_grid(8192)
+    sha = lambda a: np.frombuffer(hashlib.sha256(np.ascontiguousarray(a).tobytes()).digest(), dtype=np.uint8)
+    assert np.array_equal(sha(benign), g["benign_sha"]) and np.array_equal(sha(benign[:8192]), g["benign8192_sha"])
+    assert np.array_equal(sha(bounds), g["bounds_sha"])
+    g.update(x=x, benign=benign, bounds=bounds)
+    return g
+
+
+@pytest.fixture(scope="session")
 def oracle():
     from oracle import cpu
 

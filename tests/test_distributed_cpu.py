@@ -49,6 +49,13 @@ def _worker(rank, world, port, P, q):
     want2 = oracle.wiener_like_batch(x, prm2, 1e-4, 2, 2, 0, 1e-3, 0.1)
     ok_trial = bool(np.isneginf(tot.numpy()[4]) and np.isneginf(want2[4]) and
                     np.allclose(tot.numpy()[:4], want2[:4], rtol=1e-12, atol=0))
+    # -inf on one rank meeting NaN / +inf on another: the zero-density flag wins (wfpt.pyx:71-72), a plain sum would say NaN
+    def fake(xt, pt, **opts):
+        return torch.tensor([float("-inf") if rank == 0 else float("nan"), float("-inf") if rank == 0 else float("inf"),
+                             float("nan") if rank == 0 else 1.0, 2.0], dtype=torch.float64)
+
+    mixed = D.wiener_like_batch_trial_sharded(torch.from_numpy(x), torch.from_numpy(prm[:4]), evaluate=fake).numpy()
+    ok_trial = ok_trial and bool(np.isneginf(mixed[0]) and np.isneginf(mixed[1]) and np.isnan(mixed[2]) and mixed[3] == 2.0 * world)
     hist = torch.full((4, 8, 2), rank + 1, dtype=torch.int64)
     D.merge_histograms(hist)
     ok = bool(np.array_equal(full.numpy(), want)) and calls[0] == len(D.shard_rows(P, rank, world)) and \

@@ -33,8 +33,8 @@ def test_full_pdf_cases(golden, wfpt_gpu, variant):
     """6000 single-trial densities over every dispatch branch (sv/sz/st on/off, fixed/adaptive, err 1e-13..1)."""
     cases, vals = golden["full_pdf_cases"], golden["full_pdf_vals"]
     # group by option tuple so that each group is one pdf_array-style launch per case row (n=1 calls are slow)
-    got = np.array([wfpt_gpu.full_pdf(*c[:9], int(c[9]), int(c[10]), int(c[11]), c[12]) for c in cases[:1500]])
-    want = vals[:1500]
+    got = np.array([wfpt_gpu.full_pdf(*c[:9], int(c[9]), int(c[10]), int(c[11]), c[12]) for c in cases])
+    want = vals
     assert np.array_equal(got == 0, want == 0)                 # validity mask: exact zeros in the same places
     assert np.array_equal(np.isnan(got), np.isnan(want))
     ok = np.isfinite(want) & (want != 0)
@@ -217,6 +217,32 @@ def test_pdf_array_and_cdf_helpers(golden, oracle, wfpt_gpu, variant):
     assert np.mean(x1 == g["x_cfg1"]) > 0.995 and np.max(np.abs(x1 - g["x_cfg1"])) <= 1.5e-3
     xs, cdf = wfpt_gpu.gen_cdf_using_pdf(0.7, 0.8, 1.6, 0.45, 0.2, 0.25, 0.15, 1e-4, N=300, time=5.0)
     assert 0 <= cdf[0] < 1e-4 and cdf[-1] == 1 and np.all(np.diff(cdf) >= 0) and len(xs) == 601
+    # numbers, not only shape (wfpt.pyx:582-607): the oracle's pdf_array on the same grid + scipy's unit-spacing cumulative
+    # trapezoid (the `cumtrapz` the reference calls, under its current name) + the same normalisation
+    from scipy.integrate import cumulative_trapezoid
+
+    for args, kw in (((0.7, 0.8, 1.6, 0.45, 0.2, 0.25, 0.15, 1e-4), dict(N=300, time=5.0)),
+                     ((-1.1, 0.0, 2.1, 0.6, 0.0, 0.3, 0.0, 1e-4), dict(N=500, time=5.0, p_outlier=0.05, w_outlier=0.1)),
+                     ((0.3, 1.5, 1.2, 0.5, 0.1, 0.2, 0.2, 1e-6), dict(N=64, time=3.0, n_st=4, n_sz=4, use_adaptive=0))):
+        xs, cdf = wfpt_gpu.gen_cdf_using_pdf(*args, **kw)
+        N, time = kw["N"], kw["time"]
+        grid = np.linspace(-time, time, 2 * N + 1)
+        assert np.array_equal(xs, grid)
+        dens = oracle.pdf_array(grid, *args, 0, kw.get("n_st", 2), kw.get("n_sz", 2), kw.get("use_adaptive", 1),
+                                kw.get("simps_err", 1e-3), kw.get("p_outlier", 0), kw.get("w_outlier", 0))
+        want = np.empty_like(dens)
+        want[0] = dens[0]
+        want[1:] = cumulative_trapezoid(dens)
+        want /= want[-1]
+        assert np.max(np.abs(cdf - want)) < 1e-12, args
+        # split_cdf (wfpt.pyx:610-626) on the GPU-made CDF against the same slicing done by hand on the oracle's
+        x_lb, lb, x_ub, ub = wfpt_gpu.split_cdf(xs, cdf.copy())
+        w_lb = np.cumsum(np.concatenate([[0.0], -np.diff(want[:N][::-1])]))
+        w_ub = want[N + 1:] - want[N + 1]
+        assert np.array_equal(x_lb, -grid[:N][::-1]) and np.array_equal(x_ub, grid[N + 1:])
+        assert np.max(np.abs(lb - w_lb)) < 1e-12 and np.max(np.abs(ub - w_ub)) < 1e-12
+    with pytest.raises(ValueError):
+        wfpt_gpu.gen_cdf_using_pdf(0.7, 0.8, 1.6, 1.2, 0.2, 0.25, 0.15, 1e-4)
 
 
 def test_density_integrates_to_one(wfpt_gpu, variant):
@@ -335,3 +361,74 @@ def test_random_option_sweep_vs_oracle(oracle, wfpt_gpu):
         fin = np.isfinite(want)
         if fin.any():
             assert rel_err(got[fin], want[fin]) < TOL, ctx
+
+
+def test_whole_benchmark_grids_vs_reference_fixture(grid_golden, wfpt_gpu):
+    """Every set of the benchmark grids against the reference's own answers (tests/golden/grid_golden.npz): the 65,536
+    benign sets on the fixed grid (the headline workload), the first 8,192 of them with adaptive integration, the 8,192
+    sets over the whole param_bounds box in both modes, and the hand-picked special sets."""
+    import torch
+
+    g = grid_golden
+    dx = torch.from_numpy(wfpt_gpu.sort_rts(g["x"])).cuda()
+    runs = (("benign", "benign_fixed", 0, slice(None)), ("benign", "benign_adaptive", 1, slice(0, 8192)),
+            ("bounds", "bounds_fixed", 0, slice(None)), ("bounds", "bounds_adaptive", 1, slice(None)),
+            ("special_params", "special_fixed", 0, slice(None)), ("special_params", "special_adaptive", 1, slice(None)))
+    for pname, wname, ad, sl in runs:
+        prm = torch.from_numpy(np.ascontiguousarray(g[pname][sl])).cuda()
+        got = wfpt_gpu.wiener_like_batch(dx, prm, 1e-4, 2, 2, ad, 1e-3, 0.1).cpu().numpy()
+        want = g[wname]
+        assert got.shape == want.shape
+        assert np.array_equal(np.isnan(got), np.isnan(want)), wname
+        assert np.array_equal(np.isneginf(got), np.isneginf(want)) and not np.isposinf(got).any(), wname
+        assert rel_err(got, want) <= TOL, (wname, rel_err(got, want))
+
+
+def test_fixed_grid_with_odd_interval_counts(oracle, wfpt_gpu, variant):
+    """integrate.pxi:30-45 does not insist on an even number of intervals: with an odd one the last node carries weight 3."""
+    rng = np.random.default_rng(12)
+    x = np.where(rng.random(500) < 0.7, 1.0, -1.0) * rng.uniform(0.4, 3.0, 500)
+    P = 24
+    prm = np.stack([rng.uniform(-3, 3, P), rng.uniform(0, 2, P), rng.uniform(1, 3, P), rng.uniform(0.3, 0.7, P),
+                    rng.uniform(0.01, 0.25, P), rng.uniform(0.1, 0.3, P), rng.uniform(0.01, 0.2, P), np.full(P, 0.05)], axis=1)
+    prm[::5, 4] = 0.0
+    prm[1::5, 6] = 0.0
+    for n_st, n_sz in ((1, 1), (3, 3), (5, 2), (2, 5), (1, 4), (7, 3)):
+        want = oracle.wiener_like_batch(x, prm, 1e-4, n_st, n_sz, 0, 1e-3, 0.1)
+        got = wfpt_gpu.wiener_like_batch(x, prm, 1e-4, n_st, n_sz, 0, 1e-3, 0.1, variant=variant)
+        assert rel_err(got, want) <= TOL, (n_st, n_sz)
+
+
+def test_series_term_census_has_no_flips(grid_golden, wfpt_gpu):
+    """The fast kernels decide the expansion and K on a tt formed from a reciprocal; the reference on x'/pow(a,2).  Over
+    8,192 benign sets x 10,000 RTs x 3 t-nodes (fixed grid) and 5 t-nodes (adaptive first level): how often the two tt
+    differ at all, and how often that changes the table's answer (must be never).  The table itself is then held against
+    the reference's formulas (host libm) at tt values of these very inputs, and pow(a, 2) against a*a for every a."""
+    import ctypes as C
+
+    import torch
+
+    from hddm_b200 import _lib
+
+    g = grid_golden
+    L = _lib.load()
+    dx = torch.from_numpy(g["x"]).cuda()
+    prm = np.ascontiguousarray(np.concatenate([g["benign"][:8192], g["bounds"]]))
+    dp = torch.from_numpy(prm).cuda()
+    for ad in (0, 1):
+        counts = torch.zeros(3, dtype=torch.int64, device="cuda")
+        _lib.check(L.wfpt_kflip_census(dx.data_ptr(), len(g["x"]), dp.data_ptr(), len(prm), 1e-4, 2, 2, ad, counts.data_ptr(), None))
+        torch.cuda.synchronize()
+        seen, tt_diff, flips = (int(v) for v in counts.cpu())
+        assert seen > 1e8 and flips == 0, (ad, seen, tt_diff, flips)
+        assert tt_diff < 1e-3 * seen   # the reciprocal form is correctly rounded nearly always
+    import math
+
+    assert all(math.pow(a, 2.0) == a * a for a in prm[:, 2])
+    kt = _lib.ktable(1e-4)
+    thr, desc = np.array(kt["thr"]), np.array([kt["desc0"]] + kt["desc"])
+    for q in prm[::257]:
+        t_nodes = (q[5] - q[6] / 2) + (q[6] / 2) * np.arange(3)
+        xp = (np.abs(g["x"])[:, None] - t_nodes[None, :]).ravel()
+        tt = xp[xp > 0] / math.pow(q[2], 2.0)
+        assert np.array_equal(desc[np.searchsorted(thr, tt, side="right")], _lib.ktable_decision_array(tt, 1e-4))

@@ -206,3 +206,41 @@ def test_cdf_fixture_comes_from_the_reference_library():
     # sanity of the quantity itself: in signed-RT convention the CDF rises from 0 to 1 (outlier-free row)
     y = g["vals"][1]
     assert abs(y[0]) < 5e-3 and abs(y[180] - 1) < 5e-3 and np.all(np.diff(y[:181]) >= -1e-12)
+
+
+def test_oracle_matches_whole_grid_fixture_on_a_sample(grid_golden, oracle):
+    """The C oracle against the reference's answers for the benchmark grids (every 211th benign set, every 61st of the
+    whole-box grid, both integration modes, and the hand-picked special sets): bit for bit."""
+    g = grid_golden
+    x = g["x"]
+    idx = np.arange(0, 65536, 211)
+    got = oracle.wiener_like_batch(x, g["benign"][idx], 1e-4, 2, 2, 0, 1e-3, 0.1)
+    assert np.array_equal(got, g["benign_fixed"][idx])
+    idx = np.arange(0, 8192, 61)
+    for tag, ad in (("fixed", 0), ("adaptive", 1)):
+        got = oracle.wiener_like_batch(x, g["bounds"][idx], 1e-4, 2, 2, ad, 1e-3, 0.1)
+        assert np.array_equal(got, g["bounds_" + tag][idx], equal_nan=True)
+        got = oracle.wiener_like_batch(x, g["special_params"], 1e-4, 2, 2, ad, 1e-3, 0.1)
+        assert np.array_equal(got, g["special_" + tag], equal_nan=True)
+    got = oracle.wiener_like_batch(x, g["benign"][idx], 1e-4, 2, 2, 1, 1e-3, 0.1)
+    assert np.array_equal(got, g["benign_adaptive"][idx])
+    # the special sets say what they are meant to say
+    sp = g["special_fixed"]
+    assert sp[0] == pytest.approx(len(x) * math.log(0.1 * 0.05), rel=1e-12) and np.isneginf(sp[[1, 2, 4]]).all()
+    assert np.isnan(sp[5]) and np.isfinite(sp[[3, 6, 7, 8, 9]]).all()
+
+
+def test_fixed_grid_with_odd_interval_counts(oracle, ref_wfpt):
+    """integrate.pxi:30-45 with an odd number of intervals (the "n even" asserts are commented out): the last node ends up
+    with weight 3.  The oracle follows the reference bit for bit there too."""
+    rng = np.random.default_rng(12)
+    x = np.where(rng.random(40) < 0.7, 1.0, -1.0) * rng.uniform(0.4, 3.0, 40)
+    for n_st, n_sz in ((1, 1), (3, 3), (5, 2), (2, 5), (1, 4), (3, 0), (0, 3)):
+        for sz, st in ((0.2, 0.1), (0.0, 0.1), (0.2, 0.0)):
+            if (sz and not n_sz) or (st and not n_st):
+                continue
+            want = ref_wfpt.wiener_like(x, 0.8, 0.9, 1.9, 0.45, sz, 0.3, st, 1e-4, n_st=n_st, n_sz=n_sz, use_adaptive=0,
+                                        simps_err=1e-3, p_outlier=0.05, w_outlier=0.1)
+            got = oracle.wiener_like(x, 0.8, 0.9, 1.9, 0.45, sz, 0.3, st, 1e-4, n_st=n_st, n_sz=n_sz, use_adaptive=0,
+                                     simps_err=1e-3, p_outlier=0.05, w_outlier=0.1)
+            assert got == want, (n_st, n_sz, sz, st)

@@ -74,6 +74,31 @@ def test_noalloc_matches_like_batch_on_consecutive_calls(variant):
     _agree(got, ref)
 
 
+def test_noalloc_leaves_free_memory_unchanged():
+    """The point of the entry point: a call of a shape the process has never run before must not take device memory.
+    cudaMemGetInfo before and after (through torch, which only reports the driver's numbers) must agree."""
+    import torch
+
+    from hddm_b200 import _lib
+
+    L = _lib.load()
+    x, prm = _inputs(5, 7001, 5)            # 5 sets x many trial slices: scratch needed
+    dx = torch.from_numpy(x).cuda()
+    dp = torch.from_numpy(np.ascontiguousarray(prm)).cuda()
+    out = torch.empty(len(prm), dtype=torch.float64, device="cuda")
+    stream = torch.cuda.current_stream().cuda_stream
+    # first call on this device (symbol look-up) outside the measurement, as the header asks
+    _lib.check(L.wfpt_like_batch_noalloc(dx.data_ptr(), 16, dp.data_ptr(), 1, *OPTS, 0.1, 0, out.data_ptr(), stream))
+    torch.cuda.synchronize()
+    free0, _ = torch.cuda.mem_get_info()
+    for variant in (0, 1):
+        _lib.check(L.wfpt_like_batch_noalloc(dx.data_ptr(), len(x), dp.data_ptr(), len(prm), *OPTS, 0.1, variant,
+                                             out.data_ptr(), stream))
+    torch.cuda.synchronize()
+    free1, _ = torch.cuda.mem_get_info()
+    assert free1 == free0, (free0, free1)
+
+
 def test_noalloc_rejects_batches_beyond_its_scratch():
     import torch
 
