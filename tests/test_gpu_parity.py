@@ -37,9 +37,11 @@ def test_full_pdf_cases(golden, wfpt_gpu, variant):
     want = vals
     assert np.array_equal(got == 0, want == 0)                 # validity mask: exact zeros in the same places
     assert np.array_equal(np.isnan(got), np.isnan(want))
-    ok = np.isfinite(want) & (want != 0)
+    ok = np.isfinite(want) & (np.abs(want) > 1e-300)
     # a K flip (1-ulp libm difference at an integer ks/kl) would show up here as an error of order `err`
     assert rel_err(got[ok], want[ok]) < 1e-9
+    tiny = np.isfinite(want) & (want != 0) & ~ok     # subnormal results carry only a few digits in either implementation
+    assert np.all(np.abs(got[tiny] - want[tiny]) < 1e-300)
 
 
 def test_wiener_like_cases(golden, wfpt_gpu, variant):
@@ -403,7 +405,7 @@ def test_series_term_census_has_no_flips(grid_golden, wfpt_gpu):
     """The fast kernels decide the expansion and K on a tt formed from a reciprocal; the reference on x'/pow(a,2).  Over
     8,192 benign sets x 10,000 RTs x 3 t-nodes (fixed grid) and 5 t-nodes (adaptive first level): how often the two tt
     differ at all, and how often that changes the table's answer (must be never).  The table itself is then held against
-    the reference's formulas (host libm) at tt values of these very inputs, and pow(a, 2) against a*a for every a."""
+    the reference's formulas (host libm) at tt values of these very inputs."""
     import ctypes as C
 
     import torch
@@ -424,11 +426,12 @@ def test_series_term_census_has_no_flips(grid_golden, wfpt_gpu):
         assert tt_diff < 1e-3 * seen   # the reciprocal form is correctly rounded nearly always
     import math
 
-    assert all(math.pow(a, 2.0) == a * a for a in prm[:, 2])
+    # (the compiled reference forms a^2 as a*a: gcc folds Cython's pow(a, 2.0) into a multiplication, which is what the
+    # bit-for-bit agreement of oracle/wfpt_oracle.c with oracle/_ref rests on; libm's pow(a, 2.0) itself is not always a*a)
     kt = _lib.ktable(1e-4)
     thr, desc = np.array(kt["thr"]), np.array([kt["desc0"]] + kt["desc"])
     for q in prm[::257]:
         t_nodes = (q[5] - q[6] / 2) + (q[6] / 2) * np.arange(3)
         xp = (np.abs(g["x"])[:, None] - t_nodes[None, :]).ravel()
-        tt = xp[xp > 0] / math.pow(q[2], 2.0)
+        tt = xp[xp > 0] / (q[2] * q[2])
         assert np.array_equal(desc[np.searchsorted(thr, tt, side="right")], _lib.ktable_decision_array(tt, 1e-4))
