@@ -36,6 +36,15 @@ def _declare(L):
     opts = [d, i, i, i, d]  # err, n_st, n_sz, use_adaptive, simps_err
     L.wfpt_like_batch.argtypes = [vp, i64, vp, i64] + opts + [d, i, vp, vp]
     L.wfpt_like_batch_host.argtypes = [vp, i64, vp, i64] + opts + [d, i, vp]
+    L.wfpt_like_batch_host_presort.argtypes = [vp, i64, vp, i64] + opts + [d, i, vp]
+    L.wfpt_like_cached_host.argtypes = [vp, i64, vp, i64] + opts + [d, i, vp]
+    L.wfpt_sort_rts.argtypes = [vp, i64, vp, vp]
+    L.wfpt_cache_config.argtypes = [i64, i64]
+    L.wfpt_cache_clear.argtypes = []
+    L.wfpt_cache_stats.argtypes = [vp, vp, vp, vp, vp]
+    for name in ("wfpt_like_batch_host_presort", "wfpt_like_cached_host", "wfpt_sort_rts", "wfpt_cache_config",
+                 "wfpt_cache_clear", "wfpt_cache_stats"):
+        getattr(L, name).restype = i
     L.wfpt_like_batch_noalloc.argtypes = [vp, i64, vp, i64] + opts + [d, i, vp, vp]
     L.wfpt_like_batch_noalloc.restype = i
     L.wfpt_pdf_array.argtypes = [vp, i64, c_double_p] + opts + [d, i, i, vp, vp]

@@ -10,6 +10,7 @@
 #include <cstring>
 #include <mutex>
 #include <new>
+#include <unordered_map>
 
 #include "../../include/wfpt_b200.h"
 #include "common.cuh"
@@ -39,7 +40,7 @@ void count_launch(int k) { g_launches.fetch_add(k, std::memory_order_relaxed); }
 // ---- per-device grow-only scratch ------------------------------------------------------------------------------------
 enum Slot { kPartSum = 0, kPartZero, kDone, kStageX, kStageParams, kStageOut, kStageAux0, kStageAux1, kStageAux2, kStageAux3,
             kStageAux4, kStageAux5, kStageAux6, kStageAux7, kStageAux8, kStageAux9, kStageAux10, kStageAux11, kSim0, kSim1, kSim2,
-            kSim3, kSim4, kSim5, kNumSlots };
+            kSim3, kSim4, kSim5, kSorted, kNumSlots };
 constexpr int kMaxDev = 16;
 struct Buf { void* p = nullptr; size_t cap = 0; };
 static Buf g_buf[kMaxDev][kNumSlots];
@@ -161,6 +162,45 @@ __global__ void finalize_kernel(const double* __restrict__ part_sum, const int* 
     }
     out[p] = (early_exit && z) ? -CUDART_INF : s;
 }
+
+// RTs reordered by |rt|, ties in array order (what np.argsort(np.abs(x), kind="stable") gives): every element counts the
+// elements that precede it and writes itself there.  n^2 compares, all independent: 10,000 RTs take a few microseconds,
+// which is why the host-buffer entry points sort here instead of on the host (0.4 ms of argsort per call before).
+// 256 threads = 64 elements x 4 quarters of the array; keys are the bit patterns of |x| (monotone for non-negative doubles).
+constexpr int kSortTile = 64;
+__global__ void __launch_bounds__(256) rank_sort_kernel(const double* __restrict__ x, int n, double* __restrict__ out)
+{
+    __shared__ unsigned long long keys[1024];
+    const int e = threadIdx.x >> 2, part = threadIdx.x & 3;
+    const int i = blockIdx.x * kSortTile + e;
+    const double xi = (i < n) ? x[i] : 0.0;
+    const unsigned long long ki = (unsigned long long)__double_as_longlong(fabs(xi));
+    const int per = (n + 3) / 4;
+    const int j0 = part * per, j1 = min(n, j0 + per);
+    int rank = 0;
+    // all threads walk the same number of tiles (barriers inside); each compares against its own quarter
+    for (int base = 0; base < per; base += 256) {
+        __syncthreads();
+        for (int q = 0; q < 4; q++) {
+            const int j = q * per + base + threadIdx.x;
+            keys[q * 256 + threadIdx.x] = (j < n && base + threadIdx.x < per)
+                                              ? (unsigned long long)__double_as_longlong(fabs(x[j])) : ~0ull;
+        }
+        __syncthreads();
+        const unsigned long long* kq = keys + part * 256;
+        const int lim = min(256, j1 - (j0 + base));
+#pragma unroll 4
+        for (int k = 0; k < lim; k++) {
+            const unsigned long long kj = kq[k];
+            const int j = j0 + base + k;
+            rank += (kj < ki) || (kj == ki && j < i);
+        }
+    }
+    rank += __shfl_xor_sync(0xffffffffu, rank, 1);
+    rank += __shfl_xor_sync(0xffffffffu, rank, 2);
+    if (part == 0 && i < n) out[rank] = xi;
+}
+constexpr int64_t kDeviceSortMax = 32768;   // beyond this the quadratic count loses to a host sort
 
 // Rescorla-Wagner recurrence of wiener_like_rlddm (/root/reference/src/wfpt.pyx:118-152), one thread per split_by
 // group.  Writes, for every trial j, the drift scale (Q_upper - Q_lower) seen BEFORE that trial's update, and marks the
@@ -558,8 +598,30 @@ int wfpt_like_batch(const double* d_x, int64_t n, const double* d_params, int64_
     return 0;
 }
 
-int wfpt_like_batch_host(const double* h_x, int64_t n, const double* h_params, int64_t P, double err, int n_st,
-                         int n_sz, int use_adaptive, double simps_err, double w_outlier, int variant, double* h_out)
+// |rt|-sorted copy of n RTs that already sit on the device: counted into place there when small enough (see
+// rank_sort_kernel).  Returns the pointer to use in *sorted (the input itself when there is nothing to sort).
+static int sort_on_device(const double* d_x, int64_t n, const double** sorted)
+{
+    *sorted = d_x;
+    if (n < 2) return 0;
+    void* ds;
+    if (scratch(kSorted, sizeof(double) * (size_t)n, &ds)) return 1;
+    rank_sort_kernel<<<(unsigned)((n + kSortTile - 1) / kSortTile), 256>>>(d_x, (int)n, (double*)ds);
+    CK(cudaGetLastError());
+    count_launch(1);
+    *sorted = (const double*)ds;
+    return 0;
+}
+// Host sort for arrays too long for the quadratic device count: stable by |x| (bit patterns), as the device kernel orders.
+static void sort_on_host(const double* h_x, int64_t n, double* dst)
+{
+    if (dst != h_x) memcpy(dst, h_x, sizeof(double) * (size_t)n);
+    std::stable_sort(dst, dst + n, [](double a, double b) { return std::fabs(a) < std::fabs(b); });
+}
+
+static int like_batch_host_impl(const double* h_x, int64_t n, const double* h_params, int64_t P, double err, int n_st,
+                                int n_sz, int use_adaptive, double simps_err, double w_outlier, int variant, int presort,
+                                double* h_out)
 {
     HostCall guard_;
     if (n < 0 || P < 0) return fail("negative size");
@@ -567,17 +629,23 @@ int wfpt_like_batch_host(const double* h_x, int64_t n, const double* h_params, i
     if (!h_params || !h_out || (n > 0 && !h_x)) return fail("null pointer argument");
     void *dx, *dp, *dout;
     const size_t in_bytes = sizeof(double) * (8 * (size_t)P + (size_t)n);
+    const bool dev_sort = presort && n >= 2 && n <= kDeviceSortMax;
+    const bool host_sort = presort && n > kDeviceSortMax;
     if (sizeof(double) * (size_t)P <= kPinOutBytes && in_bytes <= kPinMaxIn) {
         // small call: [params | x] through the pinned block in one copy, results straight into its mapped head
         char *ph, *pd;
         if (pinned(in_bytes, &ph, &pd)) return 1;
         if (scratch(kStageX, in_bytes, &dx)) return 1;
         memcpy(ph + kPinOutBytes, h_params, sizeof(double) * 8 * (size_t)P);
-        if (n > 0) memcpy(ph + kPinOutBytes + sizeof(double) * 8 * (size_t)P, h_x, sizeof(double) * (size_t)n);
+        double* px = (double*)(ph + kPinOutBytes + sizeof(double) * 8 * (size_t)P);
+        if (host_sort) sort_on_host(h_x, n, px);
+        else if (n > 0) memcpy(px, h_x, sizeof(double) * (size_t)n);
         const double* in_dev = (const double*)dx;
         CK(cudaMemcpyAsync(dx, ph + kPinOutBytes, in_bytes, cudaMemcpyHostToDevice, 0));   // (reading the RTs through the
         // mapped block instead was measured slower: every thread then waits on the bus before its first trial)
-        if (wfpt_like_batch(in_dev + 8 * P, n, in_dev, P, err, n_st, n_sz, use_adaptive, simps_err, w_outlier, variant,
+        const double* xs = in_dev + 8 * P;
+        if (dev_sort && sort_on_device(xs, n, &xs)) return 1;
+        if (wfpt_like_batch(xs, n, in_dev, P, err, n_st, n_sz, use_adaptive, simps_err, w_outlier, variant,
                             (double*)pd, nullptr))
             return 1;
         CK(cudaStreamSynchronize(0));
@@ -587,13 +655,199 @@ int wfpt_like_batch_host(const double* h_x, int64_t n, const double* h_params, i
     if (scratch(kStageX, sizeof(double) * (size_t)(n > 0 ? n : 1), &dx)) return 1;
     if (scratch(kStageParams, sizeof(double) * 8 * (size_t)P, &dp)) return 1;
     if (scratch(kStageOut, sizeof(double) * (size_t)P, &dout)) return 1;
-    if (n > 0) CK(cudaMemcpyAsync(dx, h_x, sizeof(double) * (size_t)n, cudaMemcpyHostToDevice, 0));
+    double* tmp = nullptr;
+    if (host_sort) {
+        tmp = (double*)malloc(sizeof(double) * (size_t)n);
+        if (!tmp) return fail("out of host memory");
+        sort_on_host(h_x, n, tmp);
+    }
+    cudaError_t e = cudaSuccess;
+    if (n > 0) e = cudaMemcpyAsync(dx, tmp ? tmp : h_x, sizeof(double) * (size_t)n, cudaMemcpyHostToDevice, 0);
+    if (tmp) { cudaStreamSynchronize(0); free(tmp); }
+    CK(e);
     CK(cudaMemcpyAsync(dp, h_params, sizeof(double) * 8 * (size_t)P, cudaMemcpyHostToDevice, 0));
-    if (wfpt_like_batch((const double*)dx, n, (const double*)dp, P, err, n_st, n_sz, use_adaptive, simps_err, w_outlier,
+    const double* xs = (const double*)dx;
+    if (dev_sort && sort_on_device(xs, n, &xs)) return 1;
+    if (wfpt_like_batch(xs, n, (const double*)dp, P, err, n_st, n_sz, use_adaptive, simps_err, w_outlier,
                         variant, (double*)dout, nullptr))
         return 1;
     CK(cudaMemcpyAsync(h_out, dout, sizeof(double) * (size_t)P, cudaMemcpyDeviceToHost, 0));
     CK(cudaStreamSynchronize(0));
+    return 0;
+}
+
+int wfpt_like_batch_host(const double* h_x, int64_t n, const double* h_params, int64_t P, double err, int n_st,
+                         int n_sz, int use_adaptive, double simps_err, double w_outlier, int variant, double* h_out)
+{
+    return like_batch_host_impl(h_x, n, h_params, P, err, n_st, n_sz, use_adaptive, simps_err, w_outlier, variant, 0, h_out);
+}
+
+int wfpt_like_batch_host_presort(const double* h_x, int64_t n, const double* h_params, int64_t P, double err, int n_st,
+                                 int n_sz, int use_adaptive, double simps_err, double w_outlier, int variant, double* h_out)
+{
+    return like_batch_host_impl(h_x, n, h_params, P, err, n_st, n_sz, use_adaptive, simps_err, w_outlier, variant, 1, h_out);
+}
+
+int wfpt_sort_rts(const double* d_x, int64_t n, double* d_out, void* stream)
+{
+    if (n < 0) return fail("negative size");
+    if (n == 0) return 0;
+    if (!d_x || !d_out) return fail("null pointer argument");
+    if (n > kDeviceSortMax) return fail("wfpt_sort_rts: %lld RTs exceed the %lld the device sort takes", (long long)n, (long long)kDeviceSortMax);
+    if (n == 1) { CK(cudaMemcpyAsync(d_out, d_x, sizeof(double), cudaMemcpyDeviceToDevice, (cudaStream_t)stream)); return 0; }
+    rank_sort_kernel<<<(unsigned)((n + kSortTile - 1) / kSortTile), 256, 0, (cudaStream_t)stream>>>(d_x, (int)n, d_out);
+    CK(cudaGetLastError());
+    count_launch(1);
+    return 0;
+}
+
+// ---- identity-keyed resident cache behind the reference-shaped call ----------------------------------------------------
+// HDDM evaluates wiener_like on the SAME RT array (one per subject x condition node) five to ten times per stochastic and
+// MCMC iteration (/root/reference/hddm/likelihoods.py:117-121, hddm/models/hddm_info.py:539-558); only the eight
+// parameters change.  The cache keeps, per device, a device copy of every array it has seen, keyed by (host address,
+// length), next to a host copy that each later call is compared with byte for byte (a few KB: well under a microsecond) --
+// so an array changed in place, or a different array that landed on a freed one's address, is noticed and re-uploaded, and
+// a hit can never return another array's likelihood.  A hit sends 64 bytes of parameters per row instead of the RTs.
+struct CacheEntry {
+    double* h_copy = nullptr;
+    double* d_x = nullptr;
+    int64_t n = 0;
+    uint64_t stamp = 0;
+};
+struct CacheKey {
+    const void* p; int64_t n;
+    bool operator==(const CacheKey& o) const { return p == o.p && n == o.n; }
+};
+struct CacheKeyHash {
+    size_t operator()(const CacheKey& k) const { return std::hash<const void*>()(k.p) ^ (std::hash<int64_t>()(k.n) * 0x9e3779b97f4a7c15ull); }
+};
+struct Cache {
+    std::unordered_map<CacheKey, CacheEntry, CacheKeyHash> map;
+    size_t bytes = 0;
+    uint64_t clock = 0, hits = 0, misses = 0, stale = 0;
+};
+static Cache g_cache[kMaxDev];
+static size_t g_cache_max_entries = 65536, g_cache_max_bytes = (size_t)2 << 30;
+
+static void cache_drop(Cache& c, std::unordered_map<CacheKey, CacheEntry, CacheKeyHash>::iterator it)
+{
+    cudaFree(it->second.d_x);
+    free(it->second.h_copy);
+    c.bytes -= sizeof(double) * (size_t)it->second.n;
+    c.map.erase(it);
+}
+
+// Device copy of h_x[0..n) from the cache of the current device (uploaded now when new or changed).
+static int cache_lookup(const double* h_x, int64_t n, const double** d_x)
+{
+    int dev = 0;
+    CK(cudaGetDevice(&dev));
+    if (dev >= kMaxDev) return fail("device index %d beyond the %d this library tracks", dev, kMaxDev);
+    Cache& c = g_cache[dev];
+    const size_t bytes = sizeof(double) * (size_t)n;
+    const CacheKey key{h_x, n};
+    auto it = c.map.find(key);
+    if (it != c.map.end()) {
+        it->second.stamp = ++c.clock;
+        if (memcmp(it->second.h_copy, h_x, bytes) == 0) {
+            c.hits++;
+            *d_x = it->second.d_x;
+            return 0;
+        }
+        c.stale++;                       // same address and length, other contents: refresh in place
+        memcpy(it->second.h_copy, h_x, bytes);
+        CK(cudaMemcpyAsync(it->second.d_x, it->second.h_copy, bytes, cudaMemcpyHostToDevice, 0));
+        *d_x = it->second.d_x;
+        return 0;
+    }
+    c.misses++;
+    while (!c.map.empty() && (c.map.size() >= g_cache_max_entries || c.bytes + bytes > g_cache_max_bytes)) {
+        auto oldest = c.map.begin();
+        for (auto j = c.map.begin(); j != c.map.end(); ++j)
+            if (j->second.stamp < oldest->second.stamp) oldest = j;
+        CK(cudaStreamSynchronize(0));    // nothing in flight may still read the copy being freed
+        cache_drop(c, oldest);
+    }
+    CacheEntry e;
+    e.n = n;
+    e.stamp = ++c.clock;
+    e.h_copy = (double*)malloc(bytes);
+    if (!e.h_copy) return fail("out of host memory");
+    memcpy(e.h_copy, h_x, bytes);
+    cudaError_t err = cudaMalloc(&e.d_x, bytes);
+    if (err == cudaSuccess) err = cudaMemcpyAsync(e.d_x, e.h_copy, bytes, cudaMemcpyHostToDevice, 0);
+    if (err != cudaSuccess) {
+        cudaFree(e.d_x);
+        free(e.h_copy);
+        return fail("%s", cudaGetErrorString(err));
+    }
+    c.bytes += bytes;
+    c.map.emplace(key, e);
+    *d_x = e.d_x;
+    return 0;
+}
+
+int wfpt_like_cached_host(const double* h_x, int64_t n, const double* h_params, int64_t P, double err, int n_st,
+                          int n_sz, int use_adaptive, double simps_err, double w_outlier, int variant, double* h_out)
+{
+    HostCall guard_;
+    if (n < 0 || P < 0) return fail("negative size");
+    if (P == 0) return 0;
+    if (!h_params || !h_out || (n > 0 && !h_x)) return fail("null pointer argument");
+    const size_t pbytes = sizeof(double) * 8 * (size_t)P, obytes = sizeof(double) * (size_t)P;
+    if (n == 0 || obytes > kPinOutBytes || pbytes > kPinMaxIn || g_cache_max_entries == 0)
+        return wfpt_like_batch_host(h_x, n, h_params, P, err, n_st, n_sz, use_adaptive, simps_err, w_outlier, variant, h_out);
+    const double* dx;
+    if (cache_lookup(h_x, n, &dx)) return 1;
+    char *ph, *pd;
+    void* dp;
+    if (pinned(pbytes, &ph, &pd)) return 1;
+    memcpy(ph + kPinOutBytes, h_params, pbytes);
+    const double* params_dev = (const double*)(pd + kPinOutBytes);   // rows read straight from the mapped block
+    if (pbytes > kZeroCopyMax) {
+        if (scratch(kStageParams, pbytes, &dp)) return 1;
+        CK(cudaMemcpyAsync(dp, ph + kPinOutBytes, pbytes, cudaMemcpyHostToDevice, 0));
+        params_dev = (const double*)dp;
+    }
+    if (wfpt_like_batch(dx, n, params_dev, P, err, n_st, n_sz, use_adaptive, simps_err, w_outlier, variant, (double*)pd, nullptr))
+        return 1;
+    CK(cudaStreamSynchronize(0));
+    memcpy(h_out, ph, obytes);
+    return 0;
+}
+
+int wfpt_cache_config(int64_t max_entries, int64_t max_bytes)
+{
+    if (max_entries < 0 || max_bytes < 0) return fail("negative cache limit");
+    g_cache_max_entries = (size_t)max_entries;
+    g_cache_max_bytes = (size_t)max_bytes;
+    return 0;
+}
+
+int wfpt_cache_clear(void)
+{
+    HostCall guard_;
+    int dev = 0;
+    CK(cudaGetDevice(&dev));
+    if (dev >= kMaxDev) return 0;
+    CK(cudaStreamSynchronize(0));
+    Cache& c = g_cache[dev];
+    while (!c.map.empty()) cache_drop(c, c.map.begin());
+    return 0;
+}
+
+int wfpt_cache_stats(int64_t* entries, int64_t* bytes, int64_t* hits, int64_t* misses, int64_t* stale)
+{
+    HostCall guard_;
+    int dev = 0;
+    CK(cudaGetDevice(&dev));
+    if (dev >= kMaxDev) return fail("device index beyond the tracked range");
+    const Cache& c = g_cache[dev];
+    if (entries) *entries = (int64_t)c.map.size();
+    if (bytes) *bytes = (int64_t)c.bytes;
+    if (hits) *hits = (int64_t)c.hits;
+    if (misses) *misses = (int64_t)c.misses;
+    if (stale) *stale = (int64_t)c.stale;
     return 0;
 }
 

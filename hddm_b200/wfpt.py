@@ -24,7 +24,7 @@ from .lan import __all__ as _lan_all
 __all__ = [
     "pdf_array", "wiener_like", "wiener_like_rlddm", "wiener_like_rl", "wiener_like_multi", "wiener_like_multi_rlddm",
     "wiener_like_contaminant", "gen_rts_from_cdf", "gen_cdf_using_pdf", "split_cdf", "full_pdf", "wiener_like_batch", "sort_rts",
-    "set_variant", "get_variant", "ResidentData", "wiener_like_segments",
+    "set_variant", "get_variant", "ResidentData", "wiener_like_segments", "cache_config", "cache_clear", "cache_stats",
 ] + list(_lan_all)
 
 _variant = FAST
@@ -117,7 +117,8 @@ def wiener_like_batch(x, params, err=1e-4, n_st=2, n_sz=2, use_adaptive=1, simps
     resident; the kernels are enqueued on torch's current stream and a torch tensor is returned without a sync).
 
     `presort`: reorder the RTs by |rt| before the launch (see sort_rts).  Default: on for host buffers when the grid
-    is large enough to pay for the host argsort (P >= 64), off for device tensors (sort resident data once yourself).
+    is large enough to gain from it (P >= 64; done inside the library, on the device), off for device tensors (sort
+    resident data once yourself).
     """
     var = _variant if variant is None else variant
     L = _lib.load()
@@ -127,11 +128,10 @@ def wiener_like_batch(x, params, err=1e-4, n_st=2, n_sz=2, use_adaptive=1, simps
         ps = np.ascontiguousarray(params, dtype=np.double)
         if ps.ndim != 2 or ps.shape[1] != 8:
             raise ValueError("params must have shape (P, 8): v, sv, a, z, sz, t, st, p_outlier")
-        if presort or (presort is None and ps.shape[0] >= 64):
-            xs = sort_rts(xs)
         res = np.empty(ps.shape[0], dtype=np.double) if out is None else out
-        _lib.check(L.wfpt_like_batch_host(_ptr(xs), xs.shape[0], _ptr(ps), ps.shape[0], *o, float(w_outlier), var,
-                                          _ptr(res)))
+        # the reordering happens inside the library (on the device for up to 32,768 RTs): no host argsort per call
+        fn = L.wfpt_like_batch_host_presort if (presort or (presort is None and ps.shape[0] >= 64)) else L.wfpt_like_batch_host
+        _lib.check(fn(_ptr(xs), xs.shape[0], _ptr(ps), ps.shape[0], *o, float(w_outlier), var, _ptr(res)))
         return res
     import torch  # the batching boundary: device tensors in, device tensor out
 
@@ -155,6 +155,27 @@ def wiener_like_batch(x, params, err=1e-4, n_st=2, n_sz=2, use_adaptive=1, simps
     return res
 
 
+# ---- resident cache behind wiener_like ------------------------------------------------------------
+_cache_on = True
+
+
+def cache_config(enabled=True, max_entries=65536, max_bytes=2 << 30):
+    """The resident-array cache behind `wiener_like`: on by default.  `enabled=False` makes every call upload its RTs."""
+    global _cache_on
+    _cache_on = bool(enabled)
+    _lib.check(_lib.load().wfpt_cache_config(int(max_entries) if enabled else 0, int(max_bytes)))
+
+
+def cache_clear():
+    _lib.check(_lib.load().wfpt_cache_clear())
+
+
+def cache_stats() -> dict:
+    v = [C.c_int64() for _ in range(5)]
+    _lib.check(_lib.load().wfpt_cache_stats(*[C.byref(k) for k in v]))
+    return dict(zip(("entries", "bytes", "hits", "misses", "stale"), (k.value for k in v)))
+
+
 # ---- src/wfpt.pyx:54-76 --------------------------------------------------------------------------------------------------
 _F64 = np.dtype(np.float64)
 _Prm8 = C.c_double * 8
@@ -170,7 +191,10 @@ def wiener_like(x, v, sv, a, z, sz, t, st, err, n_st=10, n_sz=10, use_adaptive=1
     except TypeError:                            # 0-d arrays and other things float() accepts
         prm = _Prm8(float(v), float(sv), float(a), float(z), float(sz), float(t), float(st), float(p_outlier))
     res = C.c_double()
-    fn = _lib.load().wfpt_like_batch_host
+    # the same array comes back thousands of times under MCMC: the library keeps it on the device (keyed by address and
+    # length, every call compared byte for byte with the copy it holds) and only the parameters travel
+    L = _lib.load()
+    fn = L.wfpt_like_cached_host if _cache_on else L.wfpt_like_batch_host
     try:
         rc = fn(x.ctypes.data, x.shape[0], prm, 1, err, n_st, n_sz, 1 if use_adaptive else 0, simps_err, w_outlier,
                 _variant, C.byref(res))

@@ -84,6 +84,30 @@ int wfpt_like_batch(const double* d_x, int64_t n, const double* d_params, int64_
 int wfpt_like_batch_host(const double* h_x, int64_t n, const double* h_params, int64_t P, double err, int n_st,
                          int n_sz, int use_adaptive, double simps_err, double w_outlier, int variant, double* h_out);
 
+/* wfpt_like_batch_host with the RTs reordered by |rt| first (ties in array order, as np.argsort(np.abs(x), kind="stable")):
+ * tt = (|rt| - t)/a^2 is then monotone along the thread index, so the lanes of a warp take the same series expansion and K;
+ * only the summation order changes (~1e-16 relative).  Up to 32,768 RTs are counted into place on the device (a few
+ * microseconds), longer arrays are sorted on the host.  wfpt_sort_rts is the device-to-device form of that reordering
+ * (n <= 32,768).  No reference counterpart (a launch-geometry matter). */
+int wfpt_like_batch_host_presort(const double* h_x, int64_t n, const double* h_params, int64_t P, double err, int n_st,
+                                 int n_sz, int use_adaptive, double simps_err, double w_outlier, int variant, double* h_out);
+int wfpt_sort_rts(const double* d_x, int64_t n, double* d_out, void* stream);
+
+/* wfpt_like_batch_host (same arguments, bit-identical results) for the caller HDDM is: a sampler that evaluates
+ * wiener_like on the SAME RT array over and over with new parameters (hddm/likelihoods.py:117-121, one array per
+ * subject x condition node, hddm/models/base.py:1488-1493; 5-10 calls per stochastic and iteration under SliceStep,
+ * hddm/models/hddm_info.py:539-558).  The library keeps a device copy of every array it has been given, keyed by
+ * (h_x, n) per device, beside a host copy that every later call is compared with byte for byte: an array changed in
+ * place -- or another array at a recycled address -- is noticed and uploaded again.  A hit moves 64 bytes per parameter
+ * row.  Least-recently-used entries are dropped beyond wfpt_cache_config's limits (defaults 65,536 arrays, 2 GiB;
+ * max_entries == 0 turns the cache off and the call becomes wfpt_like_batch_host).  wfpt_cache_clear frees the current
+ * device's entries; wfpt_cache_stats reports them (any pointer may be NULL). */
+int wfpt_like_cached_host(const double* h_x, int64_t n, const double* h_params, int64_t P, double err, int n_st,
+                          int n_sz, int use_adaptive, double simps_err, double w_outlier, int variant, double* h_out);
+int wfpt_cache_config(int64_t max_entries, int64_t max_bytes);
+int wfpt_cache_clear(void);
+int wfpt_cache_stats(int64_t* entries, int64_t* bytes, int64_t* hits, int64_t* misses, int64_t* stale);
+
 /* The computation of wfpt_like_batch for callers that cannot allocate device memory (a process whose GPU memory is
  * already owned by another pool, a latency-bound caller that cannot afford cudaMalloc's device synchronisation, a
  * context in which allocation calls are not permitted).  It has no counterpart in the reference.
