@@ -87,6 +87,8 @@ def _declare(L):
     sim_tail = [i, i, i64, i64, f, f, f, C.c_uint64, vp, vp, vp, i, f, vp, vp, i]
     L.wfpt_sim_run.argtypes = [i, vp] + sim_tail + [vp]
     L.wfpt_sim_run.restype = i
+    L.wfpt_sim_run_sharded.argtypes = [i, vp, i, i, i, i, i64, i64, f, f, f, C.c_uint64, vp, vp, vp, i, f, vp, vp, i, vp]
+    L.wfpt_sim_run_sharded.restype = i
     L.wfpt_sim_run_host.argtypes = [i, vp] + sim_tail
     L.wfpt_sim_run_host.restype = i
     L.wfpt_sim_race_run_host.argtypes = [i, i, i, vp, i, i64, i64, f, f, f, C.c_uint64, vp, vp, vp, i, f, vp]

@@ -44,6 +44,8 @@ struct Args {
     int n_sets;
     long long n_samples;       // particles per set in this launch
     long long sample_offset;   // global index of this launch's first particle (multi-GPU particle sharding)
+    int set_offset = 0, set_stride = 1;   // global index of local set k is set_offset + k * set_stride (multi-GPU set sharding):
+                                          // the Philox counter carries the GLOBAL set index, so a shard reproduces the unsharded run
     long long out_stride_samples;  // rows of the (n_samples_total, n_sets) output arrays written by this launch start at 0
     float dt, max_t, s;
     unsigned long long seed;
@@ -251,6 +253,7 @@ __global__ void __launch_bounds__(kSimBlock) sim_kernel(const Args A)
 
         SetConst c;
         load_set<MODEL>(c, A.theta + (size_t)set * A.n_par, A);
+        const unsigned int gset = (unsigned int)(A.set_offset + set * A.set_stride);
 
         // particles are handed out one at a time from a shared counter: a lane that finishes takes the next one, so the
         // lanes of the CTA run dry together (results do not depend on who simulates which particle)
@@ -276,7 +279,7 @@ __global__ void __launch_bounds__(kSimBlock) sim_kernel(const Args A)
                 if (Traits<MODEL>::zero_a) y = __fmul_rn(c.z, c.a);
                 else y = __fadd_rn(-b, __fmul_rn(__fmul_rn(c.z, 2.f), b));
                 if (Traits<MODEL>::full || Traits<MODEL>::sdv) {
-                    const uint4 r = philox4x32(plo, phi, (unsigned int)set, 0xFFFFFFFFu, rk);
+                    const uint4 r = philox4x32(plo, phi, gset, 0xFFFFFFFFu, rk);
                     const float g = sqrtf(-2.0f * __logf(u01(r.x))) * __cosf(6.283185307179586f * u01(r.y));
                     if (Traits<MODEL>::full) {
                         // theta = v, a, z, t, sz, sv, st  (:228-235, :812-820)
@@ -291,7 +294,7 @@ __global__ void __launch_bounds__(kSimBlock) sim_kernel(const Args A)
                 walking = true;
             }
             // ---- one Philox block for everybody, then up to four sub-steps ----
-            const uint4 r = philox4x32(plo, phi, (unsigned int)set, blk++, rk);
+            const uint4 r = philox4x32(plo, phi, gset, blk++, rk);
             float4 nn;
             if (MODEL == WFPT_SIM_LEVY) {
                 nn.x = stable_draw(c.alpha, u01(r.x), u01(r.y));
@@ -847,6 +850,16 @@ extern "C" int wfpt_sim_run(int model, const float* d_theta, int n_par, int n_se
                             uint32_t* d_hist, int nbins, float hist_max_t, uint64_t* d_steps, float* d_traj, int traj_len,
                             void* stream)
 {
+    return wfpt_sim_run_sharded(model, d_theta, n_par, n_sets, 0, 1, n_samples, sample_offset, delta_t, max_t, s, seed, d_rts,
+                                d_choices, d_hist, nbins, hist_max_t, d_steps, d_traj, traj_len, stream);
+}
+
+extern "C" int wfpt_sim_run_sharded(int model, const float* d_theta, int n_par, int n_sets, int set_offset, int set_stride,
+                                    int64_t n_samples, int64_t sample_offset, float delta_t, float max_t, float s,
+                                    uint64_t seed, float* d_rts, int32_t* d_choices, uint32_t* d_hist, int nbins,
+                                    float hist_max_t, uint64_t* d_steps, float* d_traj, int traj_len, void* stream)
+{
+    if (set_offset < 0 || set_stride < 1) return api_fail("wfpt_sim_run_sharded: set_offset must be >= 0 and set_stride >= 1");
     const int want = sim::n_params_of(model);
     if (want < 0) { char m[96]; snprintf(m, sizeof m, "wfpt_sim_run: unknown model id %d", model); return api_fail(m); }
     if (n_par != want) { char m[128]; snprintf(m, sizeof m, "wfpt_sim_run: model %d takes %d parameters per set, got %d", model, want, n_par); return api_fail(m); }
@@ -861,6 +874,7 @@ extern "C" int wfpt_sim_run(int model, const float* d_theta, int n_par, int n_se
 
     sim::Args A;
     A.theta = d_theta; A.n_par = n_par; A.n_sets = n_sets; A.n_samples = n_samples; A.sample_offset = sample_offset;
+    A.set_offset = set_offset; A.set_stride = set_stride;
     A.out_stride_samples = n_samples;
     A.dt = delta_t; A.max_t = max_t; A.s = s; A.set_seed(seed); A.rts = d_rts; A.choices = d_choices;
     A.hist = d_hist; A.nbins = d_hist ? nbins : 0;

@@ -88,3 +88,51 @@ def merge_histograms(counts, group=None):
     if dist.is_initialized() and dist.get_world_size(group) > 1:
         dist.all_reduce(counts, op=dist.ReduceOp.SUM, group=group)
     return counts
+
+
+def simulate_histograms_sharded(theta, model="angle", n_samples=100000, nbins=512, shard="sets", group=None, simulate=None,
+                                **kw):
+    """Config 5 across GPUs: RT x choice histograms of `theta` (float32 CUDA tensor [n_sets, n_par], the same on every
+    rank) with the work split over the ranks of `group` and merged by NCCL on the stream the kernels run on -- no host
+    round trip.  shard="sets": rank r simulates sets r, r+W, ... and the per-set histograms are all-gathered;
+    shard="particles": every rank simulates n_samples/W particles of every set (global particle offsets) and the counts
+    are all-reduced.  Either way the random streams are keyed by GLOBAL set and particle indices, so the merged
+    histogram equals the single-GPU one bit for bit.  Returns (hist int32[n_sets, nbins, 2], steps int64[1]) on every rank.
+    (Histogram semantics: /root/reference/graveyard/basic_simulator_old.py:70-119.)"""
+    import torch
+    import torch.distributed as dist
+
+    if simulate is None:
+        from . import simulators
+
+        simulate = simulators.simulate_histograms_device
+    world = dist.get_world_size(group) if dist.is_initialized() else 1
+    rank = dist.get_rank(group) if dist.is_initialized() else 0
+    n_sets = theta.shape[0]
+    if world == 1:
+        return simulate(theta, model=model, n_samples=n_samples, nbins=nbins, **kw)
+    if shard == "particles":
+        per = -(-int(n_samples) // world)
+        lo = min(rank * per, int(n_samples))
+        mine = min(per, int(n_samples) - lo)
+        hist = torch.zeros((n_sets, int(nbins), 2), dtype=torch.int32, device=theta.device)
+        steps = torch.zeros(1, dtype=torch.int64, device=theta.device)
+        if mine > 0:
+            simulate(theta, model=model, n_samples=mine, nbins=nbins, sample_offset=lo, hist=hist, steps=steps, **kw)
+        dist.all_reduce(hist, op=dist.ReduceOp.SUM, group=group)
+        dist.all_reduce(steps, op=dist.ReduceOp.SUM, group=group)
+        return hist, steps
+    if shard != "sets":
+        raise ValueError("shard must be 'sets' or 'particles'")
+    rows = torch.from_numpy(shard_rows(n_sets, rank, world)).to(theta.device)
+    per = -(-n_sets // world)
+    padded = torch.zeros((per, int(nbins), 2), dtype=torch.int32, device=theta.device)
+    steps = torch.zeros(1, dtype=torch.int64, device=theta.device)
+    if rows.numel():
+        simulate(theta.index_select(0, rows).contiguous(), model=model, n_samples=n_samples, nbins=nbins, set_offset=rank,
+                 set_stride=world, hist=padded[: rows.numel()], steps=steps, **kw)
+    gathered = torch.empty((per * world, int(nbins), 2), dtype=torch.int32, device=theta.device)
+    dist.all_gather_into_tensor(gathered, padded, group=group)
+    dist.all_reduce(steps, op=dist.ReduceOp.SUM, group=group)
+    idx = torch.from_numpy(unshard_order(n_sets, world)).to(theta.device)
+    return gathered.index_select(0, idx), steps

@@ -373,6 +373,39 @@ def simulate_histograms(theta, model="angle", n_samples=100000, nbins=512, delta
     return hist, steps
 
 
+def simulate_histograms_device(theta, model="angle", n_samples=100000, nbins=512, delta_t=0.001, max_t=20, no_noise=False,
+                               random_state=0, sample_offset=0, set_offset=0, set_stride=1, hist=None, steps=None):
+    """simulate_histograms with everything left on the device (the batching boundary of the simulators): `theta` is a
+    float32 CUDA tensor [n_sets, n_par]; the launch goes to torch's current stream and nothing synchronises.  Returns
+    (hist int32[n_sets, nbins, 2] -- the uint32 counts, ADDED to `hist` when one is passed -- and steps int64[1]).
+    `set_offset` / `set_stride` name the global index of the local sets (rank r of W sharding sets round-robin passes
+    r, W), `sample_offset` the global index of the first particle: both only key the random streams, so a shard's counts
+    equal the same sets' / particles' counts in an unsharded run bit for bit, and an NCCL all-gather / all-reduce issued
+    on the same stream right behind this call merges them without a host round trip
+    (hddm_b200.distributed.simulate_histograms_sharded)."""
+    import torch
+
+    name = _resolve(model)
+    if name in _RACE or name in _PAR2 or name in _HIER:
+        raise NotImplementedError("device-resident histograms exist for the single-accumulator models (wfpt_sim_run)")
+    if not (isinstance(theta, torch.Tensor) and theta.is_cuda and theta.dtype == torch.float32 and theta.dim() == 2):
+        raise TypeError("theta must be a float32 CUDA tensor [n_sets, n_par]")
+    theta = theta.contiguous()
+    n_sets, n_par = theta.shape
+    if hist is None:
+        hist = torch.zeros((n_sets, int(nbins), 2), dtype=torch.int32, device=theta.device)
+    if steps is None:
+        steps = torch.zeros(1, dtype=torch.int64, device=theta.device)
+    L = _lib.load()
+    with torch.cuda.device(theta.device):
+        st = torch.cuda.current_stream().cuda_stream
+        _lib.check(L.wfpt_sim_run_sharded(_M[name][0], theta.data_ptr(), n_par, n_sets, int(set_offset), int(set_stride),
+                                          int(n_samples), int(sample_offset), float(delta_t), float(max_t),
+                                          0.0 if no_noise else 1.0, _seed(random_state), None, None, hist.data_ptr(), int(nbins),
+                                          float(max_t), steps.data_ptr(), None, 0, st))
+    return hist, steps
+
+
 def bin_simulator_output(out, bin_dt=0.04, nbins=0, max_t=-1, freq_cnt=False):
     """Host restatement of basic_simulator_old.py:70-119 for already-materialised (rts, choices, metadata)."""
     if max_t == -1:

@@ -255,6 +255,14 @@ int wfpt_sim_n_params(int model);
 int wfpt_sim_run(int model, const float* d_theta, int n_par, int n_sets, int64_t n_samples, int64_t sample_offset,
                  float delta_t, float max_t, float s, uint64_t seed, float* d_rts, int32_t* d_choices, uint32_t* d_hist,
                  int nbins, float hist_max_t, uint64_t* d_steps, float* d_traj, int traj_len, void* stream);
+/* wfpt_sim_run for one rank's share of the parameter sets: local set k is global set set_offset + k * set_stride, and
+ * that global index is what keys the random streams, so histograms and samples of a shard are bit-identical to the same
+ * sets' in an unsharded run (ranks sharding sets round-robin pass set_offset = rank, set_stride = world size).
+ * wfpt_sim_run is this with (0, 1). */
+int wfpt_sim_run_sharded(int model, const float* d_theta, int n_par, int n_sets, int set_offset, int set_stride,
+                         int64_t n_samples, int64_t sample_offset, float delta_t, float max_t, float s, uint64_t seed,
+                         float* d_rts, int32_t* d_choices, uint32_t* d_hist, int nbins, float hist_max_t,
+                         uint64_t* d_steps, float* d_traj, int traj_len, void* stream);
 int wfpt_sim_run_host(int model, const float* h_theta, int n_par, int n_sets, int64_t n_samples, int64_t sample_offset,
                       float delta_t, float max_t, float s, uint64_t seed, float* h_rts, int32_t* h_choices,
                       uint32_t* h_hist, int nbins, float hist_max_t, uint64_t* h_steps, float* h_traj, int traj_len);

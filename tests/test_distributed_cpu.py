@@ -56,6 +56,30 @@ def _worker(rank, world, port, P, q):
 
     mixed = D.wiener_like_batch_trial_sharded(torch.from_numpy(x), torch.from_numpy(prm[:4]), evaluate=fake).numpy()
     ok_trial = ok_trial and bool(np.isneginf(mixed[0]) and np.isneginf(mixed[1]) and np.isnan(mixed[2]) and mixed[3] == 2.0 * world)
+    # simulator histograms sharded by sets and by particles, merged by collectives: equal to the unsharded counts.  The
+    # injected stand-in counts, per global (set, particle), into a bin derived from those indices alone (what the device
+    # kernel's counter-based streams guarantee).
+    def fake_sim(theta, model="angle", n_samples=0, nbins=8, sample_offset=0, set_offset=0, set_stride=1, hist=None, steps=None):
+        n_sets = theta.shape[0]
+        hist = torch.zeros((n_sets, nbins, 2), dtype=torch.int32) if hist is None else hist
+        steps = torch.zeros(1, dtype=torch.int64) if steps is None else steps
+        for k in range(n_sets):
+            gs = set_offset + k * set_stride
+            assert float(theta[k, 0]) == float(gs)          # the shard really holds the rows it claims
+            for p in range(sample_offset, sample_offset + n_samples):
+                h = (gs * 7919 + p * 104729) % (2 * nbins)
+                hist[k, h // 2, h % 2] += 1
+                steps += gs + p
+        return hist, steps
+
+    n_sets_h = 7
+    theta = torch.arange(n_sets_h, dtype=torch.float32).reshape(-1, 1).repeat(1, 5)
+    want_h, want_s = fake_sim(theta, n_samples=23)
+    ok_hist = True
+    for mode in ("sets", "particles"):
+        got_h, got_s = D.simulate_histograms_sharded(theta, n_samples=23, nbins=8, shard=mode, simulate=fake_sim)
+        ok_hist = ok_hist and bool(torch.equal(got_h, want_h)) and int(got_s) == int(want_s)
+    ok_trial = ok_trial and ok_hist
     hist = torch.full((4, 8, 2), rank + 1, dtype=torch.int64)
     D.merge_histograms(hist)
     ok = bool(np.array_equal(full.numpy(), want)) and calls[0] == len(D.shard_rows(P, rank, world)) and \
