@@ -20,7 +20,7 @@ OBJ = os.path.join(CSRC, "_obj")
 LIB = os.path.join(HERE, "libwfpt_b200.so")
 INCLUDE = os.path.join(os.path.dirname(HERE), "include")
 
-SOURCES = ["api.cu", "cdf.cu", "ktable.cpp", "like_faithful.cu", "like_fast.cu", "noalloc.cu", "sim.cu"]
+SOURCES = ["api.cu", "cdf.cu", "ktable.cpp", "like_faithful.cu", "like_fast.cu", "like_lean.cu", "noalloc.cu", "sim.cu"]
 NO_FMAD = {"like_faithful.cu", "cdf.cu"}
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 COMMON = ["-O3", "-lineinfo", "-std=c++17", "-Xcompiler", "-fPIC", "-I", INCLUDE, "-I", CSRC]

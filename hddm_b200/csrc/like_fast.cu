@@ -1,4 +1,6 @@
 // Fast-variant instantiations of the likelihood kernels (table-driven evaluator, wfpt_fast.cuh).
+#include <cstdlib>
+
 #include "like_kernels.cuh"
 #include "wfpt_fast.cuh"
 
@@ -70,6 +72,10 @@ cudaError_t launch_like_batch_fast(const BatchArgs& a)
 {
     const int64_t nblk = a.P * (int64_t)a.slices;
     if (nblk == 0) return cudaSuccess;
+    {
+        const KTable kt = get_ktable(a.o.err);
+        if (lean_applies(a, kt) && !getenv("WFPT_NO_LEAN")) return launch_like_lean(a, kt);
+    }
     if (a.o.use_adaptive)
         like_batch_kernel<FastImpl, true><<<(unsigned)nblk, kBlock, 0, a.stream>>>(
             a.x, a.n, a.params, a.P, a.o, a.w_outlier, a.slices, a.chunk, a.slices > 1 ? a.part_sum : a.out,

@@ -1,0 +1,519 @@
+// Lean fixed-grid likelihood kernel: the instantiation the headline benchmark (BASELINE.json configs[3] with configs[1]'s
+// fixed 3x3 Simpson grid) and every other fixed-grid launch with n_sz = 2 run through.
+//
+// Same mathematics, tables and results as like_batch_kernel<FastImpl, false> (wfpt_fast.cuh): the series-term table, the
+// staged quadrature nodes, the lattice factorisation of the small-time series, p*exp(E) instead of exp(log p + E).  What
+// differs is how the trial loop is organised around the WARP:
+//
+//  * RTs arrive |rt|-sorted, so the 32 trials a warp holds in one round sit next to each other on the tt axis and nearly
+//    always share the series expansion and its term count K.  The warp keeps, per t-node, the piece of the series-term
+//    table it was in last time (bounds on the high word of tt, in shared memory); one vote tells whether every lane is
+//    still inside.  If so the descriptor is a warp-uniform value: every branch on "small or large time" and on K is a
+//    uniform branch, and each (expansion, K) combination runs straight-line code with exactly its terms.  Otherwise the
+//    lanes look their pieces up and the node is evaluated once per distinct descriptor present, lanes of other pieces
+//    riding along with their results discarded (two passes at a piece boundary, nothing diverges).
+//  * exp arguments are range-checked once per node set through the high words (one three-input max), the check's vote
+//    is uniform as well; a node set with an argument outside the branch-free exp kernel's range sends its trial to a short
+//    list in shared memory that the CTA evaluates after the loop with the general evaluator (library exp, every term the
+//    reference sums) -- no call site and no slow path inside the hot loop.
+//  * per-thread state is small enough for six resident CTAs per SM without spills: set constants live in shared memory,
+//    the exp chains of a node set run three at a time.
+//
+// Reference: /root/reference/src/pdf.pxi:28-146 (ftt_01w, pdf_sv, full_pdf), /root/reference/src/integrate.pxi:12-68
+// (simpson_1D / simpson_2D), /root/reference/src/wfpt.pyx:54-76 (wiener_like).
+#include "like_kernels.cuh"
+#include "wfpt_fast.cuh"
+
+namespace wfpt {
+namespace lean {
+
+using fast::NodeTab;
+using fast::Tables;
+
+constexpr int kWarps = kBlock / 32;
+constexpr int kDeferCap = 256;          // trials per CTA the post-loop general evaluator takes before the CTA starts over
+constexpr unsigned kFull = 0xffffffffu;
+
+// Set constants the loop reads from shared memory (one 16-byte load brings two).
+struct alignas(16) SetConst {
+    double a2, inv_a2;        // a^2 and its reciprocal
+    double sv2, nv2;          // sv^2, -v^2
+    double pref_s, pref_l;    // 1/(sqrt(2 pi) a^2), pi/a^2
+    double omp, wp;           // 1 - p_outlier, w_outlier * p_outlier
+    double tlo, ct;           // t - st/2 (validity bound on |x|), Simpson scale along t
+};
+
+struct alignas(16) PieceCache { int lo_hi, hi_hi, desc, pad; };   // high words of tt strictly inside (lo_hi, hi_hi) -> desc
+
+struct Shared {
+    SetConst sc;
+    PieceCache piece[kWarps][fast::kMaxNodes];
+    double defer[kDeferCap];
+    int ndefer;
+    int nt, sv_nonzero, nzn;
+};
+
+// sum_i log(p_i) as log(prod_i p_i) (see LogProduct in like_kernels.cuh), with the zero flag kept inside and a 32-bit exponent
+// (a thread sees at most 2^30 trials of at most 2^10 binades each... the slice limit of plan_slices keeps the sum in range).
+struct LogProd {
+    double m = 1.0, slow = 0.0;
+    int e = 0, zero = 0;
+    __device__ __forceinline__ void add(double p)
+    {
+        const int hi = __double2hiint(p);
+        if ((unsigned)(hi - 0x00200000) < 0x7fb00000u) {  // 2^-1020 <= p < 2^1022
+            m *= p;
+            const int hm = __double2hiint(m);
+            e += (hm >> 20) - 1023;
+            m = __hiloint2double((hm & 0x000fffff) | 0x3ff00000, __double2loint(m));
+        } else {
+            add_slow(p);
+        }
+    }
+    __device__ __forceinline__ void add_slow(double p)
+    {
+        zero |= (p == 0);
+        slow += log(p);
+    }
+    __device__ __forceinline__ double value() const { return slow + fma((double)e, 0.6931471805599453, log(m)); }
+};
+
+__device__ __forceinline__ Shared& shared()
+{
+    __shared__ Shared s;
+    return s;
+}
+
+// ---- exp, three or four independent chains side by side -------------------------------------------------------------------
+// exp(x) = 2^e * 2^(j/64) * exp(r) as in fast::exp_core; Horner form (one constant operand per step).  |x| < 708.
+__constant__ double kE[8] = {92.33248261689366, 6755399441055744.0, -0.01083042469326756, -2.9815858269852933e-12,
+                             1.0 / 120.0, 1.0 / 24.0, 1.0 / 6.0, 0.5};
+
+template <int M>
+__device__ __forceinline__ void expv(const double (&x)[M], double (&out)[M], const double* __restrict__ tab)
+{
+    double t[M], r[M];
+    int ki[M];
+#pragma unroll
+    for (int i = 0; i < M; i++) t[i] = fma(x[i], kE[0], kE[1]);
+#pragma unroll
+    for (int i = 0; i < M; i++) {
+        ki[i] = __double2loint(t[i]);
+        t[i] = t[i] - kE[1];
+    }
+#pragma unroll
+    for (int i = 0; i < M; i++) r[i] = fma(t[i], kE[2], x[i]);
+#pragma unroll
+    for (int i = 0; i < M; i++) r[i] = fma(t[i], kE[3], r[i]);
+#pragma unroll
+    for (int i = 0; i < M; i++) t[i] = fma(r[i], kE[4], kE[5]);
+#pragma unroll
+    for (int i = 0; i < M; i++) t[i] = fma(t[i], r[i], kE[6]);
+#pragma unroll
+    for (int i = 0; i < M; i++) t[i] = fma(t[i], r[i], kE[7]);
+#pragma unroll
+    for (int i = 0; i < M; i++) t[i] = fma(t[i], r[i] * r[i], r[i]);
+#pragma unroll
+    for (int i = 0; i < M; i++) {
+        const double T = tab[ki[i] & 63];
+        const double res = fma(T, t[i], T);
+        int hi;
+        asm("mad.lo.s32 %0, %1, 16384, %2;" : "=r"(hi) : "r"(ki[i] & ~63), "r"(__double2hiint(res)));
+        out[i] = __hiloint2double(hi, __double2loint(res));
+    }
+}
+
+// non-positive argument whose exp may underflow: anything below -707 is taken as -707 (the result only ever multiplies
+// terms that are then 1e-307 of the leading one)
+__device__ __forceinline__ double clamp_neg(double x)
+{
+    const unsigned hi = min((unsigned)__double2hiint(x), 0xC0861800u);
+    return __hiloint2double((int)hi, __double2loint(x));
+}
+__device__ __forceinline__ int abs_hi(double x) { return __double2hiint(x) & 0x7fffffff; }
+constexpr int kExpHiLimit = 0x40862000;   // |x| < 708 <=> abs_hi(x) < this (NaN and inf fail too)
+
+// 1/sqrt(x), normal positive x: hardware seed, then one third-order step and one Newton step
+__device__ __forceinline__ double rsqrt_d(double x)
+{
+    double y;
+    asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
+    const double hx = 0.5 * x;
+    double e = fma(-hx * y, y, 0.5);
+    y = fma(y, e, y);
+    e = fma(-hx * y, y, 0.5);
+    return fma(y, e, y);
+}
+
+// ---- one t-node: inner z-integral (or the single node) for a warp-uniform descriptor ---------------------------------------
+// d = (small << 8) | K, uniform over the warp.  Lanes whose own descriptor differs, or that carry no live node (x' <= 0),
+// compute along and are ignored by the caller.  Returns the Simpson sum over z times cz (NZN == 3) or the node (NZN == 1);
+// ored into `neg`: sign bits of the series sums; `bad` |= an exp argument outside the fast kernel's range.
+template <int NZN, bool SV>
+__device__ __forceinline__ double tnode_value(int d, double xp, double tt, const NodeTab* __restrict__ Z,
+                                              const Tables& T, const SetConst& sc, int sign, int& neg, int& bad)
+{
+    const double* tab = T.exptab;
+    double rs = 1.0, c = 0.5;
+    if (SV) {
+        rs = rsqrt_d(fma(sc.sv2, xp, 1.0));
+        c = 0.5 * rs * rs;
+    }
+    const double E0 = sc.nv2 * xp * c;
+    double E[NZN], y[NZN];
+#pragma unroll
+    for (int n = 0; n < NZN; n++) E[n] = fma(Z[n].A, c, E0);
+    const int K = d & 0xff;
+    double pref;
+    if (d >> 8) {
+        const double r = rsqrt_d(tt);
+        const double tau = r * r, m2t = -2.0 * tau;
+        pref = tau * r * sc.pref_s * rs;
+        double a[NZN], e0[NZN];
+#pragma unroll
+        for (int n = 0; n < NZN; n++) a[n] = fma(Z[n].uh1, tau, E[n]);
+        if (NZN == 3) bad |= (max(max(abs_hi(a[0]), abs_hi(a[1])), abs_hi(a[NZN - 1])) >= kExpHiLimit);
+        else bad |= (abs_hi(a[0]) >= kExpHiLimit);
+        expv<NZN>(a, e0, tab);
+        const double z_first = Z[0].u[1], z_last = Z[NZN - 1].u[1];
+        if (NZN == 3) {
+            double g[3], w[3];
+            g[0] = clamp_neg(fma(m2t, z_first, m2t));          // R   = exp(-2 (z_0 + 1) / tt)
+            g[1] = clamp_neg(fma(-m2t, z_last, m2t));          // Q   = exp(-2 (1 - z_last) / tt)
+            g[2] = clamp_neg(m2t * T.zstep[sign]);             // rho = exp(-2 step / tt)
+            expv<3>(g, w, tab);
+            const double rho = w[2];
+            double Rn[3], Qn[3];
+            Rn[0] = w[0];
+            Rn[1] = Rn[0] * rho;
+            Rn[2] = Rn[1] * rho;
+            Qn[2] = (K >= 3) ? w[1] : 0.0;                     // K == 2 sums k = 0, 1 only
+            Qn[1] = Qn[2] * rho;
+            Qn[0] = Qn[1] * rho;
+#pragma unroll
+            for (int n = 0; n < 3; n++) {
+                double inner = fma(Z[n].u[2], Rn[n], Z[n].u[1]);
+                inner = fma(Z[n].u[0], Qn[n], inner);
+                y[n] = inner;
+            }
+            if (K >= 4) {                                      // uniform: k = +2 term, e(k=2)/e(k=1) = R_n * exp(-4/tt)
+                const double H = w[0] * (w[1] * rho * rho);
+#pragma unroll
+                for (int n = 0; n < 3; n++) y[n] = fma(Z[n].u[3], Rn[n] * Rn[n] * H, y[n]);
+            }
+#pragma unroll
+            for (int n = 0; n < 3; n++) y[n] = fma(e0[n], y[n], 0.0);
+        } else {
+            double g[2], w[2];
+            g[0] = clamp_neg(fma(m2t, z_first, m2t));
+            g[1] = clamp_neg(fma(-m2t, z_last, m2t));
+            expv<2>(g, w, tab);
+            const double R = w[0], Q = (K >= 3) ? w[1] : 0.0;
+            double inner = fma(Z[0].u[2], R, Z[0].u[1]);
+            inner = fma(Z[0].u[0], Q, inner);
+            if (K >= 4) inner = fma(Z[0].u[3], R * R * (w[0] * w[1]), inner);
+            y[0] = fma(e0[0], inner, 0.0);
+        }
+    } else {
+        pref = sc.pref_l * rs;
+        double a[NZN + 1], w[NZN + 1];
+        a[NZN] = -fast::kHalfPiSq * tt;
+#pragma unroll
+        for (int n = 0; n < NZN; n++) a[n] = E[n];
+        if (NZN == 3) bad |= (max(max(max(abs_hi(a[0]), abs_hi(a[1])), abs_hi(a[2])), abs_hi(a[3])) >= kExpHiLimit);
+        else bad |= (max(abs_hi(a[0]), abs_hi(a[1])) >= kExpHiLimit);
+        expv<NZN + 1>(a, w, tab);
+        const double q = w[NZN], q2 = q * q, q4 = q2 * q2;
+#pragma unroll
+        for (int n = 0; n < NZN; n++) y[n] = q * Z[n].S[0];
+        if (K >= 2) {
+#pragma unroll
+            for (int n = 0; n < NZN; n++) y[n] = fma(q4, Z[n].S[1], y[n]);
+        }
+        if (K >= 3) {
+            const double q8 = q4 * q4, q9 = q8 * q;
+#pragma unroll
+            for (int n = 0; n < NZN; n++) y[n] = fma(q9, Z[n].S[2], y[n]);
+            if (K >= 4) {
+                const double q16 = q8 * q8;
+#pragma unroll
+                for (int n = 0; n < NZN; n++) y[n] = fma(q16, Z[n].S[3], y[n]);
+            }
+        }
+#pragma unroll
+        for (int n = 0; n < NZN; n++) y[n] = fma(y[n], w[n], 0.0);
+    }
+#pragma unroll
+    for (int n = 0; n < NZN; n++) {
+        y[n] *= pref;                       // pref > 0: the sign is the series sum's
+        neg |= __double2hiint(y[n]);
+    }
+    if (NZN == 3) return (fma(4.0, y[1], y[0]) + y[2]) * T.cz[sign];   // integrate.pxi:30-45 with n_sz = 2
+    return y[0];
+}
+
+// Per-lane table lookup (slow path only).
+__device__ __forceinline__ int lookup_lane(const Tables& T, double tt, int* piece)
+{
+    const long long b = __double_as_longlong(tt);
+    int p = 0;
+    const int n = T.npieces;
+    while (p < n && b >= T.thr[p]) p++;
+    *piece = p;
+    return T.desc[p];
+}
+
+// Density of the warp's 32 trials (one per lane; `live` lanes only) on the staged fixed grid.
+template <int NZN, bool SV>
+__device__ __forceinline__ double warp_density(double ax, int sign, bool live, const Tables& T, Shared& S, int nt,
+                                               int& neg, int& bad)
+{
+    const SetConst& sc = S.sc;
+    const int w = threadIdx.x >> 5;
+    const NodeTab* Z = T.z[sign];
+    double acc = 0.0;
+#pragma unroll 1
+    for (int i = 0; i <= nt; i++) {
+        const double xp = ax - T.tn[i];
+        const bool alive = live && (xp > 0);
+        // tt = x'/a^2, correctly rounded from the reciprocal (quotient + one residual correction): K is decided on it
+        const double q0 = xp * sc.inv_a2;
+        const double tt = fma(fma(-q0, sc.a2, xp), sc.inv_a2, q0);
+        const int th = __double2hiint(tt);
+        const PieceCache pc = S.piece[w][i];
+        double val = 0.0;
+        const unsigned am = __ballot_sync(kFull, alive);
+        if (am == 0) continue;                                  // nobody has this node (x' <= 0 everywhere): contributes 0
+        if (__all_sync(kFull, !alive || (th > pc.lo_hi && th < pc.hi_hi))) {
+            int ng = 0, bd = 0;
+            val = tnode_value<NZN, SV>(pc.desc, xp, tt, Z, T, sc, sign, ng, bd);
+            if (alive) { neg |= ng; bad |= bd; }                // lanes without the node computed along on garbage
+        } else {
+            // a piece boundary runs through the warp (or the warp has moved on): look up per lane, evaluate once per
+            // distinct descriptor present, and remember the piece of the last live lane for the next round
+            int piece = 0;
+            const int mine = alive ? lookup_lane(T, tt, &piece) : -1;
+            unsigned todo = am;
+            int neg_l = 0, bad_l = 0;
+            while (todo) {
+                const int src = __ffs(todo) - 1;
+                const int d = __shfl_sync(kFull, mine, src);
+                const bool match = (mine == d);
+                int ng = 0, bd = 0;
+                const double v = tnode_value<NZN, SV>(d, xp, tt, Z, T, sc, sign, ng, bd);
+                if (match) { val = v; neg_l = ng; bad_l = bd; }
+                todo &= ~__ballot_sync(kFull, match);
+            }
+            neg |= neg_l;
+            bad |= bad_l;
+            {
+                const int last = 31 - __clz(am);
+                const int p = __shfl_sync(kFull, piece, last);
+                if ((threadIdx.x & 31) == 0) {
+                    PieceCache nc;
+                    // strict high-word bounds: inside means lo_b <= bits(tt) < hi_b whatever the low words are
+                    nc.lo_hi = (p > 0) ? (int)(T.thr[p - 1] >> 32) : (int)0x80000000;
+                    nc.hi_hi = (p < T.npieces) ? (int)(T.thr[p] >> 32) : 0x7fffffff;
+                    nc.desc = T.desc[p];
+                    nc.pad = 0;
+                    S.piece[w][i] = nc;
+                }
+                __syncwarp();
+            }
+        }
+        if (!alive) val = 0.0;
+        acc = fma(T.wts_t[i], val, acc);
+    }
+    return acc * sc.ct;
+}
+
+__device__ __forceinline__ bool lean_set_ok(int mode, int kind)
+{
+    return mode == fast::kModeZero || mode == fast::kModePoint || (mode == fast::kModeFixed && (kind == 0 || kind == 1));
+}
+
+// General evaluator for the handful of trials the loop defers, and for the whole slice when the list overflows.
+static __device__ __noinline__ double general_density(double x, const Tables* Tp, int kind, int nz, int nt, int kl_max, int mode,
+                                                       double tlo)
+{
+    fast::Set s;
+    fast::rebuild_set(s, Tp, kind, kl_max);
+    s.mode = mode;
+    s.nz = nz;
+    s.nt = nt;
+    s.tlo = tlo;
+    bool defer;
+    return fast::density<false>(x, s, &defer);
+}
+
+__global__ void __launch_bounds__(kBlock, 6) like_lean_kernel(const double* __restrict__ x, int64_t n,
+                                                             const double* __restrict__ params, int64_t P, Opts o,
+                                                             double w_outlier, int slices, int64_t chunk,
+                                                             double* __restrict__ out_sum, int* __restrict__ out_zero,
+                                                             int* __restrict__ done, double* __restrict__ final_out,
+                                                             const __grid_constant__ KTable kt)
+{
+    const int64_t bid = blockIdx.x;
+    const int64_t p = bid / slices;
+    const int s = (int)(bid - p * slices);
+    if (p >= P) return;
+    const double* row = params + 8 * p;
+    Params prm{row[0], row[1], row[2], row[3], row[4], row[5], row[6], row[7]};
+    const double po = prm.p_outlier;
+    // wfpt.pyx:63-64: p_outlier outside [0,1] -> -inf for the whole set
+    if (!((po >= 0) & (po <= 1))) {
+        if (threadIdx.x == 0) {
+            if (out_zero) { out_sum[bid] = 0.0; out_zero[bid] = 1; }
+            else out_sum[bid] = -CUDART_INF;
+            if (out_zero && done) final_out[p] = -CUDART_INF;
+        }
+        return;
+    }
+    Shared& S = shared();
+    int mode, kind, nz, nt, kl_max;
+    {
+        fast::Set set;
+        fast::prepare(set, prm, o, kt);     // CTA-collective: fills fast::Tables
+        mode = set.mode; kind = set.kind; nz = set.nz; nt = set.nt; kl_max = set.kl_max;
+        if (threadIdx.x == 0) {
+            SetConst c;
+            c.a2 = set.a2; c.inv_a2 = set.inv_a2; c.sv2 = set.sv2; c.nv2 = -set.v2;
+            c.pref_s = fast::kInvSqrt2Pi * set.inv_a2; c.pref_l = kPi * set.inv_a2;
+            c.omp = __dsub_rn(1.0, po); c.wp = __dmul_rn(w_outlier, po);
+            c.tlo = set.tlo;
+            c.ct = 1.0;
+            S.sc = c;
+            S.ndefer = 0;
+            S.nt = nt; S.sv_nonzero = set.sv_nonzero; S.nzn = nz + 1;
+        }
+        for (int i = threadIdx.x; i < kWarps * fast::kMaxNodes; i += kBlock) {
+            PieceCache e{0, 0, 0, 0};       // empty interval: the first round looks its pieces up
+            (&S.piece[0][0])[i] = e;
+        }
+    }
+    __syncthreads();
+    const Tables& T = fast::tables();
+    if (threadIdx.x == 0) S.sc.ct = T.ct;
+    __syncthreads();
+
+    const int64_t beg = (int64_t)s * chunk;
+    const int64_t end = (beg + chunk < n) ? beg + chunk : n;
+    int64_t b = beg;
+    const bool head = (reinterpret_cast<uintptr_t>(x + b) & 15) && b < end;
+    if (head) b++;
+    const int npair = (int)((end - b) >> 1);
+    const bool tail = (end > b) && ((end - b) & 1);
+    const double2* x2 = reinterpret_cast<const double2*>(x + b);
+    const int rounds = (npair + kBlock - 1) / kBlock + 1;   // + 1: the head / tail elements
+
+    LogProd lp;
+    const bool usable = lean_set_ok(mode, kind);
+    const bool zero_set = (mode == fast::kModeZero);
+    const bool sv = S.sv_nonzero != 0;
+    const bool z3 = (kind == 1);
+
+    if (usable) {
+#pragma unroll 1
+        for (int r = 0; r < rounds; r++) {
+            double v0 = 0.0, v1 = 0.0;
+            int cnt = 0;
+            const int i = r * kBlock + threadIdx.x;
+            if (i < npair) {
+                const double2 xx = __ldg(x2 + i);
+                v0 = xx.x;
+                v1 = xx.y;
+                cnt = 2;
+            } else if (r == rounds - 1) {
+                if (head && threadIdx.x == 0) { v0 = x[beg]; cnt = 1; }
+                if (tail && threadIdx.x == kBlock - 1) { v0 = x[end - 1]; cnt = 1; }
+            }
+            const int wcnt = __reduce_max_sync(kFull, cnt);
+#pragma unroll 1
+            for (int h = 0; h < wcnt; h++) {
+                const double xv = h ? v1 : v0;
+                const double ax = fabs(xv);
+                const bool have = h < cnt;
+                const bool live = have && !zero_set && !((ax - S.sc.tlo) < 0);   // pdf.pxi:112, the trial-dependent part
+                double dens = 0.0;
+                if (__any_sync(kFull, live)) {
+                    const int sign = xv > 0;
+                    int neg = 0, bad = 0;
+                    if (z3) dens = sv ? warp_density<3, true>(ax, sign, live, T, S, nt, neg, bad)
+                                      : warp_density<3, false>(ax, sign, live, T, S, nt, neg, bad);
+                    else dens = sv ? warp_density<1, true>(ax, sign, live, T, S, nt, neg, bad)
+                                   : warp_density<1, false>(ax, sign, live, T, S, nt, neg, bad);
+                    // a negative truncated series anywhere makes pdf_sv's log(p) NaN (pdf.pxi:102); pdf (sv == 0) lets it through
+                    if (sv && neg < 0) dens = CUDART_NAN;
+                    if (!live) dens = 0.0;
+                    if (live && bad) {
+                        // an exp argument outside the branch-free kernel's range: the general evaluator takes this trial later
+                        const int slot = atomicAdd(&S.ndefer, 1);
+                        if (slot < kDeferCap) S.defer[slot] = xv;
+                        continue;
+                    }
+                }
+                if (have) lp.add(mix_outlier(dens, S.sc.omp, S.sc.wp));
+            }
+        }
+    }
+    __syncthreads();
+    const int nd = S.ndefer;
+    if (!usable || nd > kDeferCap) {
+        // not a layout this kernel stages, or too many deferred trials: the whole slice through the general evaluator
+        lp = LogProd();
+#pragma unroll 1
+        for (int64_t i = beg + threadIdx.x; i < end; i += kBlock)
+            lp.add_slow(mix_outlier(general_density(x[i], &T, kind, nz, nt, kl_max, mode, S.sc.tlo), S.sc.omp, S.sc.wp));
+    } else {
+#pragma unroll 1
+        for (int q = threadIdx.x; q < nd; q += kBlock)
+            lp.add_slow(mix_outlier(general_density(S.defer[q], &T, kind, nz, nt, kl_max, mode, S.sc.tlo), S.sc.omp, S.sc.wp));
+    }
+    const double acc = lp.value();
+    int any_zero;
+    const double tot = block_sum_or<kBlock>(acc, lp.zero, &any_zero);
+    if (threadIdx.x == 0) {
+        if (out_zero) {
+            out_sum[bid] = tot;
+            out_zero[bid] = any_zero;
+            if (done) {
+                __threadfence();
+                if (atomicAdd(&done[p], 1) == slices - 1) {
+                    __threadfence();
+                    double sum = 0.0;
+                    int z = 0;
+                    for (int k = 0; k < slices; k++) {
+                        sum += __ldcg(&out_sum[p * slices + k]);
+                        z |= __ldcg(&out_zero[p * slices + k]);
+                    }
+                    final_out[p] = z ? -CUDART_INF : sum;
+                    done[p] = 0;
+                }
+            }
+        } else {
+            out_sum[bid] = any_zero ? -CUDART_INF : tot;   // wfpt.pyx:71-72
+        }
+    }
+}
+
+}  // namespace lean
+
+// Which fixed-grid launches the lean kernel takes (decided from the options alone; per-set layouts inside are then always
+// ones it stages: no integration, t only, or n_sz = 2 with any n_st).
+bool lean_applies(const BatchArgs& a, const KTable& kt)
+{
+    return !a.o.use_adaptive && !a.seg && !a.one_each && kt.n >= 0 && kt.kl_max <= 4 && kt.ks_max <= 4 && a.o.n_sz == 2 &&
+           a.o.n_st >= 1 && a.o.n_st < fast::kMaxNodes;
+}
+
+cudaError_t launch_like_lean(const BatchArgs& a, const KTable& kt)
+{
+    const int64_t nblk = a.P * (int64_t)a.slices;
+    if (nblk == 0) return cudaSuccess;
+    lean::like_lean_kernel<<<(unsigned)nblk, kBlock, 0, a.stream>>>(
+        a.x, a.n, a.params, a.P, a.o, a.w_outlier, a.slices, a.chunk, a.slices > 1 ? a.part_sum : a.out,
+        a.slices > 1 ? a.part_zero : nullptr, a.slices > 1 ? a.done : nullptr, a.out, kt);
+    return cudaGetLastError();
+}
+
+}  // namespace wfpt
