@@ -84,13 +84,38 @@ __device__ __forceinline__ Shared& shared()
     return s;
 }
 
+// ---- shared memory by 32-bit address ------------------------------------------------------------------------------------------
+// The tables are read through explicit shared-window addresses (one base per CTA, member offsets as immediates): left to
+// itself the compiler re-derives the window base (cluster CTA id, shift, add) at most use sites, a dozen uniform-datapath
+// instructions per t-node that all take issue slots.  The loads are declared without side effects: the tables do not
+// change once the CTA has passed the barrier behind prepare().
+template <int OFF>
+__device__ __forceinline__ double2 lds2(unsigned a)
+{
+    double2 v;
+    asm("ld.shared.v2.f64 {%0, %1}, [%2+%3];" : "=d"(v.x), "=d"(v.y) : "r"(a), "n"(OFF));
+    return v;
+}
+template <int OFF>
+__device__ __forceinline__ double lds1(unsigned a)
+{
+    double v;
+    asm("ld.shared.f64 %0, [%1+%2];" : "=d"(v) : "r"(a), "n"(OFF));
+    return v;
+}
+constexpr int kOffZ = (int)offsetof(Tables, z), kOffTn = (int)offsetof(Tables, tn), kOffWt = (int)offsetof(Tables, wts_t),
+              kOffCz = (int)offsetof(Tables, cz), kOffZstep = (int)offsetof(Tables, zstep), kOffExp = (int)offsetof(Tables, exptab);
+constexpr int kNodeBytes = (int)sizeof(NodeTab), kSignBytes = kNodeBytes * fast::kMaxNodes;
+constexpr int kNA = (int)offsetof(NodeTab, A), kNU = (int)offsetof(NodeTab, u), kNS = (int)offsetof(NodeTab, S);
+static_assert(kNA % 16 == 0 && kNU % 16 == 0 && kNS % 16 == 0 && kNodeBytes % 16 == 0, "NodeTab pairs must be 16-byte aligned");
+
 // ---- exp, three or four independent chains side by side -------------------------------------------------------------------
 // exp(x) = 2^e * 2^(j/64) * exp(r) as in fast::exp_core; Horner form (one constant operand per step).  |x| < 708.
 __constant__ double kE[8] = {92.33248261689366, 6755399441055744.0, -0.01083042469326756, -2.9815858269852933e-12,
                              1.0 / 120.0, 1.0 / 24.0, 1.0 / 6.0, 0.5};
 
 template <int M>
-__device__ __forceinline__ void expv(const double (&x)[M], double (&out)[M], const double* __restrict__ tab)
+__device__ __forceinline__ void expv(const double (&x)[M], double (&out)[M], unsigned tab)
 {
     double t[M], r[M];
     int ki[M];
@@ -115,7 +140,7 @@ __device__ __forceinline__ void expv(const double (&x)[M], double (&out)[M], con
     for (int i = 0; i < M; i++) t[i] = fma(t[i], r[i] * r[i], r[i]);
 #pragma unroll
     for (int i = 0; i < M; i++) {
-        const double T = tab[ki[i] & 63];
+        const double T = lds1<0>(tab + ((ki[i] & 63) << 3));
         const double res = fma(T, t[i], T);
         int hi;
         asm("mad.lo.s32 %0, %1, 16384, %2;" : "=r"(hi) : "r"(ki[i] & ~63), "r"(__double2hiint(res)));
@@ -150,19 +175,17 @@ __device__ __forceinline__ double rsqrt_d(double x)
 // compute along and are ignored by the caller.  Returns the Simpson sum over z times cz (NZN == 3) or the node (NZN == 1);
 // ored into `neg`: sign bits of the series sums; `bad` |= an exp argument outside the fast kernel's range.
 template <int NZN, bool SV>
-__device__ __forceinline__ double tnode_value(int d, double xp, double tt, const NodeTab* __restrict__ Z,
-                                              const Tables& T, const SetConst& sc, int sign, int& neg, int& bad)
+__device__ __forceinline__ double tnode_value(int d, double xp, double tt, unsigned tb, unsigned zb, const SetConst& sc,
+                                              int sign, int& neg, int& bad)
 {
-    const double* tab = T.exptab;
+    const unsigned tab = tb + kOffExp;
     double rs = 1.0, c = 0.5;
     if (SV) {
         rs = rsqrt_d(fma(sc.sv2, xp, 1.0));
         c = 0.5 * rs * rs;
     }
     const double E0 = sc.nv2 * xp * c;
-    double E[NZN], y[NZN];
-#pragma unroll
-    for (int n = 0; n < NZN; n++) E[n] = fma(Z[n].A, c, E0);
+    double y[NZN];
     const int K = d & 0xff;
     double pref;
     if (d >> 8) {
@@ -170,17 +193,27 @@ __device__ __forceinline__ double tnode_value(int d, double xp, double tt, const
         const double tau = r * r, m2t = -2.0 * tau;
         pref = tau * r * sc.pref_s * rs;
         double a[NZN], e0[NZN];
-#pragma unroll
-        for (int n = 0; n < NZN; n++) a[n] = fma(Z[n].uh1, tau, E[n]);
+        {
+            const double2 Au0 = lds2<kNA>(zb);                                // (A, -z^2/2) of node 0, 1, 2
+            a[0] = fma(Au0.y, tau, fma(Au0.x, c, E0));
+            if (NZN == 3) {
+                const double2 Au1 = lds2<kNA + kNodeBytes>(zb), Au2 = lds2<kNA + 2 * kNodeBytes>(zb);
+                a[1] = fma(Au1.y, tau, fma(Au1.x, c, E0));
+                a[NZN - 1] = fma(Au2.y, tau, fma(Au2.x, c, E0));
+            }
+        }
         if (NZN == 3) bad |= (max(max(abs_hi(a[0]), abs_hi(a[1])), abs_hi(a[NZN - 1])) >= kExpHiLimit);
         else bad |= (abs_hi(a[0]) >= kExpHiLimit);
         expv<NZN>(a, e0, tab);
-        const double z_first = Z[0].u[1], z_last = Z[NZN - 1].u[1];
         if (NZN == 3) {
+            const double2 ua0 = lds2<kNU>(zb), ua1 = lds2<kNU + kNodeBytes>(zb), ua2 = lds2<kNU + 2 * kNodeBytes>(zb);   // (z-2, z)
+            const double2 ub0 = lds2<kNU + 16>(zb), ub1 = lds2<kNU + 16 + kNodeBytes>(zb), ub2 = lds2<kNU + 16 + 2 * kNodeBytes>(zb);   // (z+2, z+4)
+            const double um2[3] = {ua0.x, ua1.x, ua2.x}, u0[3] = {ua0.y, ua1.y, ua2.y}, up2[3] = {ub0.x, ub1.x, ub2.x},
+                         up4[3] = {ub0.y, ub1.y, ub2.y};
             double g[3], w[3];
-            g[0] = clamp_neg(fma(m2t, z_first, m2t));          // R   = exp(-2 (z_0 + 1) / tt)
-            g[1] = clamp_neg(fma(-m2t, z_last, m2t));          // Q   = exp(-2 (1 - z_last) / tt)
-            g[2] = clamp_neg(m2t * T.zstep[sign]);             // rho = exp(-2 step / tt)
+            g[0] = clamp_neg(fma(m2t, u0[0], m2t));            // R   = exp(-2 (z_0 + 1) / tt)
+            g[1] = clamp_neg(fma(-m2t, u0[2], m2t));           // Q   = exp(-2 (1 - z_last) / tt)
+            g[2] = clamp_neg(m2t * lds1<kOffZstep>(tb + 8 * sign));   // rho = exp(-2 step / tt)
             expv<3>(g, w, tab);
             const double rho = w[2];
             double Rn[3], Qn[3];
@@ -191,53 +224,60 @@ __device__ __forceinline__ double tnode_value(int d, double xp, double tt, const
             Qn[1] = Qn[2] * rho;
             Qn[0] = Qn[1] * rho;
 #pragma unroll
-            for (int n = 0; n < 3; n++) {
-                double inner = fma(Z[n].u[2], Rn[n], Z[n].u[1]);
-                inner = fma(Z[n].u[0], Qn[n], inner);
-                y[n] = inner;
-            }
+            for (int n = 0; n < 3; n++) y[n] = fma(um2[n], Qn[n], fma(up2[n], Rn[n], u0[n]));
             if (K >= 4) {                                      // uniform: k = +2 term, e(k=2)/e(k=1) = R_n * exp(-4/tt)
                 const double H = w[0] * (w[1] * rho * rho);
 #pragma unroll
-                for (int n = 0; n < 3; n++) y[n] = fma(Z[n].u[3], Rn[n] * Rn[n] * H, y[n]);
+                for (int n = 0; n < 3; n++) y[n] = fma(up4[n], Rn[n] * Rn[n] * H, y[n]);
             }
 #pragma unroll
             for (int n = 0; n < 3; n++) y[n] = fma(e0[n], y[n], 0.0);
         } else {
+            const double2 ua = lds2<kNU>(zb), ub = lds2<kNU + 16>(zb);
             double g[2], w[2];
-            g[0] = clamp_neg(fma(m2t, z_first, m2t));
-            g[1] = clamp_neg(fma(-m2t, z_last, m2t));
+            g[0] = clamp_neg(fma(m2t, ua.y, m2t));
+            g[1] = clamp_neg(fma(-m2t, ua.y, m2t));
             expv<2>(g, w, tab);
             const double R = w[0], Q = (K >= 3) ? w[1] : 0.0;
-            double inner = fma(Z[0].u[2], R, Z[0].u[1]);
-            inner = fma(Z[0].u[0], Q, inner);
-            if (K >= 4) inner = fma(Z[0].u[3], R * R * (w[0] * w[1]), inner);
+            double inner = fma(ua.x, Q, fma(ub.x, R, ua.y));
+            if (K >= 4) inner = fma(ub.y, R * R * (w[0] * w[1]), inner);
             y[0] = fma(e0[0], inner, 0.0);
         }
     } else {
         pref = sc.pref_l * rs;
         double a[NZN + 1], w[NZN + 1];
         a[NZN] = -fast::kHalfPiSq * tt;
-#pragma unroll
-        for (int n = 0; n < NZN; n++) a[n] = E[n];
+        a[0] = fma(lds1<kNA>(zb), c, E0);
+        if (NZN == 3) {
+            a[1] = fma(lds1<kNA + kNodeBytes>(zb), c, E0);
+            a[NZN - 1] = fma(lds1<kNA + 2 * kNodeBytes>(zb), c, E0);
+        }
         if (NZN == 3) bad |= (max(max(max(abs_hi(a[0]), abs_hi(a[1])), abs_hi(a[2])), abs_hi(a[3])) >= kExpHiLimit);
         else bad |= (max(abs_hi(a[0]), abs_hi(a[1])) >= kExpHiLimit);
         expv<NZN + 1>(a, w, tab);
         const double q = w[NZN], q2 = q * q, q4 = q2 * q2;
-#pragma unroll
-        for (int n = 0; n < NZN; n++) y[n] = q * Z[n].S[0];
-        if (K >= 2) {
-#pragma unroll
-            for (int n = 0; n < NZN; n++) y[n] = fma(q4, Z[n].S[1], y[n]);
+        {
+            const double2 s0 = lds2<kNS>(zb);                                  // (sin, 2 sin 2) of node 0, 1, 2
+            y[0] = q * s0.x;
+            if (K >= 2) y[0] = fma(q4, s0.y, y[0]);
+            if (NZN == 3) {
+                const double2 s1 = lds2<kNS + kNodeBytes>(zb), s2 = lds2<kNS + 2 * kNodeBytes>(zb);
+                y[1] = q * s1.x;
+                y[NZN - 1] = q * s2.x;
+                if (K >= 2) {
+                    y[1] = fma(q4, s1.y, y[1]);
+                    y[NZN - 1] = fma(q4, s2.y, y[NZN - 1]);
+                }
+            }
         }
         if (K >= 3) {
-            const double q8 = q4 * q4, q9 = q8 * q;
-#pragma unroll
-            for (int n = 0; n < NZN; n++) y[n] = fma(q9, Z[n].S[2], y[n]);
-            if (K >= 4) {
-                const double q16 = q8 * q8;
-#pragma unroll
-                for (int n = 0; n < NZN; n++) y[n] = fma(q16, Z[n].S[3], y[n]);
+            const double q8 = q4 * q4, q9 = q8 * q, q16 = (K >= 4) ? q8 * q8 : 0.0;
+            const double2 s0 = lds2<kNS + 16>(zb);                             // (3 sin 3, 4 sin 4)
+            y[0] = fma(q16, s0.y, fma(q9, s0.x, y[0]));
+            if (NZN == 3) {
+                const double2 s1 = lds2<kNS + 16 + kNodeBytes>(zb), s2 = lds2<kNS + 16 + 2 * kNodeBytes>(zb);
+                y[1] = fma(q16, s1.y, fma(q9, s1.x, y[1]));
+                y[NZN - 1] = fma(q16, s2.y, fma(q9, s2.x, y[NZN - 1]));
             }
         }
 #pragma unroll
@@ -248,7 +288,7 @@ __device__ __forceinline__ double tnode_value(int d, double xp, double tt, const
         y[n] *= pref;                       // pref > 0: the sign is the series sum's
         neg |= __double2hiint(y[n]);
     }
-    if (NZN == 3) return (fma(4.0, y[1], y[0]) + y[2]) * T.cz[sign];   // integrate.pxi:30-45 with n_sz = 2
+    if (NZN == 3) return (fma(4.0, y[1], y[0]) + y[NZN - 1]) * lds1<kOffCz>(tb + 8 * sign);   // integrate.pxi:30-45 with n_sz = 2
     return y[0];
 }
 
@@ -266,15 +306,15 @@ __device__ __forceinline__ int lookup_lane(const Tables& T, double tt, int* piec
 // Density of the warp's 32 trials (one per lane; `live` lanes only) on the staged fixed grid.
 template <int NZN, bool SV>
 __device__ __forceinline__ double warp_density(double ax, int sign, bool live, const Tables& T, Shared& S, int nt,
-                                               int& neg, int& bad)
+                                               unsigned tb, int& neg, int& bad)
 {
     const SetConst& sc = S.sc;
     const int w = threadIdx.x >> 5;
-    const NodeTab* Z = T.z[sign];
+    const unsigned zb = tb + kOffZ + sign * kSignBytes;
     double acc = 0.0;
 #pragma unroll 1
     for (int i = 0; i <= nt; i++) {
-        const double xp = ax - T.tn[i];
+        const double xp = ax - lds1<kOffTn>(tb + 8 * i);
         const bool alive = live && (xp > 0);
         // tt = x'/a^2, correctly rounded from the reciprocal (quotient + one residual correction): K is decided on it
         const double q0 = xp * sc.inv_a2;
@@ -286,7 +326,7 @@ __device__ __forceinline__ double warp_density(double ax, int sign, bool live, c
         if (am == 0) continue;                                  // nobody has this node (x' <= 0 everywhere): contributes 0
         if (__all_sync(kFull, !alive || (th > pc.lo_hi && th < pc.hi_hi))) {
             int ng = 0, bd = 0;
-            val = tnode_value<NZN, SV>(pc.desc, xp, tt, Z, T, sc, sign, ng, bd);
+            val = tnode_value<NZN, SV>(pc.desc, xp, tt, tb, zb, sc, sign, ng, bd);
             if (alive) { neg |= ng; bad |= bd; }                // lanes without the node computed along on garbage
         } else {
             // a piece boundary runs through the warp (or the warp has moved on): look up per lane, evaluate once per
@@ -300,7 +340,7 @@ __device__ __forceinline__ double warp_density(double ax, int sign, bool live, c
                 const int d = __shfl_sync(kFull, mine, src);
                 const bool match = (mine == d);
                 int ng = 0, bd = 0;
-                const double v = tnode_value<NZN, SV>(d, xp, tt, Z, T, sc, sign, ng, bd);
+                const double v = tnode_value<NZN, SV>(d, xp, tt, tb, zb, sc, sign, ng, bd);
                 if (match) { val = v; neg_l = ng; bad_l = bd; }
                 todo &= ~__ballot_sync(kFull, match);
             }
@@ -322,7 +362,7 @@ __device__ __forceinline__ double warp_density(double ax, int sign, bool live, c
             }
         }
         if (!alive) val = 0.0;
-        acc = fma(T.wts_t[i], val, acc);
+        acc = fma(lds1<kOffWt>(tb + 8 * i), val, acc);
     }
     return acc * sc.ct;
 }
@@ -333,11 +373,10 @@ __device__ __forceinline__ bool lean_set_ok(int mode, int kind)
 }
 
 // General evaluator for the handful of trials the loop defers, and for the whole slice when the list overflows.
-static __device__ __noinline__ double general_density(double x, const Tables* Tp, int kind, int nz, int nt, int kl_max, int mode,
-                                                       double tlo)
+static __device__ __noinline__ double general_density(double x, int kind, int nz, int nt, int kl_max, int mode, double tlo)
 {
     fast::Set s;
-    fast::rebuild_set(s, Tp, kind, kl_max);
+    fast::rebuild_set(s, &fast::tables(), kind, kl_max);
     s.mode = mode;
     s.nz = nz;
     s.nt = nt;
@@ -346,7 +385,7 @@ static __device__ __noinline__ double general_density(double x, const Tables* Tp
     return fast::density<false>(x, s, &defer);
 }
 
-__global__ void __launch_bounds__(kBlock, 6) like_lean_kernel(const double* __restrict__ x, int64_t n,
+__global__ void __launch_bounds__(kBlock, 5) like_lean_kernel(const double* __restrict__ x, int64_t n,
                                                              const double* __restrict__ params, int64_t P, Opts o,
                                                              double w_outlier, int slices, int64_t chunk,
                                                              double* __restrict__ out_sum, int* __restrict__ out_zero,
@@ -406,6 +445,7 @@ __global__ void __launch_bounds__(kBlock, 6) like_lean_kernel(const double* __re
     const double2* x2 = reinterpret_cast<const double2*>(x + b);
     const int rounds = (npair + kBlock - 1) / kBlock + 1;   // + 1: the head / tail elements
 
+    const unsigned tb = (unsigned)__cvta_generic_to_shared(&fast::tables());
     LogProd lp;
     const bool usable = lean_set_ok(mode, kind);
     const bool zero_set = (mode == fast::kModeZero);
@@ -438,10 +478,10 @@ __global__ void __launch_bounds__(kBlock, 6) like_lean_kernel(const double* __re
                 if (__any_sync(kFull, live)) {
                     const int sign = xv > 0;
                     int neg = 0, bad = 0;
-                    if (z3) dens = sv ? warp_density<3, true>(ax, sign, live, T, S, nt, neg, bad)
-                                      : warp_density<3, false>(ax, sign, live, T, S, nt, neg, bad);
-                    else dens = sv ? warp_density<1, true>(ax, sign, live, T, S, nt, neg, bad)
-                                   : warp_density<1, false>(ax, sign, live, T, S, nt, neg, bad);
+                    if (z3) dens = sv ? warp_density<3, true>(ax, sign, live, T, S, nt, tb, neg, bad)
+                                      : warp_density<3, false>(ax, sign, live, T, S, nt, tb, neg, bad);
+                    else dens = sv ? warp_density<1, true>(ax, sign, live, T, S, nt, tb, neg, bad)
+                                   : warp_density<1, false>(ax, sign, live, T, S, nt, tb, neg, bad);
                     // a negative truncated series anywhere makes pdf_sv's log(p) NaN (pdf.pxi:102); pdf (sv == 0) lets it through
                     if (sv && neg < 0) dens = CUDART_NAN;
                     if (!live) dens = 0.0;
@@ -463,11 +503,11 @@ __global__ void __launch_bounds__(kBlock, 6) like_lean_kernel(const double* __re
         lp = LogProd();
 #pragma unroll 1
         for (int64_t i = beg + threadIdx.x; i < end; i += kBlock)
-            lp.add_slow(mix_outlier(general_density(x[i], &T, kind, nz, nt, kl_max, mode, S.sc.tlo), S.sc.omp, S.sc.wp));
+            lp.add_slow(mix_outlier(general_density(x[i], kind, nz, nt, kl_max, mode, S.sc.tlo), S.sc.omp, S.sc.wp));
     } else {
 #pragma unroll 1
         for (int q = threadIdx.x; q < nd; q += kBlock)
-            lp.add_slow(mix_outlier(general_density(S.defer[q], &T, kind, nz, nt, kl_max, mode, S.sc.tlo), S.sc.omp, S.sc.wp));
+            lp.add_slow(mix_outlier(general_density(S.defer[q], kind, nz, nt, kl_max, mode, S.sc.tlo), S.sc.omp, S.sc.wp));
     }
     const double acc = lp.value();
     int any_zero;
