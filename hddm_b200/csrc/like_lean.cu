@@ -21,6 +21,9 @@
 //
 // Reference: /root/reference/src/pdf.pxi:28-146 (ftt_01w, pdf_sv, full_pdf), /root/reference/src/integrate.pxi:12-68
 // (simpson_1D / simpson_2D), /root/reference/src/wfpt.pyx:54-76 (wiener_like).
+#include <cmath>
+#include <mutex>
+
 #include "like_kernels.cuh"
 #include "wfpt_fast.cuh"
 
@@ -33,6 +36,7 @@ using fast::Tables;
 constexpr int kWarps = kBlock / 32;
 constexpr int kDeferCap = 256;          // trials per CTA the post-loop general evaluator takes before the CTA starts over
 constexpr unsigned kFull = 0xffffffffu;
+constexpr int kExpBits = 11, kExpN = 1 << kExpBits;   // entries of the exp kernel's 2^(j/N) table
 
 // Set constants the loop reads from shared memory (one 16-byte load brings two).
 struct alignas(16) SetConst {
@@ -46,6 +50,7 @@ struct alignas(16) SetConst {
 struct alignas(16) PieceCache { int lo_hi, hi_hi, desc, pad; };   // high words of tt strictly inside (lo_hi, hi_hi) -> desc
 
 struct Shared {
+    double exptab[kExpN];
     SetConst sc;
     PieceCache piece[kWarps][fast::kMaxNodes];
     double defer[kDeferCap];
@@ -110,9 +115,12 @@ constexpr int kNA = (int)offsetof(NodeTab, A), kNU = (int)offsetof(NodeTab, u), 
 static_assert(kNA % 16 == 0 && kNU % 16 == 0 && kNS % 16 == 0 && kNodeBytes % 16 == 0, "NodeTab pairs must be 16-byte aligned");
 
 // ---- exp, three or four independent chains side by side -------------------------------------------------------------------
-// exp(x) = 2^e * 2^(j/64) * exp(r) as in fast::exp_core; Horner form (one constant operand per step).  |x| < 708.
-__constant__ double kE[8] = {92.33248261689366, 6755399441055744.0, -0.01083042469326756, -2.9815858269852933e-12,
-                             1.0 / 120.0, 1.0 / 24.0, 1.0 / 6.0, 0.5};
+// exp(x) = 2^e * 2^(j/2048) * exp(r),  k = rint(2048 x / ln 2) = 2048 e + j,  r = x - k ln2/2048, |r| <= 1.7e-4, so that
+// exp(r) - 1 = r + r^2 (1/2 + r/6) to 3.4e-17: eight FP64 instructions per exp (the 64-entry form of wfpt_fast.cuh needs
+// ten).  The table (16 KB per CTA, correctly rounded entries computed once on the host) is the price.  |x| < 708.
+__constant__ double kE[6] = {2954.639443740597, 6755399441055744.0, -0.0003384507713235507, -4.3423507025813853e-13,
+                             1.0 / 6.0, 0.5};
+__device__ double g_exp_table[kExpN];   // 2^(j/2048); filled by ensure_exp_table()
 
 template <int M>
 __device__ __forceinline__ void expv(const double (&x)[M], double (&out)[M], unsigned tab)
@@ -133,17 +141,14 @@ __device__ __forceinline__ void expv(const double (&x)[M], double (&out)[M], uns
 #pragma unroll
     for (int i = 0; i < M; i++) t[i] = fma(r[i], kE[4], kE[5]);
 #pragma unroll
-    for (int i = 0; i < M; i++) t[i] = fma(t[i], r[i], kE[6]);
-#pragma unroll
-    for (int i = 0; i < M; i++) t[i] = fma(t[i], r[i], kE[7]);
-#pragma unroll
     for (int i = 0; i < M; i++) t[i] = fma(t[i], r[i] * r[i], r[i]);
 #pragma unroll
     for (int i = 0; i < M; i++) {
-        const double T = lds1<0>(tab + ((ki[i] & 63) << 3));
+        const double T = lds1<0>(tab + ((ki[i] & (kExpN - 1)) << 3));
         const double res = fma(T, t[i], T);
         int hi;
-        asm("mad.lo.s32 %0, %1, 16384, %2;" : "=r"(hi) : "r"(ki[i] & ~63), "r"(__double2hiint(res)));
+        // add e = k >> 11 to the exponent field: (k - j) * 2^9 = e << 20
+        asm("mad.lo.s32 %0, %1, 512, %2;" : "=r"(hi) : "r"(ki[i] & ~(kExpN - 1)), "r"(__double2hiint(res)));
         out[i] = __hiloint2double(hi, __double2loint(res));
     }
 }
@@ -158,16 +163,14 @@ __device__ __forceinline__ double clamp_neg(double x)
 __device__ __forceinline__ int abs_hi(double x) { return __double2hiint(x) & 0x7fffffff; }
 constexpr int kExpHiLimit = 0x40862000;   // |x| < 708 <=> abs_hi(x) < this (NaN and inf fail too)
 
-// 1/sqrt(x), normal positive x: hardware seed, then one third-order step and one Newton step
+// 1/sqrt(x), normal positive x: hardware seed (about 2^-23 accurate), one third-order step (-> 2^-66), five FP64 instructions
 __device__ __forceinline__ double rsqrt_d(double x)
 {
     double y;
     asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
-    const double hx = 0.5 * x;
-    double e = fma(-hx * y, y, 0.5);
-    y = fma(y, e, y);
-    e = fma(-hx * y, y, 0.5);
-    return fma(y, e, y);
+    const double e = fma(-x * y, y, 1.0);                 // 1 - x y^2
+    const double p = fma(e, 0.375, 0.5) * e;              // e/2 + 3 e^2/8
+    return fma(y, p, y);
 }
 
 // ---- one t-node: inner z-integral (or the single node) for a warp-uniform descriptor ---------------------------------------
@@ -175,10 +178,9 @@ __device__ __forceinline__ double rsqrt_d(double x)
 // compute along and are ignored by the caller.  Returns the Simpson sum over z times cz (NZN == 3) or the node (NZN == 1);
 // ored into `neg`: sign bits of the series sums; `bad` |= an exp argument outside the fast kernel's range.
 template <int NZN, bool SV>
-__device__ __forceinline__ double tnode_value(int d, double xp, double tt, unsigned tb, unsigned zb, const SetConst& sc,
+__device__ __forceinline__ double tnode_value(int d, double xp, double tt, unsigned tb, unsigned zb, unsigned tab, const SetConst& sc,
                                               int sign, int& neg, int& bad)
 {
-    const unsigned tab = tb + kOffExp;
     double rs = 1.0, c = 0.5;
     if (SV) {
         rs = rsqrt_d(fma(sc.sv2, xp, 1.0));
@@ -306,7 +308,7 @@ __device__ __forceinline__ int lookup_lane(const Tables& T, double tt, int* piec
 // Density of the warp's 32 trials (one per lane; `live` lanes only) on the staged fixed grid.
 template <int NZN, bool SV>
 __device__ __forceinline__ double warp_density(double ax, int sign, bool live, const Tables& T, Shared& S, int nt,
-                                               unsigned tb, int& neg, int& bad)
+                                               unsigned tb, unsigned etab, int& neg, int& bad)
 {
     const SetConst& sc = S.sc;
     const int w = threadIdx.x >> 5;
@@ -326,7 +328,7 @@ __device__ __forceinline__ double warp_density(double ax, int sign, bool live, c
         if (am == 0) continue;                                  // nobody has this node (x' <= 0 everywhere): contributes 0
         if (__all_sync(kFull, !alive || (th > pc.lo_hi && th < pc.hi_hi))) {
             int ng = 0, bd = 0;
-            val = tnode_value<NZN, SV>(pc.desc, xp, tt, tb, zb, sc, sign, ng, bd);
+            val = tnode_value<NZN, SV>(pc.desc, xp, tt, tb, zb, etab, sc, sign, ng, bd);
             if (alive) { neg |= ng; bad |= bd; }                // lanes without the node computed along on garbage
         } else {
             // a piece boundary runs through the warp (or the warp has moved on): look up per lane, evaluate once per
@@ -340,7 +342,7 @@ __device__ __forceinline__ double warp_density(double ax, int sign, bool live, c
                 const int d = __shfl_sync(kFull, mine, src);
                 const bool match = (mine == d);
                 int ng = 0, bd = 0;
-                const double v = tnode_value<NZN, SV>(d, xp, tt, tb, zb, sc, sign, ng, bd);
+                const double v = tnode_value<NZN, SV>(d, xp, tt, tb, zb, etab, sc, sign, ng, bd);
                 if (match) { val = v; neg_l = ng; bad_l = bd; }
                 todo &= ~__ballot_sync(kFull, match);
             }
@@ -425,6 +427,7 @@ __global__ void __launch_bounds__(kBlock, 5) like_lean_kernel(const double* __re
             S.ndefer = 0;
             S.nt = nt; S.sv_nonzero = set.sv_nonzero; S.nzn = nz + 1;
         }
+        for (int i = threadIdx.x; i < kExpN; i += kBlock) S.exptab[i] = g_exp_table[i];
         for (int i = threadIdx.x; i < kWarps * fast::kMaxNodes; i += kBlock) {
             PieceCache e{0, 0, 0, 0};       // empty interval: the first round looks its pieces up
             (&S.piece[0][0])[i] = e;
@@ -446,6 +449,7 @@ __global__ void __launch_bounds__(kBlock, 5) like_lean_kernel(const double* __re
     const int rounds = (npair + kBlock - 1) / kBlock + 1;   // + 1: the head / tail elements
 
     const unsigned tb = (unsigned)__cvta_generic_to_shared(&fast::tables());
+    const unsigned etab = (unsigned)__cvta_generic_to_shared(S.exptab);
     LogProd lp;
     const bool usable = lean_set_ok(mode, kind);
     const bool zero_set = (mode == fast::kModeZero);
@@ -478,10 +482,10 @@ __global__ void __launch_bounds__(kBlock, 5) like_lean_kernel(const double* __re
                 if (__any_sync(kFull, live)) {
                     const int sign = xv > 0;
                     int neg = 0, bad = 0;
-                    if (z3) dens = sv ? warp_density<3, true>(ax, sign, live, T, S, nt, tb, neg, bad)
-                                      : warp_density<3, false>(ax, sign, live, T, S, nt, tb, neg, bad);
-                    else dens = sv ? warp_density<1, true>(ax, sign, live, T, S, nt, tb, neg, bad)
-                                   : warp_density<1, false>(ax, sign, live, T, S, nt, tb, neg, bad);
+                    if (z3) dens = sv ? warp_density<3, true>(ax, sign, live, T, S, nt, tb, etab, neg, bad)
+                                      : warp_density<3, false>(ax, sign, live, T, S, nt, tb, etab, neg, bad);
+                    else dens = sv ? warp_density<1, true>(ax, sign, live, T, S, nt, tb, etab, neg, bad)
+                                   : warp_density<1, false>(ax, sign, live, T, S, nt, tb, etab, neg, bad);
                     // a negative truncated series anywhere makes pdf_sv's log(p) NaN (pdf.pxi:102); pdf (sv == 0) lets it through
                     if (sv && neg < 0) dens = CUDART_NAN;
                     if (!live) dens = 0.0;
@@ -546,8 +550,30 @@ bool lean_applies(const BatchArgs& a, const KTable& kt)
            a.o.n_st >= 1 && a.o.n_st < fast::kMaxNodes;
 }
 
+// 2^(j/2048) rounded correctly (long double exp2l), uploaded once per device.
+static cudaError_t ensure_exp_table()
+{
+    static std::mutex mu;
+    static bool ready[64] = {false};
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (dev < 0 || dev >= 64) return cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> lk(mu);
+    if (ready[dev]) return cudaSuccess;
+    static double host[lean::kExpN];
+    for (int j = 0; j < lean::kExpN; j++) host[j] = (double)exp2l((long double)j / (long double)lean::kExpN);
+    e = cudaMemcpyToSymbol(lean::g_exp_table, host, sizeof(host));
+    if (e == cudaSuccess) ready[dev] = true;
+    return e;
+}
+
 cudaError_t launch_like_lean(const BatchArgs& a, const KTable& kt)
 {
+    {
+        const cudaError_t e = ensure_exp_table();
+        if (e != cudaSuccess) return e;
+    }
     const int64_t nblk = a.P * (int64_t)a.slices;
     if (nblk == 0) return cudaSuccess;
     lean::like_lean_kernel<<<(unsigned)nblk, kBlock, 0, a.stream>>>(
