@@ -47,13 +47,19 @@ struct alignas(16) SetConst {
     double tlo, ct;           // t - st/2 (validity bound on |x|), Simpson scale along t
 };
 
-struct alignas(16) PieceCache { int lo_hi, hi_hi, desc, pad; };   // high words of tt strictly inside (lo_hi, hi_hi) -> desc
+// Cached piece of the series-term table, on the x' axis: a lane whose x' has its high word strictly inside (lo_hi, hi_hi) has
+// tt = x'/a^2 (as the reference rounds it) inside the piece -- the bounds are the high words of thr * a^2 moved inwards by
+// one unit (2^-20 relative), far more than the rounding of that product and of the quotient can shift anything.
+struct alignas(16) PieceCache { int lo_hi, hi_hi, desc, pad; };
+
+struct alignas(16) TRec { double tn, wt; };   // t-node position, and its Simpson weight times the t-axis scale
 
 struct Shared {
     double exptab[kExpN];
-    SetConst sc;
-    PieceCache piece[kWarps][fast::kMaxNodes];
+    TRec trec[fast::kMaxNodes + 1];
+    PieceCache piece[kWarps][fast::kMaxNodes + 1];
     double defer[kDeferCap];
+    int xthr_hi[kMaxPieces + 1];   // high words of thr[p] * a^2: the series-term table's thresholds on the x' axis
     int ndefer;
     int nt, sv_nonzero, nzn;
 };
@@ -178,14 +184,11 @@ __device__ __forceinline__ double rsqrt_d(double x)
 // compute along and are ignored by the caller.  Returns the Simpson sum over z times cz (NZN == 3) or the node (NZN == 1);
 // ored into `neg`: sign bits of the series sums; `bad` |= an exp argument outside the fast kernel's range.
 template <int NZN, bool SV>
-__device__ __forceinline__ double tnode_value(int d, double xp, double tt, unsigned tb, unsigned zb, unsigned tab, const SetConst& sc,
-                                              int sign, int& neg, int& bad)
+__device__ __forceinline__ double tnode_value(int d, double xp, double tt, double rs, double c, unsigned tb, unsigned zb,
+                                              unsigned tab, const SetConst& sc, int sign, int& neg, int& bad)
 {
-    double rs = 1.0, c = 0.5;
-    if (SV) {
-        rs = rsqrt_d(fma(sc.sv2, xp, 1.0));
-        c = 0.5 * rs * rs;
-    }
+    // rs = 1/sqrt(sv^2 x' + 1), c = rs^2 / 2 (1 and 1/2 without drift variability); tt = x'/a^2 to the last bit or so (the
+    // series-term decision was taken by the caller on exact grounds)
     const double E0 = sc.nv2 * xp * c;
     double y[NZN];
     const int K = d & 0xff;
@@ -307,34 +310,44 @@ __device__ __forceinline__ int lookup_lane(const Tables& T, double tt, int* piec
 
 // Density of the warp's 32 trials (one per lane; `live` lanes only) on the staged fixed grid.
 template <int NZN, bool SV>
-__device__ __forceinline__ double warp_density(double ax, int sign, bool live, const Tables& T, Shared& S, int nt,
-                                               unsigned tb, unsigned etab, int& neg, int& bad)
+__device__ __forceinline__ double warp_density(double ax, int sign, bool live, const Tables& T, Shared& S, const SetConst& sc,
+                                               int nt, unsigned tb, unsigned etab, int& neg, int& bad)
 {
-    const SetConst& sc = S.sc;
     const int w = threadIdx.x >> 5;
     const unsigned zb = tb + kOffZ + sign * kSignBytes;
     double acc = 0.0;
+    // the record of the next t-node (position, weight, cached table piece) is fetched one node ahead: shared-memory latency
+    // stays off the dependent chain
+    TRec rec_n = S.trec[0];
+    PieceCache pc_n = S.piece[w][0];
 #pragma unroll 1
     for (int i = 0; i <= nt; i++) {
-        const double xp = ax - lds1<kOffTn>(tb + 8 * i);
+        const TRec rec = rec_n;
+        const PieceCache pc = pc_n;
+        rec_n = S.trec[i + 1];
+        pc_n = S.piece[w][i + 1];
+        const double xp = ax - rec.tn;
         const bool alive = live && (xp > 0);
-        // tt = x'/a^2, correctly rounded from the reciprocal (quotient + one residual correction): K is decided on it
-        const double q0 = xp * sc.inv_a2;
-        const double tt = fma(fma(-q0, sc.a2, xp), sc.inv_a2, q0);
-        const int th = __double2hiint(tt);
-        const PieceCache pc = S.piece[w][i];
+        const int th = __double2hiint(xp);
         double val = 0.0;
         const unsigned am = __ballot_sync(kFull, alive);
         if (am == 0) continue;                                  // nobody has this node (x' <= 0 everywhere): contributes 0
+        const double tt = xp * sc.inv_a2;
+        double rs = 1.0, c = 0.5;
+        if (SV) {
+            rs = rsqrt_d(fma(sc.sv2, xp, 1.0));
+            c = 0.5 * rs * rs;
+        }
         if (__all_sync(kFull, !alive || (th > pc.lo_hi && th < pc.hi_hi))) {
             int ng = 0, bd = 0;
-            val = tnode_value<NZN, SV>(pc.desc, xp, tt, tb, zb, etab, sc, sign, ng, bd);
+            val = tnode_value<NZN, SV>(pc.desc, xp, tt, rs, c, tb, zb, etab, sc, sign, ng, bd);
             if (alive) { neg |= ng; bad |= bd; }                // lanes without the node computed along on garbage
         } else {
-            // a piece boundary runs through the warp (or the warp has moved on): look up per lane, evaluate once per
-            // distinct descriptor present, and remember the piece of the last live lane for the next round
+            // a piece boundary runs through the warp (or the warp has moved on): look up per lane on the reference's own
+            // tt = x'/pow(a, 2) (pdf.pxi:81,98), evaluate once per distinct descriptor present, and remember the piece of the
+            // last live lane for the next round
             int piece = 0;
-            const int mine = alive ? lookup_lane(T, tt, &piece) : -1;
+            const int mine = alive ? lookup_lane(T, __ddiv_rn(xp, sc.a2), &piece) : -1;
             unsigned todo = am;
             int neg_l = 0, bad_l = 0;
             while (todo) {
@@ -342,7 +355,7 @@ __device__ __forceinline__ double warp_density(double ax, int sign, bool live, c
                 const int d = __shfl_sync(kFull, mine, src);
                 const bool match = (mine == d);
                 int ng = 0, bd = 0;
-                const double v = tnode_value<NZN, SV>(d, xp, tt, tb, zb, etab, sc, sign, ng, bd);
+                const double v = tnode_value<NZN, SV>(d, xp, tt, rs, c, tb, zb, etab, sc, sign, ng, bd);
                 if (match) { val = v; neg_l = ng; bad_l = bd; }
                 todo &= ~__ballot_sync(kFull, match);
             }
@@ -353,9 +366,8 @@ __device__ __forceinline__ double warp_density(double ax, int sign, bool live, c
                 const int p = __shfl_sync(kFull, piece, last);
                 if ((threadIdx.x & 31) == 0) {
                     PieceCache nc;
-                    // strict high-word bounds: inside means lo_b <= bits(tt) < hi_b whatever the low words are
-                    nc.lo_hi = (p > 0) ? (int)(T.thr[p - 1] >> 32) : (int)0x80000000;
-                    nc.hi_hi = (p < T.npieces) ? (int)(T.thr[p] >> 32) : 0x7fffffff;
+                    nc.lo_hi = (p > 0) ? S.xthr_hi[p - 1] + 1 : (int)0x80000000;
+                    nc.hi_hi = (p < T.npieces) ? S.xthr_hi[p] - 1 : 0x7fffffff;
                     nc.desc = T.desc[p];
                     nc.pad = 0;
                     S.piece[w][i] = nc;
@@ -364,9 +376,72 @@ __device__ __forceinline__ double warp_density(double ax, int sign, bool live, c
             }
         }
         if (!alive) val = 0.0;
-        acc = fma(lds1<kOffWt>(tb + 8 * i), val, acc);
+        acc = fma(rec.wt, val, acc);
     }
-    return acc * sc.ct;
+    return acc;
+}
+
+// The common grid, n_st = 2: three t-nodes.  Everything the three nodes need before their series -- x', the votes on
+// the cached table pieces, tt, 1/sqrt(sv^2 x' + 1) -- is formed for all three side by side (three independent chains instead
+// of one after the other), then the three node sets run back to back.  Returns false (nothing computed) when some node's
+// lanes are not all inside its cached piece; the caller then takes the node-by-node routine above, which looks pieces up.
+template <int NZN, bool SV>
+__device__ __forceinline__ bool warp_density3(double ax, int sign, bool live, Shared& S, const SetConst& sc, unsigned tb,
+                                              unsigned etab, double* out, int& neg, int& bad)
+{
+    const int w = threadIdx.x >> 5;
+    const unsigned zb = tb + kOffZ + sign * kSignBytes;
+    TRec rec[3];
+    PieceCache pc[3];
+#pragma unroll
+    for (int i = 0; i < 3; i++) {
+        rec[i] = S.trec[i];
+        pc[i] = S.piece[w][i];
+    }
+    double xp[3];
+    bool alive[3];
+    bool inside = true;
+#pragma unroll
+    for (int i = 0; i < 3; i++) {
+        xp[i] = ax - rec[i].tn;
+        alive[i] = live && (xp[i] > 0);
+        const int th = __double2hiint(xp[i]);
+        inside &= !alive[i] || (th > pc[i].lo_hi && th < pc[i].hi_hi);
+    }
+    if (!__all_sync(kFull, inside)) return false;
+    double tt[3], rs[3], c[3];
+#pragma unroll
+    for (int i = 0; i < 3; i++) {
+        tt[i] = xp[i] * sc.inv_a2;
+        rs[i] = 1.0;
+        c[i] = 0.5;
+    }
+    if (SV) {
+        double u[3], y[3];
+#pragma unroll
+        for (int i = 0; i < 3; i++) u[i] = fma(sc.sv2, xp[i], 1.0);
+#pragma unroll
+        for (int i = 0; i < 3; i++) asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y[i]) : "d"(u[i]));
+#pragma unroll
+        for (int i = 0; i < 3; i++) u[i] = fma(-u[i] * y[i], y[i], 1.0);
+#pragma unroll
+        for (int i = 0; i < 3; i++) rs[i] = fma(y[i], fma(u[i], 0.375, 0.5) * u[i], y[i]);
+#pragma unroll
+        for (int i = 0; i < 3; i++) c[i] = 0.5 * rs[i] * rs[i];
+    }
+    double acc = 0.0;
+#pragma unroll
+    for (int i = 0; i < 3; i++) {
+        if (__any_sync(kFull, alive[i])) {                      // (x' <= 0 on every lane: the node contributes 0)
+            int ng = 0, bd = 0;
+            double val = tnode_value<NZN, SV>(pc[i].desc, xp[i], tt[i], rs[i], c[i], tb, zb, etab, sc, sign, ng, bd);
+            if (alive[i]) { neg |= ng; bad |= bd; }             // lanes without the node computed along on garbage
+            else val = 0.0;
+            acc = fma(rec[i].wt, val, acc);
+        }
+    }
+    *out = acc;
+    return true;
 }
 
 __device__ __forceinline__ bool lean_set_ok(int mode, int kind)
@@ -411,32 +486,36 @@ __global__ void __launch_bounds__(kBlock, 5) like_lean_kernel(const double* __re
         return;
     }
     Shared& S = shared();
-    int mode, kind, nz, nt, kl_max;
+    int mode, kind, nz, nt, kl_max, sv_nonzero;
+    SetConst sc;                            // per-thread copy: the loop reads these from registers
     {
         fast::Set set;
-        fast::prepare(set, prm, o, kt);     // CTA-collective: fills fast::Tables
-        mode = set.mode; kind = set.kind; nz = set.nz; nt = set.nt; kl_max = set.kl_max;
-        if (threadIdx.x == 0) {
-            SetConst c;
-            c.a2 = set.a2; c.inv_a2 = set.inv_a2; c.sv2 = set.sv2; c.nv2 = -set.v2;
-            c.pref_s = fast::kInvSqrt2Pi * set.inv_a2; c.pref_l = kPi * set.inv_a2;
-            c.omp = __dsub_rn(1.0, po); c.wp = __dmul_rn(w_outlier, po);
-            c.tlo = set.tlo;
-            c.ct = 1.0;
-            S.sc = c;
-            S.ndefer = 0;
-            S.nt = nt; S.sv_nonzero = set.sv_nonzero; S.nzn = nz + 1;
-        }
+        fast::prepare(set, prm, o, kt);     // CTA-collective: fills fast::Tables (barrier inside)
+        mode = set.mode; kind = set.kind; nz = set.nz; nt = set.nt; kl_max = set.kl_max; sv_nonzero = set.sv_nonzero;
+        sc.a2 = set.a2; sc.inv_a2 = set.inv_a2; sc.sv2 = set.sv2; sc.nv2 = -set.v2;
+        sc.pref_s = fast::kInvSqrt2Pi * set.inv_a2; sc.pref_l = kPi * set.inv_a2;
+        sc.omp = __dsub_rn(1.0, po); sc.wp = __dmul_rn(w_outlier, po);
+        sc.tlo = set.tlo;
+        sc.ct = 1.0;
+        if (threadIdx.x == 0) S.ndefer = 0;
         for (int i = threadIdx.x; i < kExpN; i += kBlock) S.exptab[i] = g_exp_table[i];
-        for (int i = threadIdx.x; i < kWarps * fast::kMaxNodes; i += kBlock) {
+        for (int i = threadIdx.x; i < kWarps * (fast::kMaxNodes + 1); i += kBlock) {
             PieceCache e{0, 0, 0, 0};       // empty interval: the first round looks its pieces up
             (&S.piece[0][0])[i] = e;
+        }
+        if (mode != fast::kModeZero && mode != fast::kModeGeneric) {
+            const Tables& T0 = fast::tables();
+            for (int i = threadIdx.x; i < kt.n; i += kBlock)
+                S.xthr_hi[i] = __double2hiint(__longlong_as_double(kt.thr[i]) * sc.a2);
+            for (int i = threadIdx.x; i <= fast::kMaxNodes; i += kBlock) {
+                TRec t{0.0, 0.0};
+                if (i <= nt) { t.tn = T0.tn[i]; t.wt = T0.wts_t[i] * T0.ct; }   // ct == 1 when the t axis is not integrated
+                S.trec[i] = t;
+            }
         }
     }
     __syncthreads();
     const Tables& T = fast::tables();
-    if (threadIdx.x == 0) S.sc.ct = T.ct;
-    __syncthreads();
 
     const int64_t beg = (int64_t)s * chunk;
     const int64_t end = (beg + chunk < n) ? beg + chunk : n;
@@ -453,17 +532,20 @@ __global__ void __launch_bounds__(kBlock, 5) like_lean_kernel(const double* __re
     LogProd lp;
     const bool usable = lean_set_ok(mode, kind);
     const bool zero_set = (mode == fast::kModeZero);
-    const bool sv = S.sv_nonzero != 0;
+    const bool sv = sv_nonzero != 0;
     const bool z3 = (kind == 1);
 
     if (usable) {
 #pragma unroll 1
+        double2 nxt = make_double2(0.0, 0.0);          // the pair of the NEXT round is loaded a round ahead
+        if ((int)threadIdx.x < npair) nxt = __ldg(x2 + threadIdx.x);
         for (int r = 0; r < rounds; r++) {
             double v0 = 0.0, v1 = 0.0;
             int cnt = 0;
             const int i = r * kBlock + threadIdx.x;
+            const double2 xx = nxt;
+            if (i + kBlock < npair) nxt = __ldg(x2 + i + kBlock);
             if (i < npair) {
-                const double2 xx = __ldg(x2 + i);
                 v0 = xx.x;
                 v1 = xx.y;
                 cnt = 2;
@@ -477,15 +559,17 @@ __global__ void __launch_bounds__(kBlock, 5) like_lean_kernel(const double* __re
                 const double xv = h ? v1 : v0;
                 const double ax = fabs(xv);
                 const bool have = h < cnt;
-                const bool live = have && !zero_set && !((ax - S.sc.tlo) < 0);   // pdf.pxi:112, the trial-dependent part
+                const bool live = have && !zero_set && !((ax - sc.tlo) < 0);   // pdf.pxi:112, the trial-dependent part
                 double dens = 0.0;
                 if (__any_sync(kFull, live)) {
                     const int sign = xv > 0;
                     int neg = 0, bad = 0;
-                    if (z3) dens = sv ? warp_density<3, true>(ax, sign, live, T, S, nt, tb, etab, neg, bad)
-                                      : warp_density<3, false>(ax, sign, live, T, S, nt, tb, etab, neg, bad);
-                    else dens = sv ? warp_density<1, true>(ax, sign, live, T, S, nt, tb, etab, neg, bad)
-                                   : warp_density<1, false>(ax, sign, live, T, S, nt, tb, etab, neg, bad);
+                    if (z3 && sv) {
+                        if (!(nt == 2 && warp_density3<3, true>(ax, sign, live, S, sc, tb, etab, &dens, neg, bad)))
+                            dens = warp_density<3, true>(ax, sign, live, T, S, sc, nt, tb, etab, neg, bad);
+                    } else if (z3) dens = warp_density<3, false>(ax, sign, live, T, S, sc, nt, tb, etab, neg, bad);
+                    else dens = sv ? warp_density<1, true>(ax, sign, live, T, S, sc, nt, tb, etab, neg, bad)
+                                   : warp_density<1, false>(ax, sign, live, T, S, sc, nt, tb, etab, neg, bad);
                     // a negative truncated series anywhere makes pdf_sv's log(p) NaN (pdf.pxi:102); pdf (sv == 0) lets it through
                     if (sv && neg < 0) dens = CUDART_NAN;
                     if (!live) dens = 0.0;
@@ -496,7 +580,7 @@ __global__ void __launch_bounds__(kBlock, 5) like_lean_kernel(const double* __re
                         continue;
                     }
                 }
-                if (have) lp.add(mix_outlier(dens, S.sc.omp, S.sc.wp));
+                if (have) lp.add(mix_outlier(dens, sc.omp, sc.wp));
             }
         }
     }
@@ -507,11 +591,11 @@ __global__ void __launch_bounds__(kBlock, 5) like_lean_kernel(const double* __re
         lp = LogProd();
 #pragma unroll 1
         for (int64_t i = beg + threadIdx.x; i < end; i += kBlock)
-            lp.add_slow(mix_outlier(general_density(x[i], kind, nz, nt, kl_max, mode, S.sc.tlo), S.sc.omp, S.sc.wp));
+            lp.add_slow(mix_outlier(general_density(x[i], kind, nz, nt, kl_max, mode, sc.tlo), sc.omp, sc.wp));
     } else {
 #pragma unroll 1
         for (int q = threadIdx.x; q < nd; q += kBlock)
-            lp.add_slow(mix_outlier(general_density(S.defer[q], kind, nz, nt, kl_max, mode, S.sc.tlo), S.sc.omp, S.sc.wp));
+            lp.add_slow(mix_outlier(general_density(S.defer[q], kind, nz, nt, kl_max, mode, sc.tlo), sc.omp, sc.wp));
     }
     const double acc = lp.value();
     int any_zero;
