@@ -6,7 +6,7 @@ import os
 import threading
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libwfpt_b200.so")
+LIB_PATH = os.environ.get("WFPT_B200_LIB") or os.path.join(HERE, "libwfpt_b200.so")   # (override: A/B runs of two builds)
 
 c_double_p = C.POINTER(C.c_double)
 c_int64_p = C.POINTER(C.c_int64)

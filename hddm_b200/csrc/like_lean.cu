@@ -536,9 +536,9 @@ __global__ void __launch_bounds__(kBlock, 5) like_lean_kernel(const double* __re
     const bool z3 = (kind == 1);
 
     if (usable) {
-#pragma unroll 1
         double2 nxt = make_double2(0.0, 0.0);          // the pair of the NEXT round is loaded a round ahead
         if ((int)threadIdx.x < npair) nxt = __ldg(x2 + threadIdx.x);
+#pragma unroll 1
         for (int r = 0; r < rounds; r++) {
             double v0 = 0.0, v1 = 0.0;
             int cnt = 0;
