@@ -58,6 +58,7 @@ cudaError_t launch_like_batch_faithful(const BatchArgs& a);
 cudaError_t launch_like_batch_fast(const BatchArgs& a);
 struct KTable;
 bool lean_applies(const BatchArgs& a, const KTable& kt);           // like_lean.cu: fixed-grid launches with n_sz = 2
+bool lean_adapt_applies(const BatchArgs& a, const KTable& kt);     // like_lean.cu: adaptive launches on one RT array
 cudaError_t launch_like_lean(const BatchArgs& a, const KTable& kt);
 
 cudaError_t launch_kflip_census(const double* x, int64_t n, const double* params, int64_t P, const Opts& o,

@@ -74,7 +74,7 @@ cudaError_t launch_like_batch_fast(const BatchArgs& a)
     if (nblk == 0) return cudaSuccess;
     {
         const KTable kt = get_ktable(a.o.err);
-        if (lean_applies(a, kt) && !getenv("WFPT_NO_LEAN")) return launch_like_lean(a, kt);
+        if ((lean_applies(a, kt) || lean_adapt_applies(a, kt)) && !getenv("WFPT_NO_LEAN")) return launch_like_lean(a, kt);
     }
     if (a.o.use_adaptive)
         like_batch_kernel<FastImpl, true><<<(unsigned)nblk, kBlock, 0, a.stream>>>(

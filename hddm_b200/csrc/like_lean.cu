@@ -297,6 +297,108 @@ __device__ __forceinline__ double tnode_value(int d, double xp, double tt, doubl
     return y[0];
 }
 
+// ---- one t-node of the first ADAPTIVE level: five equally spaced z-nodes ------------------------------------------------------
+// integrate.pxi:72-141 with the five quarter points of [z - sz/2, z + sz/2] staged.  The exponent of node n is quadratic in
+// n (a_n = a_0 + n beta + n^2 gamma), so e0_{n+1}/e0_n = exp(beta + gamma) exp(2 gamma)^n: three exps for the five leading
+// terms (small time) or the five exp(E_n) (large time).  Returns the first-level value of the z-integral; *deeper |= the
+// reference's recursion would go below the first level here (the trial is then parked for the refinement routines).
+constexpr int kOffZq = (int)offsetof(Tables, zq), kOffWz = (int)offsetof(Tables, wz), kOffIwz = (int)offsetof(Tables, inv_wz);
+
+template <bool SV>
+__device__ __forceinline__ double tnode_value5(int d, double xp, double tt, double rs, double c, unsigned tb, unsigned zb,
+                                               unsigned tab, const SetConst& sc, int sign, double simps_err, int depth_z,
+                                               int& neg, int& bad, bool& deeper)
+{
+    const double E0 = sc.nv2 * xp * c;
+    const int K = d & 0xff;
+    // (the quadratic-exponent coefficients are 8-byte aligned in fast::Tables: single loads)
+    const double2 zq01 = make_double2(lds1<kOffZq>(tb + 32 * sign), lds1<kOffZq + 8>(tb + 32 * sign));
+    const double2 zq23 = make_double2(lds1<kOffZq + 16>(tb + 32 * sign), lds1<kOffZq + 24>(tb + 32 * sign));
+    double y[5];
+    double pref;
+    if (d >> 8) {
+        const double r = rsqrt_d(tt);
+        const double tau = r * r, m2t = -2.0 * tau;
+        pref = tau * r * sc.pref_s * rs;
+        const double gam = fma(zq01.y, c, zq01.x * tau), bet = fma(zq23.y, c, zq23.x * tau);
+        const double2 Au0 = lds2<kNA>(zb);
+        const double2 ua0 = lds2<kNU>(zb), ua4 = lds2<kNU + 4 * kNodeBytes>(zb);          // (z - 2, z) of the end nodes
+        double g[6], w[6];
+        g[0] = fma(Au0.y, tau, fma(Au0.x, c, E0));
+        g[1] = bet + gam;                                               // a_1 - a_0
+        g[2] = 2.0 * gam;
+        const double a4 = fma(4.0, bet, fma(16.0, gam, g[0]));           // exponent of the last node
+        // every e0_n and every ratio between neighbours must be inside the exp kernel's range
+        bad |= (max(abs_hi(g[0]), abs_hi(a4)) >= kExpHiLimit) | !(fabs(g[1]) < 700.0) | !(fabs(fma(7.0, gam, bet)) < 700.0);
+        g[3] = clamp_neg(fma(m2t, ua0.y, m2t));                          // R   = exp(-2 (z_0 + 1) / tt)
+        g[4] = clamp_neg(fma(-m2t, ua4.y, m2t));                         // Q   = exp(-2 (1 - z_last) / tt)
+        g[5] = clamp_neg(m2t * lds1<kOffZstep>(tb + 8 * sign));          // rho = exp(-2 step / tt)
+        expv<6>(g, w, tab);
+        double e0[5], Rn[5], Qn[5];
+        e0[0] = w[0];
+        double ratio = w[1];
+#pragma unroll
+        for (int n = 1; n < 5; n++) {
+            e0[n] = e0[n - 1] * ratio;
+            ratio *= w[2];
+        }
+        const double rho = w[5];
+        Rn[0] = w[3];
+        Qn[4] = (K >= 3) ? w[4] : 0.0;                                   // K == 2 sums k = 0, 1 only
+#pragma unroll
+        for (int n = 1; n < 5; n++) {
+            Rn[n] = Rn[n - 1] * rho;
+            Qn[4 - n] = Qn[5 - n] * rho;
+        }
+        const double H = Rn[0] * Qn[0];                                  // exp(-4/tt), for the k = +2 term
+#pragma unroll
+        for (int n = 0; n < 5; n++) {
+            const double2 ua = (n == 0) ? ua0 : (n == 4) ? ua4 : lds2<kNU>(zb + n * kNodeBytes);
+            const double2 ub = lds2<kNU + 16>(zb + n * kNodeBytes);      // (z + 2, z + 4)
+            double inner = fma(ua.x, Qn[n], fma(ub.x, Rn[n], ua.y));
+            if (K >= 4) inner = fma(ub.y, Rn[n] * Rn[n] * H, inner);
+            y[n] = fma(e0[n], inner, 0.0);
+        }
+    } else {
+        pref = sc.pref_l * rs;
+        const double gam = zq01.y * c, bet = zq23.y * c;
+        double g[4], w[4];
+        g[0] = fma(lds1<kNA>(zb), c, E0);
+        g[1] = bet + gam;
+        g[2] = 2.0 * gam;
+        g[3] = -fast::kHalfPiSq * tt;
+        const double a4 = fma(4.0, bet, fma(16.0, gam, g[0]));
+        bad |= (max(max(abs_hi(g[0]), abs_hi(a4)), abs_hi(g[3])) >= kExpHiLimit) | !(fabs(g[1]) < 700.0) |
+               !(fabs(fma(7.0, gam, bet)) < 700.0);
+        expv<4>(g, w, tab);
+        const double q = w[3], q2 = q * q, q4 = q2 * q2, q8 = q4 * q4;
+        const double q9 = (K >= 3) ? q8 * q : 0.0, q16 = (K >= 4) ? q8 * q8 : 0.0, q4k = (K >= 2) ? q4 : 0.0;
+        double ex = w[0], ratio = w[1];
+#pragma unroll
+        for (int n = 0; n < 5; n++) {
+            const double2 s01 = lds2<kNS>(zb + n * kNodeBytes);
+            double acc = fma(q4k, s01.y, q * s01.x);
+            if (K >= 3) {
+                const double2 s23 = lds2<kNS + 16>(zb + n * kNodeBytes);
+                acc = fma(q16, s23.y, fma(q9, s23.x, acc));
+            }
+            y[n] = fma(acc, ex, 0.0);
+            ex *= ratio;
+            ratio *= w[2];
+        }
+    }
+    const double iw = lds1<kOffIwz>(tb + 8 * sign);
+#pragma unroll
+    for (int n = 0; n < 5; n++) {
+        y[n] *= pref;                       // pref > 0: the sign is the series sum's
+        neg |= __double2hiint(y[n]);
+        y[n] *= iw;
+    }
+    double val;
+    deeper |= !fast::adaptive_level1(y[0], y[1], y[2], y[3], y[4], lds1<kOffWz>(tb + 8 * sign), simps_err, depth_z, &val);
+    return val;
+}
+
 // Per-lane table lookup (slow path only).
 __device__ __forceinline__ int lookup_lane(const Tables& T, double tt, int* piece)
 {
@@ -442,6 +544,94 @@ __device__ __forceinline__ bool warp_density3(double ax, int sign, bool live, Sh
     }
     *out = acc;
     return true;
+}
+
+// First adaptive level of the warp's 32 trials (integrate.pxi:72-206): five t-nodes (or the single one when the t axis is not
+// integrated), each with the five-node z-integral (or the single node).  *deeper |= the reference would refine this trial
+// below the first level, along t or inside some z-integral: the caller parks it.  The three Simpson sums of the t level are
+// accumulated node by node in the reference's order of additions.
+constexpr int kOffWtA = (int)offsetof(Tables, wt), kOffIwt = (int)offsetof(Tables, inv_wt);
+
+template <int NZN, bool SV>
+__device__ __forceinline__ double warp_density_adapt(double ax, int sign, bool live, const Tables& T, Shared& S,
+                                                     const SetConst& sc, int nt, unsigned tb, unsigned etab, double simps_err,
+                                                     int depth_z, int depth_t, int& neg, int& bad, bool& deeper)
+{
+    const int w = threadIdx.x >> 5;
+    const unsigned zb = tb + kOffZ + sign * kSignBytes;
+    const double inv_wt = (nt > 0) ? lds1<kOffIwt>(tb) : 1.0;
+    double Sa = 0.0, Sl = 0.0, Sr = 0.0, single = 0.0;
+    TRec rec_n = S.trec[0];
+    PieceCache pc_n = S.piece[w][0];
+#pragma unroll 1
+    for (int i = 0; i <= nt; i++) {
+        const TRec rec = rec_n;
+        const PieceCache pc = pc_n;
+        rec_n = S.trec[i + 1];
+        pc_n = S.piece[w][i + 1];
+        const double xp = ax - rec.tn;
+        const bool alive = live && (xp > 0);
+        const int th = __double2hiint(xp);
+        double val = 0.0;
+        const unsigned am = __ballot_sync(kFull, alive);
+        if (am != 0) {
+            const double tt = xp * sc.inv_a2;
+            double rs = 1.0, c = 0.5;
+            if (SV) {
+                rs = rsqrt_d(fma(sc.sv2, xp, 1.0));
+                c = 0.5 * rs * rs;
+            }
+            const bool uniform = __all_sync(kFull, !alive || (th > pc.lo_hi && th < pc.hi_hi));
+            int piece = 0, mine = pc.desc;
+            unsigned todo = 0;
+            if (!uniform) {
+                // a piece boundary runs through the warp (or the warp has moved on): per-lane lookups on the reference's own
+                // tt = x'/pow(a, 2), one pass per distinct descriptor, lanes of other pieces riding along
+                mine = alive ? lookup_lane(T, __ddiv_rn(xp, sc.a2), &piece) : -1;
+                todo = am;
+            }
+            int ng = 0, bd = 0;
+            bool dp = false;
+#pragma unroll 1
+            do {
+                const int d = uniform ? pc.desc : __shfl_sync(kFull, mine, __ffs(todo) - 1);
+                int ng1 = 0, bd1 = 0;
+                bool dp1 = false;
+                double v;
+                if (NZN == 5) v = tnode_value5<SV>(d, xp, tt, rs, c, tb, zb, etab, sc, sign, simps_err, depth_z, ng1, bd1, dp1);
+                else v = tnode_value<1, SV>(d, xp, tt, rs, c, tb, zb, etab, sc, sign, ng1, bd1);
+                const bool match = uniform || (mine == d);
+                if (match) { val = v; ng = ng1; bd = bd1; dp = dp1; }
+                todo &= ~__ballot_sync(kFull, match);
+            } while (todo);
+            if (alive) { neg |= ng; bad |= bd; deeper |= dp; }        // lanes without the node computed along on garbage
+            else val = 0.0;
+            if (!uniform) {
+                const int p = __shfl_sync(kFull, piece, 31 - __clz(am));   // remember the piece of the last live lane
+                if ((threadIdx.x & 31) == 0) {
+                    PieceCache nc;
+                    nc.lo_hi = (p > 0) ? S.xthr_hi[p - 1] + 1 : (int)0x80000000;
+                    nc.hi_hi = (p < T.npieces) ? S.xthr_hi[p] - 1 : 0x7fffffff;
+                    nc.desc = T.desc[p];
+                    nc.pad = 0;
+                    S.piece[w][i] = nc;
+                }
+                __syncwarp();
+            }
+        }
+        // integrate.pxi:99-105 (first level): S = f0 + 4 f2 + f4, Sleft = f0 + 4 f1 + f2, Sright = f2 + 4 f3 + f4
+        const double g = val * inv_wt;
+        if (i == 0) { Sa = g; Sl = g; single = val; }
+        else if (i == 1) Sl = fma(4.0, g, Sl);
+        else if (i == 2) { Sa = fma(4.0, g, Sa); Sl += g; Sr = g; }
+        else if (i == 3) Sr = fma(4.0, g, Sr);
+        else { Sa += g; Sr += g; }
+    }
+    if (nt == 0) return single;
+    const double h12 = lds1<kOffWtA>(tb) * (1.0 / 12.0);
+    const double S1 = (2.0 * h12) * Sa, S2 = h12 * Sl + h12 * Sr;
+    deeper |= !((depth_t <= 0) || (fabs(S2 - S1) <= 15 * simps_err));
+    return fma(S2 - S1, 1.0 / 15.0, S2);
 }
 
 __device__ __forceinline__ bool lean_set_ok(int mode, int kind)
@@ -624,6 +814,212 @@ __global__ void __launch_bounds__(kBlock, 5) like_lean_kernel(const double* __re
     }
 }
 
+// ---- adaptive launches (use_adaptive != 0: what HDDM runs by default, likelihoods.py:105-113) -----------------------------------
+// The first level of the reference's recursion (5 x 5 quarter points) runs in the warp-organised loop above; a trial whose
+// recursion goes deeper is parked in shared memory (fast::Tables::queue) and evaluated by the refinement routines of
+// wfpt_fast.cuh -- by the whole CTA whenever the lot is nearly full, and after the loop -- which split intervals and add
+// results in the reference's order.
+__device__ __forceinline__ void write_result(double tot, int any_zero, int64_t bid, int64_t p, int slices,
+                                             double* __restrict__ out_sum, int* __restrict__ out_zero,
+                                             int* __restrict__ done, double* __restrict__ final_out)
+{
+    if (out_zero) {
+        out_sum[bid] = tot;
+        out_zero[bid] = any_zero;
+        if (done) {
+            // whoever finishes last adds the set's partials up in slice order and leaves the counter at zero
+            __threadfence();
+            if (atomicAdd(&done[p], 1) == slices - 1) {
+                __threadfence();
+                double sum = 0.0;
+                int z = 0;
+                for (int k = 0; k < slices; k++) {
+                    sum += __ldcg(&out_sum[p * slices + k]);
+                    z |= __ldcg(&out_zero[p * slices + k]);
+                }
+                final_out[p] = z ? -CUDART_INF : sum;
+                done[p] = 0;
+            }
+        }
+    } else {
+        out_sum[bid] = any_zero ? -CUDART_INF : tot;   // wfpt.pyx:71-72
+    }
+}
+
+constexpr int kParkRounds = 3;   // rounds between two looks at the parking lot
+static_assert(fast::kQueue > kParkRounds * 2 * kBlock, "parking lot smaller than what can arrive between two checks");
+
+__global__ void __launch_bounds__(kBlock, 5) like_lean_adapt_kernel(const double* __restrict__ x, int64_t n,
+                                                                   const double* __restrict__ params, int64_t P, Opts o,
+                                                                   double w_outlier, int slices, int64_t chunk,
+                                                                   double* __restrict__ out_sum, int* __restrict__ out_zero,
+                                                                   int* __restrict__ done, double* __restrict__ final_out,
+                                                                   const __grid_constant__ KTable kt)
+{
+    const int64_t bid = blockIdx.x;
+    const int64_t p = bid / slices;
+    const int s = (int)(bid - p * slices);
+    if (p >= P) return;
+    const double* row = params + 8 * p;
+    Params prm{row[0], row[1], row[2], row[3], row[4], row[5], row[6], row[7]};
+    const double po = prm.p_outlier;
+    if (!((po >= 0) & (po <= 1))) {   // wfpt.pyx:63-64
+        if (threadIdx.x == 0) {
+            if (out_zero) { out_sum[bid] = 0.0; out_zero[bid] = 1; }
+            else out_sum[bid] = -CUDART_INF;
+            if (out_zero && done) final_out[p] = -CUDART_INF;
+        }
+        return;
+    }
+    Shared& S = shared();
+    int mode, kind, nt, kl_max, sv_nonzero;
+    SetConst sc;
+    {
+        fast::Set set;
+        fast::prepare(set, prm, o, kt);     // CTA-collective: fills fast::Tables (barrier inside), empties the parking lot
+        mode = set.mode; kind = set.kind; nt = set.nt; kl_max = set.kl_max; sv_nonzero = set.sv_nonzero;
+        sc.a2 = set.a2; sc.inv_a2 = set.inv_a2; sc.sv2 = set.sv2; sc.nv2 = -set.v2;
+        sc.pref_s = fast::kInvSqrt2Pi * set.inv_a2; sc.pref_l = kPi * set.inv_a2;
+        sc.omp = __dsub_rn(1.0, po); sc.wp = __dmul_rn(w_outlier, po);
+        sc.tlo = set.tlo;
+        sc.ct = 1.0;
+        for (int i = threadIdx.x; i < kExpN; i += kBlock) S.exptab[i] = g_exp_table[i];
+        for (int i = threadIdx.x; i < kWarps * (fast::kMaxNodes + 1); i += kBlock) {
+            PieceCache e{0, 0, 0, 0};
+            (&S.piece[0][0])[i] = e;
+        }
+        if (mode == fast::kModeAdaptive || mode == fast::kModePoint) {
+            const Tables& T0 = fast::tables();
+            for (int i = threadIdx.x; i < kt.n; i += kBlock)
+                S.xthr_hi[i] = __double2hiint(__longlong_as_double(kt.thr[i]) * sc.a2);
+            for (int i = threadIdx.x; i <= fast::kMaxNodes; i += kBlock) {
+                TRec t{0.0, 0.0};
+                if (i <= nt) t.tn = T0.tn[i];
+                S.trec[i] = t;
+            }
+        }
+    }
+    __syncthreads();
+    const Tables& T = fast::tables();
+    const double simps_err = o.simps_err;
+    const int depth_z = o.n_sz, depth_t = o.n_st;
+
+    const int64_t beg = (int64_t)s * chunk;
+    const int64_t end = (beg + chunk < n) ? beg + chunk : n;
+    int64_t b = beg;
+    const bool head = (reinterpret_cast<uintptr_t>(x + b) & 15) && b < end;
+    if (head) b++;
+    const int npair = (int)((end - b) >> 1);
+    const bool tail = (end > b) && ((end - b) & 1);
+    const double2* x2 = reinterpret_cast<const double2*>(x + b);
+    const int rounds = (npair + kBlock - 1) / kBlock + 1;   // + 1: the head / tail elements
+
+    const unsigned tb = (unsigned)__cvta_generic_to_shared(&fast::tables());
+    const unsigned etab = (unsigned)__cvta_generic_to_shared(S.exptab);
+    LogProd lp;
+    const bool zero_set = (mode == fast::kModeZero);
+    const bool usable = zero_set || mode == fast::kModePoint || mode == fast::kModeAdaptive;
+    const bool sv = sv_nonzero != 0;
+    const bool z5 = (kind == 3 || kind == 4);
+    const bool parks = (mode == fast::kModeAdaptive || mode == fast::kModePoint);   // (a point set parks on exp range only)
+    const bool point = (mode == fast::kModePoint);
+
+    // parked trials: a handful -> one warp each (lanes share the trial's quadrature nodes); many -> one thread each
+    auto drain = [&](int parked) {
+        if (point) {   // nothing to refine: the operation-for-operation evaluator takes the trial (library exp, every term)
+#pragma unroll 1
+            for (int q = threadIdx.x; q < parked; q += kBlock)
+                lp.add_slow(mix_outlier(fast::generic_full_pdf(fast::tables().queue[q], fast::tables().prm, fast::tables().o), sc.omp, sc.wp));
+            return;
+        }
+        if (parked <= 32 && kind != 4 && depth_t == 2) {
+#pragma unroll 1
+            for (int q = threadIdx.x >> 5; q < parked; q += kWarps) {
+                const double p0 = mix_outlier(fast::refine_coop(fast::tables().queue[q], &fast::tables(), kind, kl_max), sc.omp, sc.wp);
+                if ((threadIdx.x & 31) == 0) lp.add_slow(p0);
+            }
+            return;
+        }
+#pragma unroll 1
+        for (int q = threadIdx.x; q < parked; q += kBlock)
+            lp.add_slow(mix_outlier(fast::adaptive_refine(fast::tables().queue[q], &fast::tables(), kind, kl_max), sc.omp, sc.wp));
+    };
+
+    if (usable) {
+        double2 nxt = make_double2(0.0, 0.0);          // the pair of the NEXT round is loaded a round ahead
+        if ((int)threadIdx.x < npair) nxt = __ldg(x2 + threadIdx.x);
+#pragma unroll 1
+        for (int r = 0; r < rounds; r++) {
+            double v0 = 0.0, v1 = 0.0;
+            int cnt = 0;
+            const int i = r * kBlock + threadIdx.x;
+            const double2 xx = nxt;
+            if (i + kBlock < npair) nxt = __ldg(x2 + i + kBlock);
+            if (i < npair) {
+                v0 = xx.x;
+                v1 = xx.y;
+                cnt = 2;
+            } else if (r == rounds - 1) {
+                if (head && threadIdx.x == 0) { v0 = x[beg]; cnt = 1; }
+                if (tail && threadIdx.x == kBlock - 1) { v0 = x[end - 1]; cnt = 1; }
+            }
+            const int wcnt = __reduce_max_sync(kFull, cnt);
+#pragma unroll 1
+            for (int h = 0; h < wcnt; h++) {
+                const double xv = h ? v1 : v0;
+                const double ax = fabs(xv);
+                const bool have = h < cnt;
+                const bool live = have && !zero_set && !((ax - sc.tlo) < 0);   // pdf.pxi:112, the trial-dependent part
+                double dens = 0.0;
+                if (__any_sync(kFull, live)) {
+                    const int sign = xv > 0;
+                    int neg = 0, bad = 0;
+                    bool deeper = false;
+                    if (z5) dens = sv ? warp_density_adapt<5, true>(ax, sign, live, T, S, sc, nt, tb, etab, simps_err, depth_z, depth_t, neg, bad, deeper)
+                                      : warp_density_adapt<5, false>(ax, sign, live, T, S, sc, nt, tb, etab, simps_err, depth_z, depth_t, neg, bad, deeper);
+                    else dens = sv ? warp_density_adapt<1, true>(ax, sign, live, T, S, sc, nt, tb, etab, simps_err, depth_z, depth_t, neg, bad, deeper)
+                                   : warp_density_adapt<1, false>(ax, sign, live, T, S, sc, nt, tb, etab, simps_err, depth_z, depth_t, neg, bad, deeper);
+                    // a negative truncated series anywhere makes pdf_sv's log(p) NaN (pdf.pxi:102); pdf (sv == 0) lets it through
+                    if (sv && neg < 0) dens = CUDART_NAN;
+                    if (!live) dens = 0.0;
+                    if (live && (deeper || bad)) {
+                        // below the first level, or an exp argument outside the branch-free kernel's range: the refinement
+                        // routines take the trial (the lot is drained before it can overflow, see below)
+                        const int slot = atomicAdd(&fast::tables().qcount, 1);
+                        if (slot >= fast::kQueue) __trap();
+                        fast::tables().queue[slot] = xv;
+                        continue;
+                    }
+                }
+                if (have) lp.add(mix_outlier(dens, sc.omp, sc.wp));
+            }
+            if (parks && (r % kParkRounds) == kParkRounds - 1) {   // uniform over the CTA
+                __syncthreads();
+                const int parked = fast::tables().qcount;
+                if (parked > fast::kQueue - kParkRounds * 2 * kBlock) {
+                    drain(parked);
+                    __syncthreads();
+                    if (threadIdx.x == 0) fast::tables().qcount = 0;
+                    __syncthreads();
+                }
+            }
+        }
+        if (parks) {
+            __syncthreads();
+            drain(fast::tables().qcount);
+        }
+    } else {
+        // a layout the tables do not cover: every trial through the general evaluator
+#pragma unroll 1
+        for (int64_t i = beg + threadIdx.x; i < end; i += kBlock)
+            lp.add_slow(mix_outlier(fast::generic_full_pdf(x[i], fast::tables().prm, fast::tables().o), sc.omp, sc.wp));
+    }
+    const double acc = lp.value();
+    int any_zero;
+    const double tot = block_sum_or<kBlock>(acc, lp.zero, &any_zero);
+    if (threadIdx.x == 0) write_result(tot, any_zero, bid, p, slices, out_sum, out_zero, done, final_out);
+}
+
 }  // namespace lean
 
 // Which fixed-grid launches the lean kernel takes (decided from the options alone; per-set layouts inside are then always
@@ -652,6 +1048,11 @@ static cudaError_t ensure_exp_table()
     return e;
 }
 
+bool lean_adapt_applies(const BatchArgs& a, const KTable& kt)
+{
+    return a.o.use_adaptive && !a.seg && !a.one_each && kt.n >= 0 && kt.kl_max <= 4 && kt.ks_max <= 4;
+}
+
 cudaError_t launch_like_lean(const BatchArgs& a, const KTable& kt)
 {
     {
@@ -660,6 +1061,12 @@ cudaError_t launch_like_lean(const BatchArgs& a, const KTable& kt)
     }
     const int64_t nblk = a.P * (int64_t)a.slices;
     if (nblk == 0) return cudaSuccess;
+    if (a.o.use_adaptive) {
+        lean::like_lean_adapt_kernel<<<(unsigned)nblk, kBlock, 0, a.stream>>>(
+            a.x, a.n, a.params, a.P, a.o, a.w_outlier, a.slices, a.chunk, a.slices > 1 ? a.part_sum : a.out,
+            a.slices > 1 ? a.part_zero : nullptr, a.slices > 1 ? a.done : nullptr, a.out, kt);
+        return cudaGetLastError();
+    }
     lean::like_lean_kernel<<<(unsigned)nblk, kBlock, 0, a.stream>>>(
         a.x, a.n, a.params, a.P, a.o, a.w_outlier, a.slices, a.chunk, a.slices > 1 ? a.part_sum : a.out,
         a.slices > 1 ? a.part_zero : nullptr, a.slices > 1 ? a.done : nullptr, a.out, kt);
