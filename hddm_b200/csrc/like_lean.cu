@@ -323,42 +323,52 @@ __device__ __forceinline__ double tnode_value5(int d, double xp, double tt, doub
         const double gam = fma(zq01.y, c, zq01.x * tau), bet = fma(zq23.y, c, zq23.x * tau);
         const double2 Au0 = lds2<kNA>(zb);
         const double2 ua0 = lds2<kNU>(zb), ua4 = lds2<kNU + 4 * kNodeBytes>(zb);          // (z - 2, z) of the end nodes
-        double g[6], w[6];
+        // two batches of three exps, node values streamed: the leading terms run up the nodes (e0, R_n by running products),
+        // the k = -1 terms run down them (Q_n); only y[] and e0_n (z_n - 2) stay live in between
+        double g[3], w[3];
         g[0] = fma(Au0.y, tau, fma(Au0.x, c, E0));
         g[1] = bet + gam;                                               // a_1 - a_0
         g[2] = 2.0 * gam;
         const double a4 = fma(4.0, bet, fma(16.0, gam, g[0]));           // exponent of the last node
         // every e0_n and every ratio between neighbours must be inside the exp kernel's range
         bad |= (max(abs_hi(g[0]), abs_hi(a4)) >= kExpHiLimit) | !(fabs(g[1]) < 700.0) | !(fabs(fma(7.0, gam, bet)) < 700.0);
-        g[3] = clamp_neg(fma(m2t, ua0.y, m2t));                          // R   = exp(-2 (z_0 + 1) / tt)
-        g[4] = clamp_neg(fma(-m2t, ua4.y, m2t));                         // Q   = exp(-2 (1 - z_last) / tt)
-        g[5] = clamp_neg(m2t * lds1<kOffZstep>(tb + 8 * sign));          // rho = exp(-2 step / tt)
-        expv<6>(g, w, tab);
-        double e0[5], Rn[5], Qn[5];
-        e0[0] = w[0];
-        double ratio = w[1];
+        double h[3], u[3];
+        h[0] = clamp_neg(fma(m2t, ua0.y, m2t));                          // R   = exp(-2 (z_0 + 1) / tt)
+        h[1] = clamp_neg(fma(-m2t, ua4.y, m2t));                         // Q   = exp(-2 (1 - z_last) / tt)
+        h[2] = clamp_neg(m2t * lds1<kOffZstep>(tb + 8 * sign));          // rho = exp(-2 step / tt)
+        expv<3>(g, w, tab);
+        expv<3>(h, u, tab);
+        const double rho = u[2], rho2 = rho * rho;
+        const double H = u[0] * (u[1] * (rho2 * rho2));                  // R_0 Q_0 = exp(-4/tt), for the k = +2 term
+        double v[5];
+        {
+            double e = w[0], ratio = w[1], Rn = u[0], R2H = u[0] * u[0] * H;     // R_n^2 H runs up the nodes by rho^2
 #pragma unroll
-        for (int n = 1; n < 5; n++) {
-            e0[n] = e0[n - 1] * ratio;
-            ratio *= w[2];
+            for (int n = 0; n < 5; n++) {
+                const double2 ua = (n == 0) ? ua0 : (n == 4) ? ua4 : lds2<kNU>(zb + n * kNodeBytes);
+                const double2 ub = lds2<kNU + 16>(zb + n * kNodeBytes);  // (z + 2, z + 4)
+                double t = fma(ub.x, Rn, ua.y);
+                if (K >= 4) {
+                    t = fma(ub.y, R2H, t);
+                    R2H *= rho2;
+                }
+                y[n] = e * t;
+                v[n] = e * ua.x;
+                e *= ratio;
+                ratio *= w[2];
+                Rn *= rho;
+            }
         }
-        const double rho = w[5];
-        Rn[0] = w[3];
-        Qn[4] = (K >= 3) ? w[4] : 0.0;                                   // K == 2 sums k = 0, 1 only
+        if (K >= 3) {                                                    // (K == 2 sums k = 0, 1 only)
+            double Qn = u[1];
 #pragma unroll
-        for (int n = 1; n < 5; n++) {
-            Rn[n] = Rn[n - 1] * rho;
-            Qn[4 - n] = Qn[5 - n] * rho;
+            for (int n = 4; n >= 0; n--) {
+                y[n] = fma(v[n], Qn, y[n]);
+                Qn *= rho;
+            }
         }
-        const double H = Rn[0] * Qn[0];                                  // exp(-4/tt), for the k = +2 term
 #pragma unroll
-        for (int n = 0; n < 5; n++) {
-            const double2 ua = (n == 0) ? ua0 : (n == 4) ? ua4 : lds2<kNU>(zb + n * kNodeBytes);
-            const double2 ub = lds2<kNU + 16>(zb + n * kNodeBytes);      // (z + 2, z + 4)
-            double inner = fma(ua.x, Qn[n], fma(ub.x, Rn[n], ua.y));
-            if (K >= 4) inner = fma(ub.y, Rn[n] * Rn[n] * H, inner);
-            y[n] = fma(e0[n], inner, 0.0);
-        }
+        for (int n = 0; n < 5; n++) y[n] += 0.0;                         // an underflowed e0 times a negative sum: +0, not -0
     } else {
         pref = sc.pref_l * rs;
         const double gam = zq01.y * c, bet = zq23.y * c;
@@ -387,12 +397,11 @@ __device__ __forceinline__ double tnode_value5(int d, double xp, double tt, doub
             ratio *= w[2];
         }
     }
-    const double iw = lds1<kOffIwz>(tb + 8 * sign);
+    const double piw = pref * lds1<kOffIwz>(tb + 8 * sign);   // pref / width of the z interval, > 0: the sign is the series sum's
 #pragma unroll
     for (int n = 0; n < 5; n++) {
-        y[n] *= pref;                       // pref > 0: the sign is the series sum's
         neg |= __double2hiint(y[n]);
-        y[n] *= iw;
+        y[n] *= piw;
     }
     double val;
     deeper |= !fast::adaptive_level1(y[0], y[1], y[2], y[3], y[4], lds1<kOffWz>(tb + 8 * sign), simps_err, depth_z, &val);
@@ -849,7 +858,7 @@ __device__ __forceinline__ void write_result(double tot, int any_zero, int64_t b
 constexpr int kParkRounds = 3;   // rounds between two looks at the parking lot
 static_assert(fast::kQueue > kParkRounds * 2 * kBlock, "parking lot smaller than what can arrive between two checks");
 
-__global__ void __launch_bounds__(kBlock, 5) like_lean_adapt_kernel(const double* __restrict__ x, int64_t n,
+__global__ void __launch_bounds__(kBlock, 4) like_lean_adapt_kernel(const double* __restrict__ x, int64_t n,
                                                                    const double* __restrict__ params, int64_t P, Opts o,
                                                                    double w_outlier, int slices, int64_t chunk,
                                                                    double* __restrict__ out_sum, int* __restrict__ out_zero,
