@@ -37,7 +37,7 @@ for key, rep, units in zip(args[0::3], args[1::3], args[2::3]):
     rd, wr = nbytes("dram__bytes_read.sum"), nbytes("dram__bytes_write.sum")
     e = {
         "kernel": d.get("Kernel Name"), "units_per_launch": units, "evals_per_launch": units,
-        "capture_time_ms": num("gpu__time_duration.sum", 0.0) * {"nsecond": 1e-6, "usecond": 1e-3, "msecond": 1.0, "second": 1e3}.get(u.get("gpu__time_duration.sum"), 1e-6),
+        "capture_time_ms": num("gpu__time_duration.sum", 0.0) * {"ns": 1e-6, "us": 1e-3, "ms": 1.0, "s": 1e3, "nsecond": 1e-6, "usecond": 1e-3, "msecond": 1.0, "second": 1e3}.get(u.get("gpu__time_duration.sum"), 1e-6),
         "registers": num("launch__registers_per_thread"),
         "fp64_thread_inst_per_eval": fp64_w * 32 / units if fp64_w else None,
         "thread_inst_per_eval": inst_w * 32 / units if inst_w else None,
