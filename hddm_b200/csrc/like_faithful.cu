@@ -37,6 +37,7 @@ struct FaithfulImpl {
     __device__ static __forceinline__ bool park(Set&, double) { return false; }
     __device__ static __forceinline__ int parked_count(const Set&) { return 0; }
     __device__ static __forceinline__ double parked(const Set&, int) { return 0.0; }
+    __device__ static __forceinline__ void prepare_multi(const Ctx&) {}
     __device__ static __forceinline__ double density_once(double x, const Params& prm, const Opts& o, const Ctx&)
     {
         return faithful::full_pdf(x, prm.v, prm.sv, prm.a, prm.z, prm.sz, prm.t, prm.st, o);

@@ -61,6 +61,7 @@ struct FastImpl {
         return n < fast::kQueue ? n : fast::kQueue;
     }
     __device__ static __forceinline__ double parked(const Set&, int q) { return fast::tables().queue[q]; }
+    __device__ static __forceinline__ void prepare_multi(const Ctx& kt) { fast::prepare_series_only(kt); }
     __device__ static __forceinline__ double density_once(double x, const Params& prm, const Opts& o, const Ctx& kt)
     {
         return fast::density_once(x, prm, o, kt);

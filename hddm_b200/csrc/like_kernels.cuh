@@ -260,6 +260,7 @@ __global__ void __launch_bounds__(kBlock) like_multi_kernel(const double* __rest
 {
     const double wp = __dmul_rn(w_outlier, p_outlier);
     const double omp = __dsub_rn(1.0, p_outlier);
+    Impl::prepare_multi(ctx);   // CTA-collective: shared tables of the per-trial evaluator (fast variant)
     double acc = 0.0;
     int zero = 0;
     const int64_t stride = (int64_t)gridDim.x * kBlock;

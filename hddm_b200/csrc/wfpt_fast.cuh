@@ -823,6 +823,94 @@ static __device__ __noinline__ double adaptive_full_pdf(double x, const Tables* 
     return faithful::simpson_adaptive(in, lb_t, ub_t, __dsub_rn(ub_t, lb_t), T.o.simps_err, T.o.n_st);
 }
 
+// full_pdf (pdf.pxi:104-146) for a parameter set of its own per trial (wiener_like_multi, the RL-DDM flavours with sz or st
+// above the 1e-3 thresholds): nothing can be staged per CTA, but every node still goes through the table-driven evaluator
+// above instead of 2 log + 6 sqrt + 2 div + K library exps.  Tp needs exptab and the series-term table only
+// (prepare_series_only).  Branch structure as the reference's, node positions of the fixed grids rounded separately.
+template <class F>
+__device__ __forceinline__ double adhoc_simpson_fixed(const F& f, double lb, double ub, int n)
+{
+    const double h = __ddiv_rn(__dsub_rn(ub, lb), (double)n);
+    double S = 0, y = 0;
+    for (int i = 0; i <= n; i++) {   // integrate.pxi:30-45: 1, 4, 2, ..., then one f(b) taken back
+        y = f(i == 0 ? lb : __dadd_rn(lb, __dmul_rn(h, (double)i)));
+        S = (i == 0) ? y : S + ((i & 1) ? (4 * y) : (2 * y));
+    }
+    S = S - y;
+    S = S / __dsub_rn(ub, lb);
+    return (h * S / 3);
+}
+struct AdhocInnerFixed {   // fixed-grid z-integral as the integrand of the t-integral (integrate.pxi:47-70)
+    AdhocCtx c;
+    double x, lb_z, ub_z;
+    int n_sz;
+    __device__ __forceinline__ double operator()(double t_node) const
+    {
+        const AdhocAxis ax{c, x, t_node, true};
+        return adhoc_simpson_fixed(ax, lb_z, ub_z, n_sz);
+    }
+};
+
+static __device__ __noinline__ double full_pdf_adhoc(double x, const Params& p, const Opts& o, const Tables* Tp)
+{
+    double v = p.v, z = p.z, sz = p.sz, st = p.st;
+    const double t = p.t, a = p.a, sv = p.sv;
+    if ((z < 0) || (z > 1) || (a < 0) || (t < 0) || (st < 0) || (sv < 0) || (sz < 0) || (sz > 1) ||
+        ((fabs(x) - (t - st / 2.)) < 0) || (z + sz / 2. > 1) || (z - sz / 2. < 0) || (t - st / 2. < 0))
+        return 0.0;
+    if (x > 0) {
+        v = -v;
+        z = __dsub_rn(1., z);
+    }
+    x = fabs(x);
+    if (st < 1e-3) st = 0;
+    if (sz < 1e-3) sz = 0;
+    AdhocCtx c;
+    c.v = v; c.v2 = v * v; c.sv2 = sv * sv; c.a = a; c.a2 = a * a; c.inv_a2 = 1.0 / c.a2;
+    c.asv2 = c.a2 * c.sv2; c.sv_nonzero = (sv != 0); c.T = Tp;
+    if (sz == 0 && st == 0) return pdf_sv_adhoc(c, x - t, z);
+    const double lb_z = __dsub_rn(z, __ddiv_rn(sz, 2.)), ub_z = __dadd_rn(z, __ddiv_rn(sz, 2.));
+    const double lb_t = __dsub_rn(t, __ddiv_rn(st, 2.)), ub_t = __dadd_rn(t, __ddiv_rn(st, 2.));
+    if (sz == 0 || st == 0) {
+        // one axis (the reference's choice of axis and interval, see faithful::full_pdf)
+        const bool adapt = o.use_adaptive != 0;
+        bool over_z;
+        double lo, hi;
+        int n;
+        if (st == 0) {
+            over_z = true; lo = lb_z; hi = ub_z; n = o.n_sz;
+        } else {
+            over_z = adapt ? (__dsub_rn(ub_t, lb_t) == 0) : (o.n_st == 0);
+            lo = over_z ? z : lb_t; hi = over_z ? z : ub_t; n = o.n_st;
+        }
+        const AdhocAxis ax{c, x, over_z ? t : z, over_z};
+        if (adapt)
+            return adhoc_axis_integral(ax, lo, hi, (st == 0) ? __dsub_rn(ub_z, lb_z) : (over_z ? 0.0 : __dsub_rn(ub_t, lb_t)),
+                                       o.simps_err, n);
+        return adhoc_simpson_fixed(ax, lo, hi, n > 0 ? n : 0);
+    }
+    if (o.use_adaptive) {
+        const AdhocInner in{c, x, lb_z, ub_z, o.simps_err, o.n_sz};
+        return faithful::simpson_adaptive(in, lb_t, ub_t, __dsub_rn(ub_t, lb_t), o.simps_err, o.n_st);
+    }
+    const AdhocInnerFixed in{c, x, lb_z, ub_z, o.n_sz};
+    return adhoc_simpson_fixed(in, lb_t, ub_t, o.n_st);
+}
+
+// CTA-collective: the part of prepare() the per-trial evaluator needs (exp table, series-term table).
+__device__ __forceinline__ void prepare_series_only(const KTable& kt)
+{
+    Tables& T = tables();
+    if (kt.n < 0) return;
+    for (int i = threadIdx.x; i < 64; i += blockDim.x) T.exptab[i] = exp2((double)i * (1.0 / 64.0));
+    for (int i = threadIdx.x; i <= kt.n; i += blockDim.x) {
+        T.desc[i] = (i == 0) ? kt.desc0 : kt.desc[i - 1];
+        if (i < kt.n) T.thr[i] = kt.thr[i];
+    }
+    if (threadIdx.x == 0) T.npieces = kt.n;
+    __syncthreads();
+}
+
 // Refinement along t with the staged z-nodes.  Nearly every trial that fails the first-level test does so on the t axis
 // (an RT close to t +- st/2, where the integrand switches on), while each inner z-integral still stops at its first
 // level.  Such a trial needs the reference's walk over t only, and every new t-node costs what a staged one costs:
@@ -1096,7 +1184,13 @@ __device__ __forceinline__ double density_generic(double x, const Set& s)
 __device__ __forceinline__ double density_once(double x, const Params& prm, const Opts& o, const KTable& kt)
 {
     const double z = prm.z, a = prm.a, t = prm.t, sv = prm.sv, sz = prm.sz, st = prm.st;
-    if (!(sz < 1e-3 && st < 1e-3) || kt.n < 0 || kt.kl_max > kMaxKLarge) return generic_full_pdf(x, prm, o);
+    if (kt.n < 0 || kt.kl_max > kMaxKLarge) return generic_full_pdf(x, prm, o);
+    // integration over z and / or t with this trial's own parameters: table-driven nodes, the reference's recursion
+    // (n == 0 on an integrated axis is the reference's division-by-zero corner, Appendix A.12: operation for operation)
+    if (!(sz < 1e-3 && st < 1e-3)) {
+        if (!o.use_adaptive && ((sz >= 1e-3 && o.n_sz == 0) || (st >= 1e-3 && o.n_st == 0))) return generic_full_pdf(x, prm, o);
+        return full_pdf_adhoc(x, prm, o, &tables());
+    }
     if ((z < 0) || (z > 1) || (a < 0) || (t < 0) || (st < 0) || (sv < 0) || (sz < 0) || (sz > 1) ||
         ((fabs(x) - (t - st / 2.)) < 0) || (z + sz / 2. > 1) || (z - sz / 2. < 0) || (t - st / 2. < 0))
         return 0.0;

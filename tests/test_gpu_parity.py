@@ -435,3 +435,29 @@ def test_series_term_census_has_no_flips(grid_golden, wfpt_gpu):
         xp = (np.abs(g["x"])[:, None] - t_nodes[None, :]).ravel()
         tt = xp[xp > 0] / (q[2] * q[2])
         assert np.array_equal(desc[np.searchsorted(thr, tt, side="right")], _lib.ktable_decision_array(tt, 1e-4))
+
+
+def test_multi_with_integration_vs_oracle(oracle, wfpt_gpu, variant):
+    """wiener_like_multi with per-trial v, a, t (and z) while sz / st are above the 1e-3 thresholds: every trial integrates
+    with its own parameter set (what HDDMRegressor asks for, /root/reference/hddm/models/hddm_regression.py:48-61, with the
+    reference's depth-10 adaptive defaults, src/wfpt.pyx:357-387), plus fixed grids and the one-axis cases."""
+    rng = np.random.default_rng(41)
+    n = 1500
+    x = np.where(rng.random(n) < 0.75, 1.0, -1.0) * rng.uniform(0.3, 3.5, n)
+    x[5], x[9] = 999.0, -999.0          # choice-only trials (wfpt.pyx:370-379)
+    v, a, t, z = rng.normal(0.8, 0.5, n), rng.uniform(1.2, 2.8, n), rng.uniform(0.1, 0.4, n), rng.uniform(0.35, 0.65, n)
+    cases = [
+        (dict(sv=0.6, sz=0.15, st=0.12), ["v", "a", "t"], dict()),                                   # defaults: adaptive, depth 10
+        (dict(sv=0.0, sz=0.2, st=0.0), ["v", "a", "t", "z"], dict()),                                # z axis only
+        (dict(sv=1.1, sz=0.0, st=0.2), ["v", "t"], dict(n_st=3, n_sz=3, simps_err=1e-5)),            # t axis only
+        (dict(sv=0.6, sz=0.15, st=0.12), ["v", "a", "t"], dict(use_adaptive=0, n_st=2, n_sz=2)),      # fixed 3 x 3
+        (dict(sv=0.3, sz=0.1, st=0.15), ["a"], dict(use_adaptive=0, n_st=5, n_sz=4)),                 # odd grid
+        (dict(sv=0.6, sz=5e-4, st=0.12), ["v", "a", "t"], dict(use_adaptive=0, n_st=4, n_sz=0)),      # sz under the threshold
+    ]
+    for fixed, multi, kw in cases:
+        vals = dict(v=v if "v" in multi else 0.9, a=a if "a" in multi else 2.0, t=t if "t" in multi else 0.25,
+                    z=z if "z" in multi else 0.5, **fixed)
+        args = (vals["v"], vals["sv"], vals["a"], vals["z"], vals["sz"], vals["t"], vals["st"], 1e-4)
+        want = oracle.wiener_like_multi(x, *args, multi, p_outlier=0.05, w_outlier=0.1, **kw)
+        got = wfpt_gpu.wiener_like_multi(x, *args, multi, p_outlier=0.05, w_outlier=0.1, **kw)
+        assert np.isfinite(want) and abs(got - want) <= TOL * abs(want), (fixed, multi, kw, got, want)
