@@ -249,7 +249,7 @@ int wfpt_sim_n_params(int model);
  * buffer holds, with the bin edges of bin_simulator_output (graveyard/basic_simulator_old.py:70-119): nbins edges
  * linspace(0, hist_max_t, nbins) plus +inf, column 0 = lower / first choice, column 1 = upper; steps: total Euler steps
  * (added); traj: path of particle 0 of set 0 (float32[traj_len], caller pre-fills with -999 like the reference).
- * Random numbers: Philox4x32-10 keyed by `seed`, counter = (sample_offset + particle index, set): results do not depend
+ * Random numbers: Philox4x32-7 keyed by `seed`, counter = (sample_offset + particle index, set): results do not depend
  * on launch geometry, and ranks that shard particles pass their global offset in `sample_offset`.
  * Replaces the compiled simulators behind hddm.simulators.simulator (hddm/simulators/basic_simulator.py:6-36). */
 int wfpt_sim_run(int model, const float* d_theta, int n_par, int n_sets, int64_t n_samples, int64_t sample_offset,
