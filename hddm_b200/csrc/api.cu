@@ -38,7 +38,7 @@ static int fail(const char* fmt, ...)
 void count_launch(int k) { g_launches.fetch_add(k, std::memory_order_relaxed); }
 
 // ---- per-device grow-only scratch ------------------------------------------------------------------------------------
-enum Slot { kPartSum = 0, kPartZero, kDone, kStageX, kStageParams, kStageOut, kStageAux0, kStageAux1, kStageAux2, kStageAux3,
+enum Slot { kPartSum = 0, kPartZero, kDone, kParkX, kParkN, kStageX, kStageParams, kStageOut, kStageAux0, kStageAux1, kStageAux2, kStageAux3,
             kStageAux4, kStageAux5, kStageAux6, kStageAux7, kStageAux8, kStageAux9, kStageAux10, kStageAux11, kSim0, kSim1, kSim2,
             kSim3, kSim4, kSim5, kSorted, kNumSlots };
 constexpr int kMaxDev = 16;
@@ -584,7 +584,8 @@ int wfpt_like_batch(const double* d_x, int64_t n, const double* d_params, int64_
     if ((double)P * a.slices > 2.0e9) return fail("P*slices too large for one launch (P=%lld)", (long long)P);
     a.part_sum = nullptr;
     a.part_zero = nullptr;
-    if (a.slices > 1) {
+    const bool two_kernels = use_adaptive && !a.one_each && variant == WFPT_VARIANT_FAST && n > 0;
+    if (a.slices > 1 || two_kernels) {
         void *ps, *pz, *dn;
         if (scratch(kPartSum, sizeof(double) * (size_t)P * a.slices, &ps)) return 1;
         if (scratch(kPartZero, sizeof(int) * (size_t)P * a.slices, &pz)) return 1;
@@ -592,6 +593,17 @@ int wfpt_like_batch(const double* d_x, int64_t n, const double* d_params, int64_
         a.part_sum = (double*)ps;
         a.part_zero = (int*)pz;
         a.done = (int*)dn;   // the last slice of each set sums the partials: one launch in all
+    }
+    if (two_kernels) {
+        // adaptive launches on big grids: first level in one kernel, parked trials refined by a second one (like_lean.cu).
+        // Every (set, slice) item owns a region of the list; a list that outgrows it is refined inside the first kernel.
+        const int64_t cap = a.chunk < 2048 ? ((a.chunk + 1) & ~(int64_t)1) : 2048;
+        void *px, *pn;
+        if (scratch(kParkX, sizeof(double) * (size_t)P * a.slices * (size_t)cap, &px)) return 1;
+        if (scratch(kParkN, sizeof(int) * (size_t)P * a.slices, &pn)) return 1;
+        a.park_x = (double*)px;
+        a.park_n = (int*)pn;
+        a.park_cap = (int)cap;
     }
     CK(variant == WFPT_VARIANT_FAITHFUL ? launch_like_batch_faithful(a) : launch_like_batch_fast(a));
     count_launch(1);

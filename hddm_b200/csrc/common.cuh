@@ -49,6 +49,9 @@ struct BatchArgs {
     cudaStream_t stream;
     const int64_t* seg = nullptr;  // optional [P][2] (device): set p is evaluated on x[seg[p][0] .. seg[p][1]) instead of all of x
     int one_each = 0;              // 1: chunk may be as small as one RT per thread (small grids; see plan_slices)
+    double* park_x = nullptr;      // adaptive launches: [P*slices][park_cap] trials parked for the refinement kernel, and
+    int* park_n = nullptr;         // [P*slices] their counts (library scratch; without them the one-kernel form runs)
+    int park_cap = 0;
     int* done = nullptr;           // optional [P] zeroed counters (device): when given (slices > 1), the slice that finishes last
                                    // sums its set's partials in slice order into out[p] and re-zeroes the counter, so that no
                                    // separate finalize launch is needed

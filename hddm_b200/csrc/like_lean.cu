@@ -555,6 +555,27 @@ __device__ __forceinline__ bool warp_density3(double ax, int sign, bool live, Sh
     return true;
 }
 
+// Out-of-line copy of the node evaluation for the piece-boundary passes (cold on sorted inputs): keeps the loop's hot path the
+// only inlined copy.  flags: bit 31.. = sign bits seen (neg), bit 0 = bad, bit 1 = deeper.
+struct NodeOut { double val; int neg; int flags; };
+template <int NZN, bool SV>
+static __device__ __noinline__ NodeOut node_call(int d, double xp, double tt, double rs, double c, unsigned tb, unsigned zb,
+                                                 unsigned etab, double a2, double inv_a2, double sv2, double nv2, double pref_s,
+                                                 double pref_l, int sign, double simps_err, int depth_z)
+{
+    SetConst sc;
+    sc.a2 = a2; sc.inv_a2 = inv_a2; sc.sv2 = sv2; sc.nv2 = nv2; sc.pref_s = pref_s; sc.pref_l = pref_l;
+    sc.omp = sc.wp = sc.tlo = sc.ct = 0.0;
+    NodeOut o;
+    int ng = 0, bd = 0;
+    bool dp = false;
+    if (NZN == 5) o.val = tnode_value5<SV>(d, xp, tt, rs, c, tb, zb, etab, sc, sign, simps_err, depth_z, ng, bd, dp);
+    else o.val = tnode_value<1, SV>(d, xp, tt, rs, c, tb, zb, etab, sc, sign, ng, bd);
+    o.neg = ng;
+    o.flags = (bd ? 1 : 0) | (dp ? 2 : 0);
+    return o;
+}
+
 // First adaptive level of the warp's 32 trials (integrate.pxi:72-206): five t-nodes (or the single one when the t axis is not
 // integrated), each with the five-node z-integral (or the single node).  *deeper |= the reference would refine this trial
 // below the first level, along t or inside some z-integral: the caller parks it.  The three Simpson sums of the t level are
@@ -590,32 +611,31 @@ __device__ __forceinline__ double warp_density_adapt(double ax, int sign, bool l
                 rs = rsqrt_d(fma(sc.sv2, xp, 1.0));
                 c = 0.5 * rs * rs;
             }
-            const bool uniform = __all_sync(kFull, !alive || (th > pc.lo_hi && th < pc.hi_hi));
-            int piece = 0, mine = pc.desc;
-            unsigned todo = 0;
-            if (!uniform) {
+            auto node = [&](int d, int& ng1, int& bd1, bool& dp1) -> double {
+                if (NZN == 5) return tnode_value5<SV>(d, xp, tt, rs, c, tb, zb, etab, sc, sign, simps_err, depth_z, ng1, bd1, dp1);
+                return tnode_value<1, SV>(d, xp, tt, rs, c, tb, zb, etab, sc, sign, ng1, bd1);
+            };
+            if (__all_sync(kFull, !alive || (th > pc.lo_hi && th < pc.hi_hi))) {
+                int ng = 0, bd = 0;
+                bool dp = false;
+                val = node(pc.desc, ng, bd, dp);
+                if (alive) { neg |= ng; bad |= bd; deeper |= dp; }    // lanes without the node computed along on garbage
+                else val = 0.0;
+            } else {
                 // a piece boundary runs through the warp (or the warp has moved on): per-lane lookups on the reference's own
                 // tt = x'/pow(a, 2), one pass per distinct descriptor, lanes of other pieces riding along
-                mine = alive ? lookup_lane(T, __ddiv_rn(xp, sc.a2), &piece) : -1;
-                todo = am;
-            }
-            int ng = 0, bd = 0;
-            bool dp = false;
+                int piece = 0;
+                const int mine = alive ? lookup_lane(T, __ddiv_rn(xp, sc.a2), &piece) : -1;
+                unsigned todo = am;
 #pragma unroll 1
-            do {
-                const int d = uniform ? pc.desc : __shfl_sync(kFull, mine, __ffs(todo) - 1);
-                int ng1 = 0, bd1 = 0;
-                bool dp1 = false;
-                double v;
-                if (NZN == 5) v = tnode_value5<SV>(d, xp, tt, rs, c, tb, zb, etab, sc, sign, simps_err, depth_z, ng1, bd1, dp1);
-                else v = tnode_value<1, SV>(d, xp, tt, rs, c, tb, zb, etab, sc, sign, ng1, bd1);
-                const bool match = uniform || (mine == d);
-                if (match) { val = v; ng = ng1; bd = bd1; dp = dp1; }
-                todo &= ~__ballot_sync(kFull, match);
-            } while (todo);
-            if (alive) { neg |= ng; bad |= bd; deeper |= dp; }        // lanes without the node computed along on garbage
-            else val = 0.0;
-            if (!uniform) {
+                while (todo) {
+                    const int d = __shfl_sync(kFull, mine, __ffs(todo) - 1);
+                    const NodeOut o = node_call<NZN, SV>(d, xp, tt, rs, c, tb, zb, etab, sc.a2, sc.inv_a2, sc.sv2, sc.nv2, sc.pref_s,
+                                                         sc.pref_l, sign, simps_err, depth_z);
+                    const bool match = (mine == d);
+                    if (match) { val = o.val; neg |= o.neg; bad |= o.flags & 1; deeper |= (o.flags & 2) != 0; }
+                    todo &= ~__ballot_sync(kFull, match);
+                }
                 const int p = __shfl_sync(kFull, piece, 31 - __clz(am));   // remember the piece of the last live lane
                 if ((threadIdx.x & 31) == 0) {
                     PieceCache nc;
@@ -861,10 +881,13 @@ static_assert(fast::kQueue > kParkRounds * 2 * kBlock, "parking lot smaller than
 __global__ void __launch_bounds__(kBlock, 4) like_lean_adapt_kernel(const double* __restrict__ x, int64_t n,
                                                                    const double* __restrict__ params, int64_t P, Opts o,
                                                                    double w_outlier, int slices, int64_t chunk,
-                                                                   double* __restrict__ out_sum, int* __restrict__ out_zero,
-                                                                   int* __restrict__ done, double* __restrict__ final_out,
-                                                                   const __grid_constant__ KTable kt)
+                                                                   double* __restrict__ part_sum, int* __restrict__ part_zero,
+                                                                   double* __restrict__ park_x, int* __restrict__ park_n,
+                                                                   int park_cap, const __grid_constant__ KTable kt)
 {
+    // Writes, per (set, slice) item: the sum of the log terms of the trials settled at the first level, the zero flag, and
+    // the list of parked trials (park_x[item * park_cap ..], park_n[item]) for like_lean_refine_kernel, which adds the
+    // parked trials' terms and produces the final sums.  Only a list that overflows its region is refined here.
     const int64_t bid = blockIdx.x;
     const int64_t p = bid / slices;
     const int s = (int)(bid - p * slices);
@@ -872,12 +895,8 @@ __global__ void __launch_bounds__(kBlock, 4) like_lean_adapt_kernel(const double
     const double* row = params + 8 * p;
     Params prm{row[0], row[1], row[2], row[3], row[4], row[5], row[6], row[7]};
     const double po = prm.p_outlier;
-    if (!((po >= 0) & (po <= 1))) {   // wfpt.pyx:63-64
-        if (threadIdx.x == 0) {
-            if (out_zero) { out_sum[bid] = 0.0; out_zero[bid] = 1; }
-            else out_sum[bid] = -CUDART_INF;
-            if (out_zero && done) final_out[p] = -CUDART_INF;
-        }
+    if (!((po >= 0) & (po <= 1))) {   // wfpt.pyx:63-64: the refine kernel turns the flag into -inf
+        if (threadIdx.x == 0) { part_sum[bid] = 0.0; part_zero[bid] = 1; park_n[bid] = 0; }
         return;
     }
     Shared& S = shared();
@@ -934,26 +953,28 @@ __global__ void __launch_bounds__(kBlock, 4) like_lean_adapt_kernel(const double
     const bool point = (mode == fast::kModePoint);
 
     // parked trials: a handful -> one warp each (lanes share the trial's quadrature nodes); many -> one thread each
-    auto drain = [&](int parked) {
+    auto drain = [&](int first, int parked) {   // lot entries first .. parked - 1
         if (point) {   // nothing to refine: the operation-for-operation evaluator takes the trial (library exp, every term)
 #pragma unroll 1
-            for (int q = threadIdx.x; q < parked; q += kBlock)
+            for (int q = first + threadIdx.x; q < parked; q += kBlock)
                 lp.add_slow(mix_outlier(fast::generic_full_pdf(fast::tables().queue[q], fast::tables().prm, fast::tables().o), sc.omp, sc.wp));
             return;
         }
-        if (parked <= 32 && kind != 4 && depth_t == 2) {
 #pragma unroll 1
-            for (int q = threadIdx.x >> 5; q < parked; q += kWarps) {
-                const double p0 = mix_outlier(fast::refine_coop(fast::tables().queue[q], &fast::tables(), kind, kl_max), sc.omp, sc.wp);
-                if ((threadIdx.x & 31) == 0) lp.add_slow(p0);
-            }
-            return;
-        }
-#pragma unroll 1
-        for (int q = threadIdx.x; q < parked; q += kBlock)
+        for (int q = first + threadIdx.x; q < parked; q += kBlock)
             lp.add_slow(mix_outlier(fast::adaptive_refine(fast::tables().queue[q], &fast::tables(), kind, kl_max), sc.omp, sc.wp));
     };
 
+    // the shared-memory lot goes to this item's region of the global list; what does not fit is refined here
+    int flushed = 0;
+    auto flush = [&](int parked) {
+        const int room = park_cap - flushed;
+        const int take = parked < room ? parked : room;
+        double* dst = park_x + (size_t)bid * park_cap + flushed;
+        for (int q = threadIdx.x; q < take; q += kBlock) dst[q] = fast::tables().queue[q];
+        flushed += take;
+        if (take < parked) drain(take, parked);
+    };
     if (usable) {
         double2 nxt = make_double2(0.0, 0.0);          // the pair of the NEXT round is loaded a round ahead
         if ((int)threadIdx.x < npair) nxt = __ldg(x2 + threadIdx.x);
@@ -1006,7 +1027,7 @@ __global__ void __launch_bounds__(kBlock, 4) like_lean_adapt_kernel(const double
                 __syncthreads();
                 const int parked = fast::tables().qcount;
                 if (parked > fast::kQueue - kParkRounds * 2 * kBlock) {
-                    drain(parked);
+                    flush(parked);
                     __syncthreads();
                     if (threadIdx.x == 0) fast::tables().qcount = 0;
                     __syncthreads();
@@ -1015,7 +1036,7 @@ __global__ void __launch_bounds__(kBlock, 4) like_lean_adapt_kernel(const double
         }
         if (parks) {
             __syncthreads();
-            drain(fast::tables().qcount);
+            flush(fast::tables().qcount);
         }
     } else {
         // a layout the tables do not cover: every trial through the general evaluator
@@ -1026,7 +1047,67 @@ __global__ void __launch_bounds__(kBlock, 4) like_lean_adapt_kernel(const double
     const double acc = lp.value();
     int any_zero;
     const double tot = block_sum_or<kBlock>(acc, lp.zero, &any_zero);
-    if (threadIdx.x == 0) write_result(tot, any_zero, bid, p, slices, out_sum, out_zero, done, final_out);
+    if (threadIdx.x == 0) {
+        part_sum[bid] = tot;
+        part_zero[bid] = any_zero;
+        park_n[bid] = flushed;
+    }
+}
+
+// Second kernel of an adaptive launch: one CTA per (set, slice) item refines the trials the first kernel parked for it
+// (integrate.pxi:72-206 below the first level; the routines of wfpt_fast.cuh: one warp per trial for a handful, one thread
+// per trial otherwise), adds their log terms to the item's first-level sum in a fixed order and writes the result.  Keeping
+// the refinement out of the first kernel keeps both instruction working sets small: run inside it, the two code paths
+// evicted each other from the instruction cache (7 of 13 stalled warps per issue cycle waiting for instructions on the
+// whole-box grid).
+__global__ void __launch_bounds__(kBlock, 4) like_lean_refine_kernel(const double* __restrict__ params, int64_t P, Opts o,
+                                                                    double w_outlier, int slices,
+                                                                    double* __restrict__ part_sum, int* __restrict__ part_zero,
+                                                                    const double* __restrict__ park_x,
+                                                                    const int* __restrict__ park_n, int park_cap,
+                                                                    int* __restrict__ done, double* __restrict__ final_out,
+                                                                    const __grid_constant__ KTable kt)
+{
+    const int64_t bid = blockIdx.x;
+    const int64_t p = bid / slices;
+    if (p >= P) return;
+    const int cnt = park_n[bid];
+    double tot = part_sum[bid];
+    int any_zero = part_zero[bid];
+    if (cnt > 0) {      // uniform over the CTA
+        const double* row = params + 8 * p;
+        Params prm{row[0], row[1], row[2], row[3], row[4], row[5], row[6], row[7]};
+        const double po = prm.p_outlier;
+        const double omp = __dsub_rn(1.0, po), wp = __dmul_rn(w_outlier, po);
+        fast::Set set;
+        fast::prepare(set, prm, o, kt);
+        const int kind = set.kind, kl_max = set.kl_max;
+        const double* list = park_x + (size_t)bid * park_cap;
+        LogProd lp;
+        if (set.mode == fast::kModePoint) {
+#pragma unroll 1
+            for (int q = threadIdx.x; q < cnt; q += kBlock)
+                lp.add_slow(mix_outlier(fast::generic_full_pdf(list[q], fast::tables().prm, fast::tables().o), omp, wp));
+        } else if (cnt <= 32 && kind != 4 && o.n_st == 2) {
+#pragma unroll 1
+            for (int q = threadIdx.x >> 5; q < cnt; q += kWarps) {
+                const double p0 = mix_outlier(fast::refine_coop(list[q], &fast::tables(), kind, kl_max), omp, wp);
+                if ((threadIdx.x & 31) == 0) lp.add_slow(p0);
+            }
+        } else {
+#pragma unroll 1
+            for (int q = threadIdx.x; q < cnt; q += kBlock)
+                lp.add_slow(mix_outlier(fast::adaptive_refine(list[q], &fast::tables(), kind, kl_max), omp, wp));
+        }
+        int z2;
+        const double add = block_sum_or<kBlock>(lp.value(), lp.zero, &z2);
+        tot += add;
+        any_zero |= z2;
+    }
+    if (threadIdx.x == 0) {
+        if (slices > 1) write_result(tot, any_zero, bid, p, slices, part_sum, part_zero, done, final_out);
+        else final_out[p] = any_zero ? -CUDART_INF : tot;
+    }
 }
 
 }  // namespace lean
@@ -1059,7 +1140,8 @@ static cudaError_t ensure_exp_table()
 
 bool lean_adapt_applies(const BatchArgs& a, const KTable& kt)
 {
-    return a.o.use_adaptive && !a.seg && !a.one_each && kt.n >= 0 && kt.kl_max <= 4 && kt.ks_max <= 4;
+    return a.o.use_adaptive && !a.seg && !a.one_each && a.park_x && a.park_n && a.part_sum && a.part_zero && kt.n >= 0 &&
+           kt.kl_max <= 4 && kt.ks_max <= 4;
 }
 
 cudaError_t launch_like_lean(const BatchArgs& a, const KTable& kt)
@@ -1072,8 +1154,14 @@ cudaError_t launch_like_lean(const BatchArgs& a, const KTable& kt)
     if (nblk == 0) return cudaSuccess;
     if (a.o.use_adaptive) {
         lean::like_lean_adapt_kernel<<<(unsigned)nblk, kBlock, 0, a.stream>>>(
-            a.x, a.n, a.params, a.P, a.o, a.w_outlier, a.slices, a.chunk, a.slices > 1 ? a.part_sum : a.out,
-            a.slices > 1 ? a.part_zero : nullptr, a.slices > 1 ? a.done : nullptr, a.out, kt);
+            a.x, a.n, a.params, a.P, a.o, a.w_outlier, a.slices, a.chunk, a.part_sum, a.part_zero, a.park_x, a.park_n,
+            a.park_cap, kt);
+        cudaError_t e = cudaGetLastError();
+        if (e != cudaSuccess) return e;
+        lean::like_lean_refine_kernel<<<(unsigned)nblk, kBlock, 0, a.stream>>>(
+            a.params, a.P, a.o, a.w_outlier, a.slices, a.part_sum, a.part_zero, a.park_x, a.park_n, a.park_cap,
+            a.slices > 1 ? a.done : nullptr, a.out, kt);
+        count_launch(1);
         return cudaGetLastError();
     }
     lean::like_lean_kernel<<<(unsigned)nblk, kBlock, 0, a.stream>>>(
