@@ -28,6 +28,12 @@ struct MultiSrc {
     double scalar[7];
 };
 
+// One parameter row carried in the kernel arguments (P == 1 calls from the host).
+struct InlineRow {
+    double v[8];
+    int use;
+};
+
 constexpr int kBlock = 128;          // threads per CTA for the likelihood kernels
 constexpr int kMaxDepth = 24;        // deepest adaptive-Simpson recursion accepted (2^24 nodes is already absurd)
 constexpr double kPi = 3.14159265358979323846;       // M_PI
@@ -52,10 +58,19 @@ struct BatchArgs {
     double* park_x = nullptr;      // adaptive launches: [P*slices][park_cap] trials parked for the refinement kernel, and
     int* park_n = nullptr;         // [P*slices] their counts (library scratch; without them the one-kernel form runs)
     int park_cap = 0;
+    const double* host_row = nullptr;  // P == 1 and the caller holds the row on the host: passed in the kernel arguments
     int* done = nullptr;           // optional [P] zeroed counters (device): when given (slices > 1), the slice that finishes last
                                    // sums its set's partials in slice order into out[p] and re-zeroes the counter, so that no
                                    // separate finalize launch is needed
 };
+
+inline InlineRow inline_row(const BatchArgs& a)
+{
+    InlineRow r;
+    r.use = (a.host_row != nullptr && a.P == 1) ? 1 : 0;
+    for (int k = 0; k < 8; k++) r.v[k] = r.use ? a.host_row[k] : 0.0;
+    return r;
+}
 
 cudaError_t launch_like_batch_faithful(const BatchArgs& a);
 cudaError_t launch_like_batch_fast(const BatchArgs& a);

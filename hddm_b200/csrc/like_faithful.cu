@@ -51,7 +51,7 @@ cudaError_t launch_like_batch_faithful(const BatchArgs& a)
     if (nblk == 0) return cudaSuccess;
     like_batch_kernel<FaithfulImpl, false><<<(unsigned)nblk, kBlock, 0, a.stream>>>(
         a.x, a.n, a.params, a.P, a.o, a.w_outlier, a.slices, a.chunk, a.slices > 1 ? a.part_sum : a.out,
-        a.slices > 1 ? a.part_zero : nullptr, a.seg, a.slices > 1 ? a.done : nullptr, a.out, a.one_each, FaithfulImpl::Ctx{0});
+        a.slices > 1 ? a.part_zero : nullptr, a.seg, a.slices > 1 ? a.done : nullptr, a.out, a.one_each, inline_row(a), FaithfulImpl::Ctx{0});
     return cudaGetLastError();
 }
 

@@ -80,11 +80,11 @@ cudaError_t launch_like_batch_fast(const BatchArgs& a)
     if (a.o.use_adaptive)
         like_batch_kernel<FastImpl, true><<<(unsigned)nblk, kBlock, 0, a.stream>>>(
             a.x, a.n, a.params, a.P, a.o, a.w_outlier, a.slices, a.chunk, a.slices > 1 ? a.part_sum : a.out,
-            a.slices > 1 ? a.part_zero : nullptr, a.seg, a.slices > 1 ? a.done : nullptr, a.out, a.one_each, get_ktable(a.o.err));
+            a.slices > 1 ? a.part_zero : nullptr, a.seg, a.slices > 1 ? a.done : nullptr, a.out, a.one_each, inline_row(a), get_ktable(a.o.err));
     else
         like_batch_kernel<FastImpl, false><<<(unsigned)nblk, kBlock, 0, a.stream>>>(
             a.x, a.n, a.params, a.P, a.o, a.w_outlier, a.slices, a.chunk, a.slices > 1 ? a.part_sum : a.out,
-            a.slices > 1 ? a.part_zero : nullptr, a.seg, a.slices > 1 ? a.done : nullptr, a.out, a.one_each, get_ktable(a.o.err));
+            a.slices > 1 ? a.part_zero : nullptr, a.seg, a.slices > 1 ? a.done : nullptr, a.out, a.one_each, inline_row(a), get_ktable(a.o.err));
     return cudaGetLastError();
 }
 

@@ -60,6 +60,7 @@ __global__ void __launch_bounds__(kBlock, MINB) like_batch_kernel(const double* 
                                                           double* __restrict__ out_sum, int* __restrict__ out_zero,
                                                           const int64_t* __restrict__ seg, int* __restrict__ done,
                                                           double* __restrict__ final_out, int one_each,
+                                                          const __grid_constant__ InlineRow inl,
                                                           const __grid_constant__ typename Impl::Ctx ctx)
 {
     const int64_t bid = blockIdx.x;
@@ -76,7 +77,8 @@ __global__ void __launch_bounds__(kBlock, MINB) like_batch_kernel(const double* 
         if (chunk < 2) chunk = 2;
     }
 
-    const double* row = params + 8 * p;
+    // (a single parameter set given by a host caller rides in the kernel arguments: no memory read before the first trial)
+    const double* row = inl.use ? inl.v : params + 8 * p;
     Params prm{row[0], row[1], row[2], row[3], row[4], row[5], row[6], row[7]};
     const double po = prm.p_outlier;
 
