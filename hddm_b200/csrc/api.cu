@@ -645,7 +645,9 @@ static int like_batch_impl(const double* d_x, int64_t n, const double* d_params,
     if (two_kernels) {
         // adaptive launches on big grids: first level in one kernel, parked trials refined by a second one (like_lean.cu).
         // Every (set, slice) item owns a region of the list; a list that outgrows it is refined inside the first kernel.
-        const int64_t cap = a.chunk < 2048 ? ((a.chunk + 1) & ~(int64_t)1) : 2048;
+        int64_t cap = a.chunk < 2048 ? ((a.chunk + 1) & ~(int64_t)1) : 2048;
+        const int64_t items = P * (int64_t)a.slices, budget = (int64_t)1 << 28;   // at most 2 GiB of list (2^28 doubles)
+        if (items * cap > budget) cap = budget / items > 64 ? (budget / items) & ~(int64_t)1 : 64;
         void *px, *pn;
         if (scratch(kParkX, sizeof(double) * (size_t)P * a.slices * (size_t)cap, &px)) return 1;
         if (scratch(kParkN, sizeof(int) * (size_t)P * a.slices, &pn)) return 1;
