@@ -461,3 +461,33 @@ def test_multi_with_integration_vs_oracle(oracle, wfpt_gpu, variant):
         want = oracle.wiener_like_multi(x, *args, multi, p_outlier=0.05, w_outlier=0.1, **kw)
         got = wfpt_gpu.wiener_like_multi(x, *args, multi, p_outlier=0.05, w_outlier=0.1, **kw)
         assert np.isfinite(want) and abs(got - want) <= TOL * abs(want), (fixed, multi, kw, got, want)
+
+
+def test_adaptive_two_kernel_lists_overflow_and_shrink(oracle, wfpt_gpu):
+    """Adaptive launches keep, per (set, slice) item, a list of the trials whose recursion goes below the first level for
+    the refinement kernel.  Here nearly every trial lands in it (all RTs inside the t +- st/2 window), on a grid large
+    enough that the library shrinks the per-item regions to stay under its 2 GiB budget: lists overflow and the
+    overflow is refined inside the first kernel.  Same answers as the one-kernel general path and as the oracle."""
+    import os
+
+    import torch
+
+    rng = np.random.default_rng(77)
+    n, P = 2100, 140000
+    x = np.where(rng.random(n) < 0.7, 1.0, -1.0) * rng.uniform(0.42, 0.6, n)
+    prm = np.stack([rng.uniform(-2, 2, P), rng.uniform(0, 2, P), rng.uniform(0.8, 2.0, P), rng.uniform(0.35, 0.65, P),
+                    rng.uniform(0.05, 0.25, P), rng.uniform(0.48, 0.52, P), rng.uniform(0.2, 0.25, P), np.full(P, 0.05)], axis=1)
+    dx = torch.from_numpy(wfpt_gpu.sort_rts(x)).cuda()
+    dp = torch.from_numpy(prm).cuda()
+    kw = dict(err=1e-4, n_st=2, n_sz=2, use_adaptive=1, simps_err=1e-3, w_outlier=0.1)
+    got = wfpt_gpu.wiener_like_batch(dx, dp, **kw).cpu().numpy()
+    os.environ["WFPT_NO_LEAN"] = "1"
+    try:
+        sub = slice(0, 2048)
+        general = wfpt_gpu.wiener_like_batch(dx, dp[sub].contiguous(), **kw).cpu().numpy()
+    finally:
+        del os.environ["WFPT_NO_LEAN"]
+    assert np.all(np.isfinite(got)) and rel_err(got[sub], general) < 1e-12
+    idx = rng.choice(P, 24, replace=False)
+    want = oracle.wiener_like_batch(x, prm[idx], 1e-4, 2, 2, 1, 1e-3, 0.1)
+    assert rel_err(got[idx], want) <= TOL
