@@ -11,7 +11,9 @@
 // Cost and limits: every GPU that loads libwfpt_b200.so carries the array (kNoAllocSlots * 12 bytes = 192 KiB) until
 // the process exits.  A call needs P * slices slots, where `slices` comes from the library's general slicing rule
 // (api_plan_slices) WITHOUT the small-grid re-plan wfpt_like_batch adds for latency-bound grids: for those the two
-// entry points cut the trials differently and agree to rounding, not to the last bit.  Calls needing more than
+// entry points cut the trials differently and agree to rounding, not to the last bit.  Likewise large launches, for which
+// wfpt_like_batch picks specialised kernels that keep lists in further (allocated) scratch: this entry point stays with the
+// general kernel, whose only scratch is the array below.  Calls needing more than
 // kNoAllocSlots are refused with an error, never truncated.
 //
 // Sharing: all calls on a device use the same array and it still holds the previous call's partials on entry.

@@ -78,7 +78,10 @@ int wfpt_kflip_census(const double* d_x, int64_t n, const double* d_params, int6
 /* P independent wiener_like() evaluations on one RT array:
  *   out[j] = wiener_like(x, *params[j][0:7], err, n_st, n_sz, use_adaptive, simps_err, p_outlier=params[j][7], w_outlier)
  * replaces src/wfpt.pyx:54-76 (one call per row).  No counterpart with P>1 exists in the reference; P=1 is the
- * reference call.  Trials are summed with a deterministic two-stage tree (partials live in library scratch). */
+ * reference call.  Trials are summed with a deterministic two-stage tree (partials live in library scratch).  Large
+ * launches on one RT array run specialised kernels (like_lean.cu): fixed grids with n_sz = 2 in one launch; adaptive
+ * integration in two -- the first level, then a refinement kernel over per-set lists of the trials whose recursion goes
+ * deeper (library scratch, at most 2 GiB).  Results are independent of the launch geometry to rounding (~1e-15). */
 int wfpt_like_batch(const double* d_x, int64_t n, const double* d_params, int64_t P, double err, int n_st, int n_sz,
                     int use_adaptive, double simps_err, double w_outlier, int variant, double* d_out, void* stream);
 int wfpt_like_batch_host(const double* h_x, int64_t n, const double* h_params, int64_t P, double err, int n_st,
@@ -116,7 +119,9 @@ int wfpt_cache_stats(int64_t* entries, int64_t* bytes, int64_t* hits, int64_t* m
  * function makes no cudaMalloc/cudaFree call.  A call needs P x slices slots, where slices is the library's general
  * trial slicing for (n, P) (one slice once P reaches eight CTAs per SM, otherwise enough slices to get there, at least
  * 256 RTs each); the small-grid re-plan wfpt_like_batch applies on top of that is NOT applied here, so for small grids
- * the two functions cut the trials differently and their sums agree to rounding (<= 1e-13 relative), not bit for bit.
+ * the two functions cut the trials differently, and large launches of wfpt_like_batch go through kernels that need further
+ * library scratch (lists of trials awaiting refinement) where this one keeps to the general kernel: the sums of the two
+ * agree to rounding (<= 1e-13 relative), not bit for bit.
  * More than WFPT_NOALLOC_MAX_SLOTS slots is refused with an error.  All calls on a device share the array, so calls
  * whose kernels overlap on the GPU race; run them one after another.  The first call on each device looks the array's
  * device address up and should be made before any stream capture; the address is cached per device for the life of the
