@@ -12,8 +12,8 @@
 // the process exits.  A call needs P * slices slots, where `slices` comes from the library's general slicing rule
 // (api_plan_slices) WITHOUT the small-grid re-plan wfpt_like_batch adds for latency-bound grids: for those the two
 // entry points cut the trials differently and agree to rounding, not to the last bit.  Likewise large launches, for which
-// wfpt_like_batch picks specialised kernels that keep lists in further (allocated) scratch: this entry point stays with the
-// general kernel, whose only scratch is the array below.  Calls needing more than
+// wfpt_like_batch may pick kernels that keep lists in further (allocated) scratch (adaptive integration): this entry point
+// stays with kernels whose only scratch is the array below.  Calls needing more than
 // kNoAllocSlots are refused with an error, never truncated.
 //
 // Sharing: all calls on a device use the same array and it still holds the previous call's partials on entry.

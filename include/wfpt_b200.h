@@ -120,7 +120,8 @@ int wfpt_cache_stats(int64_t* entries, int64_t* bytes, int64_t* hits, int64_t* m
  * trial slicing for (n, P) (one slice once P reaches eight CTAs per SM, otherwise enough slices to get there, at least
  * 256 RTs each); the small-grid re-plan wfpt_like_batch applies on top of that is NOT applied here, so for small grids
  * the two functions cut the trials differently, and large launches of wfpt_like_batch go through kernels that need further
- * library scratch (lists of trials awaiting refinement) where this one keeps to the general kernel: the sums of the two
+ * library scratch (adaptive integration: lists of trials awaiting refinement) where this one keeps to kernels that need
+ * none: the sums of the two
  * agree to rounding (<= 1e-13 relative), not bit for bit.
  * More than WFPT_NOALLOC_MAX_SLOTS slots is refused with an error.  All calls on a device share the array, so calls
  * whose kernels overlap on the GPU race; run them one after another.  The first call on each device looks the array's
