@@ -494,8 +494,8 @@ __device__ __forceinline__ double warp_density(double ax, int sign, bool live, c
 
 // The common grid, n_st = 2: three t-nodes.  Everything the three nodes need before their series -- x', the votes on
 // the cached table pieces, tt, 1/sqrt(sv^2 x' + 1) -- is formed for all three side by side (three independent chains instead
-// of one after the other), then the three node sets run back to back.  Returns false (nothing computed) when some node's
-// lanes are not all inside its cached piece; the caller then takes the node-by-node routine above, which looks pieces up.
+// of one after the other), then the three node sets run back to back.  Returns false (nothing computed) unless the whole
+// warp is in the plain case; the caller then takes the node-by-node routine above, which masks and looks pieces up.
 template <int NZN, bool SV>
 __device__ __forceinline__ bool warp_density3(double ax, int sign, bool live, Shared& S, const SetConst& sc, unsigned tb,
                                               unsigned etab, double* out, int& neg, int& bad)
@@ -509,17 +509,17 @@ __device__ __forceinline__ bool warp_density3(double ax, int sign, bool live, Sh
         rec[i] = S.trec[i];
         pc[i] = S.piece[w][i];
     }
+    // only the plain case runs here: every lane carries a trial with all three nodes alive, each inside its cached piece --
+    // no masks, no per-node votes.  (Anything else: the node-by-node routine.)
     double xp[3];
-    bool alive[3];
-    bool inside = true;
+    bool good = live;
 #pragma unroll
     for (int i = 0; i < 3; i++) {
         xp[i] = ax - rec[i].tn;
-        alive[i] = live && (xp[i] > 0);
         const int th = __double2hiint(xp[i]);
-        inside &= !alive[i] || (th > pc[i].lo_hi && th < pc[i].hi_hi);
+        good &= (xp[i] > 0) && (th > pc[i].lo_hi && th < pc[i].hi_hi);
     }
-    if (!__all_sync(kFull, inside)) return false;
+    if (!__all_sync(kFull, good)) return false;
     double tt[3], rs[3], c[3];
 #pragma unroll
     for (int i = 0; i < 3; i++) {
@@ -542,15 +542,8 @@ __device__ __forceinline__ bool warp_density3(double ax, int sign, bool live, Sh
     }
     double acc = 0.0;
 #pragma unroll
-    for (int i = 0; i < 3; i++) {
-        if (__any_sync(kFull, alive[i])) {                      // (x' <= 0 on every lane: the node contributes 0)
-            int ng = 0, bd = 0;
-            double val = tnode_value<NZN, SV>(pc[i].desc, xp[i], tt[i], rs[i], c[i], tb, zb, etab, sc, sign, ng, bd);
-            if (alive[i]) { neg |= ng; bad |= bd; }             // lanes without the node computed along on garbage
-            else val = 0.0;
-            acc = fma(rec[i].wt, val, acc);
-        }
-    }
+    for (int i = 0; i < 3; i++)
+        acc = fma(rec[i].wt, tnode_value<NZN, SV>(pc[i].desc, xp[i], tt[i], rs[i], c[i], tb, zb, etab, sc, sign, neg, bad), acc);
     *out = acc;
     return true;
 }
