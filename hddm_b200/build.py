@@ -76,6 +76,14 @@ def build(force: bool = False, verbose: bool = False) -> str:
             list(ex.map(run, jobs))
     if jobs or force or _stale(LIB, objs):
         run([nvcc] + ARCH + ["-shared", "-o", LIB] + objs + ["-cudart", "static"])
+    # the CPython binding of the hot call (optional: hddm_b200.wfpt falls back to ctypes when it is missing)
+    import sysconfig
+
+    ext = os.path.join(HERE, "_wfptcall" + (sysconfig.get_config_var("EXT_SUFFIX") or ".so"))
+    src = os.path.join(CSRC, "pywfpt.c")
+    if force or _stale(ext, [src, LIB, os.path.join(INCLUDE, "wfpt_b200.h")]):
+        run(["gcc", "-O2", "-shared", "-fPIC", "-I", sysconfig.get_paths()["include"], src, "-o", ext, "-L", HERE,
+             "-l:libwfpt_b200.so", "-Wl,-rpath,$ORIGIN"])
     return LIB
 
 

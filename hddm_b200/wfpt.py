@@ -181,9 +181,23 @@ _F64 = np.dtype(np.float64)
 _Prm8 = C.c_double * 8
 
 
+try:  # CPython binding of the hot call (built beside the library; ctypes below does the same, a few microseconds slower)
+    from . import _wfptcall as _fastcall
+except ImportError:
+    _fastcall = None
+
+
 def wiener_like(x, v, sv, a, z, sz, t, st, err, n_st=10, n_sz=10, use_adaptive=1, simps_err=1e-8, p_outlier=0,
                 w_outlier=0.1):
     # The call a sampler makes millions of times: keep the Python side to a handful of microseconds.
+    if _fastcall is not None:
+        try:
+            r = _fastcall.wiener_like(x, v, sv, a, z, sz, t, st, err, n_st, n_sz, use_adaptive, simps_err, p_outlier, w_outlier,
+                                      _variant, _cache_on)
+        except RuntimeError as exc:
+            raise WfptError(str(exc)) from None
+        if r is not None:
+            return r
     if type(x) is not np.ndarray or x.dtype != _F64 or x.ndim != 1 or not x.flags.c_contiguous:
         x = _buffer(x, "x")                      # the reference's TypeError / ValueError, or a contiguous copy
     try:
