@@ -352,8 +352,8 @@ __device__ __forceinline__ double tnode_value5(int d, double xp, double tt, doub
                     t = fma(ub.y, R2H, t);
                     R2H *= rho2;
                 }
-                y[n] = e * t;
-                v[n] = e * ua.x;
+                y[n] = fma(e, t, 0.0);                                  // (+ 0.0: an underflowed e0 times a negative sum gives
+                v[n] = e * ua.x;                                        //  +0, not -0, and -0 * Q + (+0) below stays +0)
                 e *= ratio;
                 ratio *= w[2];
                 Rn *= rho;
@@ -367,8 +367,6 @@ __device__ __forceinline__ double tnode_value5(int d, double xp, double tt, doub
                 Qn *= rho;
             }
         }
-#pragma unroll
-        for (int n = 0; n < 5; n++) y[n] += 0.0;                         // an underflowed e0 times a negative sum: +0, not -0
     } else {
         pref = sc.pref_l * rs;
         const double gam = zq01.y * c, bet = zq23.y * c;
