@@ -1,5 +1,5 @@
 """One launch shape per invocation, for ncu captures (scripts/profile_all.sh): prints the units of work of ONE launch.
-    python scripts/prof_target.py fixed | adaptive_benign | adaptive_bounds | sim_angle"""
+    python scripts/prof_target.py fixed | fixed_bounds | adaptive_benign | adaptive_bounds | sim_angle"""
 import os
 import sys
 
@@ -21,7 +21,8 @@ if what == "sim_angle":
 x, benign = bench.workload(bench.P_FULL)
 dx = torch.from_numpy(wfpt.sort_rts(x)).cuda()
 prm, opts = {"fixed": (benign, bench.OPTS), "adaptive_benign": (benign[:8192], bench.ADAPT),
-             "adaptive_bounds": (bench.param_bounds_grid(8192), bench.ADAPT)}[what]
+             "adaptive_bounds": (bench.param_bounds_grid(8192), bench.ADAPT),
+             "fixed_bounds": (bench.param_bounds_grid(8192), bench.OPTS)}[what]
 dp = torch.from_numpy(np.ascontiguousarray(prm)).cuda()
 for _ in range(4):
     out = wfpt.wiener_like_batch(dx, dp, **opts)
