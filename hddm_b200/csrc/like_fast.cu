@@ -51,7 +51,7 @@ struct FastImpl {
         fast::Tables& T = fast::tables();
         const int slot = atomicAdd(&T.qcount, 1);
         if (slot >= fast::kQueue) return false;
-        T.queue[slot] = x;
+        fast::parking_lot()[slot] = x;
         return true;
     }
     __device__ static __forceinline__ int parked_count(const Set&)
@@ -60,7 +60,7 @@ struct FastImpl {
         const int n = fast::tables().qcount;
         return n < fast::kQueue ? n : fast::kQueue;
     }
-    __device__ static __forceinline__ double parked(const Set&, int q) { return fast::tables().queue[q]; }
+    __device__ static __forceinline__ double parked(const Set&, int q) { return fast::parking_lot()[q]; }
     __device__ static __forceinline__ void prepare_multi(const Ctx& kt) { fast::prepare_series_only(kt); }
     __device__ static __forceinline__ double density_once(double x, const Params& prm, const Opts& o, const Ctx& kt)
     {

@@ -25,6 +25,11 @@
 #include <mutex>
 
 #include "like_kernels.cuh"
+// The kernels of this file stage at most five z-nodes per response sign (n_sz == 2 on fixed grids, the five quarter points of
+// the first adaptive level): the z tables of fast::Tables shrink accordingly (7.4 KB -> 1.1 KB per CTA; the shared memory not
+// taken stays with L1, which holds the RT array and the loop's few spilled values).  Five keeps the two signs' tables
+// 560 bytes apart: a warp holding both signs reads them from disjoint banks.
+#define WFPT_MAX_ZNODES 5
 #include "wfpt_fast.cuh"
 
 namespace wfpt {
@@ -56,6 +61,7 @@ struct alignas(16) TRec { double tn, wt; };   // t-node position, and its Simpso
 
 struct Shared {
     double exptab[kExpN];
+    double a2, pad_;               // a^2 for the exact quotient of the piece-boundary passes (read there, not held in a register)
     TRec trec[fast::kMaxNodes + 1];
     PieceCache piece[kWarps][fast::kMaxNodes + 1];
     double defer[kDeferCap];
@@ -114,9 +120,20 @@ __device__ __forceinline__ double lds1(unsigned a)
     asm("ld.shared.f64 %0, [%1+%2];" : "=d"(v) : "r"(a), "n"(OFF));
     return v;
 }
+// volatile form: for a value that must be read where it is used (a loop-invariant one would otherwise be hoisted into
+// registers for the whole loop)
+template <int OFF>
+__device__ __forceinline__ double lds1v(unsigned a)
+{
+    double v;
+    asm volatile("ld.shared.f64 %0, [%1+%2];" : "=d"(v) : "r"(a), "n"(OFF));
+    return v;
+}
+// a^2's offset from the exp table's address (the one shared-memory base the node routines are handed)
+constexpr int kScA2 = (int)offsetof(Shared, a2) - (int)offsetof(Shared, exptab);
 constexpr int kOffZ = (int)offsetof(Tables, z), kOffTn = (int)offsetof(Tables, tn), kOffWt = (int)offsetof(Tables, wts_t),
               kOffCz = (int)offsetof(Tables, cz), kOffZstep = (int)offsetof(Tables, zstep), kOffExp = (int)offsetof(Tables, exptab);
-constexpr int kNodeBytes = (int)sizeof(NodeTab), kSignBytes = kNodeBytes * fast::kMaxNodes;
+constexpr int kNodeBytes = (int)sizeof(NodeTab), kSignBytes = kNodeBytes * fast::kMaxZNodes;
 constexpr int kNA = (int)offsetof(NodeTab, A), kNU = (int)offsetof(NodeTab, u), kNS = (int)offsetof(NodeTab, S);
 static_assert(kNA % 16 == 0 && kNU % 16 == 0 && kNS % 16 == 0 && kNodeBytes % 16 == 0, "NodeTab pairs must be 16-byte aligned");
 
@@ -456,7 +473,7 @@ __device__ __forceinline__ double warp_density(double ax, int sign, bool live, c
             // tt = x'/pow(a, 2) (pdf.pxi:81,98), evaluate once per distinct descriptor present, and remember the piece of the
             // last live lane for the next round
             int piece = 0;
-            const int mine = alive ? lookup_lane(T, __ddiv_rn(xp, sc.a2), &piece) : -1;
+            const int mine = alive ? lookup_lane(T, __ddiv_rn(xp, lds1v<kScA2>(etab)), &piece) : -1;
             unsigned todo = am;
             int neg_l = 0, bad_l = 0;
             while (todo) {
@@ -616,7 +633,7 @@ __device__ __forceinline__ double warp_density_adapt(double ax, int sign, bool l
                 // a piece boundary runs through the warp (or the warp has moved on): per-lane lookups on the reference's own
                 // tt = x'/pow(a, 2), one pass per distinct descriptor, lanes of other pieces riding along
                 int piece = 0;
-                const int mine = alive ? lookup_lane(T, __ddiv_rn(xp, sc.a2), &piece) : -1;
+                const int mine = alive ? lookup_lane(T, __ddiv_rn(xp, lds1v<kScA2>(etab)), &piece) : -1;
                 unsigned todo = am;
 #pragma unroll 1
                 while (todo) {
@@ -672,7 +689,10 @@ static __device__ __noinline__ double general_density(double x, int kind, int nz
     return fast::density<false>(x, s, &defer);
 }
 
-__global__ void __launch_bounds__(kBlock, 5) like_lean_kernel(const double* __restrict__ x, int64_t n,
+#ifndef WFPT_LEAN_MINB
+#define WFPT_LEAN_MINB 5
+#endif
+__global__ void __launch_bounds__(kBlock, WFPT_LEAN_MINB) like_lean_kernel(const double* __restrict__ x, int64_t n,
                                                              const double* __restrict__ params, int64_t P, Opts o,
                                                              double w_outlier, int slices, int64_t chunk,
                                                              double* __restrict__ out_sum, int* __restrict__ out_zero,
@@ -707,7 +727,7 @@ __global__ void __launch_bounds__(kBlock, 5) like_lean_kernel(const double* __re
         sc.omp = __dsub_rn(1.0, po); sc.wp = __dmul_rn(w_outlier, po);
         sc.tlo = set.tlo;
         sc.ct = 1.0;
-        if (threadIdx.x == 0) S.ndefer = 0;
+        if (threadIdx.x == 0) { S.ndefer = 0; S.a2 = sc.a2; }
         for (int i = threadIdx.x; i < kExpN; i += kBlock) S.exptab[i] = g_exp_table[i];
         for (int i = threadIdx.x; i < kWarps * (fast::kMaxNodes + 1); i += kBlock) {
             PieceCache e{0, 0, 0, 0};       // empty interval: the first round looks its pieces up
@@ -866,7 +886,7 @@ __device__ __forceinline__ void write_result(double tot, int any_zero, int64_t b
     }
 }
 
-constexpr int kParkRounds = 3;   // rounds between two looks at the parking lot
+constexpr int kParkRounds = (fast::kQueue >= 1024) ? 3 : 1;   // rounds between two looks at the parking lot
 static_assert(fast::kQueue > kParkRounds * 2 * kBlock, "parking lot smaller than what can arrive between two checks");
 
 __global__ void __launch_bounds__(kBlock, 4) like_lean_adapt_kernel(const double* __restrict__ x, int64_t n,
@@ -902,6 +922,7 @@ __global__ void __launch_bounds__(kBlock, 4) like_lean_adapt_kernel(const double
         sc.omp = __dsub_rn(1.0, po); sc.wp = __dmul_rn(w_outlier, po);
         sc.tlo = set.tlo;
         sc.ct = 1.0;
+        if (threadIdx.x == 0) S.a2 = sc.a2;
         for (int i = threadIdx.x; i < kExpN; i += kBlock) S.exptab[i] = g_exp_table[i];
         for (int i = threadIdx.x; i < kWarps * (fast::kMaxNodes + 1); i += kBlock) {
             PieceCache e{0, 0, 0, 0};
@@ -948,12 +969,12 @@ __global__ void __launch_bounds__(kBlock, 4) like_lean_adapt_kernel(const double
         if (point) {   // nothing to refine: the operation-for-operation evaluator takes the trial (library exp, every term)
 #pragma unroll 1
             for (int q = first + threadIdx.x; q < parked; q += kBlock)
-                lp.add_slow(mix_outlier(fast::generic_full_pdf(fast::tables().queue[q], fast::tables().prm, fast::tables().o), sc.omp, sc.wp));
+                lp.add_slow(mix_outlier(fast::generic_full_pdf(fast::parking_lot()[q], fast::tables().prm, fast::tables().o), sc.omp, sc.wp));
             return;
         }
 #pragma unroll 1
         for (int q = first + threadIdx.x; q < parked; q += kBlock)
-            lp.add_slow(mix_outlier(fast::adaptive_refine(fast::tables().queue[q], &fast::tables(), kind, kl_max), sc.omp, sc.wp));
+            lp.add_slow(mix_outlier(fast::adaptive_refine(fast::parking_lot()[q], &fast::tables(), kind, kl_max), sc.omp, sc.wp));
     };
 
     // the shared-memory lot goes to this item's region of the global list; what does not fit is refined here
@@ -962,7 +983,7 @@ __global__ void __launch_bounds__(kBlock, 4) like_lean_adapt_kernel(const double
         const int room = park_cap - flushed;
         const int take = parked < room ? parked : room;
         double* dst = park_x + (size_t)bid * park_cap + flushed;
-        for (int q = threadIdx.x; q < take; q += kBlock) dst[q] = fast::tables().queue[q];
+        for (int q = threadIdx.x; q < take; q += kBlock) dst[q] = fast::parking_lot()[q];
         flushed += take;
         if (take < parked) drain(take, parked);
     };
@@ -1008,7 +1029,7 @@ __global__ void __launch_bounds__(kBlock, 4) like_lean_adapt_kernel(const double
                         // routines take the trial (the lot is drained before it can overflow, see below)
                         const int slot = atomicAdd(&fast::tables().qcount, 1);
                         if (slot >= fast::kQueue) __trap();
-                        fast::tables().queue[slot] = xv;
+                        fast::parking_lot()[slot] = xv;
                         continue;
                     }
                 }

@@ -31,9 +31,17 @@ namespace wfpt {
 namespace fast {
 
 constexpr int kMaxNodes = 33;               // nodes per axis held in shared memory (n_st, n_sz <= 32)
+#ifndef WFPT_MAX_ZNODES
+#define WFPT_MAX_ZNODES kMaxNodes
+#endif
+constexpr int kMaxZNodes = WFPT_MAX_ZNODES;     // z-nodes held per sign (a translation unit that only stages small z grids sets it lower)
+static_assert(kMaxZNodes >= 5 && kMaxZNodes <= kMaxNodes, "the first adaptive level stages five z-nodes");
 constexpr double kInvSqrt2Pi = 0.3989422804014327;
 constexpr double kHalfPiSq = 4.934802200544679;  // pi^2 / 2
-constexpr int kQueue = 1024;                // per-CTA parking lot for trials that need the generic evaluator
+#ifndef WFPT_KQUEUE
+#define WFPT_KQUEUE 1024
+#endif
+constexpr int kQueue = WFPT_KQUEUE;                // per-CTA parking lot for trials that need the generic evaluator
 
 enum Mode : int {
     kModePoint = 0,      // sz == 0 and st == 0: one node per trial
@@ -53,7 +61,7 @@ struct alignas(16) NodeTab {   // field order and alignment chosen so that the n
 
 // Shared-memory tables of one parameter set (one CTA).
 struct Tables {
-    NodeTab z[2][kMaxNodes];  // sign 0: lower-boundary RT (v, z); sign 1: upper (-v, 1-z)
+    NodeTab z[2][kMaxZNodes];  // sign 0: lower-boundary RT (v, z); sign 1: upper (-v, 1-z)
     double tn[kMaxNodes];     // t_i
     double wz[2], hz[2];      // z interval width / step per response sign, as the reference rounds them
     double wt, ht;            // same along t
@@ -63,7 +71,7 @@ struct Tables {
     double zq[2][4];          // per sign: the exponent of node n is quadratic in n; coefficients of tau and c in its
                               // linear (beta: [2] tau, [3] c) and quadratic (gamma: [0] tau, [1] c) terms
     double wts_t[kMaxNodes];  // Simpson weights 1 4 2 ... 4 1 along t (fixed grid)
-    double wts_z[kMaxNodes];  // same along z
+    double wts_z[kMaxZNodes];  // same along z
     double exptab[64];        // 2^(j/64)
     long long thr[kMaxPieces];  // series-term table (copy of the launch's KTable)
     int desc[kMaxPieces + 1];   // desc[0] = piece below thr[0]
@@ -73,10 +81,6 @@ struct Tables {
     int depth_z, depth_t;     // adaptive recursion budgets (n_sz, n_st)
     int npieces;              // thresholds in the series-term table
     double simps_err;
-    double queue[kQueue];
-    double coop_g[4][18];     // warp-cooperative refinement: node values and flags of the trial each warp works on
-    double coop_z[4][18];     // ... and of the z-integral being refined
-    int coop_f[4][18];
 };
 
 // Per-thread (register) view of the parameter set; everything bulky lives in Tables.
@@ -105,6 +109,14 @@ __device__ __forceinline__ Tables& tables()
 {
     __shared__ Tables t;
     return t;
+}
+
+// Per-CTA parking lot for trials that wait for another evaluator (count in Tables::qcount).  Apart from Tables so that only
+// kernels that park anything carry its 8 KB: the fixed-grid lean kernel does not, and runs with that much more L1.
+__device__ __forceinline__ double* parking_lot()
+{
+    __shared__ double q[kQueue];
+    return q;
 }
 
 // ---- exp ------------------------------------------------------------------------------------------------------------------
@@ -484,7 +496,7 @@ __device__ __forceinline__ void prepare(Set& s, const Params& prm, const Opts& o
     else {
         const int nz = (sz == 0) ? 0 : o.n_sz, nt = (st == 0) ? 0 : o.n_st;
         // n == 0 on an integrated axis is the reference's division-by-zero corner (Appendix A.12): generic path
-        mode = ((sz != 0 && nz == 0) || (st != 0 && nt == 0) || nz >= kMaxNodes || nt >= kMaxNodes) ? kModeGeneric : kModeFixed;
+        mode = ((sz != 0 && nz == 0) || (st != 0 && nt == 0) || nz >= kMaxZNodes || nt >= kMaxNodes) ? kModeGeneric : kModeFixed;
     }
     s.mode = mode;
     if (threadIdx.x == 0) {
@@ -1077,9 +1089,13 @@ static __device__ __noinline__ double refine_coop(double x, const Tables* Tp, in
 {
     Tables& T = *const_cast<Tables*>(Tp);
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-    double* g = T.coop_g[w];
-    double* gz = T.coop_z[w];
-    int* fl = T.coop_f[w];            // bit 0: inner integral wants refinement, bit 1: negative series seen
+    // scratch of the walk (apart from Tables: only kernels that call this routine carry it)
+    __shared__ double coop_g[4][18];  // node values of the trial each warp works on
+    __shared__ double coop_z[4][18];  // ... and of the z-integral being refined
+    __shared__ int coop_f[4][18];     // bit 0: inner integral wants refinement, bit 1: negative series seen
+    double* g = coop_g[w];
+    double* gz = coop_z[w];
+    int* fl = coop_f[w];
     const double ax = fabs(x);
     const int sign = x > 0;
     Set s;
