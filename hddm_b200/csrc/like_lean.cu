@@ -143,7 +143,7 @@ static_assert(kNA % 16 == 0 && kNU % 16 == 0 && kNS % 16 == 0 && kNodeBytes % 16
 // ten).  The table (16 KB per CTA, correctly rounded entries computed once on the host) is the price.  |x| < 708.
 __constant__ double kE[6] = {2954.639443740597, 6755399441055744.0, -0.0003384507713235507, -4.3423507025813853e-13,
                              1.0 / 6.0, 0.5};
-__device__ double g_exp_table[kExpN];   // 2^(j/2048); filled by ensure_exp_table()
+__device__ double g_exp_table[kExpN];   // 2^(j/2048) less j * 2^9 in the high word (see expv); filled by ensure_exp_table()
 
 template <int M>
 __device__ __forceinline__ void expv(const double (&x)[M], double (&out)[M], unsigned tab)
@@ -167,12 +167,13 @@ __device__ __forceinline__ void expv(const double (&x)[M], double (&out)[M], uns
     for (int i = 0; i < M; i++) t[i] = fma(t[i], r[i] * r[i], r[i]);
 #pragma unroll
     for (int i = 0; i < M; i++) {
-        const double T = lds1<0>(tab + ((ki[i] & (kExpN - 1)) << 3));
-        const double res = fma(T, t[i], T);
+        // table entry j holds 2^(j/2048) with j * 2^9 taken off its high word, so that adding k * 2^9 = (e << 20) + j * 2^9
+        // yields S = 2^e * 2^(j/2048) in one integer multiply-add, off the chain that ends in the product below
+        const double Tb = lds1<0>(tab + ((ki[i] & (kExpN - 1)) << 3));
         int hi;
-        // add e = k >> 11 to the exponent field: (k - j) * 2^9 = e << 20
-        asm("mad.lo.s32 %0, %1, 512, %2;" : "=r"(hi) : "r"(ki[i] & ~(kExpN - 1)), "r"(__double2hiint(res)));
-        out[i] = __hiloint2double(hi, __double2loint(res));
+        asm("mad.lo.s32 %0, %1, 512, %2;" : "=r"(hi) : "r"(ki[i]), "r"(__double2hiint(Tb)));
+        const double S = __hiloint2double(hi, __double2loint(Tb));
+        out[i] = fma(S, t[i], S);
     }
 }
 
@@ -689,10 +690,7 @@ static __device__ __noinline__ double general_density(double x, int kind, int nz
     return fast::density<false>(x, s, &defer);
 }
 
-#ifndef WFPT_LEAN_MINB
-#define WFPT_LEAN_MINB 5
-#endif
-__global__ void __launch_bounds__(kBlock, WFPT_LEAN_MINB) like_lean_kernel(const double* __restrict__ x, int64_t n,
+__global__ void __launch_bounds__(kBlock, 5) like_lean_kernel(const double* __restrict__ x, int64_t n,
                                                              const double* __restrict__ params, int64_t P, Opts o,
                                                              double w_outlier, int slices, int64_t chunk,
                                                              double* __restrict__ out_sum, int* __restrict__ out_zero,
@@ -886,7 +884,7 @@ __device__ __forceinline__ void write_result(double tot, int any_zero, int64_t b
     }
 }
 
-constexpr int kParkRounds = (fast::kQueue >= 1024) ? 3 : 1;   // rounds between two looks at the parking lot
+constexpr int kParkRounds = 3;   // rounds between two looks at the parking lot
 static_assert(fast::kQueue > kParkRounds * 2 * kBlock, "parking lot smaller than what can arrive between two checks");
 
 __global__ void __launch_bounds__(kBlock, 4) like_lean_adapt_kernel(const double* __restrict__ x, int64_t n,
@@ -1144,7 +1142,13 @@ static cudaError_t ensure_exp_table()
     std::lock_guard<std::mutex> lk(mu);
     if (ready[dev]) return cudaSuccess;
     static double host[lean::kExpN];
-    for (int j = 0; j < lean::kExpN; j++) host[j] = (double)exp2l((long double)j / (long double)lean::kExpN);
+    for (int j = 0; j < lean::kExpN; j++) {
+        const double v = (double)exp2l((long double)j / (long double)lean::kExpN);   // correctly rounded 2^(j/N)
+        uint64_t bits;
+        memcpy(&bits, &v, 8);
+        bits -= (uint64_t)j << (32 + 9);                                             // see expv
+        memcpy(&host[j], &bits, 8);
+    }
     e = cudaMemcpyToSymbol(lean::g_exp_table, host, sizeof(host));
     if (e == cudaSuccess) ready[dev] = true;
     return e;

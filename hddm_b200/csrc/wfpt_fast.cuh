@@ -38,10 +38,7 @@ constexpr int kMaxZNodes = WFPT_MAX_ZNODES;     // z-nodes held per sign (a tran
 static_assert(kMaxZNodes >= 5 && kMaxZNodes <= kMaxNodes, "the first adaptive level stages five z-nodes");
 constexpr double kInvSqrt2Pi = 0.3989422804014327;
 constexpr double kHalfPiSq = 4.934802200544679;  // pi^2 / 2
-#ifndef WFPT_KQUEUE
-#define WFPT_KQUEUE 1024
-#endif
-constexpr int kQueue = WFPT_KQUEUE;                // per-CTA parking lot for trials that need the generic evaluator
+constexpr int kQueue = 1024;                // per-CTA parking lot for trials that need the generic evaluator
 
 enum Mode : int {
     kModePoint = 0,      // sz == 0 and st == 0: one node per trial
