@@ -139,10 +139,13 @@ static_assert(kNA % 16 == 0 && kNU % 16 == 0 && kNS % 16 == 0 && kNodeBytes % 16
 
 // ---- exp, three or four independent chains side by side -------------------------------------------------------------------
 // exp(x) = 2^e * 2^(j/2048) * exp(r),  k = rint(2048 x / ln 2) = 2048 e + j,  r = x - k ln2/2048, |r| <= 1.7e-4, so that
-// exp(r) - 1 = r + r^2 (1/2 + r/6) to 3.4e-17: eight FP64 instructions per exp (the 64-entry form of wfpt_fast.cuh needs
-// ten).  The table (16 KB per CTA, correctly rounded entries computed once on the host) is the price.  |x| < 708.
-__constant__ double kE[6] = {2954.639443740597, 6755399441055744.0, -0.0003384507713235507, -4.3423507025813853e-13,
-                             1.0 / 6.0, 0.5};
+// exp(r) - 1 = r + r^2 (1/2 + r/6) to 3.4e-17: seven FP64 instructions per exp, six deep (the 64-entry form of
+// wfpt_fast.cuh needs ten).  The table (16 KB per CTA, correctly rounded entries computed once on the host) is the price.
+// The reduction multiplies k by ln2/2048 rounded to double in ONE fused step: its rounding (2^-54 relative) enters as
+// exp(x (1 + 2^-54)), i.e. as half a unit in the last place of the ARGUMENT -- which every argument here already carries
+// from the operations that formed it; a two-constant reduction would buy nothing but one more link in the chain
+// (measured: 18.7 -> 17.5 ms on the headline launch, the reported parity errors unchanged to all printed digits).  |x| < 708.
+__constant__ double kE[5] = {2954.639443740597, 6755399441055744.0, -0.6931471805599453094172321 / 2048.0, 1.0 / 6.0, 0.5};
 __device__ double g_exp_table[kExpN];   // 2^(j/2048) less j * 2^9 in the high word (see expv); filled by ensure_exp_table()
 
 template <int M>
@@ -160,9 +163,7 @@ __device__ __forceinline__ void expv(const double (&x)[M], double (&out)[M], uns
 #pragma unroll
     for (int i = 0; i < M; i++) r[i] = fma(t[i], kE[2], x[i]);
 #pragma unroll
-    for (int i = 0; i < M; i++) r[i] = fma(t[i], kE[3], r[i]);
-#pragma unroll
-    for (int i = 0; i < M; i++) t[i] = fma(r[i], kE[4], kE[5]);
+    for (int i = 0; i < M; i++) t[i] = fma(r[i], kE[3], kE[4]);
 #pragma unroll
     for (int i = 0; i < M; i++) t[i] = fma(t[i], r[i] * r[i], r[i]);
 #pragma unroll
