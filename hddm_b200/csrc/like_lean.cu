@@ -62,6 +62,8 @@ struct alignas(16) TRec { double tn, wt; };   // t-node position, and its Simpso
 struct Shared {
     double exptab[kExpN];
     double a2, pad_;               // a^2 for the exact quotient of the piece-boundary passes (read there, not held in a register)
+    double pcz[2][2];              // [0][sign]: small-time prefactor 1/(sqrt(2 pi) a^2) times the z-Simpson scale cz[sign]; [1][sign]: pi/a^2 times it
+    double gk[2][4];               // per sign: -2 (z_0 + 1), -2 (1 - z_last), -2 step (the exponents of R, Q, rho are these over tt)
     TRec trec[fast::kMaxNodes + 1];
     PieceCache piece[kWarps][fast::kMaxNodes + 1];
     double defer[kDeferCap];
@@ -131,6 +133,8 @@ __device__ __forceinline__ double lds1v(unsigned a)
 }
 // a^2's offset from the exp table's address (the one shared-memory base the node routines are handed)
 constexpr int kScA2 = (int)offsetof(Shared, a2) - (int)offsetof(Shared, exptab);
+constexpr int kPczS = (int)offsetof(Shared, pcz) - (int)offsetof(Shared, exptab), kPczL = kPczS + 16,
+              kGk = (int)offsetof(Shared, gk) - (int)offsetof(Shared, exptab);
 constexpr int kOffZ = (int)offsetof(Tables, z), kOffTn = (int)offsetof(Tables, tn), kOffWt = (int)offsetof(Tables, wts_t),
               kOffCz = (int)offsetof(Tables, cz), kOffZstep = (int)offsetof(Tables, zstep), kOffExp = (int)offsetof(Tables, exptab);
 constexpr int kNodeBytes = (int)sizeof(NodeTab), kSignBytes = kNodeBytes * fast::kMaxZNodes;
@@ -215,7 +219,7 @@ __device__ __forceinline__ double tnode_value(int d, double xp, double tt, doubl
     if (d >> 8) {
         const double r = rsqrt_d(tt);
         const double tau = r * r, m2t = -2.0 * tau;
-        pref = tau * r * sc.pref_s * rs;
+        pref = (NZN == 3) ? tau * r * rs * lds1<kPczS>(tab + 8 * sign) : tau * r * sc.pref_s * rs;
         double a[NZN], e0[NZN];
         {
             const double2 Au0 = lds2<kNA>(zb);                                // (A, -z^2/2) of node 0, 1, 2
@@ -235,9 +239,12 @@ __device__ __forceinline__ double tnode_value(int d, double xp, double tt, doubl
             const double um2[3] = {ua0.x, ua1.x, ua2.x}, u0[3] = {ua0.y, ua1.y, ua2.y}, up2[3] = {ub0.x, ub1.x, ub2.x},
                          up4[3] = {ub0.y, ub1.y, ub2.y};
             double g[3], w[3];
-            g[0] = clamp_neg(fma(m2t, u0[0], m2t));            // R   = exp(-2 (z_0 + 1) / tt)
-            g[1] = clamp_neg(fma(-m2t, u0[2], m2t));           // Q   = exp(-2 (1 - z_last) / tt)
-            g[2] = clamp_neg(m2t * lds1<kOffZstep>(tb + 8 * sign));   // rho = exp(-2 step / tt)
+            {
+                const double2 k01 = lds2<kGk>(tab + 32 * sign);
+                g[0] = clamp_neg(tau * k01.x);                                  // R   = exp(-2 (z_0 + 1) / tt)
+                g[1] = clamp_neg(tau * k01.y);                                  // Q   = exp(-2 (1 - z_last) / tt)
+                g[2] = clamp_neg(tau * lds1<kGk + 16>(tab + 32 * sign));        // rho = exp(-2 step / tt)
+            }
             expv<3>(g, w, tab);
             const double rho = w[2];
             double Rn[3], Qn[3];
@@ -268,7 +275,7 @@ __device__ __forceinline__ double tnode_value(int d, double xp, double tt, doubl
             y[0] = fma(e0[0], inner, 0.0);
         }
     } else {
-        pref = sc.pref_l * rs;
+        pref = (NZN == 3) ? rs * lds1<kPczL>(tab + 8 * sign) : sc.pref_l * rs;
         double a[NZN + 1], w[NZN + 1];
         a[NZN] = -fast::kHalfPiSq * tt;
         a[0] = fma(lds1<kNA>(zb), c, E0);
@@ -308,12 +315,10 @@ __device__ __forceinline__ double tnode_value(int d, double xp, double tt, doubl
         for (int n = 0; n < NZN; n++) y[n] = fma(y[n], w[n], 0.0);
     }
 #pragma unroll
-    for (int n = 0; n < NZN; n++) {
-        y[n] *= pref;                       // pref > 0: the sign is the series sum's
-        neg |= __double2hiint(y[n]);
-    }
-    if (NZN == 3) return (fma(4.0, y[1], y[0]) + y[NZN - 1]) * lds1<kOffCz>(tb + 8 * sign);   // integrate.pxi:30-45 with n_sz = 2
-    return y[0];
+    for (int n = 0; n < NZN; n++) neg |= __double2hiint(y[n]);   // the prefactor is positive: the sign is the series sum's
+    // integrate.pxi:30-45 with n_sz = 2; prefactor and Simpson scale hz/(3 wz) applied to the sum as one multiplier
+    if (NZN == 3) return (fma(4.0, y[1], y[0]) + y[NZN - 1]) * pref;
+    return y[0] * pref;
 }
 
 // ---- one t-node of the first ADAPTIVE level: five equally spaced z-nodes ------------------------------------------------------
@@ -727,6 +732,17 @@ __global__ void __launch_bounds__(kBlock, 5) like_lean_kernel(const double* __re
         sc.tlo = set.tlo;
         sc.ct = 1.0;
         if (threadIdx.x == 0) { S.ndefer = 0; S.a2 = sc.a2; }
+
+        if (threadIdx.x < 2 && mode != fast::kModeZero && mode != fast::kModeGeneric) {
+            const Tables& Tz = fast::tables();
+            const int sg = threadIdx.x;
+            S.pcz[0][sg] = sc.pref_s * Tz.cz[sg];
+            S.pcz[1][sg] = sc.pref_l * Tz.cz[sg];
+            S.gk[sg][0] = -2.0 * (Tz.z[sg][0].u[1] + 1.0);
+            S.gk[sg][1] = -2.0 * (1.0 - Tz.z[sg][set.nz].u[1]);
+            S.gk[sg][2] = -2.0 * Tz.zstep[sg];
+            S.gk[sg][3] = 0.0;
+        }
         for (int i = threadIdx.x; i < kExpN; i += kBlock) S.exptab[i] = g_exp_table[i];
         for (int i = threadIdx.x; i < kWarps * (fast::kMaxNodes + 1); i += kBlock) {
             PieceCache e{0, 0, 0, 0};       // empty interval: the first round looks its pieces up
@@ -922,6 +938,17 @@ __global__ void __launch_bounds__(kBlock, 4) like_lean_adapt_kernel(const double
         sc.tlo = set.tlo;
         sc.ct = 1.0;
         if (threadIdx.x == 0) S.a2 = sc.a2;
+
+        if (threadIdx.x < 2 && mode != fast::kModeZero && mode != fast::kModeGeneric) {
+            const Tables& Tz = fast::tables();
+            const int sg = threadIdx.x;
+            S.pcz[0][sg] = sc.pref_s * Tz.cz[sg];
+            S.pcz[1][sg] = sc.pref_l * Tz.cz[sg];
+            S.gk[sg][0] = -2.0 * (Tz.z[sg][0].u[1] + 1.0);
+            S.gk[sg][1] = -2.0 * (1.0 - Tz.z[sg][set.nz].u[1]);
+            S.gk[sg][2] = -2.0 * Tz.zstep[sg];
+            S.gk[sg][3] = 0.0;
+        }
         for (int i = threadIdx.x; i < kExpN; i += kBlock) S.exptab[i] = g_exp_table[i];
         for (int i = threadIdx.x; i < kWarps * (fast::kMaxNodes + 1); i += kBlock) {
             PieceCache e{0, 0, 0, 0};
