@@ -103,6 +103,11 @@ __device__ __forceinline__ Shared& shared()
     return s;
 }
 
+// A value that is the same in every lane, taken through a warp reduction: it lands in a uniform register, and branches and
+// loop counters that hang on it become uniform ones (no reconvergence bookkeeping, compares on the uniform datapath).  All
+// 32 lanes must be there.
+__device__ __forceinline__ int uni(int v) { return __reduce_max_sync(kFull, v); }
+
 // ---- shared memory by 32-bit address ------------------------------------------------------------------------------------------
 // The tables are read through explicit shared-window addresses (one base per CTA, member offsets as immediates): left to
 // itself the compiler re-derives the window base (cluster CTA id, shift, add) at most use sites, a dozen uniform-datapath
@@ -473,7 +478,7 @@ __device__ __forceinline__ double warp_density(double ax, int sign, bool live, c
         }
         if (__all_sync(kFull, !alive || (th > pc.lo_hi && th < pc.hi_hi))) {
             int ng = 0, bd = 0;
-            val = tnode_value<NZN, SV>(pc.desc, xp, tt, rs, c, tb, zb, etab, sc, sign, ng, bd);
+            val = tnode_value<NZN, SV>(uni(pc.desc), xp, tt, rs, c, tb, zb, etab, sc, sign, ng, bd);
             if (alive) { neg |= ng; bad |= bd; }                // lanes without the node computed along on garbage
         } else {
             // a piece boundary runs through the warp (or the warp has moved on): look up per lane on the reference's own
@@ -563,9 +568,14 @@ __device__ __forceinline__ bool warp_density3(double ax, int sign, bool live, Sh
         for (int i = 0; i < 3; i++) c[i] = 0.5 * rs[i] * rs[i];
     }
     double acc = 0.0;
+    // the descriptors are the same in every lane (one cached piece per warp and node): as uniform values every branch on
+    // the expansion and on K is a uniform branch
+    int du[3];
+#pragma unroll
+    for (int i = 0; i < 3; i++) du[i] = uni(pc[i].desc);
 #pragma unroll
     for (int i = 0; i < 3; i++)
-        acc = fma(rec[i].wt, tnode_value<NZN, SV>(pc[i].desc, xp[i], tt[i], rs[i], c[i], tb, zb, etab, sc, sign, neg, bad), acc);
+        acc = fma(rec[i].wt, tnode_value<NZN, SV>(du[i], xp[i], tt[i], rs[i], c[i], tb, zb, etab, sc, sign, neg, bad), acc);
     *out = acc;
     return true;
 }
