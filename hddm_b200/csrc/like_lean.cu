@@ -914,7 +914,7 @@ __device__ __forceinline__ void write_result(double tot, int any_zero, int64_t b
 constexpr int kParkRounds = 3;   // rounds between two looks at the parking lot
 static_assert(fast::kQueue > kParkRounds * 2 * kBlock, "parking lot smaller than what can arrive between two checks");
 
-__global__ void __launch_bounds__(kBlock, 4) like_lean_adapt_kernel(const double* __restrict__ x, int64_t n,
+__global__ void __launch_bounds__(kBlock, 5) like_lean_adapt_kernel(const double* __restrict__ x, int64_t n,
                                                                    const double* __restrict__ params, int64_t P, Opts o,
                                                                    double w_outlier, int slices, int64_t chunk,
                                                                    double* __restrict__ part_sum, int* __restrict__ part_zero,
