@@ -347,7 +347,7 @@ __device__ __forceinline__ double tnode_value5(int d, double xp, double tt, doub
     double pref;
     if (d >> 8) {
         const double r = rsqrt_d(tt);
-        const double tau = r * r, m2t = -2.0 * tau;
+        const double tau = r * r;
         pref = tau * r * sc.pref_s * rs;
         const double gam = fma(zq01.y, c, zq01.x * tau), bet = fma(zq23.y, c, zq23.x * tau);
         const double2 Au0 = lds2<kNA>(zb);
@@ -362,9 +362,12 @@ __device__ __forceinline__ double tnode_value5(int d, double xp, double tt, doub
         // every e0_n and every ratio between neighbours must be inside the exp kernel's range
         bad |= (max(abs_hi(g[0]), abs_hi(a4)) >= kExpHiLimit) | !(fabs(g[1]) < 700.0) | !(fabs(fma(7.0, gam, bet)) < 700.0);
         double h[3], u[3];
-        h[0] = clamp_neg(fma(m2t, ua0.y, m2t));                          // R   = exp(-2 (z_0 + 1) / tt)
-        h[1] = clamp_neg(fma(-m2t, ua4.y, m2t));                         // Q   = exp(-2 (1 - z_last) / tt)
-        h[2] = clamp_neg(m2t * lds1<kOffZstep>(tb + 8 * sign));          // rho = exp(-2 step / tt)
+        {
+            const double2 k01 = lds2<kGk>(tab + 32 * sign);
+            h[0] = clamp_neg(tau * k01.x);                                  // R   = exp(-2 (z_0 + 1) / tt)
+            h[1] = clamp_neg(tau * k01.y);                                  // Q   = exp(-2 (1 - z_last) / tt)
+            h[2] = clamp_neg(tau * lds1<kGk + 16>(tab + 32 * sign));        // rho = exp(-2 step / tt)
+        }
         expv<3>(g, w, tab);
         expv<3>(h, u, tab);
         const double rho = u[2], rho2 = rho * rho;
@@ -424,15 +427,17 @@ __device__ __forceinline__ double tnode_value5(int d, double xp, double tt, doub
             ratio *= w[2];
         }
     }
-    const double piw = pref * lds1<kOffIwz>(tb + 8 * sign);   // pref / width of the z interval, > 0: the sign is the series sum's
 #pragma unroll
-    for (int n = 0; n < 5; n++) {
-        neg |= __double2hiint(y[n]);
-        y[n] *= piw;
-    }
-    double val;
-    deeper |= !fast::adaptive_level1(y[0], y[1], y[2], y[3], y[4], lds1<kOffWz>(tb + 8 * sign), simps_err, depth_z, &val);
-    return val;
+    for (int n = 0; n < 5; n++) neg |= __double2hiint(y[n]);   // the prefactor is positive: the sign is the series sum's
+    // integrate.pxi:99-105 (first level) on the five node values; prefactor, 1/width and h/12 go onto the three sums as one
+    // multiplier instead of onto the five values
+    const double s12 = pref * (lds1<kOffIwz>(tb + 8 * sign) * (lds1<kOffWz>(tb + 8 * sign) * (1.0 / 12.0)));
+    const double S = (2.0 * s12) * (y[0] + 4 * y[2] + y[4]);
+    const double Sl = s12 * (y[0] + 4 * y[1] + y[2]);
+    const double Sr = s12 * (y[2] + 4 * y[3] + y[4]);
+    const double S2 = Sl + Sr;
+    deeper |= !((depth_z <= 0) || (fabs(S2 - S) <= 15 * simps_err));
+    return fma(S2 - S, 1.0 / 15.0, S2);
 }
 
 // Per-lane table lookup (slow path only).
@@ -674,7 +679,7 @@ __device__ __forceinline__ double warp_density_adapt(double ax, int sign, bool l
             }
         }
         // integrate.pxi:99-105 (first level): S = f0 + 4 f2 + f4, Sleft = f0 + 4 f1 + f2, Sright = f2 + 4 f3 + f4
-        const double g = val * inv_wt;
+        const double g = val;   // (1 / width of the t interval goes onto the sums below)
         if (i == 0) { Sa = g; Sl = g; single = val; }
         else if (i == 1) Sl = fma(4.0, g, Sl);
         else if (i == 2) { Sa = fma(4.0, g, Sa); Sl += g; Sr = g; }
@@ -682,7 +687,7 @@ __device__ __forceinline__ double warp_density_adapt(double ax, int sign, bool l
         else { Sa += g; Sr += g; }
     }
     if (nt == 0) return single;
-    const double h12 = lds1<kOffWtA>(tb) * (1.0 / 12.0);
+    const double h12 = inv_wt * (lds1<kOffWtA>(tb) * (1.0 / 12.0));
     const double S1 = (2.0 * h12) * Sa, S2 = h12 * Sl + h12 * Sr;
     deeper |= !((depth_t <= 0) || (fabs(S2 - S1) <= 15 * simps_err));
     return fma(S2 - S1, 1.0 / 15.0, S2);
