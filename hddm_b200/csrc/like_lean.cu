@@ -108,6 +108,16 @@ __device__ __forceinline__ Shared& shared()
 // 32 lanes must be there.
 __device__ __forceinline__ int uni(int v) { return __reduce_max_sync(kFull, v); }
 
+// The exp table travels global -> shared by cp.async, issued before the set's tables are computed and awaited behind them:
+// its L2 latency is off the CTA's prologue (a prologue's duration is time in which the CTA contributes no warps).
+__device__ __forceinline__ void exptab_fetch(double* dst, const double* src)
+{
+    const unsigned d0 = (unsigned)__cvta_generic_to_shared(dst);
+    for (int i = threadIdx.x; i < kExpN / 2; i += kBlock)
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d0 + 16u * i), "l"(src + 2 * i) : "memory");
+}
+__device__ __forceinline__ void exptab_wait() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+
 // ---- shared memory by 32-bit address ------------------------------------------------------------------------------------------
 // The tables are read through explicit shared-window addresses (one base per CTA, member offsets as immediates): left to
 // itself the compiler re-derives the window base (cluster CTA id, shift, add) at most use sites, a dozen uniform-datapath
@@ -155,7 +165,7 @@ static_assert(kNA % 16 == 0 && kNU % 16 == 0 && kNS % 16 == 0 && kNodeBytes % 16
 // from the operations that formed it; a two-constant reduction would buy nothing but one more link in the chain
 // (measured: 18.7 -> 17.5 ms on the headline launch, the reported parity errors unchanged to all printed digits).  |x| < 708.
 __constant__ double kE[5] = {2954.639443740597, 6755399441055744.0, -0.6931471805599453094172321 / 2048.0, 1.0 / 6.0, 0.5};
-__device__ double g_exp_table[kExpN];   // 2^(j/2048) less j * 2^9 in the high word (see expv); filled by ensure_exp_table()
+__device__ __align__(16) double g_exp_table[kExpN];   // 2^(j/2048) less j * 2^9 in the high word (see expv); filled by ensure_exp_table()
 
 template <int M>
 __device__ __forceinline__ void expv(const double (&x)[M], double (&out)[M], unsigned tab)
@@ -735,6 +745,7 @@ __global__ void __launch_bounds__(kBlock, 5) like_lean_kernel(const double* __re
         return;
     }
     Shared& S = shared();
+    exptab_fetch(S.exptab, g_exp_table);
     int mode, kind, nz, nt, kl_max, sv_nonzero;
     SetConst sc;                            // per-thread copy: the loop reads these from registers
     {
@@ -758,7 +769,6 @@ __global__ void __launch_bounds__(kBlock, 5) like_lean_kernel(const double* __re
             S.gk[sg][2] = -2.0 * Tz.zstep[sg];
             S.gk[sg][3] = 0.0;
         }
-        for (int i = threadIdx.x; i < kExpN; i += kBlock) S.exptab[i] = g_exp_table[i];
         for (int i = threadIdx.x; i < kWarps * (fast::kMaxNodes + 1); i += kBlock) {
             PieceCache e{0, 0, 0, 0};       // empty interval: the first round looks its pieces up
             (&S.piece[0][0])[i] = e;
@@ -774,6 +784,7 @@ __global__ void __launch_bounds__(kBlock, 5) like_lean_kernel(const double* __re
             }
         }
     }
+    exptab_wait();
     __syncthreads();
     const Tables& T = fast::tables();
 
@@ -941,6 +952,7 @@ __global__ void __launch_bounds__(kBlock, 5) like_lean_adapt_kernel(const double
         return;
     }
     Shared& S = shared();
+    exptab_fetch(S.exptab, g_exp_table);
     int mode, kind, nt, kl_max, sv_nonzero;
     SetConst sc;
     {
@@ -964,7 +976,6 @@ __global__ void __launch_bounds__(kBlock, 5) like_lean_adapt_kernel(const double
             S.gk[sg][2] = -2.0 * Tz.zstep[sg];
             S.gk[sg][3] = 0.0;
         }
-        for (int i = threadIdx.x; i < kExpN; i += kBlock) S.exptab[i] = g_exp_table[i];
         for (int i = threadIdx.x; i < kWarps * (fast::kMaxNodes + 1); i += kBlock) {
             PieceCache e{0, 0, 0, 0};
             (&S.piece[0][0])[i] = e;
@@ -980,6 +991,7 @@ __global__ void __launch_bounds__(kBlock, 5) like_lean_adapt_kernel(const double
             }
         }
     }
+    exptab_wait();
     __syncthreads();
     const Tables& T = fast::tables();
     const double simps_err = o.simps_err;
