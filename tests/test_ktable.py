@@ -40,3 +40,23 @@ def test_table_shape_at_hddm_default():
     assert kinds == sorted(kinds, reverse=True)
     assert tab["desc"][-1] & 0xff == 1
     assert tab["kl_max"] <= 8 and tab["ks_max"] <= 8
+
+
+def test_exp2_table_constants_are_correctly_rounded():
+    """The 64-entry 2^(i/64) table the kernels copy per CTA (csrc/wfpt_fast.cuh, kExp2_64) against exact arithmetic: each entry
+    must be the double nearest to 2^(i/64), i.e. the 64th power of its neighbours' midpoints must bracket 2^i."""
+    import os
+    import re
+    from fractions import Fraction
+
+    src = open(os.path.join(os.path.dirname(__file__), "..", "hddm_b200", "csrc", "wfpt_fast.cuh")).read()
+    body = src[src.index("kExp2_64[64] = {"):]
+    body = body[:body.index("};")]
+    vals = [float.fromhex(h) for h in re.findall(r"0x1\.[0-9a-f]+p\+0|0x1p\+0|0x1\.0+p\+0", body)]
+    assert len(vals) == 64
+    ulp = Fraction(1, 2 ** 52)   # spacing of doubles in [1, 2)
+    for i, v in enumerate(vals):
+        f = Fraction(v)
+        assert 1 <= f < 2
+        lo, hi = f - ulp / 2, f + ulp / 2
+        assert lo ** 64 <= Fraction(2) ** i <= hi ** 64, i
