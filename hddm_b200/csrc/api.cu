@@ -666,7 +666,7 @@ static int sort_on_device(const double* d_x, int64_t n, const double** sorted)
 {
     *sorted = d_x;
     if (n < 2) return 0;
-    void* ds;
+    void* ds = nullptr;
     if (scratch(kSorted, sizeof(double) * (size_t)n, &ds)) return 1;
     rank_sort_kernel<<<(unsigned)((n + kSortTile - 1) / kSortTile), 256>>>(d_x, (int)n, (double*)ds);
     CK(cudaGetLastError());
@@ -871,7 +871,7 @@ int wfpt_like_cached_host(const double* h_x, int64_t n, const double* h_params, 
     const size_t pbytes = sizeof(double) * 8 * (size_t)P, obytes = sizeof(double) * (size_t)P;
     if (n == 0 || obytes > kPinOutBytes || pbytes > kPinMaxIn || g_cache_max_entries == 0)
         return wfpt_like_batch_host(h_x, n, h_params, P, err, n_st, n_sz, use_adaptive, simps_err, w_outlier, variant, h_out);
-    const double* dx;
+    const double* dx = nullptr;
     if (cache_lookup(h_x, n, &dx)) return 1;
     char *ph, *pd;
     void* dp;

@@ -150,8 +150,7 @@ __device__ __forceinline__ double lds1v(unsigned a)
 constexpr int kScA2 = (int)offsetof(Shared, a2) - (int)offsetof(Shared, exptab);
 constexpr int kPczS = (int)offsetof(Shared, pcz) - (int)offsetof(Shared, exptab), kPczL = kPczS + 16,
               kGk = (int)offsetof(Shared, gk) - (int)offsetof(Shared, exptab);
-constexpr int kOffZ = (int)offsetof(Tables, z), kOffTn = (int)offsetof(Tables, tn), kOffWt = (int)offsetof(Tables, wts_t),
-              kOffCz = (int)offsetof(Tables, cz), kOffZstep = (int)offsetof(Tables, zstep), kOffExp = (int)offsetof(Tables, exptab);
+constexpr int kOffZ = (int)offsetof(Tables, z);
 constexpr int kNodeBytes = (int)sizeof(NodeTab), kSignBytes = kNodeBytes * fast::kMaxZNodes;
 constexpr int kNA = (int)offsetof(NodeTab, A), kNU = (int)offsetof(NodeTab, u), kNS = (int)offsetof(NodeTab, S);
 static_assert(kNA % 16 == 0 && kNU % 16 == 0 && kNS % 16 == 0 && kNodeBytes % 16 == 0, "NodeTab pairs must be 16-byte aligned");
