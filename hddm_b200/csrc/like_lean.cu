@@ -585,8 +585,10 @@ __device__ __forceinline__ bool warp_density3(double ax, int sign, bool live, Sh
     // the descriptors are the same in every lane (one cached piece per warp and node): as uniform values every branch on
     // the expansion and on K is a uniform branch
     int du[3];
-#pragma unroll
-    for (int i = 0; i < 3; i++) du[i] = uni(pc[i].desc);
+    {
+        const int packed = uni(pc[0].desc | (pc[1].desc << 10) | (pc[2].desc << 20));   // (a descriptor has nine bits)
+        du[0] = packed & 0x3ff; du[1] = (packed >> 10) & 0x3ff; du[2] = packed >> 20;
+    }
 #pragma unroll
     for (int i = 0; i < 3; i++)
         acc = fma(rec[i].wt, tnode_value<NZN, SV>(du[i], xp[i], tt[i], rs[i], c[i], tb, zb, etab, sc, sign, neg, bad), acc);
@@ -831,12 +833,14 @@ __global__ void __launch_bounds__(kBlock, 5) like_lean_kernel(const double* __re
                 const bool have = h < cnt;
                 const bool live = have && !zero_set && !((ax - sc.tlo) < 0);   // pdf.pxi:112, the trial-dependent part
                 double dens = 0.0;
-                if (__any_sync(kFull, live)) {
-                    const int sign = xv > 0;
-                    int neg = 0, bad = 0;
-                    if (z3 && sv) {
-                        if (!(nt == 2 && warp_density3<3, true>(ax, sign, live, S, sc, tb, etab, &dens, neg, bad)))
-                            dens = warp_density<3, true>(ax, sign, live, T, S, sc, nt, tb, etab, neg, bad);
+                const int sign = xv > 0;
+                int neg = 0, bad = 0;
+                // (the three-node routine's own vote covers "somebody is live": the plain case pays one vote, not two)
+                const bool plain = z3 && sv && nt == 2 && warp_density3<3, true>(ax, sign, live, S, sc, tb, etab, &dens, neg, bad);
+                if (plain || __any_sync(kFull, live)) {
+                    if (plain) {
+                    } else if (z3 && sv) {
+                        dens = warp_density<3, true>(ax, sign, live, T, S, sc, nt, tb, etab, neg, bad);
                     } else if (z3) dens = warp_density<3, false>(ax, sign, live, T, S, sc, nt, tb, etab, neg, bad);
                     else dens = sv ? warp_density<1, true>(ax, sign, live, T, S, sc, nt, tb, etab, neg, bad)
                                    : warp_density<1, false>(ax, sign, live, T, S, sc, nt, tb, etab, neg, bad);
