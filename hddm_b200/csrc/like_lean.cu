@@ -7,17 +7,21 @@
 //
 //  * RTs arrive |rt|-sorted, so the 32 trials a warp holds in one round sit next to each other on the tt axis and nearly
 //    always share the series expansion and its term count K.  The warp keeps, per t-node, the piece of the series-term
-//    table it was in last time (bounds on the high word of tt, in shared memory); one vote tells whether every lane is
-//    still inside.  If so the descriptor is a warp-uniform value: every branch on "small or large time" and on K is a
-//    uniform branch, and each (expansion, K) combination runs straight-line code with exactly its terms.  Otherwise the
-//    lanes look their pieces up and the node is evaluated once per distinct descriptor present, lanes of other pieces
-//    riding along with their results discarded (two passes at a piece boundary, nothing diverges).
-//  * exp arguments are range-checked once per node set through the high words (one three-input max), the check's vote
-//    is uniform as well; a node set with an argument outside the branch-free exp kernel's range sends its trial to a short
-//    list in shared memory that the CTA evaluates after the loop with the general evaluator (library exp, every term the
-//    reference sums) -- no call site and no slow path inside the hot loop.
-//  * per-thread state is small enough for six resident CTAs per SM without spills: set constants live in shared memory,
-//    the exp chains of a node set run three at a time.
+//    table it was in last time (bounds on the high word of x' = tt a^2, in shared memory); one vote tells whether every
+//    lane is still inside.  If so the descriptor is taken through a warp reduction into a uniform register: every branch on
+//    "small or large time" and on K is a uniform branch, and each (expansion, K) combination runs straight-line code with
+//    exactly its terms.  Otherwise the lanes look their pieces up and the node is evaluated once per distinct descriptor
+//    present, lanes of other pieces riding along with their results discarded (two passes at a piece boundary, nothing
+//    diverges).
+//  * exp arguments are range-checked once per node set through the high words (one three-input max); a node set with an
+//    argument outside the branch-free exp kernel's range sends its trial to a short list in shared memory that the CTA
+//    evaluates after the loop with the general evaluator (library exp, every term the reference sums) -- no call site and
+//    no slow path inside the hot loop.
+//  * five resident CTAs per SM at 96 registers; the set's constants live in registers, the tables in 24 KB of shared memory
+//    (32 KB in the adaptive first-level kernel), the exp chains of a node set run three or four at a time.
+//
+// The adaptive launches' two kernels (first level here in the same warp-organised loop, refinement of the parked trials in a
+// second kernel) are further down.  DESIGN.md section 4 has the measurements behind each of these choices.
 //
 // Reference: /root/reference/src/pdf.pxi:28-146 (ftt_01w, pdf_sv, full_pdf), /root/reference/src/integrate.pxi:12-68
 // (simpson_1D / simpson_2D), /root/reference/src/wfpt.pyx:54-76 (wiener_like).
@@ -43,7 +47,8 @@ constexpr int kDeferCap = 256;          // trials per CTA the post-loop general 
 constexpr unsigned kFull = 0xffffffffu;
 constexpr int kExpBits = 11, kExpN = 1 << kExpBits;   // entries of the exp kernel's 2^(j/N) table
 
-// Set constants the loop reads from shared memory (one 16-byte load brings two).
+// The set's constants, one copy per thread: the loops read them from registers (reading them from shared memory at their use
+// was measured slower).
 struct alignas(16) SetConst {
     double a2, inv_a2;        // a^2 and its reciprocal
     double sv2, nv2;          // sv^2, -v^2
